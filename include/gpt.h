@@ -1,0 +1,203 @@
+/*
+ * gpt.h -- C-ABI of the B200-native hot path of gpu_pathtracer.
+ *
+ * The reference (aloysius-aryaputera/gpu_pathtracer) has no plugin or FFI seam: its host
+ * loaders fill flat SoA arrays (src/main.cu:165-471) and everything after that is device
+ * code launched from main() (src/main.cu:474-1870).  This header IS that seam: each entry
+ * point below replaces the launch sequence it cites, takes the same flat arrays with the
+ * same names and meaning, and returns an int status instead of exit(99)
+ * (src/main.cu:47-59).
+ *
+ * Conventions
+ *   - every pointer in an input struct is a caller-owned HOST pointer unless the function
+ *     name ends in _device; the library copies what it needs into its own HBM buffers.
+ *   - return value: GPT_OK (0) or a negative GPT_E_* code; gpt_last_error() gives text.
+ *   - no exceptions, no exit(), no torch types cross this boundary.
+ *   - all floating point is IEEE fp32, parity-critical stages are evaluated without FMA
+ *     contraction so they are bit-identical to the reference's host replay.
+ */
+#ifndef GPT_H
+#define GPT_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GPT_OK 0
+#define GPT_E_INVALID (-1)   /* bad argument / call order                                  */
+#define GPT_E_CUDA (-2)      /* a CUDA runtime call failed (text in gpt_last_error)        */
+#define GPT_E_NODEVICE (-3)  /* no CUDA device: there is NO CPU fallback                   */
+#define GPT_E_UNSUPPORTED (-4)
+#define GPT_E_NCCL (-5)
+
+/* which acceleration structure (the reference builds three: src/main.cu:826-1197) */
+#define GPT_BVH_MAIN 0         /* all triangles          src/main.cu:826-918   */
+#define GPT_BVH_TRANSPARENT 1  /* t_r > 0 triangles      src/main.cu:930-1063  */
+#define GPT_BVH_LIGHT 2        /* emissive triangles     src/main.cu:1065-1197 */
+
+/* per-triangle flag bits exported by gpt_export_triangles */
+#define GPT_TRI_LIGHT 1        /* Triangle::_check_if_light_emitting  triangle.h:123-135 */
+#define GPT_TRI_TRANSPARENT 2  /* Material::is_transparent            material.h:532-534 */
+#define GPT_TRI_SSS 4          /* material path_length > 0            material.h:497     */
+
+typedef struct gpt_ctx gpt_ctx;
+
+/* Geometry SoA exactly as produced by extract_triangle_data (src/main.cu:386-471,
+ * src/input/read_file_util.h:96-101).  Indices are 0-based; 0 where the OBJ had none. */
+typedef struct GptMesh {
+  int32_t num_vertices, num_normals, num_texcoords, num_triangles, num_objects;
+  const float *x, *y, *z;                        /* [num_vertices]  */
+  const float *x_norm, *y_norm, *z_norm;         /* [num_normals]   */
+  const float *x_tex, *y_tex;                    /* [num_texcoords] */
+  const int32_t *point_1_idx, *point_2_idx, *point_3_idx; /* [num_triangles] */
+  const int32_t *norm_1_idx, *norm_2_idx, *norm_3_idx;
+  const int32_t *tex_1_idx, *tex_2_idx, *tex_3_idx;
+  const int32_t *material_idx;                   /* [num_triangles] */
+  const int32_t *triangle_object_idx;            /* [num_triangles] */
+  const int32_t *object_num_primitives;          /* [num_objects]   */
+  const int32_t *object_primitive_offset_idx;    /* [num_objects]   */
+} GptMesh;
+
+/* Material SoA exactly as produced by extract_material_data (src/main.cu:139-156,355-383)
+ * and consumed by create_material (src/lib/world.h:101-175).  Texture (height, width,
+ * offset) triples index the planar atlas given to gpt_set_textures. */
+typedef struct GptMaterials {
+  int32_t num_materials;                         /* <= 100 (src/main.cu:130) */
+  const float *ka_x, *ka_y, *ka_z;
+  const float *kd_x, *kd_y, *kd_z;
+  const float *ks_x, *ks_y, *ks_z;
+  const float *ke_x, *ke_y, *ke_z;
+  const float *tf_x, *tf_y, *tf_z;
+  const float *path_length, *t_r, *n_s, *n_i, *bm;
+  const float *scattering_coef, *absorption_coef, *g;
+  const int32_t *material_priority;
+  const int32_t *height_diffuse, *width_diffuse, *offset_diffuse;
+  const int32_t *height_specular, *width_specular, *offset_specular;
+  const int32_t *height_emission, *width_emission, *offset_emission;
+  const int32_t *height_n_s, *width_n_s, *offset_n_s;
+  const int32_t *height_bump, *width_bump, *offset_bump;
+} GptMaterials;
+
+/* Camera constructor arguments (src/lib/world.h:85-99, src/model/camera.h:30-52). */
+typedef struct GptCamera {
+  float eye[3], center[3], up[3];
+  float fovy;
+  int32_t width, height;
+  float aperture, focus_dist;
+} GptCamera;
+
+/* Mirror of InputParam's render scalars (src/input/input_param.h:11-33). */
+typedef struct GptParams {
+  int32_t render_mode;              /* 1 = path tracing, 2 = SPPM */
+  int32_t pathtracing_sample_size;
+  int32_t pathtracing_level;
+  int32_t dof_sample_size;
+  int32_t sss_pts_per_object;
+  float hittable_pdf_weight;
+  float sky_emission[3];
+  int32_t ppm_num_photon_per_pass;
+  int32_t ppm_num_pass;
+  int32_t ppm_max_bounce;
+  float ppm_alpha;
+  float ppm_radius_scaling_factor;
+  int32_t rng_mode;                 /* 0 = reference streams (seed 1984, seq = pixel) */
+} GptParams;
+
+typedef struct GptStats {
+  double build_ms;        /* last gpt_build, main BVH only (src/main.cu:826-918)           */
+  double build_all_ms;    /* preprocessing + all three BVHs                                */
+  double trace_ms;        /* last gpt_trace* kernel time (CUDA events, device only)        */
+  double render_ms;       /* last gpt_render_pathtrace, device only                        */
+  uint64_t rays_traced;   /* closest-hit traversals of the MAIN BVH in the last call       */
+  uint64_t internal_visits; /* V_int: internal nodes whose two child boxes were tested     */
+  uint64_t leaf_tests;      /* V_leaf: triangles intersected                               */
+  uint64_t kernel_launches; /* kernels of this library launched by the last call           */
+  uint64_t shade_events;    /* path vertices shaded in the last render                     */
+} GptStats;
+
+/* ---- lifetime ---------------------------------------------------------------------- */
+int gpt_create(int device, gpt_ctx **out);
+void gpt_destroy(gpt_ctx *ctx);
+const char *gpt_last_error(const gpt_ctx *ctx);
+const char *gpt_version(void);
+/* Launch on the caller's CUDA stream (a cudaStream_t passed as an integer); 0 = the
+ * library's own stream.  Lets a host time the kernels with events on that stream. */
+int gpt_set_stream(gpt_ctx *ctx, uint64_t cuda_stream);
+
+/* ---- scene upload: replaces src/main.cu:474-640 (create_camera, create_material,
+ *      create_objects, create_world, tangent accumulation) ------------------------------ */
+int gpt_set_mesh(gpt_ctx *ctx, const GptMesh *mesh);
+int gpt_set_materials(gpt_ctx *ctx, const GptMaterials *mats);
+/* planar atlas, offset 0 = the 1x1 white default (src/input/read_image_util.h:135-144) */
+int gpt_set_textures(gpt_ctx *ctx, const float *r, const float *g, const float *b,
+                     int64_t texture_length);
+int gpt_set_background(gpt_ctx *ctx, const float *r, const float *g, const float *b,
+                       int32_t bg_height, int32_t bg_width);
+int gpt_set_camera(gpt_ctx *ctx, const GptCamera *cam);
+int gpt_set_params(gpt_ctx *ctx, const GptParams *params);
+
+/* ---- build: replaces create_world's derived data (triangle.h:254-321), tangents
+ *      (triangle_operations.h:18-61) and the three LBVH builds (src/main.cu:826-1197) --- */
+int gpt_build(gpt_ctx *ctx);
+/* Rebuild only the main BVH from the resident SoA (the timed "LBVH build ms" stage). */
+int gpt_rebuild_main_bvh(gpt_ctx *ctx);
+
+/* ---- parity exports ------------------------------------------------------------------ */
+/* Per-triangle derived data in ORIGINAL (OBJ face) order.  Any pointer may be NULL. */
+int gpt_export_triangles(gpt_ctx *ctx, float *tolerance /*N*/, float *aabb /*6N: xmin,xmax,
+                         ymin,ymax,zmin,zmax*/, float *normal /*3N*/, float *area /*N*/,
+                         int32_t *flags /*N*/, float *energy /*3N*/,
+                         float *tangents /*9N: corner 1,2,3*/);
+int gpt_bvh_num_leaves(gpt_ctx *ctx, int which, int32_t *n);
+/* Child references: c >= 0 is internal node c, c < 0 is leaf ~c (sorted position).
+ * Internal node i lives at index i, the root is 0 (bvh_building.h:63,72,179-183). */
+int gpt_export_bvh(gpt_ctx *ctx, int which, uint32_t *morton /*n, sorted*/,
+                   int32_t *sorted_to_orig /*n: original triangle index of leaf j*/,
+                   int32_t *left /*n-1*/, int32_t *right /*n-1*/,
+                   int32_t *parent_internal /*n-1, root = -1*/, int32_t *parent_leaf /*n*/,
+                   float *node_aabb /*6(n-1)*/, float *leaf_aabb /*6n*/,
+                   float *world_aabb /*6*/);
+
+/* ---- trace: replaces traverse_bvh + Triangle::hit (bvh_traversal.h:12-84,
+ *      triangle.h:343-408).  rays: n x 8 floats {ox,oy,oz,tmax, dx,dy,dz,0}; the direction
+ *      is normalised exactly as Ray::Ray does (ray.h:21-24); tmax = INFINITY reproduces
+ *      rec.t = INFINITY.  Outputs (any may be NULL): leaf_id = sorted position or -1,
+ *      tri_id = original triangle index or -1, t, bary = {b1,b2,b3}. ------------------- */
+int gpt_trace(gpt_ctx *ctx, int which, const float *rays, int64_t n, int32_t *leaf_id,
+              int32_t *tri_id, float *t, float *bary);
+/* Same, all pointers are DEVICE pointers; hits: n x 4 x 4 bytes {t, leaf_id, b1, b2}
+ * with leaf_id stored as int32 bits.  Asynchronous on the context's stream. */
+int gpt_trace_device(gpt_ctx *ctx, int which, const void *d_rays, int64_t n, void *d_hits);
+/* Count V_int / V_leaf of the same traversal (not timed) into gpt_stats. */
+int gpt_trace_count_device(gpt_ctx *ctx, int which, const void *d_rays, int64_t n);
+
+/* ---- path tracing: replaces init_curand_state + path_tracing_render
+ *      (src/main.cu:1208,1266; src/render/pathtracing.h:251-305).  out_rgb: P x 3 linear
+ *      fp32, row-major, top row first. ------------------------------------------------- */
+int gpt_render_pathtrace(gpt_ctx *ctx, float *out_rgb);
+/* Render only pixels whose 32x32 tile index t satisfies t % nranks == rank; other pixels
+ * are left untouched in d_out_rgb (DEVICE pointer, P x 3).  Asynchronous. */
+int gpt_render_pathtrace_device(gpt_ctx *ctx, void *d_out_rgb, int rank, int nranks);
+
+/* ---- SPPM: replaces src/main.cu:1282-1870 --------------------------------------------- */
+int gpt_sppm_init(gpt_ctx *ctx);
+/* One pass: photon trace of photons [photon_begin, photon_end), photon LBVH, eye pass,
+ * gather.  After the call the per-hit-point flux / count accumulators of THIS pass are in
+ * the buffer returned by gpt_sppm_flux_device so the host can allreduce them over NCCL
+ * before gpt_sppm_update applies the radius / flux update. */
+int gpt_sppm_pass(gpt_ctx *ctx, int pass, int64_t photon_begin, int64_t photon_end);
+int gpt_sppm_flux_device(gpt_ctx *ctx, void **d_flux /*P x 4 fp32: r,g,b,count*/,
+                         int64_t *num_floats);
+int gpt_sppm_update(gpt_ctx *ctx, int pass);
+int gpt_sppm_resolve(gpt_ctx *ctx, int mode /*0 global,1 direct,2 indirect*/, int passes,
+                     float *out_rgb);
+
+int gpt_stats(gpt_ctx *ctx, GptStats *out);
+int gpt_synchronize(gpt_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GPT_H */

@@ -1,0 +1,567 @@
+/*
+ * ref_replay.cpp -- TEST INFRASTRUCTURE ONLY.  Host replay of the reference's OWN code.
+ *
+ * Builds oracle/_ref/libref_replay.so from the headers under /root/reference/src (included
+ * in place, nothing copied) through oracle/ref_shim.h.  Every function here only marshals
+ * the C-ABI arrays of include/gpt.h into the reference's classes and then calls the
+ * reference's own kernels/functions by looping blockIdx/threadIdx exactly the way
+ * src/main.cu launches them.  It is the ground truth the CUDA path and the C oracle
+ * (oracle/oracle.c) are pinned against, and the "reference" CPU baseline of bench.py.
+ *
+ * It is never imported by the product path (gpu_pathtracer_b200/), only by tests/,
+ * __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs.
+ */
+#include "ref_shim.h"
+
+// same include order as src/main.cu:10-45 (minus the jpeg / input / world.h host loaders)
+#include "model/geometry/triangle.h"
+#include "model/bvh/bvh.h"
+#include "model/bvh/bvh_building.h"
+#include "model/bvh/bvh_building_photon.h"
+#include "model/bvh/bvh_building_pts.h"
+#include "model/bvh/bvh_traversal_photon.h"
+#include "model/camera.h"
+#include "model/geometry/primitive.h"
+#include "model/geometry/triangle_operations.h"
+#include "model/grid/bounding_box.h"
+#include "model/grid/bounding_box_operations.h"
+#include "model/material/material.h"
+#include "model/object/object.h"
+#include "model/object/object_operations.h"
+#include "model/point/point.h"
+#include "model/point/ppm_hit_point.h"
+#include "model/ray/ray.h"
+#include "model/vector_and_matrix/vec3.h"
+#include "render/pathtracing.h"
+#include "render/pathtracing_target_geom_operations.h"
+#include "render/ppm/image_output.h"
+#include "render/ppm/photon_pass.h"
+#include "render/ppm/ray_tracing_pass.h"
+#include "render/transparent_geom_operations.h"
+#include "util/general.h"
+
+#include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <cstring>
+#include <thread>
+#include <unordered_map>
+#include <vector>
+
+#include "../include/gpt.h"
+
+namespace {
+
+// Emulates `kernel<<<grid, block>>>(...)` with 1-D grid/block: one host call per thread.
+template <class F>
+void launch_1d(unsigned grid, unsigned block, F f) {
+  shim_gridDim = dim3(grid, 1, 1);
+  shim_blockDim = dim3(block, 1, 1);
+  for (unsigned b = 0; b < grid; b++) {
+    shim_blockIdx = {b, 0, 0};
+    for (unsigned t = 0; t < block; t++) {
+      shim_threadIdx = {t, 0, 0};
+      f();
+    }
+  }
+  shim_blockIdx = {0, 0, 0};
+  shim_threadIdx = {0, 0, 0};
+}
+
+struct Bvh {
+  int n = 0;
+  Primitive **geom = nullptr;  // sorted in place like the reference
+  Node **node_list = nullptr, **leaf_list = nullptr;
+  BoundingBox **world = nullptr;
+  std::vector<unsigned int> morton;  // sorted codes (extract_morton_code_list)
+};
+
+struct RefCtx {
+  // inputs
+  std::vector<float> x, y, z, xn, yn, zn, xt, yt;
+  std::vector<int> p1, p2, p3, n1, n2, n3, t1, t2, t3, mat_idx, obj_idx;
+  int num_triangles = 0, num_vertices = 0;
+  std::vector<float> tex_r, tex_g, tex_b, bg_r, bg_g, bg_b;
+  int bg_h = 1, bg_w = 1;
+  GptMaterials mats{};
+  std::vector<std::vector<float>> mat_f;  // owned copies
+  std::vector<std::vector<int>> mat_i;
+  GptCamera cam{};
+  GptParams params{};
+  bool have_mesh = false, have_mats = false, have_cam = false;
+
+  // reference objects
+  Material **my_material = nullptr;
+  Primitive **my_geom = nullptr;  // ORIGINAL order copy (my_geom_sorted is the sorted one)
+  Camera **my_camera = nullptr;
+  std::unordered_map<Primitive *, int> orig_index;
+  Bvh main_bvh, transparent_bvh, light_bvh;
+  std::string err;
+  double last_ms = 0;
+};
+
+void build_bvh(Bvh &b, bool cones) {
+  // src/main.cu:826-918 (main), :959-1063 (transparent), :1090-1197 (light)
+  int n = b.n;
+  b.world = new BoundingBox *[1];
+  launch_1d(1, 1, [&] { compute_world_bounding_box(b.world, b.geom, n); });
+  launch_1d(n + 1, 1, [&] { compute_morton_code_batch(b.geom, b.world, n); });
+  // thrust::stable_sort(thrust::device, geom, geom + n, sort_geom)  src/main.cu:846-855
+  std::stable_sort(b.geom, b.geom + n, [](Primitive *o1, Primitive *o2) {
+    return o1->get_bounding_box()->morton_code < o2->get_bounding_box()->morton_code;
+  });
+  b.node_list = new Node *[std::max(1, n - 1)];
+  b.leaf_list = new Node *[std::max(1, n)];
+  launch_1d(std::max(1, n), 1, [&] { build_leaf_list(b.leaf_list, b.geom, n, cones); });
+  launch_1d(std::max(1, n), 1, [&] { build_node_list(b.node_list, n, cones); });
+  b.morton.assign(std::max(1, n), 0u);
+  launch_1d(std::max(1, n), 1,
+            [&] { extract_morton_code_list(b.geom, b.morton.data(), n); });
+  launch_1d(std::max(1, n), 1, [&] {
+    set_node_relationship(b.node_list, b.leaf_list, b.morton.data(), n);
+  });
+  launch_1d(std::max(1, n), 1,
+            [&] { compute_node_bounding_boxes(b.leaf_list, b.node_list, n); });
+  if (cones) {
+    launch_1d(std::max(1, n), 1,
+              [&] { compute_node_bounding_cones(b.leaf_list, b.node_list, n); });
+  }
+}
+
+int child_ref(Node *c) { return c->is_leaf ? ~c->idx : c->idx; }
+
+Bvh *pick(RefCtx *c, int which) {
+  if (which == GPT_BVH_MAIN) return &c->main_bvh;
+  if (which == GPT_BVH_TRANSPARENT) return &c->transparent_bvh;
+  if (which == GPT_BVH_LIGHT) return &c->light_bvh;
+  return nullptr;
+}
+
+}  // namespace
+
+extern "C" {
+
+int ref_create(RefCtx **out) {
+  *out = new RefCtx();
+  return GPT_OK;
+}
+
+void ref_destroy(RefCtx *c) { delete c; /* reference objects are leaked like main.cu does */ }
+
+int ref_set_mesh(RefCtx *c, const GptMesh *m) {
+  int nt = m->num_triangles;
+  auto cpf = [](std::vector<float> &d, const float *s, int n) {
+    d.assign(s, s + std::max(0, n));
+    if (d.empty()) d.push_back(0.f);  // max(1, n) allocations, src/main.cu:412-429
+  };
+  cpf(c->x, m->x, m->num_vertices);
+  cpf(c->y, m->y, m->num_vertices);
+  cpf(c->z, m->z, m->num_vertices);
+  cpf(c->xn, m->x_norm, m->num_normals);
+  cpf(c->yn, m->y_norm, m->num_normals);
+  cpf(c->zn, m->z_norm, m->num_normals);
+  cpf(c->xt, m->x_tex, m->num_texcoords);
+  cpf(c->yt, m->y_tex, m->num_texcoords);
+  auto cpi = [&](std::vector<int> &d, const int *s) { d.assign(s, s + nt); };
+  cpi(c->p1, m->point_1_idx);
+  cpi(c->p2, m->point_2_idx);
+  cpi(c->p3, m->point_3_idx);
+  cpi(c->n1, m->norm_1_idx);
+  cpi(c->n2, m->norm_2_idx);
+  cpi(c->n3, m->norm_3_idx);
+  cpi(c->t1, m->tex_1_idx);
+  cpi(c->t2, m->tex_2_idx);
+  cpi(c->t3, m->tex_3_idx);
+  cpi(c->mat_idx, m->material_idx);
+  cpi(c->obj_idx, m->triangle_object_idx);
+  c->num_triangles = nt;
+  c->num_vertices = m->num_vertices;
+  c->have_mesh = true;
+  return GPT_OK;
+}
+
+int ref_set_materials(RefCtx *c, const GptMaterials *m) {
+  int n = m->num_materials;
+  c->mat_f.clear();
+  c->mat_i.clear();
+  c->mat_f.reserve(64);
+  c->mat_i.reserve(64);
+  GptMaterials o = *m;
+  auto F = [&](const float *&p) {
+    c->mat_f.emplace_back(p, p + n);
+    p = c->mat_f.back().data();
+  };
+  auto I = [&](const int *&p) {
+    c->mat_i.emplace_back(p, p + n);
+    p = c->mat_i.back().data();
+  };
+  F(o.ka_x); F(o.ka_y); F(o.ka_z); F(o.kd_x); F(o.kd_y); F(o.kd_z);
+  F(o.ks_x); F(o.ks_y); F(o.ks_z); F(o.ke_x); F(o.ke_y); F(o.ke_z);
+  F(o.tf_x); F(o.tf_y); F(o.tf_z);
+  F(o.path_length); F(o.t_r); F(o.n_s); F(o.n_i); F(o.bm);
+  F(o.scattering_coef); F(o.absorption_coef); F(o.g);
+  I(o.material_priority);
+  I(o.height_diffuse); I(o.width_diffuse); I(o.offset_diffuse);
+  I(o.height_specular); I(o.width_specular); I(o.offset_specular);
+  I(o.height_emission); I(o.width_emission); I(o.offset_emission);
+  I(o.height_n_s); I(o.width_n_s); I(o.offset_n_s);
+  I(o.height_bump); I(o.width_bump); I(o.offset_bump);
+  c->mats = o;
+  c->have_mats = true;
+  return GPT_OK;
+}
+
+int ref_set_textures(RefCtx *c, const float *r, const float *g, const float *b,
+                     int64_t n) {
+  c->tex_r.assign(r, r + n);
+  c->tex_g.assign(g, g + n);
+  c->tex_b.assign(b, b + n);
+  return GPT_OK;
+}
+
+int ref_set_background(RefCtx *c, const float *r, const float *g, const float *b, int h,
+                       int w) {
+  c->bg_r.assign(r, r + (size_t)h * w);
+  c->bg_g.assign(g, g + (size_t)h * w);
+  c->bg_b.assign(b, b + (size_t)h * w);
+  c->bg_h = h;
+  c->bg_w = w;
+  return GPT_OK;
+}
+
+int ref_set_camera(RefCtx *c, const GptCamera *cam) {
+  c->cam = *cam;
+  c->have_cam = true;
+  return GPT_OK;
+}
+
+int ref_set_params(RefCtx *c, const GptParams *p) {
+  c->params = *p;
+  return GPT_OK;
+}
+
+int ref_build(RefCtx *c) {
+  if (!c->have_mesh || !c->have_mats) return GPT_E_INVALID;
+  const GptMaterials &m = c->mats;
+  int nm = m.num_materials, nt = c->num_triangles;
+  if (c->tex_r.empty()) {  // the 1x1 white default texture, read_image_util.h:135-144
+    c->tex_r = {1.f}; c->tex_g = {1.f}; c->tex_b = {1.f};
+  }
+  float *ir = c->tex_r.data(), *ig = c->tex_g.data(), *ib = c->tex_b.data();
+
+  // create_material<<<1, num_materials>>>  src/main.cu:497, src/lib/world.h:101-175
+  c->my_material = new Material *[100];
+  for (int i = 0; i < nm; i++) {
+    c->my_material[i] = new Material(
+        vec3(m.ka_x[i], m.ka_y[i], m.ka_z[i]), vec3(m.kd_x[i], m.kd_y[i], m.kd_z[i]),
+        vec3(m.ks_x[i], m.ks_y[i], m.ks_z[i]), vec3(m.ke_x[i], m.ke_y[i], m.ke_z[i]),
+        vec3(m.tf_x[i], m.tf_y[i], m.tf_z[i]), m.path_length[i], m.t_r[i], m.n_s[i],
+        m.n_i[i], m.bm[i], m.scattering_coef[i], m.absorption_coef[i], m.g[i],
+        m.material_priority[i],
+        m.height_diffuse[i], m.width_diffuse[i], ir + m.offset_diffuse[i],
+        ig + m.offset_diffuse[i], ib + m.offset_diffuse[i],
+        m.height_specular[i], m.width_specular[i], ir + m.offset_specular[i],
+        ig + m.offset_specular[i], ib + m.offset_specular[i],
+        m.height_emission[i], m.width_emission[i], ir + m.offset_emission[i],
+        ig + m.offset_emission[i], ib + m.offset_emission[i],
+        m.height_n_s[i], m.width_n_s[i], ir + m.offset_n_s[i], ig + m.offset_n_s[i],
+        ib + m.offset_n_s[i],
+        m.height_bump[i], m.width_bump[i], ir + m.offset_bump[i], ig + m.offset_bump[i],
+        ib + m.offset_bump[i]);
+  }
+
+  // create_world<<<N+1, 1>>>  src/main.cu:582, src/lib/world.h:194-248
+  Primitive **geom = new Primitive *[nt];
+  c->my_geom = new Primitive *[nt];
+  const float *x = c->x.data(), *y = c->y.data(), *z = c->z.data();
+  const float *xn = c->xn.data(), *yn = c->yn.data(), *zn = c->zn.data();
+  const float *xt = c->xt.data(), *yt = c->yt.data();
+  for (int i = 0; i < nt; i++) {
+    int a = c->p1[i], b = c->p2[i], d = c->p3[i];
+    geom[i] = new Triangle(
+        vec3(x[a], y[a], z[a]), vec3(x[b], y[b], z[b]), vec3(x[d], y[d], z[d]), a, b, d,
+        c->my_material[c->mat_idx[i]], c->obj_idx[i],
+        vec3(xn[c->n1[i]], yn[c->n1[i]], zn[c->n1[i]]),
+        vec3(xn[c->n2[i]], yn[c->n2[i]], zn[c->n2[i]]),
+        vec3(xn[c->n3[i]], yn[c->n3[i]], zn[c->n3[i]]),
+        vec3(xt[c->t1[i]], yt[c->t1[i]], 0), vec3(xt[c->t2[i]], yt[c->t2[i]], 0),
+        vec3(xt[c->t3[i]], yt[c->t3[i]], 0));
+    c->my_geom[i] = geom[i];
+    c->orig_index[geom[i]] = i;
+  }
+
+  // tangents  src/main.cu:602-625
+  std::vector<vec3> tangent(std::max(1, c->num_vertices)), bitangent(tangent.size());
+  launch_1d(1, 1, [&] {
+    sum_up_tangent_and_bitangent(tangent.data(), bitangent.data(), geom, nt);
+  });
+  launch_1d(nt, 1, [&] { assign_tangent(tangent.data(), geom, nt); });
+
+  // main BVH  src/main.cu:826-918
+  c->main_bvh.n = nt;
+  c->main_bvh.geom = geom;
+  build_bvh(c->main_bvh, false);
+
+  // transparent subset, collected from the SORTED main list  src/main.cu:930-1063
+  {
+    int cnt = 0;
+    launch_1d(1, 1, [&] { compute_num_transparent_geom(geom, nt, &cnt); });
+    Bvh &b = c->transparent_bvh;
+    b.n = cnt;
+    b.geom = new Primitive *[std::max(1, cnt)];
+    launch_1d(1, 1, [&] { collect_transparent_geom(geom, nt, b.geom); });
+    if (cnt >= 2) build_bvh(b, false);
+  }
+  // light ("target") subset  src/main.cu:1065-1197
+  {
+    int cnt = 0;
+    launch_1d(1, 1, [&] { compute_num_target_geom(geom, nt, &cnt); });
+    Bvh &b = c->light_bvh;
+    b.n = cnt;
+    b.geom = new Primitive *[std::max(1, cnt)];
+    launch_1d(1, 1, [&] { collect_target_geom(geom, nt, b.geom); });
+    if (cnt >= 2) build_bvh(b, true);
+  }
+
+  if (c->have_cam) {
+    const GptCamera &k = c->cam;
+    c->my_camera = new Camera *[1];
+    c->my_camera[0] = new Camera(vec3(k.eye[0], k.eye[1], k.eye[2]),
+                                 vec3(k.center[0], k.center[1], k.center[2]),
+                                 vec3(k.up[0], k.up[1], k.up[2]), k.fovy, k.width,
+                                 k.height, k.aperture, k.focus_dist);
+  }
+  return GPT_OK;
+}
+
+// Times only the main-BVH stage (src/main.cu:826-918) on the already constructed triangles;
+// used by bench.py's cpu_baseline leg.  The geometry list is restored to OBJ order first.
+int ref_time_main_bvh_build(RefCtx *c, double *ms) {
+  int nt = c->num_triangles;
+  Primitive **geom = new Primitive *[nt];
+  memcpy(geom, c->my_geom, sizeof(Primitive *) * nt);
+  Bvh b;
+  b.n = nt;
+  b.geom = geom;
+  auto t0 = std::chrono::steady_clock::now();
+  build_bvh(b, false);
+  auto t1 = std::chrono::steady_clock::now();
+  *ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
+  // the triangles' boxes now carry the main-BVH codes again; keep this tree as the main one
+  c->main_bvh = b;
+  return GPT_OK;
+}
+
+int ref_export_triangles(RefCtx *c, float *tolerance, float *aabb, float *normal,
+                         float *area, int32_t *flags, float *energy, float *tangents) {
+  for (int i = 0; i < c->num_triangles; i++) {
+    Triangle *t = static_cast<Triangle *>(c->my_geom[i]);
+    const Triangle *p = t;
+    BoundingBox *bb = t->get_bounding_box();
+    if (tolerance) tolerance[i] = p->tolerance;
+    if (aabb) {
+      float *a = aabb + 6 * i;
+      a[0] = bb->x_min; a[1] = bb->x_max; a[2] = bb->y_min;
+      a[3] = bb->y_max; a[4] = bb->z_min; a[5] = bb->z_max;
+    }
+    if (normal) {
+      vec3 n = t->get_fixed_normal();
+      normal[3 * i] = n.x(); normal[3 * i + 1] = n.y(); normal[3 * i + 2] = n.z();
+    }
+    if (area) area[i] = t->get_area();
+    if (flags)
+      flags[i] = (t->is_light_source() ? GPT_TRI_LIGHT : 0) |
+                 (t->is_transparent_geom() ? GPT_TRI_TRANSPARENT : 0) |
+                 (t->is_sub_surface_scattering() ? GPT_TRI_SSS : 0);
+    if (energy) {
+      vec3 e = t->get_energy();
+      energy[3 * i] = e.x(); energy[3 * i + 1] = e.y(); energy[3 * i + 2] = e.z();
+    }
+    if (tangents) {
+      const vec3 *tg[3] = {&p->tangent_1, &p->tangent_2, &p->tangent_3};
+      for (int k = 0; k < 3; k++)
+        for (int a = 0; a < 3; a++) tangents[9 * i + 3 * k + a] = (*tg[k])[a];
+    }
+  }
+  return GPT_OK;
+}
+
+int ref_bvh_num_leaves(RefCtx *c, int which, int32_t *n) {
+  Bvh *b = pick(c, which);
+  if (!b) return GPT_E_INVALID;
+  *n = b->n;
+  return GPT_OK;
+}
+
+int ref_export_bvh(RefCtx *c, int which, uint32_t *morton, int32_t *sorted_to_orig,
+                   int32_t *left, int32_t *right, int32_t *parent_internal,
+                   int32_t *parent_leaf, float *node_aabb, float *leaf_aabb,
+                   float *world_aabb) {
+  Bvh *b = pick(c, which);
+  if (!b || b->n < 2) return GPT_E_INVALID;
+  int n = b->n;
+  auto put = [](float *a, BoundingBox *bb) {
+    a[0] = bb->x_min; a[1] = bb->x_max; a[2] = bb->y_min;
+    a[3] = bb->y_max; a[4] = bb->z_min; a[5] = bb->z_max;
+  };
+  for (int j = 0; j < n; j++) {
+    if (morton) morton[j] = b->morton[j];
+    if (sorted_to_orig) sorted_to_orig[j] = c->orig_index[b->geom[j]];
+    if (parent_leaf) parent_leaf[j] = b->leaf_list[j]->parent->idx;
+    if (leaf_aabb) put(leaf_aabb + 6 * j, b->leaf_list[j]->bounding_box);
+  }
+  for (int i = 0; i < n - 1; i++) {
+    Node *nd = b->node_list[i];
+    if (left) left[i] = child_ref(nd->left);
+    if (right) right[i] = child_ref(nd->right);
+    if (parent_internal) parent_internal[i] = (i == 0) ? -1 : nd->parent->idx;
+    if (node_aabb) put(node_aabb + 6 * i, nd->bounding_box);
+  }
+  if (world_aabb) put(world_aabb, b->world[0]);
+  return GPT_OK;
+}
+
+// Light-tree extras (cones + energies), for the light-sampling parity tests.
+int ref_export_light_tree(RefCtx *c, float *node_cone /*5(n-1): axis,theta_0,theta_e*/,
+                          float *node_energy /*3(n-1)*/, float *leaf_energy /*3n*/) {
+  Bvh *b = &c->light_bvh;
+  if (b->n < 2) return GPT_E_INVALID;
+  for (int i = 0; i < b->n - 1; i++) {
+    Node *nd = b->node_list[i];
+    if (node_cone) {
+      float *o = node_cone + 5 * i;
+      o[0] = nd->bounding_cone->axis.x(); o[1] = nd->bounding_cone->axis.y();
+      o[2] = nd->bounding_cone->axis.z(); o[3] = nd->bounding_cone->theta_0;
+      o[4] = nd->bounding_cone->theta_e;
+    }
+    if (node_energy)
+      for (int a = 0; a < 3; a++) node_energy[3 * i + a] = nd->energy[a];
+  }
+  if (leaf_energy)
+    for (int j = 0; j < b->n; j++)
+      for (int a = 0; a < 3; a++) leaf_energy[3 * j + a] = b->leaf_list[j]->energy[a];
+  return GPT_OK;
+}
+
+// traverse_bvh + Triangle::hit on a ray list (src/model/bvh/bvh_traversal.h:12-84).
+// nthreads <= 1 is the single-core replay BASELINE.md 3.2 asks for.
+int ref_trace(RefCtx *c, int which, const float *rays, int64_t n, int32_t *leaf_id,
+              int32_t *tri_id, float *t_out, float *bary, int nthreads) {
+  Bvh *b = pick(c, which);
+  if (!b || b->n < 2) return GPT_E_INVALID;
+  std::unordered_map<Primitive *, int> leaf_of;
+  leaf_of.reserve(b->n * 2);
+  for (int j = 0; j < b->n; j++) leaf_of[b->geom[j]] = j;
+  auto t0 = std::chrono::steady_clock::now();
+  auto work = [&](int64_t lo, int64_t hi) {
+    for (int64_t r = lo; r < hi; r++) {
+      const float *q = rays + 8 * r;
+      Ray ray(vec3(q[0], q[1], q[2]), vec3(q[4], q[5], q[6]));
+      hit_record rec;
+      bool hit = traverse_bvh(b->node_list[0], ray, rec);
+      // rec.t starts at INFINITY inside traverse_bvh; an optional finite tmax only filters
+      if (hit && rec.t > q[3]) hit = false;
+      int lj = -1, oi = -1;
+      float tt = INFINITY, b1 = 0, b2 = 0, b3 = 0;
+      if (hit) {
+        lj = leaf_of[rec.object];
+        oi = c->orig_index[rec.object];
+        tt = rec.t;
+      }
+      if (leaf_id) leaf_id[r] = lj;
+      if (tri_id) tri_id[r] = oi;
+      if (t_out) t_out[r] = tt;
+      if (bary) { bary[3 * r] = b1; bary[3 * r + 1] = b2; bary[3 * r + 2] = b3; }
+      if (hit && bary) {
+        // hit_record has no barycentrics; rec.point = b1*p1 + b2*p2 + b3*p3 is exported
+        // instead so the CUDA path's reconstruction can be compared bitwise.
+        bary[3 * r] = rec.point.x(); bary[3 * r + 1] = rec.point.y();
+        bary[3 * r + 2] = rec.point.z();
+      }
+    }
+  };
+  if (nthreads <= 1) {
+    work(0, n);
+  } else {
+    std::vector<std::thread> th;
+    int64_t chunk = (n + nthreads - 1) / nthreads;
+    for (int k = 0; k < nthreads; k++) {
+      int64_t lo = k * chunk, hi = std::min<int64_t>(n, lo + chunk);
+      if (lo < hi) th.emplace_back(work, lo, hi);
+    }
+    for (auto &x : th) x.join();
+  }
+  auto t1 = std::chrono::steady_clock::now();
+  c->last_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
+  return GPT_OK;
+}
+
+double ref_last_ms(RefCtx *c) { return c->last_ms; }
+
+// Camera::compute_ray for every pixel centre with the reference's per-pixel XORWOW stream
+// (src/model/camera.h:68-83, src/util/general.h:8-16).  rays: P x 8 as gpt_trace takes.
+int ref_primary_rays(RefCtx *c, float *rays) {
+  if (!c->my_camera) return GPT_E_INVALID;
+  int W = c->cam.width, H = c->cam.height;
+  for (int i = 0; i < H; i++)
+    for (int j = 0; j < W; j++) {
+      int pix = i * W + j;
+      curandState st;
+      curand_init(1984, pix, 0, &st);
+      Ray r = c->my_camera[0]->compute_ray(i + .5, j + .5, &st);
+      float *q = rays + 8 * (size_t)pix;
+      q[0] = r.p0.x(); q[1] = r.p0.y(); q[2] = r.p0.z(); q[3] = INFINITY;
+      q[4] = r.dir.x(); q[5] = r.dir.y(); q[6] = r.dir.z(); q[7] = 0;
+    }
+  return GPT_OK;
+}
+
+// init_curand_state + path_tracing_render (src/main.cu:1208,1266) over a pixel window
+// [row0,row1) x [col0,col1); pixels outside are left untouched in out_rgb (P x 3).
+int ref_render_pathtrace_window(RefCtx *c, float *out_rgb, int row0, int row1, int col0,
+                                int col1, int nthreads) {
+  if (!c->my_camera || c->light_bvh.n < 2) return GPT_E_INVALID;
+  int W = c->cam.width, H = c->cam.height;
+  const GptParams &p = c->params;
+  vec3 sky(p.sky_emission[0], p.sky_emission[1], p.sky_emission[2]);
+  if (c->bg_r.empty()) { c->bg_r = {1.f}; c->bg_g = {1.f}; c->bg_b = {1.f}; }
+  std::vector<vec3> fb((size_t)W * H);
+  std::vector<curandState> rs((size_t)W * H);
+  row1 = std::min(row1, H);
+  col1 = std::min(col1, W);
+  std::atomic<int> next_row(row0);
+  auto t0 = std::chrono::steady_clock::now();
+  auto work = [&] {
+    shim_blockDim = dim3(1, 1, 1);
+    for (;;) {
+      int i = next_row.fetch_add(1);
+      if (i >= row1) break;
+      for (int j = col0; j < col1; j++) {
+        shim_blockIdx = {(unsigned)j, (unsigned)i, 0};
+        shim_threadIdx = {0, 0, 0};
+        curand_init(1984, i * W + j, 0, &rs[(size_t)i * W + j]);
+        path_tracing_render(fb.data(), c->my_camera, rs.data(), p.pathtracing_sample_size,
+                            p.pathtracing_level, p.dof_sample_size, sky, c->bg_h, c->bg_w,
+                            c->bg_r.data(), c->bg_g.data(), c->bg_b.data(),
+                            c->main_bvh.node_list, nullptr, nullptr,
+                            c->light_bvh.node_list, c->light_bvh.leaf_list,
+                            c->light_bvh.geom, c->light_bvh.n, p.hittable_pdf_weight);
+        float *o = out_rgb + 3 * ((size_t)i * W + j);
+        const vec3 &v = fb[(size_t)i * W + j];
+        o[0] = v.x(); o[1] = v.y(); o[2] = v.z();
+      }
+    }
+  };
+  if (nthreads <= 1) {
+    work();
+  } else {
+    std::vector<std::thread> th;
+    for (int k = 0; k < nthreads; k++) th.emplace_back(work);
+    for (auto &x : th) x.join();
+  }
+  auto t1 = std::chrono::steady_clock::now();
+  c->last_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
+  return GPT_OK;
+}
+
+}  // extern "C"
