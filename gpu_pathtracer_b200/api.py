@@ -1,0 +1,179 @@
+"""Host-side mirror of the reference's launch sequence, bound to libgpt.so over ctypes.
+
+``PathTracer`` plays the role of the part of ``main()`` that follows the loaders
+(src/main.cu:474-1870): it takes the flat SoA the reference's OBJ/MTL loader produces (a
+``Scene``), hands it to the C-ABI (include/gpt.h) and exposes build / trace / render.
+
+There is NO CPU fallback: if the CUDA library is missing or no GPU is visible every call
+raises ``GptError``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import cabi
+from .scene import Scene
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "csrc", "libgpt.so")
+
+# every symbol include/gpt.h declares
+SYMBOLS = """gpt_create gpt_destroy gpt_last_error gpt_version gpt_set_stream gpt_set_mesh
+gpt_set_materials gpt_set_textures gpt_set_background gpt_set_camera gpt_set_params gpt_build
+gpt_rebuild_main_bvh gpt_export_triangles gpt_bvh_num_leaves gpt_export_bvh gpt_trace
+gpt_trace_device gpt_trace_count_device gpt_render_pathtrace gpt_render_pathtrace_device
+gpt_sppm_init gpt_sppm_pass gpt_sppm_flux_device gpt_sppm_update gpt_sppm_resolve gpt_stats
+gpt_synchronize""".split()
+
+
+class GptError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load_library():
+    """dlopen the in-tree libgpt.so; raise loudly when it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise GptError(
+            f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; "
+            "g.build()'` or `make -C gpu_pathtracer_b200/csrc`. There is no CPU fallback.")
+    lib = C.CDLL(LIB_PATH)
+    lib.gpt_last_error.restype = C.c_char_p
+    lib.gpt_version.restype = C.c_char_p
+    lib.gpt_destroy.restype = None
+    _lib = lib
+    return lib
+
+
+class PathTracer:
+    def __init__(self, scene: Scene | None = None, device: int = 0):
+        self.lib = load_library()
+        self.ctx = C.c_void_p()
+        rc = self.lib.gpt_create(C.c_int(device), C.byref(self.ctx))
+        if rc != 0:
+            raise GptError({-3: "no CUDA device visible (GPT_E_NODEVICE): this library has "
+                                "no CPU path"}.get(rc, f"gpt_create failed with {rc}"))
+        self.scene = None
+        if scene is not None:
+            self.set_scene(scene)
+
+    # -- plumbing ---------------------------------------------------------------------
+    def _check(self, rc):
+        if rc != 0:
+            msg = self.lib.gpt_last_error(self.ctx)
+            raise GptError(f"gpt error {rc}: {msg.decode() if msg else ''}")
+
+    def close(self):
+        if self.ctx:
+            self.lib.gpt_destroy(self.ctx)
+            self.ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_stream(self, cuda_stream: int):
+        self._check(self.lib.gpt_set_stream(self.ctx, C.c_uint64(cuda_stream)))
+
+    def synchronize(self):
+        self._check(self.lib.gpt_synchronize(self.ctx))
+
+    # -- scene ------------------------------------------------------------------------
+    def set_scene(self, scene: Scene):
+        self.scene = scene
+        cabi.upload_scene(self.lib, "gpt_", self.ctx, scene, self._check)
+
+    def set_params(self, **kw):
+        self.scene.params.update(kw)
+        p = cabi.pack_params(self.scene.params)
+        self._check(self.lib.gpt_set_params(self.ctx, C.byref(p)))
+
+    def build(self):
+        self._check(self.lib.gpt_build(self.ctx))
+        return self.stats()
+
+    def rebuild_main_bvh(self) -> float:
+        self._check(self.lib.gpt_rebuild_main_bvh(self.ctx))
+        return self.stats()["build_ms"]
+
+    def stats(self) -> dict:
+        s = cabi.GptStats()
+        self._check(self.lib.gpt_stats(self.ctx, C.byref(s)))
+        return {n: getattr(s, n) for n, _ in cabi.GptStats._fields_}
+
+    # -- parity exports -----------------------------------------------------------------
+    def export_triangles(self) -> dict:
+        n = self.scene.num_triangles
+        out = dict(tolerance=np.zeros(n, np.float32), aabb=np.zeros((n, 6), np.float32),
+                   normal=np.zeros((n, 3), np.float32), area=np.zeros(n, np.float32),
+                   flags=np.zeros(n, np.int32), energy=np.zeros((n, 3), np.float32),
+                   tangents=np.zeros((n, 9), np.float32))
+        self._check(self.lib.gpt_export_triangles(
+            self.ctx, cabi.fptr(out["tolerance"]), cabi.fptr(out["aabb"]),
+            cabi.fptr(out["normal"]), cabi.fptr(out["area"]), cabi.iptr(out["flags"]),
+            cabi.fptr(out["energy"]), cabi.fptr(out["tangents"])))
+        return out
+
+    def num_leaves(self, which=0) -> int:
+        n = C.c_int32()
+        self._check(self.lib.gpt_bvh_num_leaves(self.ctx, which, C.byref(n)))
+        return n.value
+
+    def export_bvh(self, which=0) -> dict:
+        n = self.num_leaves(which)
+        out = dict(morton=np.zeros(n, np.uint32), sorted_to_orig=np.zeros(n, np.int32),
+                   left=np.zeros(n - 1, np.int32), right=np.zeros(n - 1, np.int32),
+                   parent_internal=np.zeros(n - 1, np.int32),
+                   parent_leaf=np.zeros(n, np.int32),
+                   node_aabb=np.zeros((n - 1, 6), np.float32),
+                   leaf_aabb=np.zeros((n, 6), np.float32), world_aabb=np.zeros(6, np.float32))
+        self._check(self.lib.gpt_export_bvh(
+            self.ctx, which, cabi.uptr(out["morton"]), cabi.iptr(out["sorted_to_orig"]),
+            cabi.iptr(out["left"]), cabi.iptr(out["right"]),
+            cabi.iptr(out["parent_internal"]), cabi.iptr(out["parent_leaf"]),
+            cabi.fptr(out["node_aabb"]), cabi.fptr(out["leaf_aabb"]),
+            cabi.fptr(out["world_aabb"])))
+        return out
+
+    # -- trace --------------------------------------------------------------------------
+    def trace(self, rays: np.ndarray, which=0) -> dict:
+        """rays: (n, 8) float32 {ox,oy,oz,tmax,dx,dy,dz,0}, host memory."""
+        rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 8)
+        n = rays.shape[0]
+        out = dict(leaf_id=np.zeros(n, np.int32), tri_id=np.zeros(n, np.int32),
+                   t=np.zeros(n, np.float32), bary=np.zeros((n, 3), np.float32))
+        self._check(self.lib.gpt_trace(self.ctx, which, cabi.fptr(rays), C.c_int64(n),
+                                       cabi.iptr(out["leaf_id"]), cabi.iptr(out["tri_id"]),
+                                       cabi.fptr(out["t"]), cabi.fptr(out["bary"])))
+        return out
+
+    def trace_device(self, d_rays: int, n: int, d_hits: int, which=0):
+        """Device pointers (ints); asynchronous on the context's stream."""
+        self._check(self.lib.gpt_trace_device(self.ctx, which, C.c_void_p(d_rays),
+                                              C.c_int64(n), C.c_void_p(d_hits)))
+
+    def trace_count_device(self, d_rays: int, n: int, which=0) -> dict:
+        self._check(self.lib.gpt_trace_count_device(self.ctx, which, C.c_void_p(d_rays),
+                                                    C.c_int64(n)))
+        return self.stats()
+
+    # -- render -------------------------------------------------------------------------
+    def render_pathtrace(self) -> np.ndarray:
+        cam = self.scene.camera
+        out = np.zeros((cam["height"], cam["width"], 3), np.float32)
+        self._check(self.lib.gpt_render_pathtrace(self.ctx, cabi.fptr(out)))
+        return out
+
+    def render_pathtrace_device(self, d_out: int, rank: int = 0, nranks: int = 1):
+        self._check(self.lib.gpt_render_pathtrace_device(self.ctx, C.c_void_p(d_out),
+                                                         C.c_int(rank), C.c_int(nranks)))

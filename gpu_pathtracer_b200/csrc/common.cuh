@@ -1,0 +1,177 @@
+// common.cuh -- shared declarations of the sm_100a hot path (context, device layouts).
+//
+// ARITHMETIC CONTRACT: every .cu of this library is compiled with -fmad=false, so a*b+c is
+// evaluated as an IEEE fp32 multiply followed by an IEEE fp32 add, exactly like the
+// reference's host replay (g++ -ffp-contract=off).  Where a fused multiply-add is wanted for
+// speed in code that is NOT parity-critical it is written explicitly as fmaf().
+// Division and sqrt are the IEEE-rounded defaults (-prec-div=true -prec-sqrt=true).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+
+#include "../../include/gpt.h"
+
+#define GPT_SMALL 1e-5f  // SMALL_DOUBLE, src/param.h:6
+
+// ---- device layouts ------------------------------------------------------------------
+// BVH node, 64 B, four 16-byte words fetched with ld.global.nc.v4:
+//   q0 = (L.xmin, L.xmax, L.ymin, L.ymax)
+//   q1 = (L.zmin, L.zmax, R.xmin, R.xmax)
+//   q2 = (R.ymin, R.ymax, R.zmin, R.zmax)
+//   q3 = (left_ref, right_ref, parent_enc, range_first)  as int bits
+// child ref c >= 0: internal node c; c < 0: leaf ~c (sorted position).
+// parent_enc = parent * 2 + is_right_child, -1 for the root.
+// Internal node i lives at index i and the root is node 0, as in the reference
+// (src/model/bvh/bvh_building.h:63,72,179-183).
+//
+// Trace triangle, 48 B, three 16-byte words, stored in SORTED (leaf) order:
+//   t0 = (p1.x, p1.y, p1.z, p2.x)  t1 = (p2.y, p2.z, p3.x, p3.y)
+//   t2 = (p3.z, tolerance, prim_index bits, 0)
+
+struct BvhDev {
+  int n = 0;             // leaves
+  int capacity = 0;      // allocated leaves
+  float4 *nodes = nullptr;      // 4 * (n-1) float4
+  float4 *tris = nullptr;       // 3 * n float4 (triangle BVHs only)
+  int *parent_leaf = nullptr;   // n, encoded like parent_enc
+  uint32_t *morton = nullptr;   // n sorted keys
+  int *sorted_prim = nullptr;   // n: index into the primitive list the BVH was built over
+  int *prim_list = nullptr;     // optional subset list -> original triangle index (NULL = identity)
+  uint32_t *world_enc = nullptr;  // 6 order-preserving encoded floats: min xyz, max xyz
+  // build scratch
+  uint32_t *keys_alt = nullptr;
+  int *vals_alt = nullptr;
+  uint32_t *block_hist = nullptr;
+  int hist_capacity = 0;
+  int *flags = nullptr;         // n-1 arrival counters for the refit
+};
+
+// Per-triangle shading record in ORIGINAL order (7 float4 = 112 B), filled by preprocess:
+//   s0 = (n1.x n1.y n1.z n2.x) s1 = (n2.y n2.z n3.x n3.y) s2 = (n3.z uv1.u uv1.v uv2.u)
+//   s3 = (uv2.v uv3.u uv3.v area) s4 = (tg1.x tg1.y tg1.z tg2.x) s5 = (tg2.y tg2.z tg3.x tg3.y)
+//   s6 = (tg3.z, material_idx bits, flags bits, object_idx bits)
+
+struct MaterialDev {  // one per material, constant-ish, read through the read-only path
+  float ka[3], kd[3], ks[3], ke[3], tf[3];
+  float path_length, t_r, n_s, n_i, bm;
+  float scattering_coef, absorption_coef, extinction_coef, g, scattering_prob;
+  int priority;
+  int sss;
+  int tex_h[5], tex_w[5], tex_off[5];  // diffuse, specular, emission, n_s, bump
+  int pad;
+};
+
+struct SceneDev {
+  // raw SoA as uploaded (src/main.cu:386-450)
+  int nv = 0, nvn = 0, nvt = 0, ntri = 0, nobj = 0, nmat = 0;
+  float *x = nullptr, *y = nullptr, *z = nullptr;
+  float *xn = nullptr, *yn = nullptr, *zn = nullptr;
+  float *xt = nullptr, *yt = nullptr;
+  int *p1 = nullptr, *p2 = nullptr, *p3 = nullptr;
+  int *n1 = nullptr, *n2 = nullptr, *n3 = nullptr;
+  int *t1 = nullptr, *t2 = nullptr, *t3 = nullptr;
+  int *mat_idx = nullptr, *obj_idx = nullptr;
+  MaterialDev *mats = nullptr;
+  float *tex_r = nullptr, *tex_g = nullptr, *tex_b = nullptr;
+  int64_t tex_len = 0;
+  float *bg_r = nullptr, *bg_g = nullptr, *bg_b = nullptr;
+  int bg_h = 1, bg_w = 1;
+  // derived per triangle (original order)
+  float *tolerance = nullptr;  // N
+  float *aabb = nullptr;       // 6N: xmin,xmax,ymin,ymax,zmin,zmax
+  float *normal = nullptr;     // 3N
+  float *energy = nullptr;     // 3N
+  float4 *shade = nullptr;     // 7N
+  float *vtangent = nullptr;   // 3 * nv accumulated per-vertex tangents
+};
+
+struct gpt_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  cudaStream_t own_stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  std::string err;
+  SceneDev scene;
+  BvhDev bvh[3];
+  GptCamera cam{};
+  GptParams params{};
+  GptStats stats{};
+  bool have_mesh = false, have_mats = false, have_cam = false, built = false;
+  unsigned long long *d_counters = nullptr;  // [0] V_int [1] V_leaf [2] rays [3] overflow
+  void *render_state = nullptr;              // owned by render.cu
+  void *sppm_state = nullptr;                // owned by sppm.cu
+  uint64_t launches = 0;                     // kernels launched since last reset
+};
+
+// ---- error plumbing --------------------------------------------------------------------
+int gpt_fail(gpt_ctx *ctx, int code, const char *what, const char *file, int line);
+#define GPT_CUDA(ctx, call)                                                         \
+  do {                                                                              \
+    cudaError_t e__ = (call);                                                       \
+    if (e__ != cudaSuccess)                                                         \
+      return gpt_fail((ctx), GPT_E_CUDA, cudaGetErrorString(e__), __FILE__, __LINE__); \
+  } while (0)
+#define GPT_TRY(expr)            \
+  do {                           \
+    int rc__ = (expr);           \
+    if (rc__ != GPT_OK) return rc__; \
+  } while (0)
+#define GPT_LAUNCH_CHECK(ctx)    \
+  do {                           \
+    (ctx)->launches++;           \
+    GPT_CUDA((ctx), cudaGetLastError()); \
+  } while (0)
+
+template <class T>
+static inline int gpt_alloc(gpt_ctx *ctx, T **p, size_t count) {
+  if (*p) { cudaFree(*p); *p = nullptr; }
+  if (count == 0) count = 1;
+  GPT_CUDA(ctx, cudaMalloc((void **)p, count * sizeof(T)));
+  return GPT_OK;
+}
+template <class T>
+static inline int gpt_upload(gpt_ctx *ctx, T **p, const T *host, size_t count) {
+  GPT_TRY(gpt_alloc(ctx, p, count));
+  if (count)
+    GPT_CUDA(ctx, cudaMemcpyAsync(*p, host, count * sizeof(T), cudaMemcpyHostToDevice,
+                                  ctx->stream));
+  return GPT_OK;
+}
+
+// ---- order-preserving float <-> uint encoding for atomicMin/atomicMax -------------------
+__host__ __device__ static inline uint32_t enc_f32(float f) {
+#ifdef __CUDA_ARCH__
+  uint32_t b = __float_as_uint(f);
+#else
+  union { float f; uint32_t u; } c; c.f = f; uint32_t b = c.u;
+#endif
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__host__ __device__ static inline float dec_f32(uint32_t e) {
+  uint32_t b = (e & 0x80000000u) ? (e & 0x7fffffffu) : ~e;
+#ifdef __CUDA_ARCH__
+  return __uint_as_float(b);
+#else
+  union { float f; uint32_t u; } c; c.u = b; return c.f;
+#endif
+}
+
+// ---- stage entry points (implemented in the .cu named) ----------------------------------
+int gpt_preprocess(gpt_ctx *ctx);                                    // preprocess.cu
+int gpt_lbvh_build(gpt_ctx *ctx, int which, const int *d_prim_list, int n);  // lbvh.cu
+int gpt_lbvh_export(gpt_ctx *ctx, int which, uint32_t *morton, int32_t *sorted_to_orig,
+                    int32_t *left, int32_t *right, int32_t *parent_internal,
+                    int32_t *parent_leaf, float *node_aabb, float *leaf_aabb,
+                    float *world_aabb);
+void gpt_lbvh_free(BvhDev &b);
+int gpt_collect_subset(gpt_ctx *ctx, int flag_mask, int **d_list, int *count);  // lbvh.cu
+int gpt_trace_launch(gpt_ctx *ctx, int which, const float4 *d_rays, int64_t n,
+                     float4 *d_hits, bool normalize, bool count);     // trace.cu
+// stable LSD radix sort of (key, value) pairs on key bits [0, nbits)   // lbvh.cu
+int gpt_radix_sort_pairs(gpt_ctx *ctx, uint32_t *keys, int *vals, uint32_t *keys_alt,
+                         int *vals_alt, uint32_t *block_hist, int n, int nbits,
+                         uint32_t **keys_out, int **vals_out);
+int gpt_radix_hist_entries(int n);

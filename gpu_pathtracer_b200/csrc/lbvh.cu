@@ -1,0 +1,507 @@
+// lbvh.cu -- Karras LBVH construction for sm_100a.
+//
+// Replaces src/main.cu:826-918 (and the transparent / light repeats :930-1197):
+//   compute_world_bounding_box  (1 thread, serial)      -> k_world_reduce (grid reduction)
+//   compute_morton_code_batch   (1 thread / block)      -> k_morton
+//   thrust::stable_sort w/ pointer comparator           -> 8-bit LSD radix sort, warp-match
+//                                                          ranking (stable), 4 passes
+//   set_node_relationship       (linear scans)          -> k_emit (binary searches)
+//   compute_node_bounding_boxes (flags, no fences)      -> k_refit (atomic counters + fence),
+//                                                          fused with the 48-byte triangle pack
+// Results (codes, permutation, topology, boxes) are bit-identical to the reference: the
+// Morton arithmetic is the same fp32 sequence, the sort is stable, delta() carries the
+// same index tie-break, and min/max unions are order-independent.
+#include "common.cuh"
+#include "vecmath.cuh"
+
+namespace {
+
+constexpr int SORT_THREADS = 256;
+constexpr int SORT_ITEMS = 16;                         // keys per thread
+constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;   // 4096 keys per block
+constexpr int SORT_WARPS = SORT_THREADS / 32;
+
+// ---- world box ---------------------------------------------------------------------
+// compute_world_bounding_box (bounding_box_operations.h:12-45): min/max over the leaf boxes.
+__global__ void __launch_bounds__(256)
+k_world_reduce(const float *__restrict__ aabb, const int *__restrict__ prim_list, int n,
+               uint32_t *world_enc) {
+  float mn[3] = {INFINITY, INFINITY, INFINITY}, mx[3] = {-INFINITY, -INFINITY, -INFINITY};
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    int p = prim_list ? __ldg(prim_list + i) : i;
+    const float2 *b = reinterpret_cast<const float2 *>(aabb + 6 * (size_t)p);
+    float2 bx = __ldg(b), by = __ldg(b + 1), bz = __ldg(b + 2);
+    mn[0] = fminf(mn[0], bx.x); mx[0] = fmaxf(mx[0], bx.y);
+    mn[1] = fminf(mn[1], by.x); mx[1] = fmaxf(mx[1], by.y);
+    mn[2] = fminf(mn[2], bz.x); mx[2] = fmaxf(mx[2], bz.y);
+  }
+#pragma unroll
+  for (int a = 0; a < 3; a++) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      mn[a] = fminf(mn[a], __shfl_xor_sync(0xffffffffu, mn[a], o));
+      mx[a] = fmaxf(mx[a], __shfl_xor_sync(0xffffffffu, mx[a], o));
+    }
+  }
+  __shared__ float smn[3][8], smx[3][8];
+  int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  if (l == 0)
+    for (int a = 0; a < 3; a++) { smn[a][w] = mn[a]; smx[a][w] = mx[a]; }
+  __syncthreads();
+  if (threadIdx.x < 3) {
+    int a = threadIdx.x;
+    float lo = smn[a][0], hi = smx[a][0];
+    for (int k = 1; k < 8; k++) { lo = fminf(lo, smn[a][k]); hi = fmaxf(hi, smx[a][k]); }
+    atomicMin(world_enc + a, enc_f32(lo));
+    atomicMax(world_enc + 3 + a, enc_f32(hi));
+  }
+}
+
+__global__ void k_world_init(uint32_t *world_enc) {
+  if (threadIdx.x < 3) world_enc[threadIdx.x] = 0xffffffffu;
+  else if (threadIdx.x < 6) world_enc[threadIdx.x] = 0u;
+}
+
+// ---- Morton codes --------------------------------------------------------------------
+__device__ __forceinline__ uint32_t expand_bits10(uint32_t v) {  // bvh_util.h:4-10
+  v = (v * 0x00010001u) & 0xFF0000FFu;
+  v = (v * 0x00000101u) & 0x0F00F00Fu;
+  v = (v * 0x00000011u) & 0xC30C30C3u;
+  v = (v * 0x00000005u) & 0x49249249u;
+  return v;
+}
+__device__ __forceinline__ uint32_t quant10(float x) {  // bvh_util.h:13-18
+  return (uint32_t)fminf(fmaxf(x * 1024.0f, 0.0f), 1023.0f);
+}
+
+// compute_morton_code_batch + compute_normalized_center + compute_bb_morton_3d
+// (bvh_building.h:44-55, bounding_box.h:126-141,171-173)
+__global__ void __launch_bounds__(256)
+k_morton(const float *__restrict__ aabb, const int *__restrict__ prim_list, int n,
+         const uint32_t *__restrict__ world_enc, uint32_t *keys, int *vals) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  // world box = reduced min/max -/+ SMALL_DOUBLE, length = max - min
+  // (bounding_box_operations.h:34-43, bounding_box.h:175-177)
+  float wmin[3], wlen[3];
+#pragma unroll
+  for (int a = 0; a < 3; a++) {
+    float lo = dec_f32(world_enc[a]) - GPT_SMALL, hi = dec_f32(world_enc[3 + a]) + GPT_SMALL;
+    wmin[a] = lo;
+    wlen[a] = hi - lo;
+  }
+  int p = prim_list ? __ldg(prim_list + i) : i;
+  const float2 *b = reinterpret_cast<const float2 *>(aabb + 6 * (size_t)p);
+  float2 bx = __ldg(b), by = __ldg(b + 1), bz = __ldg(b + 2);
+  float cx = 0.5f * (bx.x + bx.y), cy = 0.5f * (by.x + by.y), cz = 0.5f * (bz.x + bz.y);
+  float nx = (cx - wmin[0]) / wlen[0], ny = (cy - wmin[1]) / wlen[1],
+        nz = (cz - wmin[2]) / wlen[2];
+  uint32_t code = expand_bits10(quant10(nx)) * 4u + expand_bits10(quant10(ny)) * 2u +
+                  expand_bits10(quant10(nz));
+  keys[i] = code;
+  vals[i] = i;
+}
+
+// ---- stable LSD radix sort -------------------------------------------------------------
+// Pass = k_sort_hist (per-block digit counts, digit-major) -> k_sort_scan (exclusive scan)
+//        -> k_sort_scatter (stable ranks via __match_any_sync + per-warp running counters).
+__global__ void __launch_bounds__(SORT_THREADS)
+k_sort_hist(const uint32_t *__restrict__ keys, int n, int shift, uint32_t mask,
+            uint32_t *__restrict__ block_hist, int nblocks) {
+  __shared__ uint32_t h[256];
+  h[threadIdx.x] = 0;
+  __syncthreads();
+  int base = blockIdx.x * SORT_TILE;
+#pragma unroll
+  for (int k = 0; k < SORT_ITEMS; k++) {
+    int i = base + k * SORT_THREADS + threadIdx.x;
+    if (i < n) atomicAdd(&h[(__ldg(keys + i) >> shift) & mask], 1u);
+  }
+  __syncthreads();
+  block_hist[(size_t)threadIdx.x * nblocks + blockIdx.x] = h[threadIdx.x];
+}
+
+// single-block exclusive scan of m counters (m = 256 * nblocks)
+__global__ void __launch_bounds__(1024) k_sort_scan(uint32_t *data, int m) {
+  __shared__ uint32_t part[1024];
+  int t = threadIdx.x;
+  int chunk = (m + 1023) / 1024;
+  int lo = t * chunk, hi = min(m, lo + chunk);
+  uint32_t s = 0;
+  for (int i = lo; i < hi; i++) s += data[i];
+  part[t] = s;
+  __syncthreads();
+  for (int o = 1; o < 1024; o <<= 1) {
+    uint32_t v = (t >= o) ? part[t - o] : 0;
+    __syncthreads();
+    part[t] += v;
+    __syncthreads();
+  }
+  uint32_t run = part[t] - s;
+  for (int i = lo; i < hi; i++) {
+    uint32_t v = data[i];
+    data[i] = run;
+    run += v;
+  }
+}
+
+__global__ void __launch_bounds__(SORT_THREADS)
+k_sort_scatter(const uint32_t *__restrict__ keys, const int *__restrict__ vals, int n,
+               int shift, uint32_t mask, const uint32_t *__restrict__ block_hist, int nblocks,
+               uint32_t *__restrict__ keys_out, int *__restrict__ vals_out) {
+  __shared__ uint32_t cnt[SORT_WARPS][256];  // running / total count per warp and digit
+  int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  for (int d = threadIdx.x; d < SORT_WARPS * 256; d += SORT_THREADS) (&cnt[0][0])[d] = 0;
+  __syncthreads();
+  // each warp owns a contiguous chunk of the tile, read 32 keys at a time in order
+  int wbase = blockIdx.x * SORT_TILE + w * (32 * SORT_ITEMS);
+  uint32_t key[SORT_ITEMS];
+  uint16_t rank[SORT_ITEMS];
+  uint32_t lt = (1u << l) - 1u;
+#pragma unroll
+  for (int k = 0; k < SORT_ITEMS; k++) {
+    int i = wbase + k * 32 + l;
+    bool ok = i < n;
+    key[k] = ok ? __ldg(keys + i) : 0xffffffffu;
+    uint32_t d = ok ? ((key[k] >> shift) & mask) : 256u;  // 256 = "no element"
+    uint32_t peers = __match_any_sync(0xffffffffu, d);
+    uint32_t before = 0;
+    if (ok) before = cnt[w][d];
+    __syncwarp();
+    rank[k] = (uint16_t)(before + __popc(peers & lt));
+    if (ok && (peers & lt) == 0) cnt[w][d] = before + __popc(peers);
+    __syncwarp();
+  }
+  __syncthreads();
+  {  // exclusive scan over warps for digit d = threadIdx.x, plus the global base
+    int d = threadIdx.x;
+    uint32_t run = __ldg(block_hist + (size_t)d * nblocks + blockIdx.x);
+#pragma unroll
+    for (int k = 0; k < SORT_WARPS; k++) {
+      uint32_t c = cnt[k][d];
+      cnt[k][d] = run;
+      run += c;
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < SORT_ITEMS; k++) {
+    int i = wbase + k * 32 + l;
+    if (i < n) {
+      uint32_t d = (key[k] >> shift) & mask;
+      uint32_t dst = cnt[w][d] + rank[k];
+      keys_out[dst] = key[k];
+      vals_out[dst] = __ldg(vals + i);
+    }
+  }
+}
+
+// ---- Karras hierarchy ---------------------------------------------------------------------
+// length_longest_common_prefix (bvh_util.h:22-31): clz(k_i ^ k_j), plus clz(i ^ j) when the
+// keys are equal, -1 out of range.
+__device__ __forceinline__ int delta(const uint32_t *__restrict__ keys, int n, int i,
+                                     uint32_t ki, int j) {
+  if (j < 0 || j >= n) return -1;
+  uint32_t kj = __ldg(keys + j);
+  int extra = (ki == kj) ? __clz(i ^ j) : 0;
+  return __clz(ki ^ kj) + extra;
+}
+
+// set_node_relationship (bvh_building.h:88-185) with the linear walks replaced by the
+// doubling + binary searches of Karras 2012; same direction rule (d1 < d2 -> -1), same
+// delta_min, same unique split, same child / parent assignment.
+__global__ void __launch_bounds__(256)
+k_emit(const uint32_t *__restrict__ keys, int n, float4 *nodes, int *parent_leaf) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n - 1) return;
+  uint32_t ki = __ldg(keys + i);
+  int d = (delta(keys, n, i, ki, i + 1) < delta(keys, n, i, ki, i - 1)) ? -1 : 1;
+  int dmin = delta(keys, n, i, ki, i - d);
+  int lmax = 2;
+  while (delta(keys, n, i, ki, i + lmax * d) > dmin) lmax <<= 1;
+  int l = 0;
+  for (int t = lmax >> 1; t >= 1; t >>= 1)
+    if (delta(keys, n, i, ki, i + (l + t) * d) > dmin) l += t;
+  int j = i + l * d;
+  int dnode = delta(keys, n, i, ki, j);
+  int s = 0, t = l;
+  do {
+    t = (t + 1) >> 1;
+    if (delta(keys, n, i, ki, i + (s + t) * d) > dnode) s += t;
+  } while (t > 1);
+  int gamma = i + s * d + min(d, 0);
+  int first = min(i, j), last = max(i, j);
+  int left = (first == gamma) ? ~gamma : gamma;
+  int right = (last == gamma + 1) ? ~(gamma + 1) : gamma + 1;
+  int *q3 = reinterpret_cast<int *>(nodes + 4 * (size_t)i + 3);
+  q3[0] = left;
+  q3[1] = right;
+  q3[3] = first;
+  if (i == 0) q3[2] = -1;
+  if (left >= 0) reinterpret_cast<int *>(nodes + 4 * (size_t)left + 3)[2] = 2 * i;
+  else parent_leaf[~left] = 2 * i;
+  if (right >= 0) reinterpret_cast<int *>(nodes + 4 * (size_t)right + 3)[2] = 2 * i + 1;
+  else parent_leaf[~right] = 2 * i + 1;
+}
+
+// compute_node_bounding_boxes (bvh_building.h:221-262): bottom-up union.  Each child writes
+// its box into its slot of the parent's 64-byte node; the second arrival (atomic counter,
+// fenced) reads the sibling slot and climbs.  Fused with the pack of the 48-byte trace
+// triangle for triangle BVHs (TRIS) -- the leaf thread already owns the primitive.
+template <bool TRIS>
+__global__ void __launch_bounds__(256)
+k_refit(const float *__restrict__ aabb, const int *__restrict__ prim_list,
+        const int *__restrict__ sorted_prim, int n, float4 *nodes,
+        const int *__restrict__ parent_leaf, int *flags, SceneDev s, float4 *tris) {
+  int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  int sp = __ldg(sorted_prim + j);
+  int p = prim_list ? __ldg(prim_list + sp) : sp;
+  const float2 *b = reinterpret_cast<const float2 *>(aabb + 6 * (size_t)p);
+  float2 bx = __ldg(b), by = __ldg(b + 1), bz = __ldg(b + 2);
+  if (TRIS) {
+    int a = __ldg(s.p1 + p), bb = __ldg(s.p2 + p), c = __ldg(s.p3 + p);
+    float4 *t = tris + 3 * (size_t)j;
+    t[0] = make_float4(__ldg(s.x + a), __ldg(s.y + a), __ldg(s.z + a), __ldg(s.x + bb));
+    t[1] = make_float4(__ldg(s.y + bb), __ldg(s.z + bb), __ldg(s.x + c), __ldg(s.y + c));
+    t[2] = make_float4(__ldg(s.z + c), __ldg(s.tolerance + p), __int_as_float(p), 0.f);
+  }
+  int pe = __ldg(parent_leaf + j);
+  while (pe >= 0) {
+    int par = pe >> 1, right = pe & 1;
+    float *nf = reinterpret_cast<float *>(nodes + 4 * (size_t)par);
+    float *slot = nf + (right ? 6 : 0);
+    // own slot: (xmin,xmax,ymin,ymax,zmin,zmax)
+    reinterpret_cast<float2 *>(slot)[0] = bx;
+    reinterpret_cast<float2 *>(slot)[1] = by;
+    reinterpret_cast<float2 *>(slot)[2] = bz;
+    __threadfence();
+    if (atomicAdd(flags + par, 1) == 0) return;  // first arrival: the sibling will climb
+    __threadfence();
+    const float2 *sib = reinterpret_cast<const float2 *>(nf + (right ? 0 : 6));
+    float2 sx = __ldcg(sib), sy = __ldcg(sib + 1), sz = __ldcg(sib + 2);
+    bx = make_float2(fminf(bx.x, sx.x), fmaxf(bx.y, sx.y));
+    by = make_float2(fminf(by.x, sy.x), fmaxf(by.y, sy.y));
+    bz = make_float2(fminf(bz.x, sz.x), fmaxf(bz.y, sz.y));
+    pe = __ldcg(reinterpret_cast<const int *>(nodes + 4 * (size_t)par + 3) + 2);
+  }
+}
+
+// flagged-subset compaction in index order (collect_*_geom, 1 thread serial in the reference:
+// transparent_geom_operations.h:28-40, pathtracing_target_geom_operations.h:36-48).
+// NOTE the reference collects from the Morton-SORTED main list (src/main.cu:952,1083).
+__global__ void __launch_bounds__(256)
+k_subset_flags(const float4 *__restrict__ shade, const int *__restrict__ sorted_main, int n,
+               int mask, uint32_t *keys, int *vals) {
+  int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  int p = __ldg(sorted_main + j);
+  int flags = __float_as_int(__ldg(&shade[7 * (size_t)p + 6].z));
+  keys[j] = (flags & mask) ? 0u : 1u;  // stable partition: flagged first, order kept
+  vals[j] = p;
+}
+__global__ void k_count_zero_keys(const uint32_t *keys, int n, int *count) {
+  int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  // keys are sorted: the boundary 0 -> 1 gives the count
+  if (keys[j] == 0u && (j == n - 1 || keys[j + 1] != 0u)) *count = j + 1;
+}
+
+__global__ void __launch_bounds__(256)
+k_export(const float4 *__restrict__ nodes, const int *__restrict__ parent_leaf,
+         const int *__restrict__ sorted_prim, const int *__restrict__ prim_list,
+         const float *__restrict__ aabb, int n, int *sorted_to_orig, int *left, int *right,
+         int *parent_internal, int *parent_leaf_out, float *node_aabb, float *leaf_aabb) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) {
+    int sp = sorted_prim[i];
+    int p = prim_list ? prim_list[sp] : sp;
+    sorted_to_orig[i] = p;
+    parent_leaf_out[i] = parent_leaf[i] >> 1;
+    for (int k = 0; k < 6; k++) leaf_aabb[6 * (size_t)i + k] = aabb[6 * (size_t)p + k];
+  }
+  if (i < n - 1) {
+    const int *q3 = reinterpret_cast<const int *>(nodes + 4 * (size_t)i + 3);
+    left[i] = q3[0];
+    right[i] = q3[1];
+    parent_internal[i] = q3[2] < 0 ? -1 : (q3[2] >> 1);
+    const float *f = reinterpret_cast<const float *>(nodes + 4 * (size_t)i);
+    for (int k = 0; k < 3; k++) {  // node box = union of its two child slots
+      node_aabb[6 * (size_t)i + 2 * k] = fminf(f[2 * k], f[6 + 2 * k]);
+      node_aabb[6 * (size_t)i + 2 * k + 1] = fmaxf(f[2 * k + 1], f[6 + 2 * k + 1]);
+    }
+  }
+}
+
+}  // namespace
+
+int gpt_radix_hist_entries(int n) {
+  int nblocks = (n + SORT_TILE - 1) / SORT_TILE;
+  return 256 * (nblocks > 0 ? nblocks : 1);
+}
+
+int gpt_radix_sort_pairs(gpt_ctx *ctx, uint32_t *keys, int *vals, uint32_t *keys_alt,
+                         int *vals_alt, uint32_t *block_hist, int n, int nbits,
+                         uint32_t **keys_out, int **vals_out) {
+  int nblocks = (n + SORT_TILE - 1) / SORT_TILE;
+  if (nblocks < 1) nblocks = 1;
+  uint32_t *ka = keys, *kb = keys_alt;
+  int *va = vals, *vb = vals_alt;
+  for (int shift = 0; shift < nbits; shift += 8) {
+    int bits = nbits - shift < 8 ? nbits - shift : 8;
+    uint32_t mask = (1u << bits) - 1u;
+    k_sort_hist<<<nblocks, SORT_THREADS, 0, ctx->stream>>>(ka, n, shift, mask, block_hist, nblocks);
+    GPT_LAUNCH_CHECK(ctx);
+    k_sort_scan<<<1, 1024, 0, ctx->stream>>>(block_hist, 256 * nblocks);
+    GPT_LAUNCH_CHECK(ctx);
+    k_sort_scatter<<<nblocks, SORT_THREADS, 0, ctx->stream>>>(ka, va, n, shift, mask, block_hist,
+                                                             nblocks, kb, vb);
+    GPT_LAUNCH_CHECK(ctx);
+    uint32_t *tk = ka; ka = kb; kb = tk;
+    int *tv = va; va = vb; vb = tv;
+  }
+  *keys_out = ka;
+  *vals_out = va;
+  return GPT_OK;
+}
+
+void gpt_lbvh_free(BvhDev &b) {
+  cudaFree(b.nodes); cudaFree(b.tris); cudaFree(b.parent_leaf); cudaFree(b.morton);
+  cudaFree(b.sorted_prim); cudaFree(b.prim_list); cudaFree(b.world_enc);
+  cudaFree(b.keys_alt); cudaFree(b.vals_alt); cudaFree(b.block_hist); cudaFree(b.flags);
+  b = BvhDev();
+}
+
+static int lbvh_reserve(gpt_ctx *ctx, BvhDev &b, int n) {
+  if (n <= b.capacity) return GPT_OK;
+  int *keep = b.prim_list;
+  b.prim_list = nullptr;
+  gpt_lbvh_free(b);
+  b.prim_list = keep;
+  size_t N = (size_t)n;
+  GPT_TRY(gpt_alloc(ctx, &b.nodes, 4 * N));
+  GPT_TRY(gpt_alloc(ctx, &b.tris, 3 * N));
+  GPT_TRY(gpt_alloc(ctx, &b.parent_leaf, N));
+  GPT_TRY(gpt_alloc(ctx, &b.morton, N));
+  GPT_TRY(gpt_alloc(ctx, &b.sorted_prim, N));
+  GPT_TRY(gpt_alloc(ctx, &b.keys_alt, N));
+  GPT_TRY(gpt_alloc(ctx, &b.vals_alt, N));
+  GPT_TRY(gpt_alloc(ctx, &b.block_hist, (size_t)gpt_radix_hist_entries(n)));
+  GPT_TRY(gpt_alloc(ctx, &b.flags, N));
+  GPT_TRY(gpt_alloc(ctx, &b.world_enc, (size_t)8));
+  b.capacity = n;
+  return GPT_OK;
+}
+
+// Build the LBVH over `n` triangles; d_prim_list (device, may be NULL = identity) maps the
+// BVH's primitive index to the original triangle index.  All work is enqueued on
+// ctx->stream; nothing synchronises with the host.
+int gpt_lbvh_build(gpt_ctx *ctx, int which, const int *d_prim_list, int n) {
+  BvhDev &b = ctx->bvh[which];
+  if (n < 2) {  // the reference cannot build or traverse such a tree (note 9)
+    b.n = n;
+    return GPT_OK;
+  }
+  GPT_TRY(lbvh_reserve(ctx, b, n));
+  b.n = n;
+  const SceneDev &s = ctx->scene;
+  cudaStream_t st = ctx->stream;
+  int grid = (n + 255) / 256;
+  k_world_init<<<1, 32, 0, st>>>(b.world_enc);
+  GPT_LAUNCH_CHECK(ctx);
+  int rgrid = grid < 148 * 8 ? grid : 148 * 8;
+  k_world_reduce<<<rgrid, 256, 0, st>>>(s.aabb, d_prim_list, n, b.world_enc);
+  GPT_LAUNCH_CHECK(ctx);
+  // keys/vals ping-pong between (morton, sorted_prim) and (keys_alt, vals_alt); 30 bits = 4
+  // passes, an even number, so the result lands back in (morton, sorted_prim).
+  k_morton<<<grid, 256, 0, st>>>(s.aabb, d_prim_list, n, b.world_enc, b.morton, b.sorted_prim);
+  GPT_LAUNCH_CHECK(ctx);
+  uint32_t *ko; int *vo;
+  GPT_TRY(gpt_radix_sort_pairs(ctx, b.morton, b.sorted_prim, b.keys_alt, b.vals_alt,
+                               b.block_hist, n, 30, &ko, &vo));
+  if (ko != b.morton) return gpt_fail(ctx, GPT_E_INVALID, "sort parity", __FILE__, __LINE__);
+  k_emit<<<grid, 256, 0, st>>>(b.morton, n, b.nodes, b.parent_leaf);
+  GPT_LAUNCH_CHECK(ctx);
+  GPT_CUDA(ctx, cudaMemsetAsync(b.flags, 0, sizeof(int) * (size_t)n, st));
+  k_refit<true><<<grid, 256, 0, st>>>(s.aabb, d_prim_list, b.sorted_prim, n, b.nodes,
+                                      b.parent_leaf, b.flags, s, b.tris);
+  GPT_LAUNCH_CHECK(ctx);
+  return GPT_OK;
+}
+
+// Ordered list of the triangles whose flags & mask != 0, taken in MAIN-BVH sorted order.
+int gpt_collect_subset(gpt_ctx *ctx, int flag_mask, int **d_list, int *count) {
+  BvhDev &m = ctx->bvh[GPT_BVH_MAIN];
+  int n = m.n;
+  uint32_t *keys = nullptr, *keys_alt = nullptr, *hist = nullptr, *ko = nullptr;
+  int *vals = nullptr, *vals_alt = nullptr, *vo = nullptr, *d_count = nullptr;
+  GPT_TRY(gpt_alloc(ctx, &keys, (size_t)n));
+  GPT_TRY(gpt_alloc(ctx, &keys_alt, (size_t)n));
+  GPT_TRY(gpt_alloc(ctx, &vals, (size_t)n));
+  GPT_TRY(gpt_alloc(ctx, &vals_alt, (size_t)n));
+  GPT_TRY(gpt_alloc(ctx, &hist, (size_t)gpt_radix_hist_entries(n)));
+  GPT_TRY(gpt_alloc(ctx, &d_count, (size_t)1));
+  GPT_CUDA(ctx, cudaMemsetAsync(d_count, 0, sizeof(int), ctx->stream));
+  int grid = (n + 255) / 256;
+  k_subset_flags<<<grid, 256, 0, ctx->stream>>>(ctx->scene.shade, m.sorted_prim, n, flag_mask,
+                                               keys, vals);
+  GPT_LAUNCH_CHECK(ctx);
+  GPT_TRY(gpt_radix_sort_pairs(ctx, keys, vals, keys_alt, vals_alt, hist, n, 1, &ko, &vo));
+  k_count_zero_keys<<<grid, 256, 0, ctx->stream>>>(ko, n, d_count);
+  GPT_LAUNCH_CHECK(ctx);
+  int c = 0;
+  GPT_CUDA(ctx, cudaMemcpyAsync(&c, d_count, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+  GPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  *count = c;
+  if (*d_list) { cudaFree(*d_list); *d_list = nullptr; }
+  GPT_TRY(gpt_alloc(ctx, d_list, (size_t)(c > 0 ? c : 1)));
+  if (c > 0)
+    GPT_CUDA(ctx, cudaMemcpyAsync(*d_list, vo, sizeof(int) * (size_t)c,
+                                  cudaMemcpyDeviceToDevice, ctx->stream));
+  GPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  cudaFree(keys); cudaFree(keys_alt); cudaFree(vals); cudaFree(vals_alt); cudaFree(hist);
+  cudaFree(d_count);
+  return GPT_OK;
+}
+
+int gpt_lbvh_export(gpt_ctx *ctx, int which, uint32_t *morton, int32_t *sorted_to_orig,
+                    int32_t *left, int32_t *right, int32_t *parent_internal,
+                    int32_t *parent_leaf, float *node_aabb, float *leaf_aabb,
+                    float *world_aabb) {
+  BvhDev &b = ctx->bvh[which];
+  int n = b.n;
+  if (n < 2) return gpt_fail(ctx, GPT_E_INVALID, "BVH has fewer than 2 leaves", __FILE__, __LINE__);
+  size_t N = (size_t)n;
+  int *d_i = nullptr; float *d_f = nullptr;
+  GPT_TRY(gpt_alloc(ctx, &d_i, 5 * N));
+  GPT_TRY(gpt_alloc(ctx, &d_f, 12 * N));
+  int *d_s2o = d_i, *d_l = d_i + N, *d_r = d_i + 2 * N, *d_pi = d_i + 3 * N, *d_pl = d_i + 4 * N;
+  float *d_na = d_f, *d_la = d_f + 6 * N;
+  k_export<<<(n + 255) / 256, 256, 0, ctx->stream>>>(b.nodes, b.parent_leaf, b.sorted_prim,
+                                                    b.prim_list, ctx->scene.aabb, n, d_s2o, d_l,
+                                                    d_r, d_pi, d_pl, d_na, d_la);
+  GPT_LAUNCH_CHECK(ctx);
+  auto dl = [&](void *h, const void *d, size_t bytes) -> cudaError_t {
+    if (!h) return cudaSuccess;
+    return cudaMemcpyAsync(h, d, bytes, cudaMemcpyDeviceToHost, ctx->stream);
+  };
+  GPT_CUDA(ctx, dl(morton, b.morton, 4 * N));
+  GPT_CUDA(ctx, dl(sorted_to_orig, d_s2o, 4 * N));
+  GPT_CUDA(ctx, dl(left, d_l, 4 * (N - 1)));
+  GPT_CUDA(ctx, dl(right, d_r, 4 * (N - 1)));
+  GPT_CUDA(ctx, dl(parent_internal, d_pi, 4 * (N - 1)));
+  GPT_CUDA(ctx, dl(parent_leaf, d_pl, 4 * N));
+  GPT_CUDA(ctx, dl(node_aabb, d_na, 24 * (N - 1)));
+  GPT_CUDA(ctx, dl(leaf_aabb, d_la, 24 * N));
+  uint32_t we[6];
+  GPT_CUDA(ctx, cudaMemcpyAsync(we, b.world_enc, sizeof(we), cudaMemcpyDeviceToHost, ctx->stream));
+  GPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if (world_aabb) {
+    for (int a = 0; a < 3; a++) {  // (xmin,xmax,ymin,ymax,zmin,zmax) -/+ SMALL_DOUBLE
+      world_aabb[2 * a] = dec_f32(we[a]) - GPT_SMALL;
+      world_aabb[2 * a + 1] = dec_f32(we[3 + a]) + GPT_SMALL;
+    }
+  }
+  cudaFree(d_i); cudaFree(d_f);
+  return GPT_OK;
+}

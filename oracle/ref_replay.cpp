@@ -50,6 +50,26 @@
 
 #include "../include/gpt.h"
 
+// The reference never initialises Node::parent (src/model/bvh/bvh.h:42-54), yet
+// compute_node_bounding_boxes stops climbing on `parent != nullptr`
+// (src/model/bvh/bvh_building.h:238-243): it silently relies on the CUDA device heap handing
+// out zero-filled memory.  The host replay reproduces that by zero-filling every `new`.
+#include <new>
+void *operator new(std::size_t n) {
+  void *p = calloc(1, n ? n : 1);
+  if (!p) throw std::bad_alloc();
+  return p;
+}
+void *operator new[](std::size_t n) {
+  void *p = calloc(1, n ? n : 1);
+  if (!p) throw std::bad_alloc();
+  return p;
+}
+void operator delete(void *p) noexcept { free(p); }
+void operator delete[](void *p) noexcept { free(p); }
+void operator delete(void *p, std::size_t) noexcept { free(p); }
+void operator delete[](void *p, std::size_t) noexcept { free(p); }
+
 namespace {
 
 // Emulates `kernel<<<grid, block>>>(...)` with 1-D grid/block: one host call per thread.

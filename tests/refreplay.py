@@ -1,0 +1,131 @@
+"""Test-side ctypes wrapper of oracle/_ref/libref_replay.so (the reference's own headers
+replayed on the host).  TEST INFRASTRUCTURE: never imported by gpu_pathtracer_b200/."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from gpu_pathtracer_b200 import cabi
+from gpu_pathtracer_b200.scene import Scene
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF_SO = os.path.join(ROOT, "oracle", "_ref", "libref_replay.so")
+
+
+def build_ref_if_possible():
+    """(Re)builds the replay library when the reference sources are present (this
+    container); on the GPU box the prebuilt .so that travelled with the snapshot is used."""
+    if os.path.isdir("/root/reference/src"):
+        subprocess.run(["make", "-s", "-C", os.path.join(ROOT, "oracle"), "ref"], check=True)
+    return os.path.exists(REF_SO)
+
+
+def available() -> bool:
+    return os.path.exists(REF_SO) or build_ref_if_possible()
+
+
+class RefError(RuntimeError):
+    pass
+
+
+def _check(rc):
+    if rc != 0:
+        raise RefError(f"ref_replay returned {rc}")
+
+
+class RefReplay:
+    """Same surface as gpu_pathtracer_b200.api.PathTracer, backed by the reference's code."""
+
+    def __init__(self, scene: Scene):
+        if not available():
+            raise RefError("oracle/_ref/libref_replay.so missing and reference sources absent")
+        self.lib = C.CDLL(REF_SO)
+        self.lib.ref_last_ms.restype = C.c_double
+        self.ctx = C.c_void_p()
+        _check(self.lib.ref_create(C.byref(self.ctx)))
+        self.scene = scene
+        cabi.upload_scene(self.lib, "ref_", self.ctx, scene, _check)
+        _check(self.lib.ref_build(self.ctx))
+        self.n = scene.num_triangles
+
+    def export_triangles(self):
+        n = self.n
+        out = dict(tolerance=np.zeros(n, np.float32), aabb=np.zeros((n, 6), np.float32),
+                   normal=np.zeros((n, 3), np.float32), area=np.zeros(n, np.float32),
+                   flags=np.zeros(n, np.int32), energy=np.zeros((n, 3), np.float32),
+                   tangents=np.zeros((n, 9), np.float32))
+        _check(self.lib.ref_export_triangles(
+            self.ctx, cabi.fptr(out["tolerance"]), cabi.fptr(out["aabb"]),
+            cabi.fptr(out["normal"]), cabi.fptr(out["area"]), cabi.iptr(out["flags"]),
+            cabi.fptr(out["energy"]), cabi.fptr(out["tangents"])))
+        return out
+
+    def num_leaves(self, which=0) -> int:
+        n = C.c_int32()
+        _check(self.lib.ref_bvh_num_leaves(self.ctx, which, C.byref(n)))
+        return n.value
+
+    def export_bvh(self, which=0):
+        n = self.num_leaves(which)
+        out = dict(morton=np.zeros(n, np.uint32), sorted_to_orig=np.zeros(n, np.int32),
+                   left=np.zeros(n - 1, np.int32), right=np.zeros(n - 1, np.int32),
+                   parent_internal=np.zeros(n - 1, np.int32),
+                   parent_leaf=np.zeros(n, np.int32),
+                   node_aabb=np.zeros((n - 1, 6), np.float32),
+                   leaf_aabb=np.zeros((n, 6), np.float32), world_aabb=np.zeros(6, np.float32))
+        _check(self.lib.ref_export_bvh(
+            self.ctx, which, cabi.uptr(out["morton"]), cabi.iptr(out["sorted_to_orig"]),
+            cabi.iptr(out["left"]), cabi.iptr(out["right"]),
+            cabi.iptr(out["parent_internal"]), cabi.iptr(out["parent_leaf"]),
+            cabi.fptr(out["node_aabb"]), cabi.fptr(out["leaf_aabb"]),
+            cabi.fptr(out["world_aabb"])))
+        return out
+
+    def export_light_tree(self):
+        n = self.num_leaves(cabi.GPT_BVH_LIGHT)
+        cone = np.zeros((n - 1, 5), np.float32)
+        ne = np.zeros((n - 1, 3), np.float32)
+        le = np.zeros((n, 3), np.float32)
+        _check(self.lib.ref_export_light_tree(self.ctx, cabi.fptr(cone), cabi.fptr(ne),
+                                              cabi.fptr(le)))
+        return dict(node_cone=cone, node_energy=ne, leaf_energy=le)
+
+    def trace(self, rays: np.ndarray, which=0, nthreads=1):
+        rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 8)
+        n = rays.shape[0]
+        out = dict(leaf_id=np.zeros(n, np.int32), tri_id=np.zeros(n, np.int32),
+                   t=np.zeros(n, np.float32), point=np.zeros((n, 3), np.float32))
+        _check(self.lib.ref_trace(self.ctx, which, cabi.fptr(rays), C.c_int64(n),
+                                  cabi.iptr(out["leaf_id"]), cabi.iptr(out["tri_id"]),
+                                  cabi.fptr(out["t"]), cabi.fptr(out["point"]),
+                                  C.c_int(nthreads)))
+        out["ms"] = self.lib.ref_last_ms(self.ctx)
+        return out
+
+    def primary_rays(self) -> np.ndarray:
+        cam = self.scene.camera
+        rays = np.zeros((cam["height"] * cam["width"], 8), np.float32)
+        _check(self.lib.ref_primary_rays(self.ctx, cabi.fptr(rays)))
+        return rays
+
+    def render_pathtrace(self, window=None, nthreads=None) -> np.ndarray:
+        cam = self.scene.camera
+        H, W = cam["height"], cam["width"]
+        if H < 100:
+            # pathtracing.h:298 does `i % (height / 100)`: integer division by zero on a CPU
+            raise RefError("the reference's progress printf needs image_height >= 100")
+        r0, r1, c0, c1 = window if window is not None else (0, H, 0, W)
+        out = np.zeros((H, W, 3), np.float32)
+        nt = nthreads or os.cpu_count() or 1
+        _check(self.lib.ref_render_pathtrace_window(
+            self.ctx, cabi.fptr(out), r0, r1, c0, c1, C.c_int(nt)))
+        self.render_ms = self.lib.ref_last_ms(self.ctx)
+        return out
+
+    def time_main_bvh_build(self) -> float:
+        ms = C.c_double()
+        _check(self.lib.ref_time_main_bvh_build(self.ctx, C.byref(ms)))
+        return ms.value
