@@ -1,0 +1,569 @@
+// render.cu -- wavefront path tracer: replaces init_curand_state + path_tracing_render
+// (src/util/general.h:8-16, src/render/pathtracing.h:69-200,251-305, launched at
+// src/main.cu:1208,1266) and the light-tree part of the build
+// (compute_node_bounding_cones' energy sums, src/model/bvh/bvh_building.h:304-348).
+//
+// Stages per iteration, each a kernel over the queue of active pixel slots:
+//   k_pt_trace  closest hit of every active path's ray against the main BVH
+//   k_pt_shade  material decision, light sampling + MIS, throughput update, next ray or next
+//               sample (ray-gen is folded into shade), warp-aggregated queue compaction
+#include <cmath>
+#include <vector>
+
+#include "lighttree.cuh"
+#include "render_state.cuh"
+
+namespace {
+
+constexpr int PT_BLOCK = 128;
+
+struct RenderCtx {
+  PathState ps{};
+  float4 *leaf_info = nullptr, *node_info = nullptr;
+  float *node_energy = nullptr;
+  int *lt_flags = nullptr;
+  int light_n = 0;
+  uint32_t *rng_init = nullptr;   // cached curand_init states for (width, height, rank set)
+  int rng_w = 0, rng_h = 0, rng_rank = -1, rng_nranks = 0;
+  int *h_counts = nullptr;        // pinned
+  float *d_fb = nullptr;          // internal framebuffer for the host API
+  size_t fb_capacity = 0;
+};
+
+struct RenderParams {
+  CameraDev cam;
+  int sample_size, level, dof_size;
+  float pdf_weight;
+  V3 sky;
+  const float *bg_r, *bg_g, *bg_b;
+  int bg_h, bg_w;
+  float inv_samples;  // (float)(1.0 / sample_size / dof_sample_size)
+};
+
+// ---- RNG init: curand_init(1984, pixel_index, 0) (general.h:15) ---------------------------
+__global__ void __launch_bounds__(128) k_rng_init(uint32_t *rng, const int *pixel, int n) {
+  int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n) return;
+  Rng r;
+  curand_init(1984, pixel[s], 0, &r.s);
+  rng_store(r, rng, s, n);
+}
+
+// ---- light tree -----------------------------------------------------------------------------
+__global__ void __launch_bounds__(128)
+k_light_leaves(SceneDev s, TexAtlas atlas, const float4 *lt_tris, int n, float4 *leaf_info) {
+  int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  const float4 *tp = lt_tris + 3 * (size_t)j;
+  float4 t0 = tp[0], t1 = tp[1], t2 = tp[2];
+  int prim = __float_as_int(t2.z);
+  const float *bb = s.aabb + 6 * (size_t)prim;
+  V3 bc = V3{0.5f * (bb[0] + bb[1]), 0.5f * (bb[2] + bb[3]), 0.5f * (bb[4] + bb[5])};
+  V3 p1 = V3{t0.x, t0.y, t0.z}, p2 = V3{t0.w, t1.x, t1.y}, p3 = V3{t1.z, t1.w, t2.x};
+  V3 cen = (p1 + p2 + p3) / 3.0f;
+  TriShade ts = load_tri_shade(s.shade, prim);
+  const float third = (float)(1.0 / 3);
+  V3 an = shading_normal(ts, s.mats[ts.mat], atlas, third, third, third);
+  const float *e = s.energy + 3 * (size_t)prim;
+  float4 *o = leaf_info + 4 * (size_t)j;
+  o[0] = make_float4(bc.x, bc.y, bc.z, ts.area);
+  o[1] = make_float4(cen.x, cen.y, cen.z, e[0]);
+  o[2] = make_float4(an.x, an.y, an.z, e[1]);
+  o[3] = make_float4(e[2], 0.f, 0.f, 0.f);
+}
+
+// bottom-up energy sums: node.energy = left.energy + right.energy (bvh_building.h:338-339)
+__global__ void __launch_bounds__(128)
+k_light_nodes(const float4 *nodes, const int *parent_leaf, const float4 *leaf_info, int n,
+              float *node_energy, float4 *node_info, int *flags) {
+  int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  int pe = parent_leaf[j];
+  while (pe >= 0) {
+    int par = pe >> 1;
+    __threadfence();
+    if (atomicAdd(flags + par, 1) == 0) return;
+    __threadfence();
+    const float4 *q = nodes + 4 * (size_t)par;
+    const int *q3 = reinterpret_cast<const int *>(q + 3);
+    int cr[2] = {__ldcg(q3), __ldcg(q3 + 1)};
+    V3 e[2];
+    for (int c = 0; c < 2; c++) {
+      if (cr[c] < 0) {
+        const float4 *li = leaf_info + 4 * (size_t)(~cr[c]);
+        e[c] = V3{__ldcg(&li[1].w), __ldcg(&li[2].w), __ldcg(&li[3].x)};
+      } else {
+        const float *ne = node_energy + 3 * (size_t)cr[c];
+        e[c] = V3{__ldcg(ne), __ldcg(ne + 1), __ldcg(ne + 2)};
+      }
+    }
+    V3 sum = e[0] + e[1];
+    node_energy[3 * (size_t)par] = sum.x;
+    node_energy[3 * (size_t)par + 1] = sum.y;
+    node_energy[3 * (size_t)par + 2] = sum.z;
+    const float *f = reinterpret_cast<const float *>(q);
+    float c3[3];
+    for (int k = 0; k < 3; k++) {
+      float lo = fminf(__ldcg(f + 2 * k), __ldcg(f + 6 + 2 * k));
+      float hi = fmaxf(__ldcg(f + 2 * k + 1), __ldcg(f + 6 + 2 * k + 1));
+      c3[k] = 0.5f * (lo + hi);
+    }
+    node_info[par] = make_float4(c3[0], c3[1], c3[2], length(sum));
+    pe = __ldcg(q3 + 2);
+  }
+}
+
+}  // namespace
+
+namespace {
+
+// Camera::compute_ray (camera.h:68-83) + Ray::Ray normalisation.
+__device__ __forceinline__ void camera_ray(const CameraDev &c, float i, float j, Rng &rng, V3 &o,
+                                           V3 &d) {
+  float w2 = (float)c.width / 2, h2 = (float)c.height / 2;
+  float alpha = (float)(c.tan_half_fovx * (double)(j - w2) / (double)w2);
+  float beta = (float)(c.tan_half_fovy * (double)(h2 - i) / (double)h2);
+  V3 dir = unit(alpha * c.u + beta * c.v - c.w);
+  V3 point = c.eye + c.focus_dist * dir;
+  V3 rd = c.lens_radius * sample_disk(rng);
+  V3 off = rd.x * c.u + rd.y * c.v;
+  o = c.eye + off;
+  d = unit(point - c.eye - off);
+}
+
+// _get_sky_color (pathtracing.h:69-82)
+__device__ __forceinline__ V3 sky_color(const RenderParams &p, V3 dir) {
+  float u = (float)(.5 + (double)atan2f(dir.z, dir.x) / (2.0 * GPT_PI));
+  float v = (float)(.5 - (double)asinf(dir.y) / GPT_PI);
+  int iu = (int)floorf((u - floorf(u)) * (float)(p.bg_w - 1));
+  int iv = (int)floorf((v - floorf(v)) * (float)(p.bg_h - 1));
+  int idx = p.bg_w * iv + iu;
+  return p.sky * V3{__ldg(p.bg_r + idx), __ldg(p.bg_g + idx), __ldg(p.bg_b + idx)};
+}
+
+__device__ __forceinline__ void start_sample(PathState &ps, int slot, V3 o, V3 d) {
+  ps.rays[2 * (size_t)slot] = make_float4(o.x, o.y, o.z, INFINITY);
+  ps.rays[2 * (size_t)slot + 1] = make_float4(d.x, d.y, d.z, 0.f);
+  MatList l;
+#pragma unroll
+  for (int k = 0; k < MATLIST_MAX; k++) l.id[k] = MAT_AIR;
+  l.len = 1;  // add_new_material(material_list, length, nullptr)  (pathtracing.h:106)
+  matlist_store(ps.matlist + slot, l);
+}
+
+__global__ void __launch_bounds__(PT_BLOCK)
+k_pt_start(PathState ps, RenderParams p, int n, float *fb) {
+  int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n) return;
+  int pix = ps.pixel[s];
+  int i = pix / p.cam.width, j = pix % p.cam.width;
+  Rng rng;
+  rng_load(rng, ps.rng, s, ps.capacity);
+  V3 o, d;
+  camera_ray(p.cam, i + .5f, j + .5f, rng, o, d);
+  rng_store(rng, ps.rng, s, ps.capacity);
+  ps.cam_o[s] = make_float4(o.x, o.y, o.z, 0.f);
+  ps.cam_d[s] = make_float4(d.x, d.y, d.z, 0.f);
+  ps.mask[s] = make_float4(1.f, 1.f, 1.f, __int_as_float(0));
+  ps.acc[s] = make_float4(0.f, 0.f, 0.f, __int_as_float(0));
+  ps.color[s] = make_float4(0.f, 0.f, 0.f, __int_as_float(0));
+  start_sample(ps, s, o, d);
+  ps.queue[0][s] = s;
+  fb[3 * (size_t)pix] = 0.f; fb[3 * (size_t)pix + 1] = 0.f; fb[3 * (size_t)pix + 2] = 0.f;
+}
+
+__global__ void __launch_bounds__(PT_BLOCK)
+k_pt_trace(PathState ps, const int *__restrict__ queue, const int *__restrict__ count,
+           const float4 *__restrict__ nodes, const float4 *__restrict__ tris,
+           const int *__restrict__ parent_leaf, unsigned long long *counters) {
+  __shared__ int stack[TRACE_STACK * PT_BLOCK];
+  int a = blockIdx.x * blockDim.x + threadIdx.x;
+  if (a >= *count) return;
+  int s = queue[a];
+  float4 ro = ps.rays[2 * (size_t)s], rd = ps.rays[2 * (size_t)s + 1];
+  RaySetup r = make_ray(ro.x, ro.y, ro.z, rd.x, rd.y, rd.z);
+  int overflow = 0;
+  HitResult h = trace_ray<false>(nodes, tris, parent_leaf, r, ro.w, stack + threadIdx.x, PT_BLOCK,
+                                 nullptr, nullptr, &overflow);
+  if (overflow) atomicExch(counters + 3, 1ull);
+  ps.hits[2 * (size_t)s] = make_float4(h.t, __int_as_float(h.leaf), __int_as_float(h.prim), 0.f);
+  ps.hits[2 * (size_t)s + 1] = make_float4(h.b1, h.b2, h.b3, 0.f);
+}
+
+// change_ref_ray + _recompute_pdf (material_operations.h:26-153)
+__device__ __forceinline__ float change_ref_ray(const LightTree &lt, const float4 *shade,
+                                                const MaterialDev *mats, const TexAtlas &atlas,
+                                                V3 point, V3 normal, V3 v_in, RefRec &ref,
+                                                float weight, Rng &rng) {
+  float rn = rng_uniform(rng);
+  V3 pivot = ref.diffuse ? normal : ref.perfect;
+  if (isinf(ref.n)) weight = 0.f;
+  if (rn < weight) {
+    int leaf = light_pick(lt, point, pivot, rng);
+    V3 target = light_sample_point(lt, leaf, rng);
+    ref.dir = unit(target - point);
+    if (ref.reflected || ref.refracted) ref.filter = phong_filter(ref.k, ref.n, pivot, ref.dir);
+  }
+  V3 d1 = unit(ref.dir);
+  float hsum = light_hittable_sum(lt, shade, mats, atlas, point, d1, point, pivot);
+  float samp = ref.diffuse ? diffuse_sampling_pdf(normal, ref.dir)
+                           : specular_sampling_pdf(v_in, ref.dir, normal, ref.perfect, ref.n,
+                                                   ref.refracted);
+  float pdf = weight * hsum + (1.f - weight) * samp;
+  float spdf = scattering_pdf(normal, ref.dir, ref.diffuse, v_in, ref.refracted);
+  return (float)((double)spdf / GPT_PI / (double)pdf);
+}
+
+__global__ void __launch_bounds__(PT_BLOCK)
+k_pt_shade(PathState ps, RenderParams p, const int *__restrict__ queue,
+           const int *__restrict__ count, int *next_queue, int *next_count, SceneDev sc,
+           TexAtlas atlas, const float4 *__restrict__ main_tris, LightTree lt, float *fb,
+           int *error_flag) {
+  int a = blockIdx.x * blockDim.x + threadIdx.x;
+  bool alive = false;
+  int s = -1;
+  if (a < *count) {
+    s = queue[a];
+    alive = true;
+    float4 ro = ps.rays[2 * (size_t)s], rdv = ps.rays[2 * (size_t)s + 1];
+    float4 h0 = ps.hits[2 * (size_t)s], h1 = ps.hits[2 * (size_t)s + 1];
+    float4 mk = ps.mask[s], ac = ps.acc[s];
+    V3 dir = V3{rdv.x, rdv.y, rdv.z};
+    V3 mask = V3{mk.x, mk.y, mk.z}, acc = V3{ac.x, ac.y, ac.z};
+    int bounce = __float_as_int(mk.w), sidx = __float_as_int(ac.w);
+    int leaf = __float_as_int(h0.y);
+    Rng rng;
+    rng_load(rng, ps.rng, s, ps.capacity);
+    bool done = false;
+    V3 result = V3{0.f, 0.f, 0.f};
+    if (leaf >= 0) {
+      int prim = __float_as_int(h0.z);
+      float b1 = h1.x, b2 = h1.y, b3 = h1.z;
+      const float4 *tp = main_tris + 3 * (size_t)leaf;
+      float4 t0 = __ldg(tp), t1 = __ldg(tp + 1), t2 = __ldg(tp + 2);
+      TriShade ts = load_tri_shade(sc.shade, prim);
+      const MaterialDev &m = sc.mats[ts.mat];
+      // hit_record (triangle.h:399-405)
+      V3 point = b1 * V3{t0.x, t0.y, t0.z} + b2 * V3{t0.w, t1.x, t1.y} + b3 * V3{t1.z, t1.w, t2.x};
+      float u = b1 * ts.u1 + b2 * ts.u2 + b3 * ts.u3;
+      float v = b1 * ts.v1 + b2 * ts.v2 + b3 * ts.v3;
+      V3 normal = shading_normal(ts, m, atlas, b1, b2, b3);
+      MatList list;
+      matlist_load(list, ps.matlist + s);
+      RefRec ref;
+      ref.reflected = false; ref.refracted = false; ref.diffuse = false;
+      ref.n = 1.f; ref.k = V3{0.f, 0.f, 0.f}; ref.perfect = V3{1.f, 0.f, 0.f}; ref.bent = false;
+      bool sss = false;
+      check_next_path(sc.mats, atlas, ts.mat, dir, normal, u, v, list, ref, sss, rng, false);
+      float factor = 1.f;
+      if (!ref.false_hit)
+        factor = change_ref_ray(lt, sc.shade, sc.mats, atlas, point, normal, dir, ref,
+                                p.pdf_weight, rng);
+      // material list bookkeeping (pathtracing.h:144-162)
+      bool ok = true;
+      if ((ref.false_hit || ref.refracted) && ref.entering) ok = matlist_add(list, ts.mat);
+      else if ((ref.false_hit || ref.refracted) && !ref.entering) matlist_remove(list, ts.mat);
+      if (!ok) *error_flag = 1;
+      matlist_store(ps.matlist + s, list);
+      if (!ref.false_hit) {
+        V3 add = de_nan(mask * mat_emission(atlas, m, u, v));
+        acc = acc + add;
+        if (factor > 0.f) {
+          mask = mask * (ref.filter * clamp_lohi(0.f, .9999f, factor));
+        } else {
+          done = true;
+          result = acc;
+        }
+      }
+      if (!done) {
+        bounce++;
+        if (bounce >= p.level) {
+          done = true;
+          result = acc;
+        } else {
+          ps.rays[2 * (size_t)s] = make_float4(point.x, point.y, point.z, INFINITY);
+          ps.rays[2 * (size_t)s + 1] = make_float4(ref.dir.x, ref.dir.y, ref.dir.z, 0.f);
+          ps.mask[s] = make_float4(mask.x, mask.y, mask.z, __int_as_float(bounce));
+          ps.acc[s] = make_float4(acc.x, acc.y, acc.z, __int_as_float(sidx));
+        }
+      }
+    } else {
+      V3 sky = sky_color(p, dir);
+      result = bounce < 1 ? sky : acc + mask * sky;
+      done = true;
+    }
+    if (done) {
+      float4 cl = ps.color[s];
+      V3 color = V3{cl.x, cl.y, cl.z} + de_nan(result);
+      int k = __float_as_int(cl.w);
+      sidx++;
+      V3 o, d;
+      bool finished = false;
+      if (sidx >= p.sample_size) {
+        sidx = 0;
+        k++;
+        if (k >= p.dof_size) {
+          finished = true;
+        } else {
+          int pix = ps.pixel[s];
+          camera_ray(p.cam, pix / p.cam.width + .5f, pix % p.cam.width + .5f, rng, o, d);
+          ps.cam_o[s] = make_float4(o.x, o.y, o.z, 0.f);
+          ps.cam_d[s] = make_float4(d.x, d.y, d.z, 0.f);
+        }
+      } else {
+        float4 co = ps.cam_o[s], cd = ps.cam_d[s];
+        o = V3{co.x, co.y, co.z};
+        d = V3{cd.x, cd.y, cd.z};
+      }
+      if (finished) {
+        int pix = ps.pixel[s];
+        V3 out = color * p.inv_samples;
+        fb[3 * (size_t)pix] = out.x; fb[3 * (size_t)pix + 1] = out.y; fb[3 * (size_t)pix + 2] = out.z;
+        alive = false;
+      } else {
+        ps.color[s] = make_float4(color.x, color.y, color.z, __int_as_float(k));
+        ps.mask[s] = make_float4(1.f, 1.f, 1.f, __int_as_float(0));
+        ps.acc[s] = make_float4(0.f, 0.f, 0.f, __int_as_float(sidx));
+        start_sample(ps, s, o, d);
+      }
+    }
+    rng_store(rng, ps.rng, s, ps.capacity);
+  }
+  // warp-aggregated compaction of the surviving slots into the next queue
+  unsigned ballot = __ballot_sync(0xffffffffu, alive);
+  if (ballot) {
+    int lane = threadIdx.x & 31;
+    int leader = __ffs(ballot) - 1;
+    int base = 0;
+    if (lane == leader) base = atomicAdd(next_count, __popc(ballot));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (alive) next_queue[base + __popc(ballot & ((1u << lane) - 1u))] = s;
+  }
+}
+
+}  // namespace
+
+// ---- host side ---------------------------------------------------------------------------
+static RenderCtx *rc_of(gpt_ctx *ctx) {
+  if (!ctx->render_state) ctx->render_state = new RenderCtx();
+  return static_cast<RenderCtx *>(ctx->render_state);
+}
+
+// Camera::Camera (camera.h:30-52): same operations, evaluated on the host
+static CameraDev derive_camera(const GptCamera &c) {
+  CameraDev d;
+  V3 eye = V3{c.eye[0], c.eye[1], c.eye[2]}, center = V3{c.center[0], c.center[1], c.center[2]};
+  V3 up = V3{c.up[0], c.up[1], c.up[2]};
+  float fovy = c.fovy;
+  float fovx = (float)(2.0f * atan(((float)c.width / (float)c.height) *
+                                   tan(M_PI * fovy / 180 / 2)) * 180 / M_PI);
+  d.eye = eye;
+  d.w = unit(eye - center);
+  d.u = unit(cross(up, d.w));
+  d.v = cross(d.w, d.u);
+  d.tan_half_fovx = tan(fovx * M_PI / 180.0 / 2);
+  d.tan_half_fovy = tan(fovy * M_PI / 180.0 / 2);
+  d.focus_dist = c.focus_dist;
+  d.lens_radius = (float)(c.aperture / 2.0);
+  d.width = c.width;
+  d.height = c.height;
+  return d;
+}
+
+static int build_light_tree(gpt_ctx *ctx, RenderCtx *rc) {
+  BvhDev &lb = ctx->bvh[GPT_BVH_LIGHT];
+  int n = lb.n;
+  if (n < 2)
+    return gpt_fail(ctx, GPT_E_INVALID, "path tracing needs >= 2 emissive triangles (src/main.cu:1124-1125)", __FILE__, __LINE__);
+  GPT_TRY(gpt_alloc(ctx, &rc->leaf_info, 4 * (size_t)n));
+  GPT_TRY(gpt_alloc(ctx, &rc->node_info, (size_t)n));
+  GPT_TRY(gpt_alloc(ctx, &rc->node_energy, 3 * (size_t)n));
+  GPT_TRY(gpt_alloc(ctx, &rc->lt_flags, (size_t)n));
+  GPT_CUDA(ctx, cudaMemsetAsync(rc->lt_flags, 0, sizeof(int) * (size_t)n, ctx->stream));
+  TexAtlas atlas{ctx->scene.tex_r, ctx->scene.tex_g, ctx->scene.tex_b};
+  int grid = (n + 127) / 128;
+  k_light_leaves<<<grid, 128, 0, ctx->stream>>>(ctx->scene, atlas, lb.tris, n, rc->leaf_info);
+  GPT_LAUNCH_CHECK(ctx);
+  k_light_nodes<<<grid, 128, 0, ctx->stream>>>(lb.nodes, lb.parent_leaf, rc->leaf_info, n,
+                                               rc->node_energy, rc->node_info, rc->lt_flags);
+  GPT_LAUNCH_CHECK(ctx);
+  rc->light_n = n;
+  return GPT_OK;
+}
+
+static int reserve_paths(gpt_ctx *ctx, RenderCtx *rc, int n) {
+  PathState &ps = rc->ps;
+  if (n <= ps.capacity) return GPT_OK;
+  size_t N = (size_t)n;
+  GPT_TRY(gpt_alloc(ctx, &ps.pixel, N));
+  GPT_TRY(gpt_alloc(ctx, &ps.rng, 6 * N));
+  GPT_TRY(gpt_alloc(ctx, &rc->rng_init, 6 * N));
+  GPT_TRY(gpt_alloc(ctx, &ps.rays, 2 * N));
+  GPT_TRY(gpt_alloc(ctx, &ps.hits, 2 * N));
+  GPT_TRY(gpt_alloc(ctx, &ps.mask, N));
+  GPT_TRY(gpt_alloc(ctx, &ps.acc, N));
+  GPT_TRY(gpt_alloc(ctx, &ps.color, N));
+  GPT_TRY(gpt_alloc(ctx, &ps.cam_o, N));
+  GPT_TRY(gpt_alloc(ctx, &ps.cam_d, N));
+  GPT_TRY(gpt_alloc(ctx, &ps.matlist, N));
+  GPT_TRY(gpt_alloc(ctx, &ps.queue[0], N));
+  GPT_TRY(gpt_alloc(ctx, &ps.queue[1], N));
+  GPT_TRY(gpt_alloc(ctx, &ps.counts, (size_t)4));
+  if (!rc->h_counts) GPT_CUDA(ctx, cudaMallocHost((void **)&rc->h_counts, 4 * sizeof(int)));
+  ps.capacity = n;
+  rc->rng_w = rc->rng_h = 0;  // cached states are gone
+  return GPT_OK;
+}
+
+// slot -> pixel map: 32x32 tiles dealt round-robin to ranks, tile-major so that one warp
+// covers one 32-pixel tile row (coherent primary rays)
+static std::vector<int> tile_pixels(int W, int H, int rank, int nranks) {
+  std::vector<int> px;
+  int tx = (W + 31) / 32, ty = (H + 31) / 32;
+  px.reserve((size_t)W * H / nranks + 1024);
+  for (int t = 0; t < tx * ty; t++) {
+    if (t % nranks != rank) continue;
+    int x0 = (t % tx) * 32, y0 = (t / tx) * 32;
+    for (int y = y0; y < y0 + 32 && y < H; y++)
+      for (int x = x0; x < x0 + 32 && x < W; x++) px.push_back(y * W + x);
+  }
+  return px;
+}
+
+static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks) {
+  if (!ctx->built) return gpt_fail(ctx, GPT_E_INVALID, "gpt_build first", __FILE__, __LINE__);
+  if (!ctx->have_cam) return gpt_fail(ctx, GPT_E_INVALID, "gpt_set_camera first", __FILE__, __LINE__);
+  if (nranks < 1 || rank < 0 || rank >= nranks) return GPT_E_INVALID;
+  const GptParams &gp = ctx->params;
+  if (gp.pathtracing_sample_size < 1 || gp.pathtracing_level < 1 || gp.dof_sample_size < 1)
+    return gpt_fail(ctx, GPT_E_INVALID, "sample_size, level and dof_sample_size must be >= 1", __FILE__, __LINE__);
+  for (int i = 0; i < ctx->scene.nmat; i++) { /* SSS is a "next" row */ }
+  GPT_CUDA(ctx, cudaSetDevice(ctx->device));
+  RenderCtx *rc = rc_of(ctx);
+  ctx->launches = 0;
+  int W = ctx->cam.width, H = ctx->cam.height;
+  bool new_map = !(rc->rng_w == W && rc->rng_h == H && rc->rng_rank == rank &&
+                   rc->rng_nranks == nranks);
+  std::vector<int> px;
+  int n;
+  if (new_map) {
+    px = tile_pixels(W, H, rank, nranks);
+    n = (int)px.size();
+    GPT_TRY(reserve_paths(ctx, rc, n));
+    GPT_CUDA(ctx, cudaMemcpyAsync(rc->ps.pixel, px.data(), sizeof(int) * (size_t)n,
+                                  cudaMemcpyHostToDevice, ctx->stream));
+    // init_curand_state (src/main.cu:1208): once per image layout, cached
+    int cap = rc->ps.capacity;
+    (void)cap;
+    k_rng_init<<<(n + 127) / 128, 128, 0, ctx->stream>>>(rc->rng_init, rc->ps.pixel, n);
+    GPT_LAUNCH_CHECK(ctx);
+    GPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    rc->rng_w = W; rc->rng_h = H; rc->rng_rank = rank; rc->rng_nranks = nranks;
+    rc->light_n = 0;
+  } else {
+    n = 0;
+    int tx = (W + 31) / 32, ty = (H + 31) / 32;
+    for (int t = rank; t < tx * ty; t += nranks) {
+      int x0 = (t % tx) * 32, y0 = (t / tx) * 32;
+      n += (std::min(32, W - x0)) * (std::min(32, H - y0));
+    }
+  }
+  if (n == 0) return GPT_OK;
+  PathState ps = rc->ps;
+  ps.capacity = n;  // stride of the RNG planes for this render
+  if (rc->light_n != ctx->bvh[GPT_BVH_LIGHT].n || new_map) GPT_TRY(build_light_tree(ctx, rc));
+
+  RenderParams p;
+  p.cam = derive_camera(ctx->cam);
+  p.sample_size = gp.pathtracing_sample_size;
+  p.level = gp.pathtracing_level;
+  p.dof_size = gp.dof_sample_size;
+  p.pdf_weight = gp.hittable_pdf_weight;
+  p.sky = V3{gp.sky_emission[0], gp.sky_emission[1], gp.sky_emission[2]};
+  p.bg_r = ctx->scene.bg_r; p.bg_g = ctx->scene.bg_g; p.bg_b = ctx->scene.bg_b;
+  p.bg_h = ctx->scene.bg_h; p.bg_w = ctx->scene.bg_w;
+  p.inv_samples = (float)(1.0 / gp.pathtracing_sample_size / gp.dof_sample_size);
+
+  BvhDev &mb = ctx->bvh[GPT_BVH_MAIN], &lb = ctx->bvh[GPT_BVH_LIGHT];
+  LightTree lt{lb.nodes, lb.tris, lb.parent_leaf, rc->leaf_info, rc->node_info, lb.n};
+  TexAtlas atlas{ctx->scene.tex_r, ctx->scene.tex_g, ctx->scene.tex_b};
+  cudaStream_t st = ctx->stream;
+
+  GPT_CUDA(ctx, cudaEventRecord(ctx->ev0, st));
+  GPT_CUDA(ctx, cudaMemcpyAsync(ps.rng, rc->rng_init, sizeof(uint32_t) * 6 * (size_t)n,
+                                cudaMemcpyDeviceToDevice, st));
+  int init_counts[4] = {n, 0, 0, 0};
+  GPT_CUDA(ctx, cudaMemcpyAsync(ps.counts, init_counts, sizeof(init_counts), cudaMemcpyHostToDevice, st));
+  k_pt_start<<<(n + PT_BLOCK - 1) / PT_BLOCK, PT_BLOCK, 0, st>>>(ps, p, n, d_fb);
+  GPT_LAUNCH_CHECK(ctx);
+  int active = n, cur = 0;
+  uint64_t rays = 0, shades = 0;
+  long long max_iters = (long long)p.sample_size * p.dof_size * p.level + 8;
+  for (long long it = 0; active > 0 && it < max_iters; it++) {
+    int grid = (active + PT_BLOCK - 1) / PT_BLOCK;
+    GPT_CUDA(ctx, cudaMemsetAsync(ps.counts + (cur ^ 1), 0, sizeof(int), st));
+    k_pt_trace<<<grid, PT_BLOCK, 0, st>>>(ps, ps.queue[cur], ps.counts + cur, mb.nodes, mb.tris,
+                                         mb.parent_leaf, ctx->d_counters);
+    GPT_LAUNCH_CHECK(ctx);
+    k_pt_shade<<<grid, PT_BLOCK, 0, st>>>(ps, p, ps.queue[cur], ps.counts + cur, ps.queue[cur ^ 1],
+                                         ps.counts + (cur ^ 1), ctx->scene, atlas, mb.tris, lt,
+                                         d_fb, ps.counts + 2);
+    GPT_LAUNCH_CHECK(ctx);
+    rays += (uint64_t)active;
+    shades += (uint64_t)active;
+    GPT_CUDA(ctx, cudaMemcpyAsync(rc->h_counts, ps.counts, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    GPT_CUDA(ctx, cudaStreamSynchronize(st));
+    cur ^= 1;
+    active = rc->h_counts[cur];
+    if (rc->h_counts[2])
+      return gpt_fail(ctx, GPT_E_UNSUPPORTED, "nested-dielectric list deeper than 12", __FILE__, __LINE__);
+  }
+  GPT_CUDA(ctx, cudaEventRecord(ctx->ev1, st));
+  GPT_CUDA(ctx, cudaEventSynchronize(ctx->ev1));
+  float ms = 0.f;
+  GPT_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+  ctx->stats.render_ms = ms;
+  ctx->stats.rays_traced = rays;
+  ctx->stats.shade_events = shades;
+  ctx->stats.kernel_launches = ctx->launches;
+  if (active > 0) return gpt_fail(ctx, GPT_E_INVALID, "path queue did not drain", __FILE__, __LINE__);
+  return GPT_OK;
+}
+
+extern "C" {
+
+void gpt_render_free(gpt_ctx *ctx) {
+  if (!ctx || !ctx->render_state) return;
+  RenderCtx *rc = static_cast<RenderCtx *>(ctx->render_state);
+  PathState &ps = rc->ps;
+  void *p[] = {ps.pixel, ps.rng, ps.rays, ps.hits, ps.mask, ps.acc, ps.color, ps.cam_o, ps.cam_d,
+               ps.matlist, ps.queue[0], ps.queue[1], ps.counts, rc->leaf_info, rc->node_info,
+               rc->node_energy, rc->lt_flags, rc->rng_init, rc->d_fb};
+  for (void *q : p) cudaFree(q);
+  if (rc->h_counts) cudaFreeHost(rc->h_counts);
+  delete rc;
+  ctx->render_state = nullptr;
+}
+
+int gpt_render_pathtrace_device(gpt_ctx *ctx, void *d_out_rgb, int rank, int nranks) {
+  if (!ctx || !d_out_rgb) return GPT_E_INVALID;
+  return render_device(ctx, (float *)d_out_rgb, rank, nranks);
+}
+
+int gpt_render_pathtrace(gpt_ctx *ctx, float *out_rgb) {
+  if (!ctx || !out_rgb) return GPT_E_INVALID;
+  if (!ctx->have_cam) return gpt_fail(ctx, GPT_E_INVALID, "gpt_set_camera first", __FILE__, __LINE__);
+  GPT_CUDA(ctx, cudaSetDevice(ctx->device));
+  RenderCtx *rc = rc_of(ctx);
+  size_t nfl = 3 * (size_t)ctx->cam.width * ctx->cam.height;
+  if (nfl > rc->fb_capacity) {
+    GPT_TRY(gpt_alloc(ctx, &rc->d_fb, nfl));
+    rc->fb_capacity = nfl;
+  }
+  GPT_TRY(render_device(ctx, rc->d_fb, 0, 1));
+  GPT_CUDA(ctx, cudaMemcpyAsync(out_rgb, rc->d_fb, sizeof(float) * nfl, cudaMemcpyDeviceToHost, ctx->stream));
+  GPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return GPT_OK;
+}
+
+}  // extern "C"

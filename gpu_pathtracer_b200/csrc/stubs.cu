@@ -6,10 +6,7 @@
 #define UNSUPPORTED(ctx, name) gpt_fail((ctx), GPT_E_UNSUPPORTED, name " is not implemented yet", __FILE__, __LINE__)
 
 extern "C" {
-void gpt_render_free(gpt_ctx *) {}
 void gpt_sppm_free(gpt_ctx *) {}
-int gpt_render_pathtrace(gpt_ctx *ctx, float *) { return UNSUPPORTED(ctx, "gpt_render_pathtrace"); }
-int gpt_render_pathtrace_device(gpt_ctx *ctx, void *, int, int) { return UNSUPPORTED(ctx, "gpt_render_pathtrace_device"); }
 int gpt_sppm_init(gpt_ctx *ctx) { return UNSUPPORTED(ctx, "gpt_sppm_init"); }
 int gpt_sppm_pass(gpt_ctx *ctx, int, int64_t, int64_t) { return UNSUPPORTED(ctx, "gpt_sppm_pass"); }
 int gpt_sppm_flux_device(gpt_ctx *ctx, void **, int64_t *) { return UNSUPPORTED(ctx, "gpt_sppm_flux_device"); }

@@ -94,7 +94,7 @@ __device__ __forceinline__ bool tri_test(const RaySetup &r, float4 t0, float4 t1
 // Reference visit rank of a leaf: leaf children are tested when their parent is processed
 // (left before right), internal nodes in left-first preorder.  preorder(X) = range_first(X)
 // + number of left-child edges on the root..X path.
-__device__ __noinline__ int leaf_visit_rank(const float4 *__restrict__ nodes,
+static __device__ __noinline__ int leaf_visit_rank(const float4 *__restrict__ nodes,
                                             const int *__restrict__ parent_leaf, int leaf) {
   int pe = __ldg(parent_leaf + leaf);
   int par = pe >> 1;

@@ -1,0 +1,58 @@
+"""GPU parity of the wavefront path tracer against the host replay of the reference's
+path_tracing_render with identical per-pixel XORWOW streams (seed 1984, seq = pixel).
+
+Shading uses libm functions (powf, cos, sin, atan2 ...) whose CUDA and glibc versions differ
+in the last ulp, so the bar here is a TOLERANCE, stated per test: the two images must agree
+to 1e-3 relative on >= 99.5 % of the pixels, and the mean luminance to 0.5 %.  (A pixel only
+falls outside when a 1-ulp difference flips a discrete decision -- a Russian-roulette-like
+branch on a uniform, a texel index, a hit/miss at a silhouette.)"""
+import numpy as np
+import pytest
+
+from gpu_pathtracer_b200 import scene as S
+
+pytestmark = pytest.mark.gpu
+
+
+def _compare(sc, window=None, min_frac=0.995):
+    from gpu_pathtracer_b200.api import PathTracer
+    from tests.refreplay import RefReplay
+    pt = PathTracer(sc)
+    pt.build()
+    got = pt.render_pathtrace()
+    ref = RefReplay(sc)
+    want = ref.render_pathtrace(window=window)
+    if window is not None:
+        r0, r1, c0, c1 = window
+        got, want = got[r0:r1, c0:c1], want[r0:r1, c0:c1]
+    assert np.isfinite(got).all()
+    close = np.abs(got - want) <= 1e-3 * (1.0 + np.abs(want))
+    frac = close.all(axis=-1).mean()
+    lum_g, lum_w = got.mean(), want.mean()
+    rmse = float(np.sqrt(np.mean((got - want) ** 2)))
+    print(f"{sc.name}: pixels within 1e-3: {frac:.5f}, mean {lum_g:.6f} vs {lum_w:.6f}, "
+          f"rmse {rmse:.3e}, exact {np.mean(got == want):.4f}")
+    assert frac >= min_frac, frac
+    assert abs(lum_g - lum_w) <= 5e-3 * abs(lum_w)
+    return frac
+
+
+def test_diffuse_only():
+    _compare(S.make_scene("small", n=24, width=128, height=128, spp=2, level=4, glass=False,
+                          metal=False, name="diffuse"))
+
+
+def test_metal_glass_nested():
+    _compare(S.make_scene("small", n=24, width=128, height=128, spp=2, level=6, name="mixed"))
+
+
+def test_textured_bump():
+    _compare(S.make_scene("small", n=24, width=128, height=128, spp=2, level=4, textured=True,
+                          name="textured"))
+
+
+def test_depth_of_field_bottle():
+    sc = S.make_scene("C3", width=160, height=120, spp=2, dof=2, level=8)
+    # 4 samples x 8 bounces through two nested dielectrics: more uniform-vs-Schlick decisions
+    # per pixel, hence a lower (stated) agreement bar
+    _compare(sc, window=(30, 100, 40, 120), min_frac=0.985)
