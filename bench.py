@@ -25,13 +25,13 @@ L2_FLUSH_BYTES = 512 << 20
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="C2", choices=["C1", "C2", "small"])
     ap.add_argument("--mode", default="auto", choices=["auto", "trace", "render"])
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel")
-    ap.add_argument("--cpu-sample-rays", type=int, default=4000000)
+    ap.add_argument("--cpu-budget-s", type=float, default=15.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
 
@@ -102,74 +102,62 @@ class ClockSampler:
         return out
 
 
-def build_ray_batches(sc, pt, rank: int, world: int):
-    """R1 (primary, pixel centres) + R2 (cosine-hemisphere bounce rays from the R1 hit
-    points, PCG64 seed 7).  Rays are dealt to ranks in interleaved 4096-ray chunks."""
-    from gpu_pathtracer_b200 import rays as R
-    r1 = R.camera_rays(sc)
-    h = pt.trace(r1)
-    hit = h["tri_id"] >= 0
-    d = r1[:, 4:7] / np.linalg.norm(r1[:, 4:7], axis=1, keepdims=True)
-    pts = r1[hit, 0:3] + h["t"][hit, None] * d[hit]
-    nrm = pt.export_triangles()["normal"][h["tri_id"][hit]]
-    flip = (nrm * d[hit]).sum(1) > 0
-    nrm = np.where(flip[:, None], -nrm, nrm)
-    r2 = R.bounce_rays(pts.astype(np.float64), nrm.astype(np.float64), seed=7)
-    allr = np.concatenate([r1, r2]).astype(np.float32)
-    if world > 1:
-        chunk = np.arange(allr.shape[0]) // 4096
-        allr = allr[chunk % world == rank]
-    return np.ascontiguousarray(allr), int(r1.shape[0]), int(r2.shape[0])
+def workload_text(sc, args):
+    p, c = sc.params, sc.camera
+    return (f"{args.workload}: {sc.num_triangles} triangles, {sc.materials['num_materials']} "
+            f"materials, {c['width']}x{c['height']} @ {p['pathtracing_sample_size']} spp x "
+            f"{p['dof_sample_size']} dof, level {p['pathtracing_level']}, path tracing")
 
 
-def cpu_baseline_trace(sc, sample_rays: np.ndarray, nthreads: int, budget_s: float):
-    """Times the reference's own traverse_bvh + Triangle::hit (oracle/_ref host replay)."""
+def reference_window(sc, budget_s: float, nthreads: int):
+    """Times the reference's own path_tracing_render (host replay of its headers,
+    oracle/_ref) on a bounded window of the SAME frame at the SAME spp, growing the window
+    until about `budget_s` seconds of CPU work were spent.  Returns Mrays/s."""
     from tests.refreplay import RefReplay, available
     if not available():
         return None
-    t0 = time.time()
     ref = RefReplay(sc)
-    build_s = time.time() - t0
-    done, ms = 0, 0.0
-    chunk = 4000 * max(1, nthreads)
-    while done < sample_rays.shape[0] and ms < budget_s * 1e3:
-        part = sample_rays[done:done + chunk]
-        ms += ref.trace(part, nthreads=nthreads)["ms"]
-        done += part.shape[0]
-    return dict(mrays=done / ms / 1e3, rays=done, ms=ms, build_s=build_s)
+    H, W = sc.camera["height"], sc.camera["width"]
+    rays, ms, rows_done = 0, 0.0, 0
+    # rows around the image centre (terrain + spheres), full width strips of 2 rows at a time
+    order = [H // 2 + (k // 2) * (1 if k % 2 == 0 else -1) - (0 if k % 2 == 0 else 1)
+             for k in range(H)]
+    cols = (W // 4, 3 * W // 4)
+    k = 0
+    while ms < budget_s * 1e3 and k < len(order):
+        r = order[k]
+        ref.render_pathtrace(window=(r, r + 1, cols[0], cols[1]), nthreads=nthreads)
+        rays += ref.render_rays
+        ms += ref.render_ms
+        rows_done += 1
+        k += 1
+    return dict(mrays=rays / ms / 1e3, rays=rays, ms=ms,
+                sample=f"{rows_done} image rows x columns [{cols[0]},{cols[1]}) around the centre "
+                       f"of the same frame at full spp ({rays} rays, {ms / 1e3:.1f} s)")
 
 
 def run_reference(args, rank, world):
-    """--impl reference: the reference's own CPU code on the host cores (rank 0 only)."""
+    """--impl reference: the reference's own CPU code on all host cores (rank 0 only)."""
     if rank != 0:
         return
-    from gpu_pathtracer_b200 import rays as R
     sc = make_workload(args.workload, args.spp)
     cores = os.cpu_count() or 1
-    from tests.refreplay import RefReplay
-    ref = RefReplay(sc)
-    r1 = R.camera_rays(sc)
-    rng = np.random.Generator(np.random.PCG64(11))
-    per_step = 20000 * cores
-    times = []
+    times, rays = [], []
+    sample = ""
     for s in range(args.warmup + args.steps):
-        idx = rng.integers(0, r1.shape[0], size=per_step)
-        ms = ref.trace(r1[idx], nthreads=cores)["ms"]
+        r = reference_window(sc, 6.0 if s >= args.warmup else 1.0, cores)
         if s >= args.warmup:
-            times.append(ms)
+            times.append(r["ms"]); rays.append(r["rays"]); sample = r["sample"]
     ms_per_step = float(np.mean(times))
-    val = per_step / ms_per_step / 1e3
+    val = float(np.sum(rays) / np.sum(times) / 1e3)
     line = {
         "impl": "reference", "metric": "Mrays/s", "value": val, "unit": "Mrays/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{args.workload}: {sc.num_triangles} triangles, "
-                               f"{sc.camera['width']}x{sc.camera['height']} primary rays",
-                   "stage": "trace (traverse_bvh + Triangle::hit)"},
+        "config": {"workload": workload_text(sc, args)},
         "cpu_baseline": {"value": val, "unit": "Mrays/s", "cores": cores, "kind": "reference",
-                         "sample": f"{per_step} primary rays per step sampled (PCG64 seed 11) "
-                                   f"from the {r1.shape[0]} camera rays, all host threads"},
+                         "sample": "per step: " + sample},
         "e2e": {"value": val, "unit": "Mrays/s", "h2d_bytes_per_step": 0,
                 "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -177,16 +165,26 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+def scene_bytes(sc) -> int:
+    n = 0
+    for d in (sc.mesh, sc.materials, sc.bg):
+        for v in d.values():
+            if isinstance(v, np.ndarray):
+                n += v.nbytes
+    return n
+
+
 def run_ours(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
-    from gpu_pathtracer_b200.api import PathTracer, GptError
+    from gpu_pathtracer_b200.api import PathTracer
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     sc = make_workload(args.workload, args.spp)
+    H, W = sc.camera["height"], sc.camera["width"]
     pt = PathTracer(sc, device=local_rank)
     # a real (non-legacy) stream: the library launches on it and the events below time it
     stream = torch.cuda.Stream(device=dev)
@@ -194,11 +192,7 @@ def run_ours(args, rank, world, local_rank):
     pt.set_stream(stream.cuda_stream)
     build_stats = pt.build()
     build_ms = min(pt.rebuild_main_bvh() for _ in range(5))
-
-    rays_np, n_r1, n_r2 = build_ray_batches(sc, pt, rank, world)
-    n = rays_np.shape[0]
-    d_rays = torch.from_numpy(rays_np).to(dev)
-    d_hits = torch.empty((n, 8), dtype=torch.float32, device=dev)
+    fb = torch.zeros((H, W, 3), dtype=torch.float32, device=dev)
     flush = torch.empty(L2_FLUSH_BYTES // 4, dtype=torch.float32, device=dev)
 
     def barrier():
@@ -206,50 +200,67 @@ def run_ours(args, rank, world, local_rank):
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- device-resident timing: K steps, L2 flushed between steps, CUDA events on the
-    #      stream the kernels are launched on
+    # ---- device-resident timing: scene + BVH already in HBM, K full-frame renders of this
+    #      rank's tiles, L2 flushed between steps, CUDA events on the launching stream
     for _ in range(args.warmup):
         flush.zero_()
-        pt.trace_device(d_rays.data_ptr(), n, d_hits.data_ptr())
+        pt.render_pathtrace_device(fb.data_ptr(), rank, world)
     barrier()
     sampler = ClockSampler(local_rank) if rank == 0 else None
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
            for _ in range(args.steps)]
-    launches = 0
+    launches, rays = 0, 0
     for a, b in evs:
         flush.zero_()
         a.record(stream)
-        pt.trace_device(d_rays.data_ptr(), n, d_hits.data_ptr())
+        pt.render_pathtrace_device(fb.data_ptr(), rank, world)
         b.record(stream)
-        launches += pt.stats()["kernel_launches"]
+        st = pt.stats()
+        launches += st["kernel_launches"]
+        rays = st["rays_traced"]
     barrier()
     step_ms = [a.elapsed_time(b) for a, b in evs]
     total_ms = float(sum(step_ms))
     clocks = sampler.stop() if sampler else None
 
-    # ---- visit counts for the algorithmic-byte roofline (same traversal, not timed)
-    cnt = pt.trace_count_device(d_rays.data_ptr(), n)
-    v_int, v_leaf = cnt["internal_visits"], cnt["leaf_tests"]
-    alg_bytes = 48.0 * n + 64.0 * v_int + 48.0 * v_leaf
+    # ---- profiling passes (not timed): per-stage kernel time, then visit counts
+    pt.set_profiling(time_stages=True)
+    pt.render_pathtrace_device(fb.data_ptr(), rank, world)
+    st_t = pt.stats()
+    pt.set_profiling(count_visits=True)
+    pt.render_pathtrace_device(fb.data_ptr(), rank, world)
+    st_c = pt.stats()
+    pt.set_profiling()
+    v_int, v_leaf = st_c["internal_visits"], st_c["leaf_tests"]
+    alg_bytes = 48.0 * rays + 64.0 * v_int + 48.0 * v_leaf
+    trace_ms, shade_ms = st_t["trace_kernel_ms"], st_t["shade_kernel_ms"]
+    n_trace = max(1, st_t["trace_launches"])
 
-    # ---- end to end through the host C-ABI call: pinned host rays in, host hits out
-    e2e_steps = max(1, min(args.steps, 5))
-    pt.trace(rays_np[:4096])
+    # ---- end to end through the reference-facing C-ABI with HOST buffers: upload the scene
+    #      SoA, build, render, read the frame back (NCCL sum = tile gather when N > 1)
+    e2e_steps = max(1, min(args.steps, 3))
     barrier()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
-        out = pt.trace(rays_np)
+        pt.set_scene(sc)
+        pt.build()
+        if world > 1:
+            fb.zero_()
+            pt.render_pathtrace_device(fb.data_ptr(), rank, world)
+            dist.reduce(fb, dst=0, op=dist.ReduceOp.SUM)
+            img = fb.cpu() if rank == 0 else None
+        else:
+            img = pt.render_pathtrace()
     barrier()
-    e2e_s = (time.perf_counter() - t0) / e2e_steps
+    e2e_ms = (time.perf_counter() - t0) / e2e_steps * 1e3
 
-    t = torch.tensor([total_ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
-    tot = torch.tensor([float(n), alg_bytes, float(v_int), float(v_leaf)], dtype=torch.float64,
-                       device=dev)
+    t = torch.tensor([total_ms, e2e_ms], dtype=torch.float64, device=dev)
+    tot = torch.tensor([float(rays)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(tot, op=dist.ReduceOp.SUM)
     total_ms, e2e_ms = t.tolist()
-    n_all, bytes_all, vint_all, vleaf_all = tot.tolist()
+    rays_all = tot.item()
     if rank != 0:
         return
     peaks = {}
@@ -259,43 +270,49 @@ def run_ours(args, rank, world, local_rank):
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     ms_per_step = total_ms / args.steps
-    value = n_all / (ms_per_step * 1e-3) / 1e6
-    achieved = (alg_bytes / (float(np.mean(step_ms)) * 1e-3)) / 1e9  # this rank's kernel
+    value = rays_all / (ms_per_step * 1e-3) / 1e6
+    spp_total = sc.params["pathtracing_sample_size"] * sc.params["dof_sample_size"]
+    achieved = alg_bytes / (trace_ms * 1e-3) / 1e9 if trace_ms > 0 else 0.0
     line = {
         "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
-        "higher_is_better": True, "scaling": "strong",
-        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
         "config": {
-            "workload": f"{args.workload}: {sc.num_triangles} triangles, "
-                        f"{sc.camera['width']}x{sc.camera['height']}: {n_r1} primary + {n_r2} "
-                        "cosine-bounce rays per step",
-            "stage": "trace (closest hit, main BVH)",
+            "workload": workload_text(sc, args),
+            "step": "one full frame: ray-gen + trace + shade wavefront over all pixels/samples",
+            "rays": "closest-hit traversals of the main BVH (primary + bounce), as the "
+                    "reference's traverse_bvh(node_list[0]) call count",
             "cache": "L2 flushed (512 MiB write) between timed steps",
-            "sharding": "rays interleaved in 4096-ray chunks across ranks, scene replicated",
+            "sharding": "scene replicated, 32x32 pixel tiles dealt round-robin to ranks",
+            "spp_per_s": spp_total / (ms_per_step * 1e-3),
+            "rays_per_frame": rays_all,
             "lbvh_build_ms": build_ms, "build_all_ms": build_stats["build_all_ms"],
-            "avg_internal_visits_per_ray": vint_all / n_all,
-            "avg_leaf_tests_per_ray": vleaf_all / n_all,
+            "rank0_stage_ms": {"trace": trace_ms, "shade": shade_ms,
+                               "frame": float(np.mean(step_ms))},
+            "avg_internal_visits_per_ray": v_int / max(1, rays),
+            "avg_leaf_tests_per_ray": v_leaf / max(1, rays),
         },
         "gpu_launches": int(launches),
-        "e2e": {"value": n_all / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s",
-                "h2d_bytes_per_step": int(32 * n_all), "d2h_bytes_per_step": int(32 * n_all)},
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+        "e2e": {"value": rays_all / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s",
+                "h2d_bytes_per_step": scene_bytes(sc), "d2h_bytes_per_step": H * W * 12,
+                "what": "gpt_set_mesh/materials/textures + gpt_build + gpt_render_pathtrace "
+                        "with host arrays in, host frame out"},
+        "roofline": {"bound": "hbm", "kernel": "k_pt_trace",
+                     "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": None,
-                     "kernel": "k_trace", "algorithmic_bytes_per_launch": alg_bytes,
-                     "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"},
+                     "launches": int(n_trace),
+                     "algorithmic_bytes_per_launch": alg_bytes / n_trace,
+                     "avg_launch_ms": trace_ms / n_trace,
+                     "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback"},
         "clocks": clocks,
     }
     if not args.no_cpu_baseline:
-        rng = np.random.Generator(np.random.PCG64(11))
-        sample = rays_np[rng.integers(0, n, size=args.cpu_sample_rays)]
-        cb = cpu_baseline_trace(sc, sample, 1, 15.0)
+        cb = reference_window(sc, args.cpu_budget_s, 1)
         if cb:
             line["cpu_baseline"] = {
                 "value": cb["mrays"], "unit": "Mrays/s", "cores": 1, "kind": "reference",
-                "sample": f"{cb['rays']} rays sampled (PCG64 seed 11) from this step's ray "
-                          f"batch, single thread of {os.cpu_count()} host cores, "
-                          f"{cb['ms'] / 1e3:.1f} s"}
+                "sample": cb["sample"] + f", 1 thread of {os.cpu_count()} host cores"}
     print(json.dumps(line), flush=True)
 
 

@@ -26,7 +26,7 @@ gpt_set_materials gpt_set_textures gpt_set_background gpt_set_camera gpt_set_par
 gpt_rebuild_main_bvh gpt_export_triangles gpt_bvh_num_leaves gpt_export_bvh gpt_trace
 gpt_trace_device gpt_trace_count_device gpt_render_pathtrace gpt_render_pathtrace_device
 gpt_sppm_init gpt_sppm_pass gpt_sppm_flux_device gpt_sppm_update gpt_sppm_resolve gpt_stats
-gpt_synchronize""".split()
+gpt_synchronize gpt_set_profiling""".split()
 
 
 class GptError(RuntimeError):
@@ -105,6 +105,10 @@ class PathTracer:
     def rebuild_main_bvh(self) -> float:
         self._check(self.lib.gpt_rebuild_main_bvh(self.ctx))
         return self.stats()["build_ms"]
+
+    def set_profiling(self, time_stages=False, count_visits=False):
+        self._check(self.lib.gpt_set_profiling(self.ctx, C.c_int(int(time_stages)),
+                                               C.c_int(int(count_visits))))
 
     def stats(self) -> dict:
         s = cabi.GptStats()

@@ -56,7 +56,8 @@ class GptStats(C.Structure):
                 ("trace_ms", C.c_double), ("render_ms", C.c_double),
                 ("rays_traced", C.c_uint64), ("internal_visits", C.c_uint64),
                 ("leaf_tests", C.c_uint64), ("kernel_launches", C.c_uint64),
-                ("shade_events", C.c_uint64)]
+                ("shade_events", C.c_uint64), ("trace_kernel_ms", C.c_double),
+                ("shade_kernel_ms", C.c_double), ("trace_launches", C.c_uint64)]
 
 
 def fptr(a: np.ndarray):

@@ -403,6 +403,13 @@ int gpt_trace(gpt_ctx *ctx, int which, const float *rays, int64_t n, int32_t *le
   return GPT_OK;
 }
 
+int gpt_set_profiling(gpt_ctx *ctx, int time_stages, int count_visits) {
+  if (!ctx) return GPT_E_INVALID;
+  ctx->prof_time_stages = time_stages != 0;
+  ctx->prof_count_visits = count_visits != 0;
+  return GPT_OK;
+}
+
 int gpt_stats(gpt_ctx *ctx, GptStats *out) {
   if (!ctx || !out) return GPT_E_INVALID;
   *out = ctx->stats;

@@ -104,6 +104,7 @@ struct gpt_ctx {
   void *render_state = nullptr;              // owned by render.cu
   void *sppm_state = nullptr;                // owned by sppm.cu
   uint64_t launches = 0;                     // kernels launched since last reset
+  bool prof_time_stages = false, prof_count_visits = false;
 };
 
 // ---- error plumbing --------------------------------------------------------------------

@@ -28,6 +28,7 @@ struct RenderCtx {
   int *h_counts = nullptr;        // pinned
   float *d_fb = nullptr;          // internal framebuffer for the host API
   size_t fb_capacity = 0;
+  std::vector<cudaEvent_t> events;  // profiling only
 };
 
 struct RenderParams {
@@ -172,6 +173,7 @@ k_pt_start(PathState ps, RenderParams p, int n, float *fb) {
   fb[3 * (size_t)pix] = 0.f; fb[3 * (size_t)pix + 1] = 0.f; fb[3 * (size_t)pix + 2] = 0.f;
 }
 
+template <bool COUNT>
 __global__ void __launch_bounds__(PT_BLOCK)
 k_pt_trace(PathState ps, const int *__restrict__ queue, const int *__restrict__ count,
            const float4 *__restrict__ nodes, const float4 *__restrict__ tris,
@@ -183,8 +185,8 @@ k_pt_trace(PathState ps, const int *__restrict__ queue, const int *__restrict__ 
   float4 ro = ps.rays[2 * (size_t)s], rd = ps.rays[2 * (size_t)s + 1];
   RaySetup r = make_ray(ro.x, ro.y, ro.z, rd.x, rd.y, rd.z);
   int overflow = 0;
-  HitResult h = trace_ray<false>(nodes, tris, parent_leaf, r, ro.w, stack + threadIdx.x, PT_BLOCK,
-                                 nullptr, nullptr, &overflow);
+  HitResult h = trace_ray<COUNT>(nodes, tris, parent_leaf, r, ro.w, stack + threadIdx.x, PT_BLOCK,
+                                 counters, counters + 1, &overflow);
   if (overflow) atomicExch(counters + 3, 1ull);
   ps.hits[2 * (size_t)s] = make_float4(h.t, __int_as_float(h.leaf), __int_as_float(h.prim), 0.f);
   ps.hits[2 * (size_t)s + 1] = make_float4(h.b1, h.b2, h.b3, 0.f);
@@ -497,18 +499,39 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks) {
   k_pt_start<<<(n + PT_BLOCK - 1) / PT_BLOCK, PT_BLOCK, 0, st>>>(ps, p, n, d_fb);
   GPT_LAUNCH_CHECK(ctx);
   int active = n, cur = 0;
-  uint64_t rays = 0, shades = 0;
+  uint64_t rays = 0, shades = 0, trace_launches = 0;
+  const bool timing = ctx->prof_time_stages, counting = ctx->prof_count_visits;
+  size_t nev = 0;
+  if (counting) GPT_CUDA(ctx, cudaMemsetAsync(ctx->d_counters, 0, 3 * sizeof(unsigned long long), st));
+  auto stamp = [&]() -> cudaError_t {
+    if (!timing) return cudaSuccess;
+    if (nev == rc->events.size()) {
+      cudaEvent_t e;
+      cudaError_t r = cudaEventCreate(&e);
+      if (r != cudaSuccess) return r;
+      rc->events.push_back(e);
+    }
+    return cudaEventRecord(rc->events[nev++], st);
+  };
   long long max_iters = (long long)p.sample_size * p.dof_size * p.level + 8;
   for (long long it = 0; active > 0 && it < max_iters; it++) {
     int grid = (active + PT_BLOCK - 1) / PT_BLOCK;
     GPT_CUDA(ctx, cudaMemsetAsync(ps.counts + (cur ^ 1), 0, sizeof(int), st));
-    k_pt_trace<<<grid, PT_BLOCK, 0, st>>>(ps, ps.queue[cur], ps.counts + cur, mb.nodes, mb.tris,
-                                         mb.parent_leaf, ctx->d_counters);
+    GPT_CUDA(ctx, stamp());
+    if (counting)
+      k_pt_trace<true><<<grid, PT_BLOCK, 0, st>>>(ps, ps.queue[cur], ps.counts + cur, mb.nodes,
+                                                 mb.tris, mb.parent_leaf, ctx->d_counters);
+    else
+      k_pt_trace<false><<<grid, PT_BLOCK, 0, st>>>(ps, ps.queue[cur], ps.counts + cur, mb.nodes,
+                                                  mb.tris, mb.parent_leaf, ctx->d_counters);
     GPT_LAUNCH_CHECK(ctx);
+    trace_launches++;
+    GPT_CUDA(ctx, stamp());
     k_pt_shade<<<grid, PT_BLOCK, 0, st>>>(ps, p, ps.queue[cur], ps.counts + cur, ps.queue[cur ^ 1],
                                          ps.counts + (cur ^ 1), ctx->scene, atlas, mb.tris, lt,
                                          d_fb, ps.counts + 2);
     GPT_LAUNCH_CHECK(ctx);
+    GPT_CUDA(ctx, stamp());
     rays += (uint64_t)active;
     shades += (uint64_t)active;
     GPT_CUDA(ctx, cudaMemcpyAsync(rc->h_counts, ps.counts, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
@@ -526,6 +549,25 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks) {
   ctx->stats.rays_traced = rays;
   ctx->stats.shade_events = shades;
   ctx->stats.kernel_launches = ctx->launches;
+  ctx->stats.trace_launches = trace_launches;
+  if (timing) {  // three stamps per iteration: before trace, between, after shade
+    double tt = 0, ts = 0;
+    for (size_t k = 0; k + 2 < nev; k += 3) {
+      float a = 0.f, b = 0.f;
+      cudaEventElapsedTime(&a, rc->events[k], rc->events[k + 1]);
+      cudaEventElapsedTime(&b, rc->events[k + 1], rc->events[k + 2]);
+      tt += a;
+      ts += b;
+    }
+    ctx->stats.trace_kernel_ms = tt;
+    ctx->stats.shade_kernel_ms = ts;
+  }
+  if (counting) {
+    unsigned long long c[4];
+    GPT_CUDA(ctx, cudaMemcpy(c, ctx->d_counters, sizeof(c), cudaMemcpyDeviceToHost));
+    ctx->stats.internal_visits = c[0];
+    ctx->stats.leaf_tests = c[1];
+  }
   if (active > 0) return gpt_fail(ctx, GPT_E_INVALID, "path queue did not drain", __FILE__, __LINE__);
   return GPT_OK;
 }
@@ -541,6 +583,7 @@ void gpt_render_free(gpt_ctx *ctx) {
                rc->node_energy, rc->lt_flags, rc->rng_init, rc->d_fb};
   for (void *q : p) cudaFree(q);
   if (rc->h_counts) cudaFreeHost(rc->h_counts);
+  for (cudaEvent_t e : rc->events) cudaEventDestroy(e);
   delete rc;
   ctx->render_state = nullptr;
 }

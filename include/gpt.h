@@ -115,6 +115,9 @@ typedef struct GptStats {
   uint64_t leaf_tests;      /* V_leaf: triangles intersected                               */
   uint64_t kernel_launches; /* kernels of this library launched by the last call           */
   uint64_t shade_events;    /* path vertices shaded in the last render                     */
+  double trace_kernel_ms;   /* sum of the trace-stage kernels of the last render (profiling) */
+  double shade_kernel_ms;   /* sum of the shade-stage kernels of the last render (profiling) */
+  uint64_t trace_launches;  /* trace-stage launches in the last render                       */
 } GptStats;
 
 /* ---- lifetime ---------------------------------------------------------------------- */
@@ -194,6 +197,12 @@ int gpt_sppm_update(gpt_ctx *ctx, int pass);
 int gpt_sppm_resolve(gpt_ctx *ctx, int mode /*0 global,1 direct,2 indirect*/, int passes,
                      float *out_rgb);
 
+/* Profiling switches for the NEXT renders (never on in a timed headline run):
+ *   time_stages  - bracket every trace / shade launch with CUDA events (fills
+ *                  trace_kernel_ms / shade_kernel_ms)
+ *   count_visits - count V_int / V_leaf of the main-BVH traversals (fills internal_visits /
+ *                  leaf_tests) */
+int gpt_set_profiling(gpt_ctx *ctx, int time_stages, int count_visits);
 int gpt_stats(gpt_ctx *ctx, GptStats *out);
 int gpt_synchronize(gpt_ctx *ctx);
 

@@ -16,6 +16,20 @@
 // same include order as src/main.cu:10-45 (minus the jpeg / input / world.h host loaders)
 #include "model/geometry/triangle.h"
 #include "model/bvh/bvh.h"
+#include "model/bvh/bvh_traversal.h"
+
+// Ray counter for the Mrays/s baseline: every later CALL of traverse_bvh (the integrators in
+// pathtracing.h, photon_pass.h, ray_tracing_pass.h, bvh_traversal_photon.h) goes through this
+// wrapper, which counts closest-hit traversals of the MAIN tree and forwards to the
+// reference's own function.  The reference source is untouched.
+static Node *g_counted_root = nullptr;
+static thread_local unsigned long long tl_ray_count = 0;
+static inline bool counted_traverse_bvh(Node *root, Ray ray, hit_record &rec) {
+  if (root == g_counted_root) tl_ray_count++;
+  return (traverse_bvh)(root, ray, rec);
+}
+#define traverse_bvh(...) counted_traverse_bvh(__VA_ARGS__)
+
 #include "model/bvh/bvh_building.h"
 #include "model/bvh/bvh_building_photon.h"
 #include "model/bvh/bvh_building_pts.h"
@@ -118,6 +132,7 @@ struct RefCtx {
   Bvh main_bvh, transparent_bvh, light_bvh;
   std::string err;
   double last_ms = 0;
+  unsigned long long last_rays = 0;
 };
 
 void build_bvh(Bvh &b, bool cones) {
@@ -550,12 +565,15 @@ int ref_render_pathtrace_window(RefCtx *c, float *out_rgb, int row0, int row1, i
   row1 = std::min(row1, H);
   col1 = std::min(col1, W);
   std::atomic<int> next_row(row0);
+  std::atomic<unsigned long long> total_rays(0);
+  g_counted_root = c->main_bvh.node_list[0];
   auto t0 = std::chrono::steady_clock::now();
   auto work = [&] {
     shim_blockDim = dim3(1, 1, 1);
+    tl_ray_count = 0;
     for (;;) {
       int i = next_row.fetch_add(1);
-      if (i >= row1) break;
+      if (i >= row1) { total_rays += tl_ray_count; break; }
       for (int j = col0; j < col1; j++) {
         shim_blockIdx = {(unsigned)j, (unsigned)i, 0};
         shim_threadIdx = {0, 0, 0};
@@ -581,7 +599,10 @@ int ref_render_pathtrace_window(RefCtx *c, float *out_rgb, int row0, int row1, i
   }
   auto t1 = std::chrono::steady_clock::now();
   c->last_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
+  c->last_rays = total_rays.load();
   return GPT_OK;
 }
+
+unsigned long long ref_last_rays(RefCtx *c) { return c->last_rays; }
 
 }  // extern "C"

@@ -44,6 +44,7 @@ class RefReplay:
             raise RefError("oracle/_ref/libref_replay.so missing and reference sources absent")
         self.lib = C.CDLL(REF_SO)
         self.lib.ref_last_ms.restype = C.c_double
+        self.lib.ref_last_rays.restype = C.c_uint64
         self.ctx = C.c_void_p()
         _check(self.lib.ref_create(C.byref(self.ctx)))
         self.scene = scene
@@ -123,6 +124,7 @@ class RefReplay:
         _check(self.lib.ref_render_pathtrace_window(
             self.ctx, cabi.fptr(out), r0, r1, c0, c1, C.c_int(nt)))
         self.render_ms = self.lib.ref_last_ms(self.ctx)
+        self.render_rays = int(self.lib.ref_last_rays(self.ctx))
         return out
 
     def time_main_bvh_build(self) -> float:
