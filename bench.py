@@ -178,6 +178,7 @@ def run_ours(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
     from gpu_pathtracer_b200.api import PathTracer
+    from gpu_pathtracer_b200.parallel import gather_frame
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
@@ -247,7 +248,7 @@ def run_ours(args, rank, world, local_rank):
         if world > 1:
             fb.zero_()
             pt.render_pathtrace_device(fb.data_ptr(), rank, world)
-            dist.reduce(fb, dst=0, op=dist.ReduceOp.SUM)
+            gather_frame(fb, dst=0)
             img = fb.cpu() if rank == 0 else None
         else:
             img = pt.render_pathtrace()

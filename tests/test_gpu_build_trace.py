@@ -86,3 +86,67 @@ def test_trace_tmax_and_empty(pair):
     none = pt.trace(r2)
     assert (none["tri_id"][hit] != full["tri_id"][hit]).all()
     assert pt.trace(np.zeros((0, 8), np.float32))["t"].shape == (0,)
+
+
+def test_against_committed_golden_vectors():
+    """Same checks against tests/golden/small_scene.npz (made from the reference's own
+    headers by tests/golden/make_golden.py): needs no reference code at run time."""
+    import os
+    from gpu_pathtracer_b200.api import PathTracer
+    from tests.golden.make_golden import golden_scene
+    from tests.parity import BVH_KEYS, TRI_KEYS, assert_bits_equal, point_from_bary
+    gold = np.load(os.path.join(os.path.dirname(__file__), "golden", "small_scene.npz"))
+    sc = golden_scene()
+    pt = PathTracer(sc)
+    pt.build()
+    tri = pt.export_triangles()
+    for k in TRI_KEYS:
+        assert_bits_equal(tri[k], gold["tri_" + k], k)
+    for which in (0, 1, 2):
+        b = pt.export_bvh(which)
+        for k in BVH_KEYS:
+            assert_bits_equal(b[k], gold[f"bvh{which}_{k}"], f"bvh{which} {k}")
+    for which in (0, 1):
+        a = pt.trace(gold["rays"], which)
+        for k in ("leaf_id", "tri_id", "t"):
+            assert_bits_equal(a[k], gold[f"trace{which}_{k}"], k)
+        assert_bits_equal(point_from_bary(sc, a["tri_id"], a["bary"]),
+                          gold[f"trace{which}_point"], "hit point")
+
+
+def test_large_scene_properties():
+    """BASELINE config-1 size (100K triangles): size-independent properties instead of a
+    replay -- sorted codes, permutation, every node/leaf referenced once, boxes nested,
+    rebuild idempotent, and closest hits agree with the plain-C oracle on a ray sample."""
+    from gpu_pathtracer_b200.api import PathTracer
+    from tests.oracle_lib import Oracle
+    from tests.parity import assert_bits_equal
+    sc = S.make_scene("C1")
+    pt = PathTracer(sc)
+    pt.build()
+    b = pt.export_bvh(0)
+    n = b["morton"].shape[0]
+    assert n == sc.num_triangles
+    assert (np.diff(b["morton"].astype(np.int64)) >= 0).all()
+    assert np.array_equal(np.sort(b["sorted_to_orig"]), np.arange(n))
+    kids = np.concatenate([b["left"], b["right"]])
+    assert np.array_equal(np.sort(kids[kids >= 0]), np.arange(1, n - 1))
+    assert np.array_equal(np.sort(~kids[kids < 0]), np.arange(n))
+    for side in ("left", "right"):
+        c = b[side]
+        cb = np.where((c >= 0)[:, None], b["node_aabb"][np.maximum(c, 0)],
+                      b["leaf_aabb"][np.maximum(~c, 0)])
+        assert (b["node_aabb"][:, 0::2] <= cb[:, 0::2]).all()
+        assert (b["node_aabb"][:, 1::2] >= cb[:, 1::2]).all()
+    pt.rebuild_main_bvh()
+    b2 = pt.export_bvh(0)
+    for k in b:
+        assert_bits_equal(b[k], b2[k], "rebuild " + k)
+    orc = Oracle(sc)
+    ob = orc.export_bvh(0)
+    for k in ("morton", "sorted_to_orig", "left", "right", "node_aabb"):
+        assert_bits_equal(b[k], ob[k], "oracle " + k)
+    r = np.concatenate([rays.camera_rays(sc)[::37], rays.random_rays(4000)])
+    a, o = pt.trace(r), orc.trace(r)
+    for k in ("leaf_id", "tri_id", "t"):
+        assert_bits_equal(a[k], o[k], k)

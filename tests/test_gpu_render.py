@@ -34,6 +34,9 @@ def _compare(sc, window=None, min_frac=0.995):
           f"rmse {rmse:.3e}, exact {np.mean(got == want):.4f}")
     assert frac >= min_frac, frac
     assert abs(lum_g - lum_w) <= 5e-3 * abs(lum_w)
+    if window is None:  # same paths => (almost) the same number of closest-hit traversals
+        rays_g, rays_w = pt.stats()["rays_traced"], ref.render_rays
+        assert abs(rays_g - rays_w) <= 5e-3 * rays_w, (rays_g, rays_w)
     return frac
 
 
@@ -56,3 +59,35 @@ def test_depth_of_field_bottle():
     # 4 samples x 8 bounces through two nested dielectrics: more uniform-vs-Schlick decisions
     # per pixel, hence a lower (stated) agreement bar
     _compare(sc, window=(30, 100, 40, 120), min_frac=0.985)
+
+
+def test_render_window_against_golden():
+    """The committed reference render window (tests/golden): no reference code at run time."""
+    import os
+    from gpu_pathtracer_b200.api import PathTracer
+    from tests.golden.make_golden import WINDOW, golden_scene
+    gold = np.load(os.path.join(os.path.dirname(__file__), "golden", "small_scene.npz"))
+    pt = PathTracer(golden_scene())
+    pt.build()
+    r0, r1, c0, c1 = WINDOW
+    got, want = pt.render_pathtrace()[r0:r1, c0:c1], gold["render_window"]
+    close = (np.abs(got - want) <= 1e-3 * (1.0 + np.abs(want))).all(axis=-1)
+    assert close.mean() >= 0.995, close.mean()
+    assert abs(got.mean() - want.mean()) <= 5e-3 * want.mean()
+
+
+def test_tile_sharded_render_is_bit_identical():
+    """2 and 3 'ranks' rendered one after the other on one GPU: the union of the tile-sharded
+    frames equals the single-rank frame bit for bit (per-pixel RNG is keyed by pixel index)."""
+    import torch
+    from gpu_pathtracer_b200.api import PathTracer
+    sc = S.make_scene("small", n=20, width=160, height=128, spp=2, level=4)
+    pt = PathTracer(sc)
+    pt.build()
+    full = pt.render_pathtrace()
+    for nranks in (2, 3):
+        fb = torch.zeros((128, 160, 3), dtype=torch.float32, device="cuda")
+        for r in range(nranks):
+            pt.render_pathtrace_device(fb.data_ptr(), r, nranks)
+        pt.synchronize()
+        assert np.array_equal(fb.cpu().numpy().view(np.uint32), full.view(np.uint32)), nranks
