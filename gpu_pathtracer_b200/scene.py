@@ -140,14 +140,20 @@ class MaterialBuilder:
         self.names = []
         self.tex = [np.ones((1, 3), F32)]
         self.tex_len = 1
+        self.images = []
 
     def add_texture(self, img: np.ndarray):
-        """img: (H, W, 3) float in [0,1], row 0 = v=0 (the loader flips rows)."""
-        img = np.asarray(img, dtype=F32)
+        """img: (H, W, 3) float in [0,1], row 0 = v=0 (the loader flips rows).  Values are
+        quantised to k/255 exactly as the reference's 8-bit image loader produces them
+        (`1.0 * lum / 255.0`, src/input/read_image_util.h:58-66), so a scene written to
+        files by write_scene_files loads back bit-identically."""
+        q = np.clip(np.rint(np.asarray(img, dtype=np.float64) * 255.0), 0, 255)
+        img = (q / 255.0).astype(F32)
         h, w, _ = img.shape
         off = self.tex_len
         self.tex.append(img.reshape(-1, 3))
         self.tex_len += h * w
+        self.images.append((h, w, off, q.astype(np.uint8)))
         return (h, w, off)
 
     def add(self, name="m", ka=(0, 0, 0), kd=(0, 0, 0), ks=(0, 0, 0), ke=(0, 0, 0),
@@ -178,6 +184,7 @@ class MaterialBuilder:
         out["tex_r"] = np.ascontiguousarray(tex[:, 0])
         out["tex_g"] = np.ascontiguousarray(tex[:, 1])
         out["tex_b"] = np.ascontiguousarray(tex[:, 2])
+        out["images"] = list(self.images)  # (h, w, offset, uint8 HxWx3) for write_scene_files
         return out
 
 
@@ -452,3 +459,97 @@ def make_scene(kind: str, **kw) -> Scene:
     if kind == "small":
         return small_scene(**kw)
     raise ValueError(kind)
+
+
+# --------------------------------------------------------------------------------------
+# file writer: the same scene as OBJ + MTL + raw textures + master file, for the
+# reference's own loaders (src/input/read_file_util.h, read_image_util.h, input_param.h)
+# --------------------------------------------------------------------------------------
+def _write_image(path: str, rgb_u8: np.ndarray):
+    """Raw image understood by oracle/jpeg_stub/jpeg.h.  The loader flips rows (it reads
+    y = H-1 .. 0 into increasing atlas rows), so atlas row r is stored as file row H-1-r."""
+    h, w, _ = rgb_u8.shape
+    with open(path, "wb") as f:
+        f.write(b"GPTIMG %d %d\n" % (w, h))
+        f.write(np.ascontiguousarray(rgb_u8[::-1]).tobytes())
+
+
+def write_scene_files(sc: Scene, folder: str, prefix: str = "scene") -> str:
+    """Writes <folder>/{prefix}.obj/.mtl, textures, bg image and master file; returns the
+    master file path.  Floats are printed with %.9g (exact fp32 round trip through stof).
+    Loader conventions honoured: material 0 of the loader is its built-in Default_123
+    (indices shift by one, values identical); vn/vt slot 0 are the explicit zero entries the
+    SoA uses for "absent"; one `usemtl` per run of equal material (faces keep their order)."""
+    os.makedirs(folder, exist_ok=True)
+    folder = os.path.join(os.path.abspath(folder), "")
+    m, mt = sc.mesh, sc.materials
+    names = [f"m{i}_{n}" for i, n in enumerate(mt["material_names"])]
+    tex_name = {0: None}
+    for (h, w, off, img) in mt["images"]:
+        tex_name[off] = f"{prefix}_tex{off}.img"
+        _write_image(folder + tex_name[off], img)
+    _write_image(folder + f"{prefix}_bg.img", np.full((1, 1, 3), 255, np.uint8))
+    g9 = lambda v: "%.9g" % float(v)
+    with open(folder + prefix + ".mtl", "w") as f:
+        for i, n in enumerate(names):
+            f.write(f"newmtl {n}\n")
+            for key, col in (("Ka", "ka"), ("Kd", "kd"), ("Ks", "ks"), ("Ke", "ke"), ("Tf", "tf")):
+                f.write(f"{key} " + " ".join(g9(mt[f"{col}_{a}"][i]) for a in "xyz") + "\n")
+            f.write(f"Tr {g9(mt['t_r'][i])}\nNs {g9(mt['n_s'][i])}\nNi {g9(mt['n_i'][i])}\n")
+            f.write(f"path_length {g9(mt['path_length'][i])}\n")
+            f.write(f"scattering_coef {g9(mt['scattering_coef'][i])}\n")
+            f.write(f"absorption_coef {g9(mt['absorption_coef'][i])}\ng {g9(mt['g'][i])}\n")
+            if mt["material_priority"][i] != -1:
+                f.write(f"priority {int(mt['material_priority'][i])}\n")
+            for key, col in (("map_Kd", "diffuse"), ("map_Ks", "specular"), ("map_Ke", "emission"),
+                             ("map_Ns", "n_s")):
+                off = int(mt["offset_" + col][i])
+                if off:
+                    f.write(f"{key} {tex_name[off]}\n")
+            off = int(mt["offset_bump"][i])
+            if off:
+                f.write(f"map_Bump -bm {g9(mt['bm'][i])} {tex_name[off]}\n")
+            f.write("\n")
+    with open(folder + prefix + ".obj", "w") as f:
+        f.write(f"mtllib {prefix}.mtl\n")
+        f.write("".join("v %.9g %.9g %.9g\n" % t for t in zip(m["x"], m["y"], m["z"])))
+        f.write("".join("vn %.9g %.9g %.9g\n" % t
+                        for t in zip(m["x_norm"], m["y_norm"], m["z_norm"])))
+        f.write("".join("vt %.9g %.9g\n" % t for t in zip(m["x_tex"], m["y_tex"])))
+        P = np.stack([m["point_1_idx"], m["point_2_idx"], m["point_3_idx"]], 1) + 1
+        T = np.stack([m["tex_1_idx"], m["tex_2_idx"], m["tex_3_idx"]], 1) + 1
+        N = np.stack([m["norm_1_idx"], m["norm_2_idx"], m["norm_3_idx"]], 1) + 1
+        mat = m["material_idx"]
+        lines, cur = [], None
+        for i in range(P.shape[0]):
+            if mat[i] != cur:
+                cur = mat[i]
+                lines.append(f"usemtl {names[cur]}\n")
+            lines.append("f %d/%d/%d %d/%d/%d %d/%d/%d\n" % (
+                P[i, 0], T[i, 0], N[i, 0], P[i, 1], T[i, 1], N[i, 1], P[i, 2], T[i, 2], N[i, 2]))
+        f.write("".join(lines))
+    c, p = sc.camera, sc.params
+    kv = [("input_folder_path", folder), ("obj_filename", prefix + ".obj"),
+          ("texture_bg_path", f"{prefix}_bg.img"), ("image_width", c["width"]),
+          ("image_height", c["height"]), ("render_mode", p["render_mode"]),
+          ("pathtracing_sample_size", p["pathtracing_sample_size"]),
+          ("pathtracing_level", p["pathtracing_level"]),
+          ("eye_x", g9(c["eye"][0])), ("eye_y", g9(c["eye"][1])), ("eye_z", g9(c["eye"][2])),
+          ("center_x", g9(c["center"][0])), ("center_y", g9(c["center"][1])),
+          ("center_z", g9(c["center"][2])), ("up_x", g9(c["up"][0])), ("up_y", g9(c["up"][1])),
+          ("up_z", g9(c["up"][2])), ("fovy", g9(c["fovy"])), ("aperture", g9(c["aperture"])),
+          ("dof_sample_size", p["dof_sample_size"]), ("focus_dist", g9(c["focus_dist"])),
+          ("sky_emission_r", g9(p["sky_emission"][0])), ("sky_emission_g", g9(p["sky_emission"][1])),
+          ("sky_emission_b", g9(p["sky_emission"][2])),
+          ("sss_pts_per_object", max(1, p["sss_pts_per_object"])),
+          ("hittable_pdf_weight", g9(p["hittable_pdf_weight"])),
+          ("ppm_num_photon_per_pass", p["ppm_num_photon_per_pass"]),
+          ("ppm_num_pass", p["ppm_num_pass"]), ("ppm_max_bounce", p["ppm_max_bounce"]),
+          ("ppm_alpha", g9(p["ppm_alpha"])),
+          ("ppm_radius_scaling_factor", g9(p["ppm_radius_scaling_factor"])),
+          ("ppm_image_output_iteration", 1000000)]
+    master = folder + prefix + "_master.txt"
+    with open(master, "w") as f:
+        for k, v in kv:
+            f.write(f"{k}\t{v}\n")
+    return master
