@@ -18,7 +18,7 @@ from . import cabi
 from .scene import Scene
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libgpt.so")
+LIB_PATH = os.environ.get("GPT_LIB", os.path.join(_HERE, "csrc", "libgpt.so"))
 
 # every symbol include/gpt.h declares
 SYMBOLS = """gpt_create gpt_destroy gpt_last_error gpt_version gpt_set_stream gpt_set_mesh

@@ -12,6 +12,7 @@
 
 #include "lighttree.cuh"
 #include "render_state.cuh"
+#include "trace_persistent.cuh"
 
 namespace {
 
@@ -173,23 +174,30 @@ k_pt_start(PathState ps, RenderParams p, int n, float *fb) {
   fb[3 * (size_t)pix] = 0.f; fb[3 * (size_t)pix + 1] = 0.f; fb[3 * (size_t)pix + 2] = 0.f;
 }
 
+// trace stage: persistent warps pull active slots from the queue (trace_persistent.cuh)
+struct QueueSource {
+  PathState ps;
+  const int *queue;
+  const int *qcount;
+  __device__ int count() const { return *qcount; }
+  __device__ void load(int i, float4 &o, float4 &d) const {
+    int s = queue[i];
+    o = ps.rays[2 * (size_t)s];
+    d = ps.rays[2 * (size_t)s + 1];
+  }
+  __device__ void store(int i, const TraceLane &l) const {
+    int s = queue[i];
+    ps.hits[2 * (size_t)s] = make_float4(l.t, __int_as_float(l.leaf), __int_as_float(l.prim), 0.f);
+    ps.hits[2 * (size_t)s + 1] = make_float4(l.b1, l.b2, l.b3, 0.f);
+  }
+};
+
 template <bool COUNT>
-__global__ void __launch_bounds__(PT_BLOCK)
-k_pt_trace(PathState ps, const int *__restrict__ queue, const int *__restrict__ count,
-           const float4 *__restrict__ nodes, const float4 *__restrict__ tris,
-           const int *__restrict__ parent_leaf, unsigned long long *counters) {
-  __shared__ int stack[TRACE_STACK * PT_BLOCK];
-  int a = blockIdx.x * blockDim.x + threadIdx.x;
-  if (a >= *count) return;
-  int s = queue[a];
-  float4 ro = ps.rays[2 * (size_t)s], rd = ps.rays[2 * (size_t)s + 1];
-  RaySetup r = make_ray(ro.x, ro.y, ro.z, rd.x, rd.y, rd.z);
-  int overflow = 0;
-  HitResult h = trace_ray<COUNT>(nodes, tris, parent_leaf, r, ro.w, stack + threadIdx.x, PT_BLOCK,
-                                 counters, counters + 1, &overflow);
-  if (overflow) atomicExch(counters + 3, 1ull);
-  ps.hits[2 * (size_t)s] = make_float4(h.t, __int_as_float(h.leaf), __int_as_float(h.prim), 0.f);
-  ps.hits[2 * (size_t)s + 1] = make_float4(h.b1, h.b2, h.b3, 0.f);
+__global__ void __launch_bounds__(TP_BLOCK)
+k_pt_trace(QueueSource src, const float4 *__restrict__ nodes, const float4 *__restrict__ tris,
+           const int *__restrict__ parent_leaf, int *next_ray, unsigned long long *counters) {
+  __shared__ int stack[TP_STACK_SMEM * TP_BLOCK];
+  trace_persistent<COUNT>(nodes, tris, parent_leaf, src, next_ray, stack, counters);
 }
 
 // change_ref_ray + _recompute_pdf (material_operations.h:26-153)
@@ -499,6 +507,14 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks) {
   k_pt_start<<<(n + PT_BLOCK - 1) / PT_BLOCK, PT_BLOCK, 0, st>>>(ps, p, n, d_fb);
   GPT_LAUNCH_CHECK(ctx);
   int active = n, cur = 0;
+  int *next_ray = reinterpret_cast<int *>(ctx->d_counters + 4);
+  static int trace_grid = 0;
+  if (!trace_grid) {
+    int sms = 148, per_sm = 4;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pt_trace<false>, TP_BLOCK, 0);
+    trace_grid = sms * (per_sm > 0 ? per_sm : 1);
+  }
   uint64_t rays = 0, shades = 0, trace_launches = 0;
   const bool timing = ctx->prof_time_stages, counting = ctx->prof_count_visits;
   size_t nev = 0;
@@ -517,13 +533,18 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks) {
   for (long long it = 0; active > 0 && it < max_iters; it++) {
     int grid = (active + PT_BLOCK - 1) / PT_BLOCK;
     GPT_CUDA(ctx, cudaMemsetAsync(ps.counts + (cur ^ 1), 0, sizeof(int), st));
+    GPT_CUDA(ctx, cudaMemsetAsync(next_ray, 0, sizeof(int), st));
     GPT_CUDA(ctx, stamp());
-    if (counting)
-      k_pt_trace<true><<<grid, PT_BLOCK, 0, st>>>(ps, ps.queue[cur], ps.counts + cur, mb.nodes,
-                                                 mb.tris, mb.parent_leaf, ctx->d_counters);
-    else
-      k_pt_trace<false><<<grid, PT_BLOCK, 0, st>>>(ps, ps.queue[cur], ps.counts + cur, mb.nodes,
-                                                  mb.tris, mb.parent_leaf, ctx->d_counters);
+    {
+      QueueSource qs{ps, ps.queue[cur], ps.counts + cur};
+      int tgrid = grid < trace_grid ? grid : trace_grid;
+      if (counting)
+        k_pt_trace<true><<<tgrid, TP_BLOCK, 0, st>>>(qs, mb.nodes, mb.tris, mb.parent_leaf, next_ray,
+                                                    ctx->d_counters);
+      else
+        k_pt_trace<false><<<tgrid, TP_BLOCK, 0, st>>>(qs, mb.nodes, mb.tris, mb.parent_leaf, next_ray,
+                                                     ctx->d_counters);
+    }
     GPT_LAUNCH_CHECK(ctx);
     trace_launches++;
     GPT_CUDA(ctx, stamp());

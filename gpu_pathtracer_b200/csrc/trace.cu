@@ -4,33 +4,46 @@
 // [level][thread] (bank-conflict free), nodes / triangles fetched as 16-byte words through
 // the read-only path.  Rays: 2 x float4 {ox,oy,oz,tmax}{dx,dy,dz,-}; hits: 2 x float4
 // {t, leaf, prim, -}{b1, b2, b3, -}.
-#include "trace_core.cuh"
+#include "trace_persistent.cuh"
 
 namespace {
 
-constexpr int TRACE_BLOCK = 128;
+template <bool NORMALIZE>
+struct ArraySource {
+  const float4 *rays;
+  float4 *hits;
+  int n;
+  __device__ int count() const { return n; }
+  __device__ void load(int i, float4 &o, float4 &d) const {
+    o = __ldg(rays + 2 * (size_t)i);
+    d = __ldg(rays + 2 * (size_t)i + 1);
+    if (NORMALIZE) {  // Ray::Ray -> unit_vector(dir) = dir / dir.length()  (ray.h:21-24)
+      float len = sqrtf(d.x * d.x + d.y * d.y + d.z * d.z);
+      d.x = d.x / len; d.y = d.y / len; d.z = d.z / len;
+    }
+  }
+  __device__ void store(int i, const TraceLane &l) const {
+    hits[2 * (size_t)i] = make_float4(l.t, __int_as_float(l.leaf), __int_as_float(l.prim), 0.f);
+    hits[2 * (size_t)i + 1] = make_float4(l.b1, l.b2, l.b3, 0.f);
+  }
+};
 
 template <bool NORMALIZE, bool COUNT>
-__global__ void __launch_bounds__(TRACE_BLOCK)
+__global__ void __launch_bounds__(TP_BLOCK)
 k_trace(const float4 *__restrict__ nodes, const float4 *__restrict__ tris,
-        const int *__restrict__ parent_leaf, const float4 *__restrict__ rays, float4 *hits,
-        long long n, unsigned long long *counters) {
-  __shared__ int stack[TRACE_STACK * TRACE_BLOCK];
-  long long i = (long long)blockIdx.x * TRACE_BLOCK + threadIdx.x;
-  if (i >= n) return;
-  float4 ro = __ldg(rays + 2 * i), rd = __ldg(rays + 2 * i + 1);
-  float dx = rd.x, dy = rd.y, dz = rd.z;
-  if (NORMALIZE) {  // Ray::Ray -> unit_vector(dir) = dir / dir.length()  (ray.h:21-24)
-    float len = sqrtf(dx * dx + dy * dy + dz * dz);
-    dx = dx / len; dy = dy / len; dz = dz / len;
-  }
-  RaySetup r = make_ray(ro.x, ro.y, ro.z, dx, dy, dz);
-  int overflow = 0;
-  HitResult h = trace_ray<COUNT>(nodes, tris, parent_leaf, r, ro.w, stack + threadIdx.x,
-                                 TRACE_BLOCK, counters, counters + 1, &overflow);
-  if (overflow) atomicExch(counters + 3, 1ull);
-  hits[2 * i] = make_float4(h.t, __int_as_float(h.leaf), __int_as_float(h.prim), 0.f);
-  hits[2 * i + 1] = make_float4(h.b1, h.b2, h.b3, 0.f);
+        const int *__restrict__ parent_leaf, ArraySource<NORMALIZE> src, int *next_ray,
+        unsigned long long *counters) {
+  __shared__ int stack[TP_STACK_SMEM * TP_BLOCK];
+  trace_persistent<COUNT>(nodes, tris, parent_leaf, src, next_ray, stack, counters);
+}
+
+template <class K>
+int persistent_grid(K kernel) {
+  int dev = 0, sms = 148, per_sm = 4;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, TP_BLOCK, 0);
+  return sms * (per_sm > 0 ? per_sm : 1);
 }
 
 }  // namespace
@@ -41,16 +54,23 @@ int gpt_trace_launch(gpt_ctx *ctx, int which, const float4 *d_rays, int64_t n, f
   BvhDev &b = ctx->bvh[which];
   if (b.n < 2) return gpt_fail(ctx, GPT_E_INVALID, "BVH not built (needs >= 2 leaves)", __FILE__, __LINE__);
   if (n <= 0) return GPT_OK;
-  unsigned grid = (unsigned)((n + TRACE_BLOCK - 1) / TRACE_BLOCK);
+  if (n > 0x7fffffff) return gpt_fail(ctx, GPT_E_INVALID, "more than 2^31 rays in one call", __FILE__, __LINE__);
   unsigned long long *c = ctx->d_counters;
+  int *next_ray = reinterpret_cast<int *>(c + 4);
   if (count) GPT_CUDA(ctx, cudaMemsetAsync(c, 0, 3 * sizeof(unsigned long long), ctx->stream));
-  if (normalize) {
-    if (count) k_trace<true, true><<<grid, TRACE_BLOCK, 0, ctx->stream>>>(b.nodes, b.tris, b.parent_leaf, d_rays, d_hits, n, c);
-    else k_trace<true, false><<<grid, TRACE_BLOCK, 0, ctx->stream>>>(b.nodes, b.tris, b.parent_leaf, d_rays, d_hits, n, c);
-  } else {
-    if (count) k_trace<false, true><<<grid, TRACE_BLOCK, 0, ctx->stream>>>(b.nodes, b.tris, b.parent_leaf, d_rays, d_hits, n, c);
-    else k_trace<false, false><<<grid, TRACE_BLOCK, 0, ctx->stream>>>(b.nodes, b.tris, b.parent_leaf, d_rays, d_hits, n, c);
-  }
+  GPT_CUDA(ctx, cudaMemsetAsync(next_ray, 0, sizeof(int), ctx->stream));
+  cudaStream_t st = ctx->stream;
+#define GPT_TRACE_LAUNCH(NORM, CNT)                                                        \
+  do {                                                                                     \
+    static int grid = persistent_grid(k_trace<NORM, CNT>);                                 \
+    long long need = (n + TP_BLOCK - 1) / TP_BLOCK;                                        \
+    ArraySource<NORM> src{d_rays, d_hits, (int)n};                                         \
+    k_trace<NORM, CNT><<<(unsigned)(need < grid ? need : grid), TP_BLOCK, 0, st>>>(        \
+        b.nodes, b.tris, b.parent_leaf, src, next_ray, c);                                 \
+  } while (0)
+  if (normalize) { if (count) GPT_TRACE_LAUNCH(true, true); else GPT_TRACE_LAUNCH(true, false); }
+  else { if (count) GPT_TRACE_LAUNCH(false, true); else GPT_TRACE_LAUNCH(false, false); }
+#undef GPT_TRACE_LAUNCH
   GPT_LAUNCH_CHECK(ctx);
   return GPT_OK;
 }
