@@ -60,7 +60,7 @@ struct RefRec {  // reflection_record (material.h:116-123)
 };
 
 // Returns with `ref` filled; `sss` as the reference sets it.
-__device__ __forceinline__ void check_next_path(const MaterialDev *mats, const TexAtlas &atlas,
+static __device__ __noinline__ void check_next_path(const MaterialDev *mats, const TexAtlas &atlas,
                                                 int mat_id, V3 v_in, V3 normal, float u, float v,
                                                 const MatList &list, RefRec &ref, bool &sss,
                                                 Rng &rng, bool force_refract) {

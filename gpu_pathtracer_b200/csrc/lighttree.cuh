@@ -33,7 +33,7 @@ __device__ __forceinline__ TriShade load_tri_shade(const float4 *__restrict__ sh
 }
 
 // Triangle::_get_normal (triangle.h:410-441): interpolated, bump-perturbed shading normal.
-__device__ __forceinline__ V3 shading_normal(const TriShade &t, const MaterialDev &m,
+static __device__ __noinline__ V3 shading_normal(const TriShade &t, const MaterialDev &m,
                                              const TexAtlas &atlas, float w1, float w2,
                                              float w3) {
   V3 nn = unit(w1 * t.n1 + w2 * t.n2 + w3 * t.n3);
@@ -59,7 +59,7 @@ struct LightTree {
   int n;
 };
 
-__device__ __forceinline__ float light_importance(const LightTree &lt, int ref, V3 point,
+static __device__ __noinline__ float light_importance(const LightTree &lt, int ref, V3 point,
                                                   V3 pivot) {
   if (ref >= 0) {
     float4 ni = __ldg(lt.node_info + ref);
@@ -111,7 +111,7 @@ __device__ __forceinline__ float light_node_pdf(const LightTree &lt, int leaf, V
 
 // Triangle::get_random_point_on_surface (triangle.h:199-224): consumes 4 uniforms, only the
 // point is used by the caller.
-__device__ __forceinline__ V3 light_sample_point(const LightTree &lt, int leaf, Rng &rng) {
+static __device__ __noinline__ V3 light_sample_point(const LightTree &lt, int leaf, Rng &rng) {
   const float4 *tp = lt.tris + 3 * (size_t)leaf;
   float4 t0 = __ldg(tp), t1 = __ldg(tp + 1), t2 = __ldg(tp + 2);
   float r1 = rng_uniform(rng), r2 = rng_uniform(rng);
@@ -125,7 +125,7 @@ __device__ __forceinline__ V3 light_sample_point(const LightTree &lt, int leaf, 
 }
 
 // Triangle::get_hittable_pdf (triangle.h:95-110) for light leaf `leaf`
-__device__ __forceinline__ float light_hittable_pdf(const LightTree &lt, const float4 *shade,
+static __device__ __noinline__ float light_hittable_pdf(const LightTree &lt, const float4 *shade,
                                                     const MaterialDev *mats,
                                                     const TexAtlas &atlas, int leaf, V3 origin,
                                                     V3 dir) {

@@ -12,7 +12,7 @@ struct TexAtlas {
   const float *r, *g, *b;
 };
 
-__device__ __forceinline__ V3 tex_fetch(const TexAtlas &a, const MaterialDev &m, int which,
+static __device__ __noinline__ V3 tex_fetch(const TexAtlas &a, const MaterialDev &m, int which,
                                         float u, float v, V3 filter) {
   int w = m.tex_w[which], h = m.tex_h[which];
   int iu = (int)floorf((u - floorf(u)) * (float)(w - 1));

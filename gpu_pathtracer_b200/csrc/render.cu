@@ -27,6 +27,8 @@ struct RenderCtx {
   uint32_t *rng_init = nullptr;   // cached curand_init states for (width, height, rank set)
   int rng_w = 0, rng_h = 0, rng_rank = -1, rng_nranks = 0;
   int *h_counts = nullptr;        // pinned
+  uint32_t *sort_key = nullptr, *sort_key_alt = nullptr, *sort_hist = nullptr;
+  int *sort_val = nullptr, *sort_val_alt = nullptr;
   float *d_fb = nullptr;          // internal framebuffer for the host API
   size_t fb_capacity = 0;
   std::vector<cudaEvent_t> events;  // profiling only
@@ -179,6 +181,9 @@ struct QueueSource {
   PathState ps;
   const int *queue;
   const int *qcount;
+  const float4 *shade;   // per-triangle shading records (material id in s6.y)
+  uint32_t *sort_key;    // out: shade-coherence key of queue entry i (material, 127 = miss)
+  int *sort_val;         // out: its slot
   __device__ int count() const { return *qcount; }
   __device__ void load(int i, float4 &o, float4 &d) const {
     int s = queue[i];
@@ -189,6 +194,13 @@ struct QueueSource {
     int s = queue[i];
     ps.hits[2 * (size_t)s] = make_float4(l.t, __int_as_float(l.leaf), __int_as_float(l.prim), 0.f);
     ps.hits[2 * (size_t)s + 1] = make_float4(l.b1, l.b2, l.b3, 0.f);
+    // Key for the material sort that precedes shade: paths that will run the same BSDF code
+    // become neighbours, which is what keeps warps converged (and the instruction cache warm)
+    // in k_pt_shade.
+    uint32_t key = 127u;
+    if (l.leaf >= 0) key = (uint32_t)__float_as_int(__ldg(&shade[7 * (size_t)l.prim + 6].y)) & 127u;
+    sort_key[i] = key;
+    sort_val[i] = s;
   }
 };
 
@@ -419,6 +431,11 @@ static int reserve_paths(gpt_ctx *ctx, RenderCtx *rc, int n) {
   GPT_TRY(gpt_alloc(ctx, &ps.queue[0], N));
   GPT_TRY(gpt_alloc(ctx, &ps.queue[1], N));
   GPT_TRY(gpt_alloc(ctx, &ps.counts, (size_t)4));
+  GPT_TRY(gpt_alloc(ctx, &rc->sort_key, N));
+  GPT_TRY(gpt_alloc(ctx, &rc->sort_key_alt, N));
+  GPT_TRY(gpt_alloc(ctx, &rc->sort_val, N));
+  GPT_TRY(gpt_alloc(ctx, &rc->sort_val_alt, N));
+  GPT_TRY(gpt_alloc(ctx, &rc->sort_hist, (size_t)gpt_radix_hist_entries(n)));
   if (!rc->h_counts) GPT_CUDA(ctx, cudaMallocHost((void **)&rc->h_counts, 4 * sizeof(int)));
   ps.capacity = n;
   rc->rng_w = rc->rng_h = 0;  // cached states are gone
@@ -536,7 +553,7 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks) {
     GPT_CUDA(ctx, cudaMemsetAsync(next_ray, 0, sizeof(int), st));
     GPT_CUDA(ctx, stamp());
     {
-      QueueSource qs{ps, ps.queue[cur], ps.counts + cur};
+      QueueSource qs{ps, ps.queue[cur], ps.counts + cur, ctx->scene.shade, rc->sort_key, rc->sort_val};
       int tgrid = grid < trace_grid ? grid : trace_grid;
       if (counting)
         k_pt_trace<true><<<tgrid, TP_BLOCK, 0, st>>>(qs, mb.nodes, mb.tris, mb.parent_leaf, next_ray,
@@ -548,7 +565,12 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks) {
     GPT_LAUNCH_CHECK(ctx);
     trace_launches++;
     GPT_CUDA(ctx, stamp());
-    k_pt_shade<<<grid, PT_BLOCK, 0, st>>>(ps, p, ps.queue[cur], ps.counts + cur, ps.queue[cur ^ 1],
+    // stable 7-bit radix sort of the active slots by material (ties keep tile order)
+    uint32_t *sk = nullptr;
+    int *sorted_slots = nullptr;
+    GPT_TRY(gpt_radix_sort_pairs(ctx, rc->sort_key, rc->sort_val, rc->sort_key_alt, rc->sort_val_alt,
+                                 rc->sort_hist, active, 7, &sk, &sorted_slots));
+    k_pt_shade<<<grid, PT_BLOCK, 0, st>>>(ps, p, sorted_slots, ps.counts + cur, ps.queue[cur ^ 1],
                                          ps.counts + (cur ^ 1), ctx->scene, atlas, mb.tris, lt,
                                          d_fb, ps.counts + 2);
     GPT_LAUNCH_CHECK(ctx);
@@ -601,7 +623,8 @@ void gpt_render_free(gpt_ctx *ctx) {
   PathState &ps = rc->ps;
   void *p[] = {ps.pixel, ps.rng, ps.rays, ps.hits, ps.mask, ps.acc, ps.color, ps.cam_o, ps.cam_d,
                ps.matlist, ps.queue[0], ps.queue[1], ps.counts, rc->leaf_info, rc->node_info,
-               rc->node_energy, rc->lt_flags, rc->rng_init, rc->d_fb};
+               rc->node_energy, rc->lt_flags, rc->rng_init, rc->d_fb, rc->sort_key,
+               rc->sort_key_alt, rc->sort_hist, rc->sort_val, rc->sort_val_alt};
   for (void *q : p) cudaFree(q);
   if (rc->h_counts) cudaFreeHost(rc->h_counts);
   for (cudaEvent_t e : rc->events) cudaEventDestroy(e);

@@ -83,7 +83,7 @@ __device__ __forceinline__ V3 sample_hemisphere_cos(Rng &rng) {
   float y = sinf(phi) * sqrtf(r2);
   return make_unit(V3{x, y, z});
 }
-__device__ __forceinline__ V3 sample_phong(float n, Rng &rng) {
+static __device__ __noinline__ V3 sample_phong(float n, Rng &rng) {
   if (ns_too_large(n)) return V3{0.f, 0.f, 1.f};  // no draws
   float r1 = rng_uniform(rng), r2 = rng_uniform(rng);
   float e2 = (float)(2.0 / (double)(n + 1.f)), e1 = (float)(1.0 / (double)(n + 1.f));
@@ -111,7 +111,7 @@ __device__ __forceinline__ V3 sample_disk(Rng &rng) {
 }
 
 // generate_ray (ray_operations.h:16-35) + Ray::Ray normalisation; returns the direction
-__device__ __forceinline__ V3 generate_dir(V3 main_dir, V3 normal, int mode, float n, Rng &rng) {
+static __device__ __noinline__ V3 generate_dir(V3 main_dir, V3 normal, int mode, float n, Rng &rng) {
   Frame f;
   V3 v;
   if (mode == 0) { f = frame_from_z(normal); v = sample_hemisphere_cos(rng); }
@@ -121,7 +121,7 @@ __device__ __forceinline__ V3 generate_dir(V3 main_dir, V3 normal, int mode, flo
 }
 
 // ---- Phong filters, Schlick, reflect (vector_util.h:207-246) -----------------------------
-__device__ __forceinline__ V3 phong_filter(V3 k, float n, V3 ideal, V3 dir) {
+static __device__ __noinline__ V3 phong_filter(V3 k, float n, V3 ideal, V3 dir) {
   if (ns_too_large(n)) return ((k * GPT_MAX_PHONG_N_S) * V3{1.f, 1.f, 1.f}) / 2.f;
   return ((k * (n + 2.f)) * powf(fmaxf(0.f, dot(ideal, dir)), n)) / 2.f;
 }
@@ -129,7 +129,7 @@ __device__ __forceinline__ V3 phong_filter_2(V3 k, float n, V3 ideal, V3 dir) {
   if (ns_too_large(n)) return k;
   return k * powf(fmaxf(0.f, dot(ideal, dir)), n);
 }
-__device__ __forceinline__ float schlick(float cos_theta, float n1, float n2) {
+static __device__ __noinline__ float schlick(float cos_theta, float n1, float n2) {
   float r0 = powf((n1 - n2) / (n1 + n2), 2.f);
   return r0 + (1.f - r0) * powf(1.f - cos_theta, 5.f);
 }
@@ -148,7 +148,7 @@ __device__ __forceinline__ float diffuse_sampling_pdf(V3 normal, V3 dir) {
   return fmaxf(0.f, (float)((double)dot(normal, dir) / GPT_PI));
 }
 // compute_specular_sampling_pdf (the (n+1)-weighted variant used by _recompute_pdf)
-__device__ __forceinline__ float specular_sampling_pdf(V3 in, V3 out, V3 normal, V3 perfect,
+static __device__ __noinline__ float specular_sampling_pdf(V3 in, V3 out, V3 normal, V3 perfect,
                                                        float n, bool refracted) {
   float d1 = dot(in, normal), d2 = dot(normal, out);
   bool side = refracted ? ((d1 >= 0 && d2 >= 0) || (d1 <= 0 && d2 <= 0))
