@@ -25,7 +25,9 @@ SYMBOLS = """gpt_create gpt_destroy gpt_last_error gpt_version gpt_set_stream gp
 gpt_set_materials gpt_set_textures gpt_set_background gpt_set_camera gpt_set_params gpt_build
 gpt_rebuild_main_bvh gpt_export_triangles gpt_bvh_num_leaves gpt_export_bvh gpt_trace
 gpt_trace_device gpt_trace_count_device gpt_render_pathtrace gpt_render_pathtrace_device
-gpt_sppm_init gpt_sppm_pass gpt_sppm_flux_device gpt_sppm_update gpt_sppm_resolve gpt_stats
+gpt_sppm_init gpt_sppm_pass gpt_sppm_flux_device gpt_sppm_update gpt_sppm_resolve
+gpt_sppm_stats gpt_sppm_export_hit_points gpt_sppm_export_photons gpt_sppm_import_photons
+gpt_sppm_pass_stages gpt_sppm_import_hit_points gpt_stats
 gpt_synchronize gpt_set_profiling""".split()
 
 
@@ -181,3 +183,89 @@ class PathTracer:
     def render_pathtrace_device(self, d_out: int, rank: int = 0, nranks: int = 1):
         self._check(self.lib.gpt_render_pathtrace_device(self.ctx, C.c_void_p(d_out),
                                                          C.c_int(rank), C.c_int(nranks)))
+
+    # -- SPPM (render_mode 2, src/main.cu:1282-1870) ---------------------------------------
+    def sppm_init(self):
+        self._check(self.lib.gpt_sppm_init(self.ctx))
+
+    def sppm_pass(self, pass_idx: int, photon_begin: int | None = None,
+                  photon_end: int | None = None):
+        if photon_begin is None:
+            photon_begin, photon_end = 0, int(self.scene.params["ppm_num_photon_per_pass"])
+        self._check(self.lib.gpt_sppm_pass(self.ctx, C.c_int(pass_idx), C.c_int64(photon_begin),
+                                           C.c_int64(photon_end)))
+
+    def sppm_flux_device(self):
+        """(device pointer, float count) of the per-pass accumulator buffer to all-reduce."""
+        p, n = C.c_void_p(), C.c_int64()
+        self._check(self.lib.gpt_sppm_flux_device(self.ctx, C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+    def sppm_update(self, pass_idx: int):
+        self._check(self.lib.gpt_sppm_update(self.ctx, C.c_int(pass_idx)))
+
+    def sppm_resolve(self, mode: int = 0, passes: int | None = None) -> np.ndarray:
+        cam = self.scene.camera
+        passes = passes or int(self.scene.params["ppm_num_pass"])
+        out = np.zeros((cam["height"], cam["width"], 3), np.float32)
+        self._check(self.lib.gpt_sppm_resolve(self.ctx, C.c_int(mode), C.c_int(passes),
+                                              cabi.fptr(out)))
+        return out
+
+    def sppm_stats(self) -> dict:
+        ns, nv, r, rays = C.c_int64(), C.c_int64(), C.c_double(), C.c_uint64()
+        self._check(self.lib.gpt_sppm_stats(self.ctx, C.byref(ns), C.byref(nv), C.byref(r),
+                                            C.byref(rays)))
+        return dict(n_surface=ns.value, n_volume=nv.value, mean_radius=r.value,
+                    rays_total=rays.value)
+
+    def sppm_export_hit_points(self) -> dict:
+        P = self.scene.camera["height"] * self.scene.camera["width"]
+        out = {k: np.zeros((P, 4), np.float32)
+               for k in ("loc_radius", "normal_vradius", "filter", "direct", "indirect")}
+        out["flux_lm"] = np.zeros((2 * P, 4), np.float32)
+        self._check(self.lib.gpt_sppm_export_hit_points(
+            self.ctx, *[cabi.fptr(out[k]) for k in ("loc_radius", "normal_vradius", "filter",
+                                                    "direct", "indirect", "flux_lm")]))
+        out["flux"], out["lm"] = out["flux_lm"][:P], out["flux_lm"][P:]
+        return out
+
+    def sppm_export_photons(self) -> dict:
+        n = C.c_int64()
+        self._check(self.lib.gpt_sppm_export_photons(self.ctx, None, None, C.c_int64(0),
+                                                     C.byref(n)))
+        kind = np.zeros(n.value, np.int32)
+        rec = np.zeros((n.value, 12), np.float32)
+        self._check(self.lib.gpt_sppm_export_photons(self.ctx, cabi.iptr(kind), cabi.fptr(rec),
+                                                     C.c_int64(n.value), C.byref(n)))
+        return dict(kind=kind, loc=rec[:, 0:3], prev=rec[:, 3:6], dir=rec[:, 6:9],
+                    color=rec[:, 9:12], rec=rec)
+
+    def sppm_import_photons(self, kind: np.ndarray, rec12: np.ndarray):
+        rec12 = np.ascontiguousarray(rec12, dtype=np.float32).reshape(-1, 12)
+        kind = np.ascontiguousarray(kind, dtype=np.int32)
+        self._check(self.lib.gpt_sppm_import_photons(self.ctx, cabi.iptr(kind), cabi.fptr(rec12),
+                                                     C.c_int64(rec12.shape[0])))
+
+    def sppm_pass_stages(self, pass_idx: int, stages: int, photon_begin: int | None = None,
+                         photon_end: int | None = None):
+        if photon_begin is None:
+            photon_begin, photon_end = 0, int(self.scene.params["ppm_num_photon_per_pass"])
+        self._check(self.lib.gpt_sppm_pass_stages(self.ctx, C.c_int(pass_idx),
+                                                  C.c_int64(photon_begin), C.c_int64(photon_end),
+                                                  C.c_int(stages)))
+
+    def sppm_import_hit_points(self, loc_radius=None, normal_vradius=None, filter=None):
+        arrs = [None if a is None else np.ascontiguousarray(a, dtype=np.float32)
+                for a in (loc_radius, normal_vradius, filter)]
+        self._check(self.lib.gpt_sppm_import_hit_points(
+            self.ctx, *[None if a is None else cabi.fptr(a) for a in arrs]))
+
+    def render_sppm(self, passes: int | None = None, mode: int = 0) -> np.ndarray:
+        """The whole render_mode 2 frame on one GPU."""
+        passes = passes or int(self.scene.params["ppm_num_pass"])
+        self.sppm_init()
+        for p in range(passes):
+            self.sppm_pass(p)
+            self.sppm_update(p)
+        return self.sppm_resolve(mode, passes)

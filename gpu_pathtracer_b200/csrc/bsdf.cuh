@@ -54,12 +54,15 @@ __device__ __forceinline__ void matlist_top2(const MaterialDev *mats, const MatL
 struct RefRec {  // reflection_record (material.h:116-123)
   V3 dir;        // ref.ray.dir (origin is the hit point)
   V3 k, filter, perfect;
+  V3 filter2;    // ref.filter_2 (compute_phong_filter_2): only filled by check_next_path<true>
   float n;
   bool diffuse, reflected, refracted, false_hit, entering, bent;
   int next_material;
 };
 
-// Returns with `ref` filled; `sss` as the reference sets it.
+// Returns with `ref` filled; `sss` as the reference sets it.  F2 = also fill ref.filter2 (the
+// SPPM passes use it, the path tracer does not).
+template <bool F2>
 static __device__ __noinline__ void check_next_path(const MaterialDev *mats, const TexAtlas &atlas,
                                                 int mat_id, V3 v_in, V3 normal, float u, float v,
                                                 const MatList &list, RefRec &ref, bool &sss,
@@ -75,6 +78,7 @@ static __device__ __noinline__ void check_next_path(const MaterialDev *mats, con
     ref.refracted = true;
     ref.dir = unit(v_in);
     ref.filter = V3{1.f, 1.f, 1.f};
+    if (F2) ref.filter2 = V3{1.f, 1.f, 1.f};
     ref.diffuse = false;
     ref.bent = false;
     ref.entering = dot(v_in, normal) <= 0.f;
@@ -147,12 +151,14 @@ static __device__ __noinline__ void check_next_path(const MaterialDev *mats, con
     ref.dir = generate_dir(v_out, normal, 1, ns, rng);
     ref.k = k;
     ref.filter = phong_filter(k, ns, v_out, ref.dir);
+    if (F2) ref.filter2 = phong_filter_2(k, ns, v_out, ref.dir);
     if (ref.next_material != MAT_AIR && ref.next_material != mat_id) {
       const MaterialDev &nm = mats[ref.next_material];
       V3 k2 = V3{nm.tf[0], nm.tf[1], nm.tf[2]} * nm.t_r;
       float ns2 = mat_ns(atlas, nm, u, v);
       ref.k = ref.k * k2;
       ref.filter = ref.filter * phong_filter(k2, ns2, v_out, ref.dir);
+      if (F2) ref.filter2 = ref.filter2 * phong_filter_2(k2, ns2, v_out, ref.dir);
     }
     return;
   }
@@ -165,6 +171,7 @@ static __device__ __noinline__ void check_next_path(const MaterialDev *mats, con
   if (rn > factor) {
     ref.dir = generate_dir(V3{0.f, 0.f, 0.f}, normal, 0, 1.f, rng);
     ref.filter = mat_diffuse(atlas, m, u, v);
+    if (F2) ref.filter2 = ref.filter;
     ref.diffuse = true; ref.reflected = false; ref.refracted = false;
     ref.k = ref.filter;
     ref.next_material = hi;
@@ -176,6 +183,7 @@ static __device__ __noinline__ void check_next_path(const MaterialDev *mats, con
   ref.dir = generate_dir(rdir, normal, 1, ns, rng);
   V3 k = mat_specular(atlas, m, u, v);
   ref.filter = phong_filter(k, ns, rdir, ref.dir);
+  if (F2) ref.filter2 = phong_filter_2(k, ns, rdir, ref.dir);
   ref.diffuse = false; ref.reflected = true; ref.refracted = false;
   ref.perfect = rdir;
   ref.n = ns;

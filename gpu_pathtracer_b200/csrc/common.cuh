@@ -167,6 +167,8 @@ int gpt_lbvh_export(gpt_ctx *ctx, int which, uint32_t *morton, int32_t *sorted_t
                     int32_t *left, int32_t *right, int32_t *parent_internal,
                     int32_t *parent_leaf, float *node_aabb, float *leaf_aabb,
                     float *world_aabb);
+int gpt_lbvh_build_boxes(gpt_ctx *ctx, BvhDev &b, const float *d_aabb, const int *d_prim_list,
+                         int n, bool with_tris);                      // lbvh.cu
 void gpt_lbvh_free(BvhDev &b);
 int gpt_collect_subset(gpt_ctx *ctx, int flag_mask, int **d_list, int *count);  // lbvh.cu
 int gpt_trace_launch(gpt_ctx *ctx, int which, const float4 *d_rays, int64_t n,

@@ -372,15 +372,16 @@ void gpt_lbvh_free(BvhDev &b) {
   b = BvhDev();
 }
 
-static int lbvh_reserve(gpt_ctx *ctx, BvhDev &b, int n) {
-  if (n <= b.capacity) return GPT_OK;
+static int lbvh_reserve(gpt_ctx *ctx, BvhDev &b, int n, bool with_tris) {
+  if (n <= b.capacity && (!with_tris || b.tris)) return GPT_OK;
+  if (n < b.capacity) n = b.capacity;
   int *keep = b.prim_list;
   b.prim_list = nullptr;
   gpt_lbvh_free(b);
   b.prim_list = keep;
   size_t N = (size_t)n;
   GPT_TRY(gpt_alloc(ctx, &b.nodes, 4 * N));
-  GPT_TRY(gpt_alloc(ctx, &b.tris, 3 * N));
+  if (with_tris) GPT_TRY(gpt_alloc(ctx, &b.tris, 3 * N));
   GPT_TRY(gpt_alloc(ctx, &b.parent_leaf, N));
   GPT_TRY(gpt_alloc(ctx, &b.morton, N));
   GPT_TRY(gpt_alloc(ctx, &b.sorted_prim, N));
@@ -393,16 +394,17 @@ static int lbvh_reserve(gpt_ctx *ctx, BvhDev &b, int n) {
   return GPT_OK;
 }
 
-// Build the LBVH over `n` triangles; d_prim_list (device, may be NULL = identity) maps the
-// BVH's primitive index to the original triangle index.  All work is enqueued on
-// ctx->stream; nothing synchronises with the host.
-int gpt_lbvh_build(gpt_ctx *ctx, int which, const int *d_prim_list, int n) {
-  BvhDev &b = ctx->bvh[which];
+// Build the LBVH over `n` boxes (aabb: 6 floats each, indexed through d_prim_list when not
+// NULL).  with_tris also packs the 48-byte trace triangles (triangle BVHs); point BVHs (SPPM
+// photons, SSS samples) pass false.  All work is enqueued on ctx->stream; nothing
+// synchronises with the host.
+int gpt_lbvh_build_boxes(gpt_ctx *ctx, BvhDev &b, const float *aabb, const int *d_prim_list,
+                         int n, bool with_tris) {
   if (n < 2) {  // the reference cannot build or traverse such a tree (note 9)
     b.n = n;
     return GPT_OK;
   }
-  GPT_TRY(lbvh_reserve(ctx, b, n));
+  GPT_TRY(lbvh_reserve(ctx, b, n, with_tris));
   b.n = n;
   const SceneDev &s = ctx->scene;
   cudaStream_t st = ctx->stream;
@@ -410,11 +412,11 @@ int gpt_lbvh_build(gpt_ctx *ctx, int which, const int *d_prim_list, int n) {
   k_world_init<<<1, 32, 0, st>>>(b.world_enc);
   GPT_LAUNCH_CHECK(ctx);
   int rgrid = grid < 148 * 8 ? grid : 148 * 8;
-  k_world_reduce<<<rgrid, 256, 0, st>>>(s.aabb, d_prim_list, n, b.world_enc);
+  k_world_reduce<<<rgrid, 256, 0, st>>>(aabb, d_prim_list, n, b.world_enc);
   GPT_LAUNCH_CHECK(ctx);
   // keys/vals ping-pong between (morton, sorted_prim) and (keys_alt, vals_alt); 30 bits = 4
   // passes, an even number, so the result lands back in (morton, sorted_prim).
-  k_morton<<<grid, 256, 0, st>>>(s.aabb, d_prim_list, n, b.world_enc, b.morton, b.sorted_prim);
+  k_morton<<<grid, 256, 0, st>>>(aabb, d_prim_list, n, b.world_enc, b.morton, b.sorted_prim);
   GPT_LAUNCH_CHECK(ctx);
   uint32_t *ko; int *vo;
   GPT_TRY(gpt_radix_sort_pairs(ctx, b.morton, b.sorted_prim, b.keys_alt, b.vals_alt,
@@ -423,10 +425,18 @@ int gpt_lbvh_build(gpt_ctx *ctx, int which, const int *d_prim_list, int n) {
   k_emit<<<grid, 256, 0, st>>>(b.morton, n, b.nodes, b.parent_leaf);
   GPT_LAUNCH_CHECK(ctx);
   GPT_CUDA(ctx, cudaMemsetAsync(b.flags, 0, sizeof(int) * (size_t)n, st));
-  k_refit<true><<<grid, 256, 0, st>>>(s.aabb, d_prim_list, b.sorted_prim, n, b.nodes,
-                                      b.parent_leaf, b.flags, s, b.tris);
+  if (with_tris)
+    k_refit<true><<<grid, 256, 0, st>>>(aabb, d_prim_list, b.sorted_prim, n, b.nodes,
+                                        b.parent_leaf, b.flags, s, b.tris);
+  else
+    k_refit<false><<<grid, 256, 0, st>>>(aabb, d_prim_list, b.sorted_prim, n, b.nodes,
+                                         b.parent_leaf, b.flags, s, nullptr);
   GPT_LAUNCH_CHECK(ctx);
   return GPT_OK;
+}
+
+int gpt_lbvh_build(gpt_ctx *ctx, int which, const int *d_prim_list, int n) {
+  return gpt_lbvh_build_boxes(ctx, ctx->bvh[which], ctx->scene.aabb, d_prim_list, n, true);
 }
 
 // Ordered list of the triangles whose flags & mask != 0, taken in MAIN-BVH sorted order.

@@ -10,8 +10,7 @@
 #include <cmath>
 #include <vector>
 
-#include "lighttree.cuh"
-#include "render_state.cuh"
+#include "integrator.cuh"
 #include "trace_persistent.cuh"
 
 namespace {
@@ -121,20 +120,6 @@ k_light_nodes(const float4 *nodes, const int *parent_leaf, const float4 *leaf_in
 
 namespace {
 
-// Camera::compute_ray (camera.h:68-83) + Ray::Ray normalisation.
-__device__ __forceinline__ void camera_ray(const CameraDev &c, float i, float j, Rng &rng, V3 &o,
-                                           V3 &d) {
-  float w2 = (float)c.width / 2, h2 = (float)c.height / 2;
-  float alpha = (float)(c.tan_half_fovx * (double)(j - w2) / (double)w2);
-  float beta = (float)(c.tan_half_fovy * (double)(h2 - i) / (double)h2);
-  V3 dir = unit(alpha * c.u + beta * c.v - c.w);
-  V3 point = c.eye + c.focus_dist * dir;
-  V3 rd = c.lens_radius * sample_disk(rng);
-  V3 off = rd.x * c.u + rd.y * c.v;
-  o = c.eye + off;
-  d = unit(point - c.eye - off);
-}
-
 // _get_sky_color (pathtracing.h:69-82)
 __device__ __forceinline__ V3 sky_color(const RenderParams &p, V3 dir) {
   float u = (float)(.5 + (double)atan2f(dir.z, dir.x) / (2.0 * GPT_PI));
@@ -212,30 +197,6 @@ k_pt_trace(QueueSource src, const float4 *__restrict__ nodes, const float4 *__re
   trace_persistent<COUNT>(nodes, tris, parent_leaf, src, next_ray, stack, counters);
 }
 
-// change_ref_ray + _recompute_pdf (material_operations.h:26-153)
-__device__ __forceinline__ float change_ref_ray(const LightTree &lt, const float4 *shade,
-                                                const MaterialDev *mats, const TexAtlas &atlas,
-                                                V3 point, V3 normal, V3 v_in, RefRec &ref,
-                                                float weight, Rng &rng) {
-  float rn = rng_uniform(rng);
-  V3 pivot = ref.diffuse ? normal : ref.perfect;
-  if (isinf(ref.n)) weight = 0.f;
-  if (rn < weight) {
-    int leaf = light_pick(lt, point, pivot, rng);
-    V3 target = light_sample_point(lt, leaf, rng);
-    ref.dir = unit(target - point);
-    if (ref.reflected || ref.refracted) ref.filter = phong_filter(ref.k, ref.n, pivot, ref.dir);
-  }
-  V3 d1 = unit(ref.dir);
-  float hsum = light_hittable_sum(lt, shade, mats, atlas, point, d1, point, pivot);
-  float samp = ref.diffuse ? diffuse_sampling_pdf(normal, ref.dir)
-                           : specular_sampling_pdf(v_in, ref.dir, normal, ref.perfect, ref.n,
-                                                   ref.refracted);
-  float pdf = weight * hsum + (1.f - weight) * samp;
-  float spdf = scattering_pdf(normal, ref.dir, ref.diffuse, v_in, ref.refracted);
-  return (float)((double)spdf / GPT_PI / (double)pdf);
-}
-
 __global__ void __launch_bounds__(PT_BLOCK)
 k_pt_shade(PathState ps, RenderParams p, const int *__restrict__ queue,
            const int *__restrict__ count, int *next_queue, int *next_count, SceneDev sc,
@@ -276,7 +237,7 @@ k_pt_shade(PathState ps, RenderParams p, const int *__restrict__ queue,
       ref.reflected = false; ref.refracted = false; ref.diffuse = false;
       ref.n = 1.f; ref.k = V3{0.f, 0.f, 0.f}; ref.perfect = V3{1.f, 0.f, 0.f}; ref.bent = false;
       bool sss = false;
-      check_next_path(sc.mats, atlas, ts.mat, dir, normal, u, v, list, ref, sss, rng, false);
+      check_next_path<false>(sc.mats, atlas, ts.mat, dir, normal, u, v, list, ref, sss, rng, false);
       float factor = 1.f;
       if (!ref.false_hit)
         factor = change_ref_ray(lt, sc.shade, sc.mats, atlas, point, normal, dir, ref,
@@ -371,45 +332,33 @@ static RenderCtx *rc_of(gpt_ctx *ctx) {
   return static_cast<RenderCtx *>(ctx->render_state);
 }
 
-// Camera::Camera (camera.h:30-52): same operations, evaluated on the host
-static CameraDev derive_camera(const GptCamera &c) {
-  CameraDev d;
-  V3 eye = V3{c.eye[0], c.eye[1], c.eye[2]}, center = V3{c.center[0], c.center[1], c.center[2]};
-  V3 up = V3{c.up[0], c.up[1], c.up[2]};
-  float fovy = c.fovy;
-  float fovx = (float)(2.0f * atan(((float)c.width / (float)c.height) *
-                                   tan(M_PI * fovy / 180 / 2)) * 180 / M_PI);
-  d.eye = eye;
-  d.w = unit(eye - center);
-  d.u = unit(cross(up, d.w));
-  d.v = cross(d.w, d.u);
-  d.tan_half_fovx = tan(fovx * M_PI / 180.0 / 2);
-  d.tan_half_fovy = tan(fovy * M_PI / 180.0 / 2);
-  d.focus_dist = c.focus_dist;
-  d.lens_radius = (float)(c.aperture / 2.0);
-  d.width = c.width;
-  d.height = c.height;
-  return d;
-}
-
-static int build_light_tree(gpt_ctx *ctx, RenderCtx *rc) {
+// Light-tree side arrays (leaf records, node centres + |E|, node energies) over the light BVH;
+// shared by the path tracer and the SPPM passes (sppm.cu).
+int gpt_build_light_tree_arrays(gpt_ctx *ctx, float4 **leaf_info, float4 **node_info,
+                                float **node_energy, int **flags) {
   BvhDev &lb = ctx->bvh[GPT_BVH_LIGHT];
   int n = lb.n;
   if (n < 2)
     return gpt_fail(ctx, GPT_E_INVALID, "path tracing needs >= 2 emissive triangles (src/main.cu:1124-1125)", __FILE__, __LINE__);
-  GPT_TRY(gpt_alloc(ctx, &rc->leaf_info, 4 * (size_t)n));
-  GPT_TRY(gpt_alloc(ctx, &rc->node_info, (size_t)n));
-  GPT_TRY(gpt_alloc(ctx, &rc->node_energy, 3 * (size_t)n));
-  GPT_TRY(gpt_alloc(ctx, &rc->lt_flags, (size_t)n));
-  GPT_CUDA(ctx, cudaMemsetAsync(rc->lt_flags, 0, sizeof(int) * (size_t)n, ctx->stream));
+  GPT_TRY(gpt_alloc(ctx, leaf_info, 4 * (size_t)n));
+  GPT_TRY(gpt_alloc(ctx, node_info, (size_t)n));
+  GPT_TRY(gpt_alloc(ctx, node_energy, 3 * (size_t)n));
+  GPT_TRY(gpt_alloc(ctx, flags, (size_t)n));
+  GPT_CUDA(ctx, cudaMemsetAsync(*flags, 0, sizeof(int) * (size_t)n, ctx->stream));
   TexAtlas atlas{ctx->scene.tex_r, ctx->scene.tex_g, ctx->scene.tex_b};
   int grid = (n + 127) / 128;
-  k_light_leaves<<<grid, 128, 0, ctx->stream>>>(ctx->scene, atlas, lb.tris, n, rc->leaf_info);
+  k_light_leaves<<<grid, 128, 0, ctx->stream>>>(ctx->scene, atlas, lb.tris, n, *leaf_info);
   GPT_LAUNCH_CHECK(ctx);
-  k_light_nodes<<<grid, 128, 0, ctx->stream>>>(lb.nodes, lb.parent_leaf, rc->leaf_info, n,
-                                               rc->node_energy, rc->node_info, rc->lt_flags);
+  k_light_nodes<<<grid, 128, 0, ctx->stream>>>(lb.nodes, lb.parent_leaf, *leaf_info, n,
+                                               *node_energy, *node_info, *flags);
   GPT_LAUNCH_CHECK(ctx);
-  rc->light_n = n;
+  return GPT_OK;
+}
+
+static int build_light_tree(gpt_ctx *ctx, RenderCtx *rc) {
+  GPT_TRY(gpt_build_light_tree_arrays(ctx, &rc->leaf_info, &rc->node_info, &rc->node_energy,
+                                      &rc->lt_flags));
+  rc->light_n = ctx->bvh[GPT_BVH_LIGHT].n;
   return GPT_OK;
 }
 

@@ -449,7 +449,49 @@ def small_scene(n: int = 24, width: int = 128, height: int = 128, spp: int = 2,
                  name=name)
 
 
+def sppm_scene(cells: int = 91, width: int = 1920, height: int = 1080, photons: int = 10_000_000,
+               passes: int = 16, fog: bool = True, sphere_subdiv: int = 4, room: float = 10.0,
+               name: str = "C4") -> Scene:
+    """Config 4: closed diffuse room (6 tessellated walls, inward normals) + a glass sphere +
+    a fog box (participating medium) + two area lights under the ceiling; render_mode 2."""
+    L = float(room)
+    mats = MaterialBuilder()
+    m_white = mats.add("white", kd=(0.75, 0.75, 0.75))
+    m_red = mats.add("red", kd=(0.75, 0.25, 0.25))
+    m_green = mats.add("green", kd=(0.25, 0.75, 0.25))
+    m_glass = mats.add("glass", t_r=1.0, n_i=1.5, n_s=1e6, priority=1)
+    m_fog = mats.add("fog", t_r=1.0, n_i=1.0, n_s=1e6, priority=3, scattering_coef=0.05,
+                     absorption_coef=0.01, g=0.3)
+    # the emitter needs a diffuse Kd: with kd = ks = 0 the reference's diffuse/specular split
+    # is 0/0 and the light never counts as a diffuse emitter in _compute_direct_radiance
+    m_light = mats.add("light", kd=(0.78, 0.78, 0.78), ke=(15.0, 15.0, 15.0))
+    mb = MeshBuilder()
+    walls = [((-L, -L, -L), (0, 0, 2 * L), (2 * L, 0, 0), m_white),   # floor    (+y)
+             ((-L, L, -L), (2 * L, 0, 0), (0, 0, 2 * L), m_white),    # ceiling  (-y)
+             ((-L, -L, -L), (2 * L, 0, 0), (0, 2 * L, 0), m_white),   # back     (+z)
+             ((-L, -L, L), (0, 2 * L, 0), (2 * L, 0, 0), m_white),    # front    (-z)
+             ((-L, -L, -L), (0, 2 * L, 0), (0, 0, 2 * L), m_red),     # left     (+x)
+             ((L, -L, -L), (0, 0, 2 * L), (0, 2 * L, 0), m_green)]    # right    (-x)
+    for p0, du, dv, m in walls:
+        v, f, uv = grid_quad(p0, du, dv, cells, cells)
+        mb.add(v, f, m, uvs=uv)
+    sv, sf, sn = icosphere((-3.0, -L + 3.0, -1.0), 3.0, sphere_subdiv)
+    mb.add(sv, sf, m_glass, normals=sn)
+    if fog:
+        bv, bf = box((-0.5 * L, -L + 0.5, -0.6 * L), (0.8 * L, 0.4 * L, 0.5 * L))
+        mb.add(bv, bf, m_fog)
+    _add_lights(mb, m_light, y=L - 0.5, size=0.2 * L, sep=0.4 * L)
+    cam = default_camera(width, height, eye=(0.0, 0.0, L - 1.0), center=(0.0, -0.2 * L, 0.0),
+                         fovy=60.0)
+    par = default_params(render_mode=2, ppm_num_photon_per_pass=photons, ppm_num_pass=passes,
+                         ppm_max_bounce=8, ppm_alpha=0.7, ppm_radius_scaling_factor=2.0,
+                         pathtracing_sample_size=1, pathtracing_level=8)
+    return Scene(mb.finish(), mats.finish(), cam, par, name=name)
+
+
 def make_scene(kind: str, **kw) -> Scene:
+    if kind in ("C4", "sppm"):
+        return sppm_scene(**kw)
     if kind in ("C1", "terrain"):
         return terrain_scene(**kw)
     if kind in ("C2", "mixed"):

@@ -184,18 +184,58 @@ int gpt_render_pathtrace(gpt_ctx *ctx, float *out_rgb);
  * are left untouched in d_out_rgb (DEVICE pointer, P x 3).  Asynchronous. */
 int gpt_render_pathtrace_device(gpt_ctx *ctx, void *d_out_rgb, int rank, int nranks);
 
-/* ---- SPPM: replaces src/main.cu:1282-1870 --------------------------------------------- */
+/* ---- SPPM: replaces the render_mode == 2 branch, src/main.cu:1282-1870 ------------------
+ * Call order of one frame (single GPU):
+ *     gpt_sppm_init(ctx);
+ *     for (pass = 0; pass < ppm_num_pass; pass++) {
+ *         gpt_sppm_pass(ctx, pass, 0, ppm_num_photon_per_pass);
+ *         gpt_sppm_update(ctx, pass);
+ *     }
+ *     gpt_sppm_resolve(ctx, 0, ppm_num_pass, out_rgb);
+ * Multi-GPU: every rank runs the same sequence with its own photon range and all-reduces
+ * (sum) the buffer of gpt_sppm_flux_device between gpt_sppm_pass and gpt_sppm_update. */
+/* ray_tracing_pass(init=true) + compute_average_radius + assign_radius_to_invalid_hit_points
+ * + compute_accummulated_light_source_energy (src/main.cu:1311-1460). */
 int gpt_sppm_init(gpt_ctx *ctx);
-/* One pass: photon trace of photons [photon_begin, photon_end), photon LBVH, eye pass,
- * gather.  After the call the per-hit-point flux / count accumulators of THIS pass are in
- * the buffer returned by gpt_sppm_flux_device so the host can allreduce them over NCCL
- * before gpt_sppm_update applies the radius / flux update. */
+/* photon_pass + gather_recorded_photons + both photon LBVHs + ray_tracing_pass + the
+ * traversal half of update_hit_point_parameters (src/main.cu:1496-1779), for the global
+ * photon indices [photon_begin, photon_end).  Leaves this pass' per-hit-point accumulators
+ * in the buffer of gpt_sppm_flux_device. */
 int gpt_sppm_pass(gpt_ctx *ctx, int pass, int64_t photon_begin, int64_t photon_end);
-int gpt_sppm_flux_device(gpt_ctx *ctx, void **d_flux /*P x 4 fp32: r,g,b,count*/,
-                         int64_t *num_floats);
+/* DEVICE buffer of 8 P floats: [0, 4P) = (flux.r, flux.g, flux.b, photon count) per pixel,
+ * [4P, 8P) = (tmp_accummulated_lm.rgb, 0) per pixel. */
+int gpt_sppm_flux_device(gpt_ctx *ctx, void **d_flux, int64_t *num_floats);
+/* PPMHitPoint::update_accummulated_reflected_flux with iteration = pass + 1
+ * (ppm_hit_point.h:115-171). */
 int gpt_sppm_update(gpt_ctx *ctx, int pass);
-int gpt_sppm_resolve(gpt_ctx *ctx, int mode /*0 global,1 direct,2 indirect*/, int passes,
-                     float *out_rgb);
+/* get_ppm_image_output (image_output.h:8-31): mode 0 = global (direct + indirect),
+ * 1 = direct, 2 = indirect; divided by `passes`.  out_rgb: P x 3 host floats. */
+int gpt_sppm_resolve(gpt_ctx *ctx, int mode, int passes, float *out_rgb);
+/* last pass: stored surface / volume photons, mean surface radius (compute_average_radius,
+ * src/main.cu:1787-1798), main-BVH rays since gpt_sppm_init.  Any pointer may be NULL. */
+int gpt_sppm_stats(gpt_ctx *ctx, int64_t *n_surface, int64_t *n_volume, double *mean_radius,
+                   uint64_t *rays_total);
+/* parity exports (host pointers, any may be NULL): hit points as P x 4 floats each --
+ * (location, surface radius) (normal, volume radius) (filter, 0) (direct radiance, 0)
+ * (indirect radiance, photons) and the 2P x 4 flux buffer described above. */
+int gpt_sppm_export_hit_points(gpt_ctx *ctx, float *loc_radius, float *normal_vradius,
+                               float *filter, float *direct, float *indirect, float *flux_lm);
+/* photons of the last pass in photon-index order: kind (0 surface, 1 volume, 2 not stored),
+ * 12 floats each (location, prev_location, direction, colour).  *count = photons traced;
+ * nothing is written when capacity < *count. */
+int gpt_sppm_export_photons(gpt_ctx *ctx, int32_t *kind, float *rec12, int64_t capacity,
+                            int64_t *count);
+/* one pass split into stages (bit mask): 1 = photon trace + compaction + both photon trees,
+ * 2 = eye pass with the volume beam gather, 4 = surface gather.  gpt_sppm_pass = mask 7. */
+int gpt_sppm_pass_stages(gpt_ctx *ctx, int pass, int64_t photon_begin, int64_t photon_end,
+                         int stage_mask);
+/* parity import: replace the photons of the current pass by n caller-supplied ones (kind +
+ * 12 floats each, as exported) and build both photon trees from them. */
+int gpt_sppm_import_photons(gpt_ctx *ctx, const int32_t *kind, const float *rec12, int64_t n);
+/* parity import: overwrite hit-point (location, surface radius) / (normal, volume radius) /
+ * filter with caller-supplied P x 4 host floats (NULL = keep). */
+int gpt_sppm_import_hit_points(gpt_ctx *ctx, const float *loc_radius,
+                               const float *normal_vradius, const float *filter);
 
 /* Profiling switches for the NEXT renders (never on in a timed headline run):
  *   time_stages  - bracket every trace / shade launch with CUDA events (fills

@@ -133,6 +133,22 @@ struct RefCtx {
   std::string err;
   double last_ms = 0;
   unsigned long long last_rays = 0;
+  struct Sppm *sppm = nullptr;
+};
+
+// SPPM state, the locals of main()'s render_mode == 2 branch (src/main.cu:1282-1494)
+struct Sppm {
+  int P = 0, nphot = 0;
+  PPMHitPoint **hit_point_list = nullptr;
+  Point **photon_list = nullptr, **surface_photon_list = nullptr, **volume_photon_list = nullptr;
+  Node **surface_photon_node_list = nullptr, **surface_photon_leaf_list = nullptr;
+  Node **volume_photon_node_list = nullptr, **volume_photon_leaf_list = nullptr;
+  float *acc_energy = nullptr;
+  curandState *rand_state_ppm = nullptr, *rand_state_image = nullptr;
+  unsigned int *surface_morton = nullptr, *volume_morton = nullptr;
+  int num_surface = 0, num_volume = 0;
+  float average_radius = 0.f;
+  unsigned long long rays = 0;
 };
 
 void build_bvh(Bvh &b, bool cones) {
@@ -604,5 +620,309 @@ int ref_render_pathtrace_window(RefCtx *c, float *out_rgb, int row0, int row1, i
 }
 
 unsigned long long ref_last_rays(RefCtx *c) { return c->last_rays; }
+
+}  // extern "C"
+
+// ---- SPPM: the reference's own kernels, launched the way src/main.cu:1282-1870 does ---------
+
+// rows [0,H) of a 2-D pixel kernel, spread over host threads (pixels are independent)
+template <class F>
+static void launch_pixels(int W, int H, int nthreads, std::atomic<unsigned long long> &rays, F f) {
+  std::atomic<int> next_row(0);
+  auto work = [&] {
+    shim_blockDim = dim3(1, 1, 1);
+    tl_ray_count = 0;
+    for (;;) {
+      int i = next_row.fetch_add(1);
+      if (i >= H) break;
+      for (int j = 0; j < W; j++) {
+        shim_blockIdx = {(unsigned)j, (unsigned)i, 0};
+        shim_threadIdx = {0, 0, 0};
+        f();
+      }
+    }
+    rays += tl_ray_count;
+    shim_blockIdx = {0, 0, 0};
+  };
+  if (nthreads <= 1) { work(); return; }
+  std::vector<std::thread> th;
+  for (int k = 0; k < nthreads; k++) th.emplace_back(work);
+  for (auto &x : th) x.join();
+}
+
+extern "C" {
+
+int ref_sppm_init(RefCtx *c, int nthreads) {
+  if (!c->my_camera || c->light_bvh.n < 2 || c->transparent_bvh.n < 2) return GPT_E_INVALID;
+  const GptParams &p = c->params;
+  int W = c->cam.width, H = c->cam.height, P = W * H, nph = p.ppm_num_photon_per_pass;
+  Sppm *s = new Sppm();
+  c->sppm = s;
+  s->P = P;
+  s->nphot = nph;
+  s->rand_state_image = new curandState[P];
+  launch_1d(P / 8 + 1, 8, [&] { init_curand_state(P, s->rand_state_image); });
+  s->hit_point_list = new PPMHitPoint *[P];
+  s->photon_list = new Point *[nph];
+  s->surface_photon_list = new Point *[nph];
+  s->volume_photon_list = new Point *[nph];
+  g_counted_root = c->main_bvh.node_list[0];
+  std::atomic<unsigned long long> rays(0);
+  auto t0 = std::chrono::steady_clock::now();
+  launch_pixels(W, H, nthreads, rays, [&] {
+    ray_tracing_pass(s->hit_point_list, c->my_camera, s->rand_state_image, nullptr,
+                     c->main_bvh.node_list, true, p.ppm_max_bounce, p.ppm_alpha, 0,
+                     c->light_bvh.n, c->light_bvh.geom, c->light_bvh.node_list,
+                     c->light_bvh.leaf_list, c->transparent_bvh.node_list,
+                     p.pathtracing_sample_size, p.ppm_radius_scaling_factor);
+  });
+  launch_1d(1, 1, [&] { compute_average_radius(s->hit_point_list, P, &s->average_radius); });
+  float avg = s->average_radius;
+  launch_1d(P, 1, [&] { assign_radius_to_invalid_hit_points(s->hit_point_list, P, avg); });
+  launch_1d(nph, 1, [&] { create_photon_list(s->photon_list, nph); });
+  s->surface_photon_node_list = new Node *[std::max(1, nph - 1)];
+  s->surface_photon_leaf_list = new Node *[nph];
+  s->volume_photon_node_list = new Node *[std::max(1, nph - 1)];
+  s->volume_photon_leaf_list = new Node *[nph];
+  s->acc_energy = new float[c->light_bvh.n];
+  launch_1d(nph, 1, [&] { init_photon_leaves(s->surface_photon_leaf_list, nph); });
+  launch_1d(nph, 1, [&] { init_photon_nodes(s->surface_photon_node_list, nph); });
+  launch_1d(nph, 1, [&] { init_photon_leaves(s->volume_photon_leaf_list, nph); });
+  launch_1d(nph, 1, [&] { init_photon_nodes(s->volume_photon_node_list, nph); });
+  launch_1d(1, 1, [&] {
+    compute_accummulated_light_source_energy(c->light_bvh.geom, c->light_bvh.n, s->acc_energy);
+  });
+  s->rand_state_ppm = new curandState[nph];
+  launch_1d(nph, 1, [&] { init_curand_state(nph, s->rand_state_ppm); });
+  s->surface_morton = new unsigned int[std::max(1, nph)];
+  s->volume_morton = new unsigned int[std::max(1, nph)];
+  auto t1 = std::chrono::steady_clock::now();
+  c->last_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
+  s->rays = rays.load();
+  c->last_rays = s->rays;
+  return GPT_OK;
+}
+
+}  // extern "C"
+
+// The photon tree of one kind (src/main.cu:1576-1752); spheres = the volume variant.
+static void build_photon_tree(Point **list, int n, int nph, Node **node_list, Node **leaf_list,
+                              unsigned int *morton, bool spheres) {
+  BoundingBox **world = new BoundingBox *[1];
+  launch_1d(1, 1, [&] { compute_world_bounding_box(world, list, n); });
+  if (n <= 0) return;
+  launch_1d(1, 1, [&] { modify_world_bounding_box(world, list, n); });
+  launch_1d(n, 1, [&] { compute_photon_morton_code_batch(list, n, world); });
+  std::stable_sort(list, list + n, [](Point *a, Point *b) {
+    return a->bounding_box->morton_code < b->bounding_box->morton_code;
+  });
+  launch_1d(nph, 1, [&] { reset_photon_nodes(node_list, nph); });
+  launch_1d(std::max(1, n), 1, [&] { assign_photons(leaf_list, list, n); });
+  launch_1d(std::max(1, n), 1, [&] { extract_sss_morton_code_list(list, morton, n); });
+  launch_1d(std::max(1, n), 1,
+            [&] { set_photon_node_relationship(node_list, leaf_list, morton, n); });
+  if (spheres)
+    launch_1d(std::max(1, n), 1, [&] { compute_node_bounding_spheres(leaf_list, node_list, n); });
+  else
+    launch_1d(std::max(1, n), 1, [&] { compute_node_bounding_boxes(leaf_list, node_list, n); });
+}
+
+extern "C" {
+
+// One pass of the loop at src/main.cu:1496-1868.
+//   photon_rng 0: photon_pass is launched once PER PHOTON with rand_state = &state[photon],
+//                 photon_list = &list[photon], num_photons = 1 -- the reference's own kernel,
+//                 with rand_state[0] (its BSDF stream, photon_pass.h:156-160) being that
+//                 photon's state instead of a state all threads race on.  Deterministic.
+//   photon_rng 1: one launch over all photons, executed sequentially: every photon draws its
+//                 BSDF decisions from rand_state[0] (one possible serialisation of the race).
+//   stage_mask: 1 photon trace + trees, 2 eye pass, 4 gather + update
+int ref_sppm_pass(RefCtx *c, int pass, int photon_rng, int stage_mask, int nthreads) {
+  Sppm *s = c->sppm;
+  if (!s) return GPT_E_INVALID;
+  const GptParams &p = c->params;
+  int W = c->cam.width, H = c->cam.height, P = s->P, nph = s->nphot;
+  g_counted_root = c->main_bvh.node_list[0];
+  std::atomic<unsigned long long> rays(0);
+  auto t0 = std::chrono::steady_clock::now();
+  if (stage_mask & 1) {
+    if (photon_rng == 0) {
+      std::atomic<int> next(0);
+      auto work = [&] {
+        shim_blockDim = dim3(1, 1, 1);
+        shim_blockIdx = {0, 0, 0};
+        shim_threadIdx = {0, 0, 0};
+        tl_ray_count = 0;
+        for (;;) {
+          int k = next.fetch_add(64);
+          if (k >= nph) break;
+          for (int q = k; q < std::min(nph, k + 64); q++)
+            photon_pass(c->light_bvh.geom, c->main_bvh.node_list, c->transparent_bvh.node_list,
+                        s->photon_list + q, c->light_bvh.n, s->acc_energy, 1, p.ppm_max_bounce,
+                        pass, s->rand_state_ppm + q);
+        }
+        rays += tl_ray_count;
+      };
+      if (nthreads <= 1) work();
+      else {
+        std::vector<std::thread> th;
+        for (int k = 0; k < nthreads; k++) th.emplace_back(work);
+        for (auto &x : th) x.join();
+      }
+    } else {
+      tl_ray_count = 0;
+      launch_1d(nph, 1, [&] {
+        photon_pass(c->light_bvh.geom, c->main_bvh.node_list, c->transparent_bvh.node_list,
+                    s->photon_list, c->light_bvh.n, s->acc_energy, nph, p.ppm_max_bounce, pass,
+                    s->rand_state_ppm);
+      });
+      rays += tl_ray_count;
+    }
+    launch_1d(1, 1, [&] {
+      gather_recorded_photons(s->photon_list, s->surface_photon_list, s->volume_photon_list, nph,
+                              &s->num_surface, &s->num_volume);
+    });
+    build_photon_tree(s->surface_photon_list, s->num_surface, nph, s->surface_photon_node_list,
+                      s->surface_photon_leaf_list, s->surface_morton, false);
+    build_photon_tree(s->volume_photon_list, s->num_volume, nph, s->volume_photon_node_list,
+                      s->volume_photon_leaf_list, s->volume_morton, true);
+  }
+  if (stage_mask & 2) {
+    launch_pixels(W, H, nthreads, rays, [&] {
+      ray_tracing_pass(s->hit_point_list, c->my_camera, s->rand_state_image,
+                       s->volume_photon_node_list, c->main_bvh.node_list, false,
+                       p.ppm_max_bounce, p.ppm_alpha, pass, c->light_bvh.n, c->light_bvh.geom,
+                       c->light_bvh.node_list, c->light_bvh.leaf_list,
+                       c->transparent_bvh.node_list, p.pathtracing_sample_size,
+                       p.ppm_radius_scaling_factor);
+    });
+  }
+  if (stage_mask & 4) {
+    std::atomic<int> next(0);
+    auto work = [&] {
+      shim_blockDim = dim3(1, 1, 1);
+      shim_threadIdx = {0, 0, 0};
+      tl_ray_count = 0;
+      for (;;) {
+        int k = next.fetch_add(256);
+        if (k >= P) break;
+        for (int q = k; q < std::min(P, k + 256); q++) {
+          shim_blockIdx = {(unsigned)q, 0, 0};
+          update_hit_point_parameters(pass + 1, s->surface_photon_node_list,
+                                      c->main_bvh.node_list, s->hit_point_list, P, nph);
+        }
+      }
+      rays += tl_ray_count;
+      shim_blockIdx = {0, 0, 0};
+    };
+    if (nthreads <= 1) work();
+    else {
+      std::vector<std::thread> th;
+      for (int k = 0; k < nthreads; k++) th.emplace_back(work);
+      for (auto &x : th) x.join();
+    }
+    launch_1d(1, 1, [&] { compute_average_radius(s->hit_point_list, P, &s->average_radius); });
+  }
+  auto t1 = std::chrono::steady_clock::now();
+  c->last_ms = std::chrono::duration<double, std::milli>(t1 - t0).count();
+  c->last_rays = rays.load();
+  s->rays += c->last_rays;
+  return GPT_OK;
+}
+
+int ref_sppm_counts(RefCtx *c, int64_t *n_surface, int64_t *n_volume, double *mean_radius) {
+  Sppm *s = c->sppm;
+  if (!s) return GPT_E_INVALID;
+  *n_surface = s->num_surface;
+  *n_volume = s->num_volume;
+  *mean_radius = s->average_radius;
+  return GPT_OK;
+}
+
+// hit-point SoA in the layout of gpt_sppm_export_hit_points (P x 4 floats each); lm = the
+// tmp_accummulated_lm of the last eye pass
+int ref_sppm_export_hit_points(RefCtx *c, float *loc_radius, float *normal_vradius, float *filter,
+                               float *direct, float *indirect, float *lm) {
+  Sppm *s = c->sppm;
+  if (!s) return GPT_E_INVALID;
+  for (int i = 0; i < s->P; i++) {
+    PPMHitPoint *h = s->hit_point_list[i];
+    auto put = [&](float *o, const vec3 &v, float w) {
+      if (!o) return;
+      o[4 * i] = v.x(); o[4 * i + 1] = v.y(); o[4 * i + 2] = v.z(); o[4 * i + 3] = w;
+    };
+    put(loc_radius, h->location, h->surface_radius);
+    put(normal_vradius, h->normal, h->volume_radius);
+    put(filter, h->filter, 0.f);
+    put(direct, h->direct_radiance, 0.f);
+    put(indirect, h->accummulated_indirect_radiance, 0.f);
+    put(lm, h->tmp_accummulated_lm, 0.f);
+  }
+  return GPT_OK;
+}
+
+// photons of the last photon pass in photon-index order (layout of gpt_sppm_export_photons)
+int ref_sppm_export_photons(RefCtx *c, int32_t *kind, float *rec12) {
+  Sppm *s = c->sppm;
+  if (!s) return GPT_E_INVALID;
+  for (int i = 0; i < s->nphot; i++) {
+    Point *p = s->photon_list[i];
+    int k = p->location.vector_is_inf() ? 2 : (p->on_surface ? 0 : 1);
+    if (kind) kind[i] = k;
+    if (rec12) {
+      float *o = rec12 + 12 * (size_t)i;
+      const vec3 *v[4] = {&p->location, &p->prev_location, &p->direction, &p->color};
+      for (int a = 0; a < 4; a++)
+        for (int b = 0; b < 3; b++) o[3 * a + b] = (*v[a])[b];
+    }
+  }
+  return GPT_OK;
+}
+
+// The traversal half of update_hit_point_parameters (bvh_traversal_photon.h:108-225) for every
+// hit point, WITHOUT the update: flux (rgb) + count per pixel, P x 4 floats.
+int ref_sppm_gather_only(RefCtx *c, float *flux_count, int nthreads) {
+  Sppm *s = c->sppm;
+  if (!s) return GPT_E_INVALID;
+  std::atomic<int> next(0);
+  auto work = [&] {
+    for (;;) {
+      int k = next.fetch_add(256);
+      if (k >= s->P) break;
+      for (int q = k; q < std::min(s->P, k + 256); q++) {
+        vec3 flux(0, 0, 0);
+        int cnt = 0;
+        if (!s->hit_point_list[q]->location.vector_is_inf())
+          _traverse_bvh_surface_photon(s->surface_photon_node_list[0], c->main_bvh.node_list[0],
+                                       s->hit_point_list[q], flux, cnt);
+        flux_count[4 * q] = flux.x(); flux_count[4 * q + 1] = flux.y();
+        flux_count[4 * q + 2] = flux.z(); flux_count[4 * q + 3] = (float)cnt;
+      }
+    }
+  };
+  if (nthreads <= 1) work();
+  else {
+    std::vector<std::thread> th;
+    for (int k = 0; k < nthreads; k++) th.emplace_back(work);
+    for (auto &x : th) x.join();
+  }
+  return GPT_OK;
+}
+
+// get_ppm_image_output (image_output.h:8-31); mode 0 direct, 1 indirect, 2 global
+int ref_sppm_resolve(RefCtx *c, int image_mode, int passes, float *out_rgb) {
+  Sppm *s = c->sppm;
+  if (!s) return GPT_E_INVALID;
+  int W = c->cam.width, H = c->cam.height;
+  std::vector<vec3> fb((size_t)s->P);
+  std::atomic<unsigned long long> dummy(0);
+  launch_pixels(W, H, 1, dummy, [&] {
+    get_ppm_image_output(passes, fb.data(), s->hit_point_list, c->my_camera, image_mode);
+  });
+  for (int i = 0; i < s->P; i++) {
+    out_rgb[3 * i] = fb[i].x(); out_rgb[3 * i + 1] = fb[i].y(); out_rgb[3 * i + 2] = fb[i].z();
+  }
+  return GPT_OK;
+}
 
 }  // extern "C"

@@ -131,3 +131,52 @@ class RefReplay:
         ms = C.c_double()
         _check(self.lib.ref_time_main_bvh_build(self.ctx, C.byref(ms)))
         return ms.value
+
+    # -- SPPM: the reference's own kernels (oracle/ref_replay.cpp) --------------------------
+    def sppm_init(self, nthreads=None):
+        _check(self.lib.ref_sppm_init(self.ctx, C.c_int(nthreads or os.cpu_count() or 1)))
+        self.sppm_ms = self.lib.ref_last_ms(self.ctx)
+        self.sppm_rays = int(self.lib.ref_last_rays(self.ctx))
+
+    def sppm_pass(self, pass_idx, photon_rng=0, stages=7, nthreads=None):
+        """stages: 1 photon trace + trees, 2 eye pass, 4 gather + update (bit mask)."""
+        _check(self.lib.ref_sppm_pass(self.ctx, C.c_int(pass_idx), C.c_int(photon_rng),
+                                      C.c_int(stages), C.c_int(nthreads or os.cpu_count() or 1)))
+        self.sppm_ms = self.lib.ref_last_ms(self.ctx)
+        self.sppm_rays = int(self.lib.ref_last_rays(self.ctx))
+
+    def sppm_counts(self) -> dict:
+        ns, nv, r = C.c_int64(), C.c_int64(), C.c_double()
+        _check(self.lib.ref_sppm_counts(self.ctx, C.byref(ns), C.byref(nv), C.byref(r)))
+        return dict(n_surface=ns.value, n_volume=nv.value, mean_radius=r.value)
+
+    def sppm_export_hit_points(self) -> dict:
+        P = self.scene.camera["height"] * self.scene.camera["width"]
+        keys = ("loc_radius", "normal_vradius", "filter", "direct", "indirect", "lm")
+        out = {k: np.zeros((P, 4), np.float32) for k in keys}
+        _check(self.lib.ref_sppm_export_hit_points(self.ctx, *[cabi.fptr(out[k]) for k in keys]))
+        return out
+
+    def sppm_export_photons(self) -> dict:
+        n = int(self.scene.params["ppm_num_photon_per_pass"])
+        kind = np.zeros(n, np.int32)
+        rec = np.zeros((n, 12), np.float32)
+        _check(self.lib.ref_sppm_export_photons(self.ctx, cabi.iptr(kind), cabi.fptr(rec)))
+        return dict(kind=kind, loc=rec[:, 0:3], prev=rec[:, 3:6], dir=rec[:, 6:9],
+                    color=rec[:, 9:12], rec=rec)
+
+    def sppm_gather_only(self, nthreads=None) -> np.ndarray:
+        P = self.scene.camera["height"] * self.scene.camera["width"]
+        out = np.zeros((P, 4), np.float32)
+        _check(self.lib.ref_sppm_gather_only(self.ctx, cabi.fptr(out),
+                                             C.c_int(nthreads or os.cpu_count() or 1)))
+        return out
+
+    def sppm_resolve(self, mode=0, passes=1) -> np.ndarray:
+        """mode 0 global, 1 direct, 2 indirect (the C-ABI's numbering)."""
+        cam = self.scene.camera
+        out = np.zeros((cam["height"], cam["width"], 3), np.float32)
+        ref_mode = {0: 2, 1: 0, 2: 1}[mode]
+        _check(self.lib.ref_sppm_resolve(self.ctx, C.c_int(ref_mode), C.c_int(passes),
+                                         cabi.fptr(out)))
+        return out
