@@ -49,7 +49,7 @@ __global__ void __launch_bounds__(128) k_rng_init(uint32_t *rng, const int *pixe
   if (s >= n) return;
   Rng r;
   curand_init(1984, pixel[s], 0, &r.s);
-  rng_store(r, rng, s, n);
+  rng_store_packed(r, rng, s);
 }
 
 // ---- light tree -----------------------------------------------------------------------------
@@ -137,7 +137,7 @@ __device__ __forceinline__ void start_sample(PathState &ps, int slot, V3 o, V3 d
 #pragma unroll
   for (int k = 0; k < MATLIST_MAX; k++) l.id[k] = MAT_AIR;
   l.len = 1;  // add_new_material(material_list, length, nullptr)  (pathtracing.h:106)
-  matlist_store(ps.matlist + slot, l);
+  matlist_store(reinterpret_cast<uint4 *>(ps.cm + 2 * (size_t)slot + 1), l);
 }
 
 __global__ void __launch_bounds__(PT_BLOCK)
@@ -147,15 +147,15 @@ k_pt_start(PathState ps, RenderParams p, int n, float *fb) {
   int pix = ps.pixel[s];
   int i = pix / p.cam.width, j = pix % p.cam.width;
   Rng rng;
-  rng_load(rng, ps.rng, s, ps.capacity);
+  rng_load_packed(rng, ps.rng, s);
   V3 o, d;
   camera_ray(p.cam, i + .5f, j + .5f, rng, o, d);
-  rng_store(rng, ps.rng, s, ps.capacity);
-  ps.cam_o[s] = make_float4(o.x, o.y, o.z, 0.f);
-  ps.cam_d[s] = make_float4(d.x, d.y, d.z, 0.f);
-  ps.mask[s] = make_float4(1.f, 1.f, 1.f, __int_as_float(0));
-  ps.acc[s] = make_float4(0.f, 0.f, 0.f, __int_as_float(0));
-  ps.color[s] = make_float4(0.f, 0.f, 0.f, __int_as_float(0));
+  rng_store_packed(rng, ps.rng, s);
+  ps.cam[2 * (size_t)s] = make_float4(o.x, o.y, o.z, 0.f);
+  ps.cam[2 * (size_t)s + 1] = make_float4(d.x, d.y, d.z, 0.f);
+  ps.ma[2 * (size_t)s] = make_float4(1.f, 1.f, 1.f, __int_as_float(0));
+  ps.ma[2 * (size_t)s + 1] = make_float4(0.f, 0.f, 0.f, __int_as_float(0));
+  ps.cm[2 * (size_t)s] = make_float4(0.f, 0.f, 0.f, __int_as_float(0));
   start_sample(ps, s, o, d);
   ps.queue[0][s] = s;
   fb[3 * (size_t)pix] = 0.f; fb[3 * (size_t)pix + 1] = 0.f; fb[3 * (size_t)pix + 2] = 0.f;
@@ -210,13 +210,13 @@ k_pt_shade(PathState ps, RenderParams p, const int *__restrict__ queue,
     alive = true;
     float4 ro = ps.rays[2 * (size_t)s], rdv = ps.rays[2 * (size_t)s + 1];
     float4 h0 = ps.hits[2 * (size_t)s], h1 = ps.hits[2 * (size_t)s + 1];
-    float4 mk = ps.mask[s], ac = ps.acc[s];
+    float4 mk = ps.ma[2 * (size_t)s], ac = ps.ma[2 * (size_t)s + 1];
     V3 dir = V3{rdv.x, rdv.y, rdv.z};
     V3 mask = V3{mk.x, mk.y, mk.z}, acc = V3{ac.x, ac.y, ac.z};
     int bounce = __float_as_int(mk.w), sidx = __float_as_int(ac.w);
     int leaf = __float_as_int(h0.y);
     Rng rng;
-    rng_load(rng, ps.rng, s, ps.capacity);
+    rng_load_packed(rng, ps.rng, s);
     bool done = false;
     V3 result = V3{0.f, 0.f, 0.f};
     if (leaf >= 0) {
@@ -232,7 +232,7 @@ k_pt_shade(PathState ps, RenderParams p, const int *__restrict__ queue,
       float v = b1 * ts.v1 + b2 * ts.v2 + b3 * ts.v3;
       V3 normal = shading_normal(ts, m, atlas, b1, b2, b3);
       MatList list;
-      matlist_load(list, ps.matlist + s);
+      matlist_load(list, reinterpret_cast<const uint4 *>(ps.cm + 2 * (size_t)s + 1));
       RefRec ref;
       ref.reflected = false; ref.refracted = false; ref.diffuse = false;
       ref.n = 1.f; ref.k = V3{0.f, 0.f, 0.f}; ref.perfect = V3{1.f, 0.f, 0.f}; ref.bent = false;
@@ -247,7 +247,7 @@ k_pt_shade(PathState ps, RenderParams p, const int *__restrict__ queue,
       if ((ref.false_hit || ref.refracted) && ref.entering) ok = matlist_add(list, ts.mat);
       else if ((ref.false_hit || ref.refracted) && !ref.entering) matlist_remove(list, ts.mat);
       if (!ok) *error_flag = 1;
-      matlist_store(ps.matlist + s, list);
+      matlist_store(reinterpret_cast<uint4 *>(ps.cm + 2 * (size_t)s + 1), list);
       if (!ref.false_hit) {
         V3 add = de_nan(mask * mat_emission(atlas, m, u, v));
         acc = acc + add;
@@ -266,8 +266,8 @@ k_pt_shade(PathState ps, RenderParams p, const int *__restrict__ queue,
         } else {
           ps.rays[2 * (size_t)s] = make_float4(point.x, point.y, point.z, INFINITY);
           ps.rays[2 * (size_t)s + 1] = make_float4(ref.dir.x, ref.dir.y, ref.dir.z, 0.f);
-          ps.mask[s] = make_float4(mask.x, mask.y, mask.z, __int_as_float(bounce));
-          ps.acc[s] = make_float4(acc.x, acc.y, acc.z, __int_as_float(sidx));
+          ps.ma[2 * (size_t)s] = make_float4(mask.x, mask.y, mask.z, __int_as_float(bounce));
+          ps.ma[2 * (size_t)s + 1] = make_float4(acc.x, acc.y, acc.z, __int_as_float(sidx));
         }
       }
     } else {
@@ -276,7 +276,7 @@ k_pt_shade(PathState ps, RenderParams p, const int *__restrict__ queue,
       done = true;
     }
     if (done) {
-      float4 cl = ps.color[s];
+      float4 cl = ps.cm[2 * (size_t)s];
       V3 color = V3{cl.x, cl.y, cl.z} + de_nan(result);
       int k = __float_as_int(cl.w);
       sidx++;
@@ -290,11 +290,11 @@ k_pt_shade(PathState ps, RenderParams p, const int *__restrict__ queue,
         } else {
           int pix = ps.pixel[s];
           camera_ray(p.cam, pix / p.cam.width + .5f, pix % p.cam.width + .5f, rng, o, d);
-          ps.cam_o[s] = make_float4(o.x, o.y, o.z, 0.f);
-          ps.cam_d[s] = make_float4(d.x, d.y, d.z, 0.f);
+          ps.cam[2 * (size_t)s] = make_float4(o.x, o.y, o.z, 0.f);
+          ps.cam[2 * (size_t)s + 1] = make_float4(d.x, d.y, d.z, 0.f);
         }
       } else {
-        float4 co = ps.cam_o[s], cd = ps.cam_d[s];
+        float4 co = ps.cam[2 * (size_t)s], cd = ps.cam[2 * (size_t)s + 1];
         o = V3{co.x, co.y, co.z};
         d = V3{cd.x, cd.y, cd.z};
       }
@@ -304,13 +304,13 @@ k_pt_shade(PathState ps, RenderParams p, const int *__restrict__ queue,
         fb[3 * (size_t)pix] = out.x; fb[3 * (size_t)pix + 1] = out.y; fb[3 * (size_t)pix + 2] = out.z;
         alive = false;
       } else {
-        ps.color[s] = make_float4(color.x, color.y, color.z, __int_as_float(k));
-        ps.mask[s] = make_float4(1.f, 1.f, 1.f, __int_as_float(0));
-        ps.acc[s] = make_float4(0.f, 0.f, 0.f, __int_as_float(sidx));
+        ps.cm[2 * (size_t)s] = make_float4(color.x, color.y, color.z, __int_as_float(k));
+        ps.ma[2 * (size_t)s] = make_float4(1.f, 1.f, 1.f, __int_as_float(0));
+        ps.ma[2 * (size_t)s + 1] = make_float4(0.f, 0.f, 0.f, __int_as_float(sidx));
         start_sample(ps, s, o, d);
       }
     }
-    rng_store(rng, ps.rng, s, ps.capacity);
+    rng_store_packed(rng, ps.rng, s);
   }
   // warp-aggregated compaction of the surviving slots into the next queue
   unsigned ballot = __ballot_sync(0xffffffffu, alive);
@@ -367,16 +367,13 @@ static int reserve_paths(gpt_ctx *ctx, RenderCtx *rc, int n) {
   if (n <= ps.capacity) return GPT_OK;
   size_t N = (size_t)n;
   GPT_TRY(gpt_alloc(ctx, &ps.pixel, N));
-  GPT_TRY(gpt_alloc(ctx, &ps.rng, 6 * N));
-  GPT_TRY(gpt_alloc(ctx, &rc->rng_init, 6 * N));
+  GPT_TRY(gpt_alloc(ctx, &ps.rng, 8 * N));
+  GPT_TRY(gpt_alloc(ctx, &rc->rng_init, 8 * N));
   GPT_TRY(gpt_alloc(ctx, &ps.rays, 2 * N));
   GPT_TRY(gpt_alloc(ctx, &ps.hits, 2 * N));
-  GPT_TRY(gpt_alloc(ctx, &ps.mask, N));
-  GPT_TRY(gpt_alloc(ctx, &ps.acc, N));
-  GPT_TRY(gpt_alloc(ctx, &ps.color, N));
-  GPT_TRY(gpt_alloc(ctx, &ps.cam_o, N));
-  GPT_TRY(gpt_alloc(ctx, &ps.cam_d, N));
-  GPT_TRY(gpt_alloc(ctx, &ps.matlist, N));
+  GPT_TRY(gpt_alloc(ctx, &ps.ma, 2 * N));
+  GPT_TRY(gpt_alloc(ctx, &ps.cm, 2 * N));
+  GPT_TRY(gpt_alloc(ctx, &ps.cam, 2 * N));
   GPT_TRY(gpt_alloc(ctx, &ps.queue[0], N));
   GPT_TRY(gpt_alloc(ctx, &ps.queue[1], N));
   GPT_TRY(gpt_alloc(ctx, &ps.counts, (size_t)4));
@@ -466,7 +463,7 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks) {
   cudaStream_t st = ctx->stream;
 
   GPT_CUDA(ctx, cudaEventRecord(ctx->ev0, st));
-  GPT_CUDA(ctx, cudaMemcpyAsync(ps.rng, rc->rng_init, sizeof(uint32_t) * 6 * (size_t)n,
+  GPT_CUDA(ctx, cudaMemcpyAsync(ps.rng, rc->rng_init, sizeof(uint32_t) * 8 * (size_t)n,
                                 cudaMemcpyDeviceToDevice, st));
   int init_counts[4] = {n, 0, 0, 0};
   GPT_CUDA(ctx, cudaMemcpyAsync(ps.counts, init_counts, sizeof(init_counts), cudaMemcpyHostToDevice, st));
@@ -570,8 +567,8 @@ void gpt_render_free(gpt_ctx *ctx) {
   if (!ctx || !ctx->render_state) return;
   RenderCtx *rc = static_cast<RenderCtx *>(ctx->render_state);
   PathState &ps = rc->ps;
-  void *p[] = {ps.pixel, ps.rng, ps.rays, ps.hits, ps.mask, ps.acc, ps.color, ps.cam_o, ps.cam_d,
-               ps.matlist, ps.queue[0], ps.queue[1], ps.counts, rc->leaf_info, rc->node_info,
+  void *p[] = {ps.pixel, ps.rng, ps.rays, ps.hits, ps.ma, ps.cm, ps.cam,
+               ps.queue[0], ps.queue[1], ps.counts, rc->leaf_info, rc->node_info,
                rc->node_energy, rc->lt_flags, rc->rng_init, rc->d_fb, rc->sort_key,
                rc->sort_key_alt, rc->sort_hist, rc->sort_val, rc->sort_val_alt};
   for (void *q : p) cudaFree(q);

@@ -18,15 +18,15 @@ struct CameraDev {  // Camera (src/model/camera.h:30-52), derived on the host
 struct PathState {
   int capacity;       // slots (pixels owned by this rank)
   int *pixel;         // slot -> global pixel index (row * width + col)
-  uint32_t *rng;      // 6 x capacity (d, v0..v4), stride = capacity
-  float4 *rays;       // 2 x capacity: {o, tmax}{d, 0}   (trace input)
-  float4 *hits;       // 2 x capacity: {t, leaf, prim, -}{b1, b2, b3, -}
-  float4 *mask;       // (mask.rgb, bounce index as int bits)
-  float4 *acc;        // (acc_color.rgb, sample index within the dof sample)
-  float4 *color;      // (pixel colour sum, dof sample index)
-  float4 *cam_o;      // camera ray of the current dof sample (reused for every spp sample)
-  float4 *cam_d;
-  uint4 *matlist;     // 12 material ids + length
+  // Slots are visited in MATERIAL-sorted order by the shade stage, i.e. at random: everything a
+  // slot touches together is packed into whole 32-byte sectors (ncu r01b: the previous
+  // plane-per-field layout moved 730 B per path vertex for ~290 B of useful state).
+  uint32_t *rng;      // 8 x capacity, packed per slot: (d, v0..v4, -, -)            1 sector
+  float4 *rays;       // 2 x capacity: {o, tmax}{d, 0}   (trace input)               1 sector
+  float4 *hits;       // 2 x capacity: {t, leaf, prim, -}{b1, b2, b3, -}             1 sector
+  float4 *ma;         // 2 x capacity: {mask.rgb, bounce}{acc_color.rgb, sample idx} 1 sector
+  float4 *cm;         // 2 x capacity: {pixel colour sum, dof idx}{12 material ids + length}
+  float4 *cam;        // 2 x capacity: camera ray {o}{d} of the current dof sample
   int *queue[2];      // active slot lists (ping-pong)
   int *counts;        // [0],[1] queue lengths; [2] matlist overflow flag
 };

@@ -35,6 +35,22 @@ __device__ __forceinline__ void rng_store(const Rng &r, uint32_t *st, size_t slo
 #pragma unroll
   for (int k = 0; k < 5; k++) st[(k + 1) * stride + slot] = r.s.v[k];
 }
+// packed variant: 8 words per slot (one 32-byte sector), for state that is visited in random
+// slot order
+__device__ __forceinline__ void rng_load_packed(Rng &r, const uint32_t *__restrict__ st, size_t slot) {
+  const uint4 *p = reinterpret_cast<const uint4 *>(st + 8 * slot);
+  uint4 a = p[0], b = p[1];
+  r.s.d = a.x; r.s.v[0] = a.y; r.s.v[1] = a.z; r.s.v[2] = a.w; r.s.v[3] = b.x; r.s.v[4] = b.y;
+  r.s.boxmuller_flag = 0;
+  r.s.boxmuller_flag_double = 0;
+  r.s.boxmuller_extra = 0.f;
+  r.s.boxmuller_extra_double = 0.0;
+}
+__device__ __forceinline__ void rng_store_packed(const Rng &r, uint32_t *st, size_t slot) {
+  uint4 *p = reinterpret_cast<uint4 *>(st + 8 * slot);
+  p[0] = make_uint4(r.s.d, r.s.v[0], r.s.v[1], r.s.v[2]);
+  p[1] = make_uint4(r.s.v[3], r.s.v[4], 0u, 0u);
+}
 __device__ __forceinline__ float rng_uniform(Rng &r) { return curand_uniform(&r.s); }
 
 // ---- clamp(lo, hi, v) (general.h:23-24) ------------------------------------------------

@@ -107,13 +107,16 @@ __device__ __forceinline__ void trace_persistent(const float4 *__restrict__ node
           tcull[c] = tn - margin;
           go[c] = ok && !(tf + margin < 0.f);
         }
-#pragma unroll
-        for (int c = 0; c < 2; c++) {
-          if (go[c] && cref[c] < 0) {
-            go[c] = false;
-            if (tcull[c] > L.best) continue;
-            int leaf = ~cref[c];
-            const float4 *tp = tris + 3 * (size_t)leaf;
+        // Leaves: the two children's tests share ONE copy of the intersection code (a leaf on
+        // either side of any lane runs in the same round), instead of two unrolled copies that
+        // each execute with ~2 of 32 lanes (ncu r01b: 37 % of issued instructions).
+        int lf0 = (go[0] && cref[0] < 0) ? ~cref[0] : -1, lf1 = (go[1] && cref[1] < 0) ? ~cref[1] : -1;
+        float lc0 = tcull[0], lc1 = tcull[1];
+        if (lf0 < 0) { lf0 = lf1; lc0 = lc1; lf1 = -1; }
+#pragma unroll 1
+        while (lf0 >= 0) {
+          if (!(lc0 > L.best)) {
+            const float4 *tp = tris + 3 * (size_t)lf0;
             float4 t0 = __ldg(tp), t1 = __ldg(tp + 1), t2 = __ldg(tp + 2);
             if (COUNT) vl++;
             RaySetup r;
@@ -123,33 +126,36 @@ __device__ __forceinline__ void trace_persistent(const float4 *__restrict__ node
               if (!(t > L.best) && !(t < t2.y)) {
                 bool take = true;
                 if (t == L.t && L.leaf >= 0)
-                  take = leaf_visit_rank(nodes, parent_leaf, leaf) >
+                  take = leaf_visit_rank(nodes, parent_leaf, lf0) >
                          leaf_visit_rank(nodes, parent_leaf, L.leaf);
                 if (take) {
-                  L.t = t; L.leaf = leaf; L.b1 = b1; L.b2 = b2; L.b3 = b3;
+                  L.t = t; L.leaf = lf0; L.b1 = b1; L.b2 = b2; L.b3 = b3;
                   L.prim = __float_as_int(t2.z);
                   L.best = t;
                 }
               }
             }
           }
+          lf0 = lf1; lc0 = lc1; lf1 = -1;
         }
-        bool gl = go[0] && !(tcull[0] > L.best);
-        bool gr = go[1] && !(tcull[1] > L.best);
-        bool finished = false;
-        if (gl && gr) {
-          bool lfirst = tnear[0] <= tnear[1];
-          int farc = lfirst ? cref[1] : cref[0];
-          if (L.sp < TP_STACK_SMEM) stack[L.sp * TP_BLOCK] = farc;
-          else if (L.sp < TRACE_STACK) spill[L.sp - TP_STACK_SMEM] = farc;
+        // Internal children, written to compile into predicated code rather than a three-way
+        // divergent branch (push / step / pop): near child first, far child pushed.
+        const bool gl = go[0] && cref[0] >= 0 && !(tcull[0] > L.best);
+        const bool gr = go[1] && cref[1] >= 0 && !(tcull[1] > L.best);
+        const bool both = gl && gr, any = gl || gr;
+        const bool lfirst = tnear[0] <= tnear[1];
+        const int nearc = (gl && (!gr || lfirst)) ? cref[0] : cref[1];
+        const int farc = lfirst ? cref[1] : cref[0];
+        if (both && L.sp < TP_STACK_SMEM) stack[L.sp * TP_BLOCK] = farc;
+        if (both && L.sp >= TP_STACK_SMEM) {  // rare: deeper than the shared-memory levels
+          if (L.sp < TRACE_STACK) spill[L.sp - TP_STACK_SMEM] = farc;
           else atomicExch(counters + 3, 1ull);
-          if (L.sp < TRACE_STACK) L.sp++;
-          L.node = lfirst ? cref[0] : cref[1];
-        } else if (gl || gr) {
-          L.node = gl ? cref[0] : cref[1];
-        } else if (L.sp == 0) {
-          finished = true;
-        } else {
+        }
+        if (both && L.sp < TRACE_STACK) L.sp++;
+        const bool finished = !any && L.sp == 0;
+        if (any) {
+          L.node = nearc;
+        } else if (L.sp > 0) {
           L.sp--;
           L.node = L.sp < TP_STACK_SMEM ? stack[L.sp * TP_BLOCK] : spill[L.sp - TP_STACK_SMEM];
         }

@@ -50,8 +50,63 @@ def gather_frame(frame, dst: int = 0, group=None):
     return frame
 
 
+class _DevicePtr:
+    """A raw device pointer dressed up with __cuda_array_interface__ so torch can alias it."""
+
+    def __init__(self, ptr: int, n_floats: int):
+        self.__cuda_array_interface__ = dict(shape=(n_floats,), typestr="<f4", data=(ptr, False),
+                                             version=2)
+
+
+def device_tensor(ptr: int, n_floats: int, device):
+    """torch.float32 view (no copy) of library-owned device memory, e.g. the SPPM flux buffer
+    of gpt_sppm_flux_device, so NCCL can reduce it in place."""
+    import torch
+    return torch.as_tensor(_DevicePtr(ptr, n_floats), device=device)
+
+
+def sppm_frame(pt, rank: int = 0, nranks: int = 1, passes: int | None = None, flux_tensor=None,
+               group=None, on_pass=None):
+    """One render_mode-2 frame (src/main.cu:1282-1870) with the photons of every pass split by
+    index range over the ranks: each rank traces its photons, builds its photon trees, runs the
+    (replicated) eye pass and gathers into ALL hit points; the per-hit-point accumulators are
+    summed over ranks -- the only collective of the path -- and every rank applies the same
+    radius / flux update, so hit-point state stays replicated.  `pt` is a PathTracer (or
+    anything with its sppm_* methods); `flux_tensor()` returns the tensor aliasing the
+    accumulator buffer (defaults to the device buffer of pt.sppm_flux_device())."""
+    n_photons = int(pt.scene.params["ppm_num_photon_per_pass"])
+    passes = passes or int(pt.scene.params["ppm_num_pass"])
+    b, e = photon_range(n_photons, rank, nranks)
+    pt.sppm_init()
+    flux = None
+    for p in range(passes):
+        pt.sppm_pass(p, b, e)
+        if nranks > 1:
+            if flux is None:
+                if flux_tensor is not None:
+                    flux = flux_tensor()
+                else:
+                    import torch
+                    ptr, n = pt.sppm_flux_device()
+                    flux = device_tensor(ptr, n, torch.device("cuda", torch.cuda.current_device()))
+            pt.synchronize()
+            allreduce_flux(flux, group=group)
+            _sync_current_stream(flux)
+        pt.sppm_update(p)
+        if on_pass is not None:
+            on_pass(p)
+    return passes
+
+
+def _sync_current_stream(t):
+    if getattr(t, "is_cuda", False):
+        import torch
+        torch.cuda.current_stream(t.device).synchronize()
+
+
 def allreduce_flux(flux, group=None):
-    """SPPM: per-hit-point (flux.rgb, photon count) of this pass summed over ranks."""
+    """SPPM: per-hit-point (flux.rgb, photon count, volume term) of this pass summed over
+    ranks."""
     import torch.distributed as dist
     if dist.is_initialized() and dist.get_world_size(group) > 1:
         dist.all_reduce(flux, op=dist.ReduceOp.SUM, group=group)
