@@ -190,7 +190,7 @@ struct QueueSource {
 };
 
 template <bool COUNT>
-__global__ void __launch_bounds__(TP_BLOCK)
+__global__ void __launch_bounds__(TP_BLOCK, TP_MINBLOCKS)
 k_pt_trace(QueueSource src, const float4 *__restrict__ nodes, const float4 *__restrict__ tris,
            const int *__restrict__ parent_leaf, int *next_ray, unsigned long long *counters) {
   __shared__ int stack[TP_STACK_SMEM * TP_BLOCK];

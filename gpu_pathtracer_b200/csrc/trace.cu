@@ -29,7 +29,7 @@ struct ArraySource {
 };
 
 template <bool NORMALIZE, bool COUNT>
-__global__ void __launch_bounds__(TP_BLOCK)
+__global__ void __launch_bounds__(TP_BLOCK, TP_MINBLOCKS)
 k_trace(const float4 *__restrict__ nodes, const float4 *__restrict__ tris,
         const int *__restrict__ parent_leaf, ArraySource<NORMALIZE> src, int *next_ray,
         unsigned long long *counters) {

@@ -13,7 +13,16 @@
 #include "trace_core.cuh"
 
 constexpr int TP_BLOCK = 128;
-constexpr int TP_STACK_SMEM = 32;   // levels kept in shared memory; deeper levels spill to local
+#ifndef TP_STACK_SMEM_V
+#define TP_STACK_SMEM_V 32
+#endif
+#ifndef TP_MINBLOCKS
+#define TP_MINBLOCKS 1
+#endif
+#ifndef TP_PREFETCH
+#define TP_PREFETCH 0
+#endif
+constexpr int TP_STACK_SMEM = TP_STACK_SMEM_V;   // levels kept in shared memory; deeper levels spill to local
 #ifndef TP_REFILL_V
 #define TP_REFILL_V 20
 #endif
@@ -147,6 +156,12 @@ __device__ __forceinline__ void trace_persistent(const float4 *__restrict__ node
         const int nearc = (gl && (!gr || lfirst)) ? cref[0] : cref[1];
         const int farc = lfirst ? cref[1] : cref[0];
         if (both && L.sp < TP_STACK_SMEM) stack[L.sp * TP_BLOCK] = farc;
+#if TP_PREFETCH
+        if (both && farc >= 0) {
+          const float4 *fq = nodes + 4 * (size_t)farc;
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(fq));
+        }
+#endif
         if (both && L.sp >= TP_STACK_SMEM) {  // rare: deeper than the shared-memory levels
           if (L.sp < TRACE_STACK) spill[L.sp - TP_STACK_SMEM] = farc;
           else atomicExch(counters + 3, 1ull);
