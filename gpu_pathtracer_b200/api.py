@@ -27,7 +27,7 @@ gpt_rebuild_main_bvh gpt_export_triangles gpt_bvh_num_leaves gpt_export_bvh gpt_
 gpt_trace_device gpt_trace_count_device gpt_render_pathtrace gpt_render_pathtrace_device
 gpt_sppm_init gpt_sppm_pass gpt_sppm_flux_device gpt_sppm_update gpt_sppm_resolve
 gpt_sppm_stats gpt_sppm_export_hit_points gpt_sppm_export_photons gpt_sppm_import_photons
-gpt_sppm_pass_stages gpt_sppm_import_hit_points gpt_stats
+gpt_sppm_pass_stages gpt_sppm_import_hit_points gpt_sss_export_points gpt_stats
 gpt_synchronize gpt_set_profiling""".split()
 
 
@@ -183,6 +183,20 @@ class PathTracer:
     def render_pathtrace_device(self, d_out: int, rank: int = 0, nranks: int = 1):
         self._check(self.lib.gpt_render_pathtrace_device(self.ctx, C.c_void_p(d_out),
                                                          C.c_int(rank), C.c_int(nranks)))
+
+    # -- SSS (src/main.cu:642-824, 1213-1232) ---------------------------------------------
+    def sss_export_points(self, first_pass: bool = True) -> dict:
+        n = C.c_int64()
+        self._check(self.lib.gpt_sss_export_points(self.ctx, 0, None, None, C.c_int64(0),
+                                                   C.byref(n)))
+        obj = np.zeros(n.value, np.int32)
+        rec = np.zeros((n.value, 12), np.float32)
+        if n.value:
+            self._check(self.lib.gpt_sss_export_points(
+                self.ctx, C.c_int(int(first_pass)), cabi.iptr(obj), cabi.fptr(rec),
+                C.c_int64(n.value), C.byref(n)))
+        return dict(object_idx=obj, loc=rec[:, 0:3], filter=rec[:, 3:6], normal=rec[:, 6:9],
+                    color=rec[:, 9:12], rec=rec)
 
     # -- SPPM (render_mode 2, src/main.cu:1282-1870) ---------------------------------------
     def sppm_init(self):

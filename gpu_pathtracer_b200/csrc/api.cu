@@ -46,6 +46,7 @@ int gpt_create(int device, gpt_ctx **out) {
 
 void gpt_render_free(gpt_ctx *ctx);  // render.cu
 void gpt_sppm_free(gpt_ctx *ctx);    // sppm.cu
+void gpt_sss_free(gpt_ctx *ctx);     // sss.cu
 
 static void free_scene(SceneDev &s) {
   void *ptrs[] = {s.x, s.y, s.z, s.xn, s.yn, s.zn, s.xt, s.yt, s.p1, s.p2, s.p3, s.n1, s.n2,
@@ -68,6 +69,7 @@ void gpt_destroy(gpt_ctx *ctx) {
   cudaDeviceSynchronize();
   gpt_render_free(ctx);
   gpt_sppm_free(ctx);
+  gpt_sss_free(ctx);
   for (int k = 0; k < 3; k++) gpt_lbvh_free(ctx->bvh[k]);
   SceneDev &s = ctx->scene;
   free_scene(s);
@@ -122,6 +124,13 @@ int gpt_set_mesh(gpt_ctx *ctx, const GptMesh *m) {
   GPT_TRY(gpt_upload(ctx, &s.t3, m->tex_3_idx, nt));
   GPT_TRY(gpt_upload(ctx, &s.mat_idx, m->material_idx, nt));
   GPT_TRY(gpt_upload(ctx, &s.obj_idx, m->triangle_object_idx, nt));
+  ctx->obj_num.clear();
+  ctx->obj_off.clear();
+  if (m->num_objects > 0 && m->object_num_primitives && m->object_primitive_offset_idx) {
+    ctx->obj_num.assign(m->object_num_primitives, m->object_num_primitives + m->num_objects);
+    ctx->obj_off.assign(m->object_primitive_offset_idx,
+                        m->object_primitive_offset_idx + m->num_objects);
+  }
   GPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // host arrays may be freed after return
   ctx->have_mesh = true;
   return GPT_OK;
@@ -261,6 +270,8 @@ int gpt_build(gpt_ctx *ctx) {
     GPT_TRY(gpt_collect_subset(ctx, mask[k], &bv.prim_list, &cnt));
     GPT_TRY(gpt_lbvh_build(ctx, which[k], bv.prim_list, cnt));
   }
+  // SSS objects: surface point clouds + per-object point LBVHs (src/main.cu:642-824)
+  GPT_TRY(gpt_sss_prepare(ctx));
   GPT_CUDA(ctx, cudaEventRecord(b, ctx->stream));
   GPT_CUDA(ctx, cudaEventSynchronize(b));
   float ms = 0.f;

@@ -11,6 +11,7 @@
 #include <stdint.h>
 
 #include <string>
+#include <vector>
 
 #include "../../include/gpt.h"
 
@@ -103,6 +104,8 @@ struct gpt_ctx {
   unsigned long long *d_counters = nullptr;  // [0] V_int [1] V_leaf [2] rays [3] overflow
   void *render_state = nullptr;              // owned by render.cu
   void *sppm_state = nullptr;                // owned by sppm.cu
+  void *sss_state = nullptr;                 // owned by sss.cu
+  std::vector<int> obj_num, obj_off;         // object_num_primitives / object_primitive_offset_idx
   uint64_t launches = 0;                     // kernels launched since last reset
   bool prof_time_stages = false, prof_count_visits = false;
 };
@@ -168,11 +171,30 @@ int gpt_lbvh_export(gpt_ctx *ctx, int which, uint32_t *morton, int32_t *sorted_t
                     int32_t *parent_leaf, float *node_aabb, float *leaf_aabb,
                     float *world_aabb);
 int gpt_lbvh_build_boxes(gpt_ctx *ctx, BvhDev &b, const float *d_aabb, const int *d_prim_list,
-                         int n, bool with_tris);                      // lbvh.cu
+                         int n, bool with_tris,
+                         const uint32_t *d_keys = nullptr);           // lbvh.cu
 void gpt_lbvh_free(BvhDev &b);
 int gpt_collect_subset(gpt_ctx *ctx, int flag_mask, int **d_list, int *count);  // lbvh.cu
 int gpt_trace_launch(gpt_ctx *ctx, int which, const float4 *d_rays, int64_t n,
                      float4 *d_hits, bool normalize, bool count);     // trace.cu
+// SSS (sss.cu): point clouds + per-object point trees at build time; the first pass (radiance
+// at the points) runs through the path-tracing wavefront (render.cu) on first use
+struct SssTree {           // per scene OBJECT; n == 0 for objects without sub-surface scattering
+  const float4 *nodes;     // AABB node64 of the object's point LBVH
+  const float4 *leaf;      // 2 float4 per point in leaf order: (location, -) (colour, -)
+  int n;
+  int pad;
+};
+struct SssView {
+  const SssTree *trees;    // device, one per object; nullptr when the scene has no SSS points
+  const float4 *pts;       // 3 float4 per point, tree order: (loc, filter.r)(filter.gb, normal.xy)(normal.z, -, -, -)
+  float4 *leaf;            // all trees' leaf records, tree order (colour written by the first pass)
+  const uint32_t *rng;     // rand_state_sss, 6 planes of stride npoints
+  int npoints;
+};
+int gpt_sss_prepare(gpt_ctx *ctx);                                   // sss.cu
+bool gpt_sss_view(gpt_ctx *ctx, SssView *out, bool *first_pass_done);  // sss.cu
+void gpt_sss_mark_first_pass_done(gpt_ctx *ctx);                     // sss.cu
 // stable LSD radix sort of (key, value) pairs on key bits [0, nbits)   // lbvh.cu
 int gpt_radix_sort_pairs(gpt_ctx *ctx, uint32_t *keys, int *vals, uint32_t *keys_alt,
                          int *vals_alt, uint32_t *block_hist, int n, int nbits,

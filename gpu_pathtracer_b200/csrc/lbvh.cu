@@ -398,8 +398,16 @@ static int lbvh_reserve(gpt_ctx *ctx, BvhDev &b, int n, bool with_tris) {
 // NULL).  with_tris also packs the 48-byte trace triangles (triangle BVHs); point BVHs (SPPM
 // photons, SSS samples) pass false.  All work is enqueued on ctx->stream; nothing
 // synchronises with the host.
+__global__ void __launch_bounds__(256)
+k_copy_keys(const uint32_t *__restrict__ src, int n, uint32_t *keys, int *vals) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  keys[i] = src[i];
+  vals[i] = i;
+}
+
 int gpt_lbvh_build_boxes(gpt_ctx *ctx, BvhDev &b, const float *aabb, const int *d_prim_list,
-                         int n, bool with_tris) {
+                         int n, bool with_tris, const uint32_t *d_keys) {
   if (n < 2) {  // the reference cannot build or traverse such a tree (note 9)
     b.n = n;
     return GPT_OK;
@@ -416,7 +424,10 @@ int gpt_lbvh_build_boxes(gpt_ctx *ctx, BvhDev &b, const float *aabb, const int *
   GPT_LAUNCH_CHECK(ctx);
   // keys/vals ping-pong between (morton, sorted_prim) and (keys_alt, vals_alt); 30 bits = 4
   // passes, an even number, so the result lands back in (morton, sorted_prim).
-  k_morton<<<grid, 256, 0, st>>>(aabb, d_prim_list, n, b.world_enc, b.morton, b.sorted_prim);
+  if (d_keys)  // caller-computed codes (the SSS point clouds normalise against their own box)
+    k_copy_keys<<<grid, 256, 0, st>>>(d_keys, n, b.morton, b.sorted_prim);
+  else
+    k_morton<<<grid, 256, 0, st>>>(aabb, d_prim_list, n, b.world_enc, b.morton, b.sorted_prim);
   GPT_LAUNCH_CHECK(ctx);
   uint32_t *ko; int *vo;
   GPT_TRY(gpt_radix_sort_pairs(ctx, b.morton, b.sorted_prim, b.keys_alt, b.vals_alt,
@@ -436,7 +447,7 @@ int gpt_lbvh_build_boxes(gpt_ctx *ctx, BvhDev &b, const float *aabb, const int *
 }
 
 int gpt_lbvh_build(gpt_ctx *ctx, int which, const int *d_prim_list, int n) {
-  return gpt_lbvh_build_boxes(ctx, ctx->bvh[which], ctx->scene.aabb, d_prim_list, n, true);
+  return gpt_lbvh_build_boxes(ctx, ctx->bvh[which], ctx->scene.aabb, d_prim_list, n, true, nullptr);
 }
 
 // Ordered list of the triangles whose flags & mask != 0, taken in MAIN-BVH sorted order.

@@ -16,7 +16,7 @@ struct TriShade {  // unpacked per-triangle shading record (common.cuh)
   float u1, v1, u2, v2, u3, v3;
   V3 g1, g2, g3;
   float area;
-  int mat, flags;
+  int mat, flags, obj;
 };
 __device__ __forceinline__ TriShade load_tri_shade(const float4 *__restrict__ shade, int prim) {
   const float4 *o = shade + 7 * (size_t)prim;
@@ -29,6 +29,7 @@ __device__ __forceinline__ TriShade load_tri_shade(const float4 *__restrict__ sh
   t.g1 = V3{s4.x, s4.y, s4.z}; t.g2 = V3{s4.w, s5.x, s5.y}; t.g3 = V3{s5.z, s5.w, s6.x};
   t.mat = __float_as_int(s6.y);
   t.flags = __float_as_int(s6.z);
+  t.obj = __float_as_int(s6.w);
   return t;
 }
 

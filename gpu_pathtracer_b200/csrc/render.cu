@@ -41,6 +41,10 @@ struct RenderParams {
   const float *bg_r, *bg_g, *bg_b;
   int bg_h, bg_w;
   float inv_samples;  // (float)(1.0 / sample_size / dof_sample_size)
+  int mode;           // 0 = camera paths into the frame buffer, 1 = SSS first pass (paths start
+                      //     at the SSS points, do_sss_first_pass pathtracing.h:202-249)
+  int use_sss;        // mode 0: SSS point trees exist -> compute_color_sss at SSS hits
+  SssView sss;
 };
 
 // ---- RNG init: curand_init(1984, pixel_index, 0) (general.h:15) ---------------------------
@@ -138,6 +142,84 @@ __device__ __forceinline__ void start_sample(PathState &ps, int slot, V3 o, V3 d
   for (int k = 0; k < MATLIST_MAX; k++) l.id[k] = MAT_AIR;
   l.len = 1;  // add_new_material(material_list, length, nullptr)  (pathtracing.h:106)
   matlist_store(reinterpret_cast<uint4 *>(ps.cm + 2 * (size_t)slot + 1), l);
+}
+
+// SSS first pass: slot s = point s (tree order); its stream is rand_state_sss[s]
+__global__ void __launch_bounds__(PT_BLOCK)
+k_sss_start(PathState ps, RenderParams p, int n) {
+  int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n) return;
+  Rng rng;
+  rng_load(rng, p.sss.rng, s, n);
+  float4 a = __ldg(p.sss.pts + 3 * (size_t)s), b = __ldg(p.sss.pts + 3 * (size_t)s + 1),
+         c = __ldg(p.sss.pts + 3 * (size_t)s + 2);
+  V3 o = V3{a.x, a.y, a.z}, nrm = V3{b.z, b.w, c.x};
+  V3 d = generate_dir(V3{0.f, 0.f, 0.f}, nrm, 0, 1.f, rng);
+  rng_store_packed(rng, ps.rng, s);
+  ps.pixel[s] = s;
+  ps.cam[2 * (size_t)s] = make_float4(o.x, o.y, o.z, 0.f);
+  ps.cam[2 * (size_t)s + 1] = make_float4(nrm.x, nrm.y, nrm.z, 0.f);
+  ps.ma[2 * (size_t)s] = make_float4(1.f, 1.f, 1.f, __int_as_float(0));
+  ps.ma[2 * (size_t)s + 1] = make_float4(0.f, 0.f, 0.f, __int_as_float(0));
+  ps.cm[2 * (size_t)s] = make_float4(0.f, 0.f, 0.f, __int_as_float(0));
+  start_sample(ps, s, o, d);
+  ps.queue[0][s] = s;
+}
+
+// compute_color_sss + traverse_bvh_pts (pathtracing_sss.h:17-42, bvh_traversal_pts.h:14-104):
+// inverse-distance weighted mean of the point colours within path_length of the hit, in the
+// reference's left-first visit order (the fp32 sums are order dependent).
+static __device__ __noinline__ V3 sss_lookup(const SssTree &t, V3 c, float r, bool &found) {
+  V3 color = V3{0.f, 0.f, 0.f};
+  float sum_w = 0.f;
+  found = false;
+  if (t.n < 2) return color;
+  int stack[64];
+  int sp = 0, node = 0;
+  while (true) {
+    const float4 *q = t.nodes + 4 * (size_t)node;
+    float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3);
+    int cref[2] = {__float_as_int(q3.x), __float_as_int(q3.y)};
+    float bxn[2] = {q0.x, q1.z}, bxx[2] = {q0.y, q1.w};
+    float byn[2] = {q0.z, q2.x}, byx[2] = {q0.w, q2.y};
+    float bzn[2] = {q1.x, q2.z}, bzx[2] = {q1.y, q2.w};
+    bool isect[2];
+#pragma unroll
+    for (int k = 0; k < 2; k++) {  // BoundingBox::is_intersection(BoundingSphere) (bounding_box.h:296-312)
+      float cx = 0.5f * (bxn[k] + bxx[k]), cy = 0.5f * (byn[k] + byx[k]), cz = 0.5f * (bzn[k] + bzx[k]);
+      isect[k] = fabsf(cx - c.x) <= (bxx[k] - cx) + r && fabsf(cy - c.y) <= (byx[k] - cy) + r &&
+                 fabsf(cz - c.z) <= (bzx[k] - cz) + r;
+    }
+#pragma unroll
+    for (int k = 0; k < 2; k++) {
+      if (isect[k] && cref[k] < 0) {
+        const float4 *lf = t.leaf + 2 * (size_t)(~cref[k]);
+        float4 a = __ldg(lf);
+        float d = dist(c, V3{a.x, a.y, a.z});
+        if (d <= r) {
+          float4 col = __ldg(lf + 1);
+          found = true;
+          float w = 1.0f / dist(V3{a.x, a.y, a.z}, c);
+          w = (float)fmin(9999.99, (double)w);
+          sum_w += w;
+          color = color + w * V3{col.x, col.y, col.z};
+        }
+      }
+    }
+    bool tl = isect[0] && cref[0] >= 0, tr = isect[1] && cref[1] >= 0;
+    if (!tl && !tr) {
+      if (sp == 0) break;
+      node = stack[--sp];
+    } else {
+      node = tl ? cref[0] : cref[1];
+      if (tl && tr && sp < 64) stack[sp++] = cref[1];
+    }
+  }
+  if (found) {
+    float k = 1.0f / sum_w;  // vec3::operator/=(float): k = 1.0 / t, then three multiplies
+    color = V3{color.x * k, color.y * k, color.z * k};
+  }
+  return color;
 }
 
 __global__ void __launch_bounds__(PT_BLOCK)
@@ -239,16 +321,23 @@ k_pt_shade(PathState ps, RenderParams p, const int *__restrict__ queue,
       bool sss = false;
       check_next_path<false>(sc.mats, atlas, ts.mat, dir, normal, u, v, list, ref, sss, rng, false);
       float factor = 1.f;
-      if (!ref.false_hit)
+      const bool sss_hit = sss && p.use_sss;  // `sss && !sss_first_pass` (pathtracing.h:129-142)
+      if (!ref.false_hit && !sss_hit)
         factor = change_ref_ray(lt, sc.shade, sc.mats, atlas, point, normal, dir, ref,
                                 p.pdf_weight, rng);
+      if (sss_hit) {  // return compute_color_sss(...): the sample IS the point-cloud estimate
+        bool found;
+        V3 col = sss_lookup(p.sss.trees[ts.obj], point, m.path_length, found);
+        result = found ? col * mat_diffuse(atlas, m, u, v) : V3{0.f, 0.f, 0.f};
+        done = true;
+      }
       // material list bookkeeping (pathtracing.h:144-162)
       bool ok = true;
       if ((ref.false_hit || ref.refracted) && ref.entering) ok = matlist_add(list, ts.mat);
       else if ((ref.false_hit || ref.refracted) && !ref.entering) matlist_remove(list, ts.mat);
-      if (!ok) *error_flag = 1;
+      if (!ok && !sss_hit) *error_flag = 1;
       matlist_store(reinterpret_cast<uint4 *>(ps.cm + 2 * (size_t)s + 1), list);
-      if (!ref.false_hit) {
+      if (!ref.false_hit && !sss_hit) {
         V3 add = de_nan(mask * mat_emission(atlas, m, u, v));
         acc = acc + add;
         if (factor > 0.f) {
@@ -282,7 +371,16 @@ k_pt_shade(PathState ps, RenderParams p, const int *__restrict__ queue,
       sidx++;
       V3 o, d;
       bool finished = false;
-      if (sidx >= p.sample_size) {
+      if (p.mode == 1) {
+        // do_sss_first_pass: every sample draws a fresh cosine-hemisphere ray at the point
+        if (sidx >= p.sample_size) {
+          finished = true;
+        } else {
+          float4 co = ps.cam[2 * (size_t)s], cn = ps.cam[2 * (size_t)s + 1];
+          o = V3{co.x, co.y, co.z};
+          d = generate_dir(V3{0.f, 0.f, 0.f}, V3{cn.x, cn.y, cn.z}, 0, 1.f, rng);
+        }
+      } else if (sidx >= p.sample_size) {
         sidx = 0;
         k++;
         if (k >= p.dof_size) {
@@ -298,7 +396,13 @@ k_pt_shade(PathState ps, RenderParams p, const int *__restrict__ queue,
         o = V3{co.x, co.y, co.z};
         d = V3{cd.x, cd.y, cd.z};
       }
-      if (finished) {
+      if (finished && p.mode == 1) {
+        // color *= (1.0 / sample_size); color *= filter; point -> assign_color(color)
+        float4 pa = __ldg(p.sss.pts + 3 * (size_t)s), pb = __ldg(p.sss.pts + 3 * (size_t)s + 1);
+        V3 out = (color * p.inv_samples) * V3{pa.w, pb.x, pb.y};
+        p.sss.leaf[2 * (size_t)s + 1] = make_float4(out.x, out.y, out.z, 0.f);
+        alive = false;
+      } else if (finished) {
         int pix = ps.pixel[s];
         V3 out = color * p.inv_samples;
         fb[3 * (size_t)pix] = out.x; fb[3 * (size_t)pix + 1] = out.y; fb[3 * (size_t)pix + 2] = out.z;
@@ -403,23 +507,38 @@ static std::vector<int> tile_pixels(int W, int H, int rank, int nranks) {
   return px;
 }
 
-static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks) {
+static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool sss_pass = false) {
   if (!ctx->built) return gpt_fail(ctx, GPT_E_INVALID, "gpt_build first", __FILE__, __LINE__);
   if (!ctx->have_cam) return gpt_fail(ctx, GPT_E_INVALID, "gpt_set_camera first", __FILE__, __LINE__);
   if (nranks < 1 || rank < 0 || rank >= nranks) return GPT_E_INVALID;
   const GptParams &gp = ctx->params;
   if (gp.pathtracing_sample_size < 1 || gp.pathtracing_level < 1 || gp.dof_sample_size < 1)
     return gpt_fail(ctx, GPT_E_INVALID, "sample_size, level and dof_sample_size must be >= 1", __FILE__, __LINE__);
-  for (int i = 0; i < ctx->scene.nmat; i++) { /* SSS is a "next" row */ }
   GPT_CUDA(ctx, cudaSetDevice(ctx->device));
   RenderCtx *rc = rc_of(ctx);
+  SssView sv{};
+  bool sss_done = true;
+  const bool have_sss = gpt_sss_view(ctx, &sv, &sss_done);
+  if (sss_pass && !have_sss) return GPT_OK;
+  if (!sss_pass && have_sss && !sss_done) {
+    // "Doing first pass for SSS objects" (src/main.cu:1213-1232), once per build
+    GPT_TRY(render_device(ctx, d_fb, 0, 1, true));
+    gpt_sss_mark_first_pass_done(ctx);
+  }
   ctx->launches = 0;
   int W = ctx->cam.width, H = ctx->cam.height;
   bool new_map = !(rc->rng_w == W && rc->rng_h == H && rc->rng_rank == rank &&
                    rc->rng_nranks == nranks);
   std::vector<int> px;
   int n;
-  if (new_map) {
+  if (sss_pass) {
+    n = sv.npoints;
+    int cap_before = rc->ps.capacity;
+    GPT_TRY(reserve_paths(ctx, rc, n));
+    if (rc->ps.capacity != cap_before) rc->light_n = 0;
+    new_map = false;
+    rc->rng_w = rc->rng_h = 0;  // the slot -> pixel map is overwritten by this pass
+  } else if (new_map) {
     px = tile_pixels(W, H, rank, nranks);
     n = (int)px.size();
     GPT_TRY(reserve_paths(ctx, rc, n));
@@ -455,7 +574,11 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks) {
   p.sky = V3{gp.sky_emission[0], gp.sky_emission[1], gp.sky_emission[2]};
   p.bg_r = ctx->scene.bg_r; p.bg_g = ctx->scene.bg_g; p.bg_b = ctx->scene.bg_b;
   p.bg_h = ctx->scene.bg_h; p.bg_w = ctx->scene.bg_w;
-  p.inv_samples = (float)(1.0 / gp.pathtracing_sample_size / gp.dof_sample_size);
+  p.inv_samples = sss_pass ? (float)(1.0 / gp.pathtracing_sample_size)
+                           : (float)(1.0 / gp.pathtracing_sample_size / gp.dof_sample_size);
+  p.mode = sss_pass ? 1 : 0;
+  p.use_sss = (!sss_pass && have_sss) ? 1 : 0;
+  p.sss = sv;
 
   BvhDev &mb = ctx->bvh[GPT_BVH_MAIN], &lb = ctx->bvh[GPT_BVH_LIGHT];
   LightTree lt{lb.nodes, lb.tris, lb.parent_leaf, rc->leaf_info, rc->node_info, lb.n};
@@ -463,11 +586,15 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks) {
   cudaStream_t st = ctx->stream;
 
   GPT_CUDA(ctx, cudaEventRecord(ctx->ev0, st));
-  GPT_CUDA(ctx, cudaMemcpyAsync(ps.rng, rc->rng_init, sizeof(uint32_t) * 8 * (size_t)n,
-                                cudaMemcpyDeviceToDevice, st));
+  if (!sss_pass)
+    GPT_CUDA(ctx, cudaMemcpyAsync(ps.rng, rc->rng_init, sizeof(uint32_t) * 8 * (size_t)n,
+                                  cudaMemcpyDeviceToDevice, st));
   int init_counts[4] = {n, 0, 0, 0};
   GPT_CUDA(ctx, cudaMemcpyAsync(ps.counts, init_counts, sizeof(init_counts), cudaMemcpyHostToDevice, st));
-  k_pt_start<<<(n + PT_BLOCK - 1) / PT_BLOCK, PT_BLOCK, 0, st>>>(ps, p, n, d_fb);
+  if (sss_pass)
+    k_sss_start<<<(n + PT_BLOCK - 1) / PT_BLOCK, PT_BLOCK, 0, st>>>(ps, p, n);
+  else
+    k_pt_start<<<(n + PT_BLOCK - 1) / PT_BLOCK, PT_BLOCK, 0, st>>>(ps, p, n, d_fb);
   GPT_LAUNCH_CHECK(ctx);
   int active = n, cur = 0;
   int *next_ray = reinterpret_cast<int *>(ctx->d_counters + 4);
@@ -576,6 +703,17 @@ void gpt_render_free(gpt_ctx *ctx) {
   for (cudaEvent_t e : rc->events) cudaEventDestroy(e);
   delete rc;
   ctx->render_state = nullptr;
+}
+
+// do_sss_first_pass on demand (parity export); a render runs it automatically
+int gpt_render_sss_first_pass(gpt_ctx *ctx) {
+  if (!ctx) return GPT_E_INVALID;
+  SssView sv{};
+  bool done = true;
+  if (!gpt_sss_view(ctx, &sv, &done) || done) return GPT_OK;
+  GPT_TRY(render_device(ctx, nullptr, 0, 1, true));
+  gpt_sss_mark_first_pass_done(ctx);
+  return GPT_OK;
 }
 
 int gpt_render_pathtrace_device(gpt_ctx *ctx, void *d_out_rgb, int rank, int nranks) {

@@ -420,7 +420,7 @@ def bottle_scene(width=1920, height=1080, spp=8, dof=8, level=8, name="C3") -> S
 
 def small_scene(n: int = 24, width: int = 128, height: int = 128, spp: int = 2,
                 level: int = 4, glass: bool = True, metal: bool = True,
-                textured: bool = False, name: str = "small") -> Scene:
+                textured: bool = False, sss_pts: int = 0, name: str = "small") -> Scene:
     """Small everything-in-one scene for parity tests that the host replay finishes fast."""
     mats = MaterialBuilder()
     kw = {}
@@ -443,9 +443,17 @@ def small_scene(n: int = 24, width: int = 128, height: int = 128, spp: int = 2,
         mb.add(sv, sf, m_glass, normals=sn)
         sv, sf, sn = icosphere((3.0, 2.0, 1.0), 1.2, 2)
         mb.add(sv, sf, m_liquid, normals=sn)
+    if sss_pts:
+        # two sub-surface-scattering objects (path_length > 0): point clouds per OBJECT
+        m_wax = mats.add("wax", kd=(0.8, 0.55, 0.4), path_length=0.6)
+        sv, sf, sn = icosphere((0.0, 3.0, 3.0), 1.2, 2)
+        mb.add(sv, sf, m_wax, normals=sn)
+        sv, sf, sn = icosphere((-4.0, 3.5, 3.5), 0.8, 1)
+        mb.add(sv, sf, m_wax, normals=sn)
     _add_lights(mb, m_light)
     return Scene(mb.finish(), mats.finish(), default_camera(width, height),
-                 default_params(pathtracing_sample_size=spp, pathtracing_level=level),
+                 default_params(pathtracing_sample_size=spp, pathtracing_level=level,
+                                sss_pts_per_object=sss_pts),
                  name=name)
 
 

@@ -184,6 +184,16 @@ int gpt_render_pathtrace(gpt_ctx *ctx, float *out_rgb);
  * are left untouched in d_out_rgb (DEVICE pointer, P x 3).  Asynchronous. */
 int gpt_render_pathtrace_device(gpt_ctx *ctx, void *d_out_rgb, int rank, int nranks);
 
+/* ---- sub-surface scattering: replaces src/main.cu:642-824 (point clouds per
+ *      SSS object + per-object point LBVHs, built by gpt_build when sss_pts_per_object > 0),
+ *      do_sss_first_pass (src/main.cu:1213-1232, run automatically by the first render) and
+ *      compute_color_sss / traverse_bvh_pts inside the bounce loop.
+ *      Parity export, points in tree order: object index + 12 floats (location, filter, normal,
+ *      colour); run_first_pass != 0 computes the colours first.  *count = number of points;
+ *      nothing is written when capacity < *count. -------------------------------------------- */
+int gpt_sss_export_points(gpt_ctx *ctx, int run_first_pass, int32_t *object_idx, float *rec12,
+                          int64_t capacity, int64_t *count);
+
 /* ---- SPPM: replaces the render_mode == 2 branch, src/main.cu:1282-1870 ------------------
  * Call order of one frame (single GPU):
  *     gpt_sppm_init(ctx);

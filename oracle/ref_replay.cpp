@@ -114,7 +114,8 @@ struct RefCtx {
   // inputs
   std::vector<float> x, y, z, xn, yn, zn, xt, yt;
   std::vector<int> p1, p2, p3, n1, n2, n3, t1, t2, t3, mat_idx, obj_idx;
-  int num_triangles = 0, num_vertices = 0;
+  std::vector<int> obj_num, obj_off;
+  int num_triangles = 0, num_vertices = 0, num_objects = 0;
   std::vector<float> tex_r, tex_g, tex_b, bg_r, bg_g, bg_b;
   int bg_h = 1, bg_w = 1;
   GptMaterials mats{};
@@ -134,6 +135,20 @@ struct RefCtx {
   double last_ms = 0;
   unsigned long long last_rays = 0;
   struct Sppm *sppm = nullptr;
+  struct Sss *sss = nullptr;
+};
+
+// SSS state, the locals of src/main.cu:555-824
+struct Sss {
+  Object **my_objects = nullptr;
+  float *triangle_area = nullptr, *accumulated_triangle_area = nullptr;
+  int num_sss_objects = 0, num_sss_points = 0, pts_per_object = 0;
+  int *pt_offset_array = nullptr, *num_pt_array = nullptr;
+  Point **sss_pts = nullptr;
+  curandState *rand_state_sss = nullptr;
+  Node **node_list = nullptr, **leaf_list = nullptr;
+  unsigned int *morton = nullptr;
+  bool first_pass_done = false;
 };
 
 // SPPM state, the locals of main()'s render_mode == 2 branch (src/main.cu:1282-1494)
@@ -190,6 +205,117 @@ Bvh *pick(RefCtx *c, int which) {
 
 }  // namespace
 
+// SSS pre-pass set-up, src/main.cu:555-824: objects, area CDFs, surface point samples, the
+// per-object point LBVHs.  create_sss_pts is launched once PER POINT with rand_state =
+// &state[idx] (the reference passes the global array to get_random_point_on_surface, so all
+// threads race on rand_state[0], object_operations.h:135-136; the per-point launch makes
+// rand_state[0] that point's own state -- deterministic, same convention as the photons).
+static void sss_prepare(RefCtx *c) {
+  int pts = c->params.sss_pts_per_object, nt = c->num_triangles, nobj = c->num_objects;
+  if (pts <= 0 || nobj <= 0) return;
+  Sss *s = new Sss();
+  s->pts_per_object = pts;
+  s->triangle_area = new float[nt];
+  s->accumulated_triangle_area = new float[nt];
+  s->my_objects = new Object *[nobj];
+  for (int i = 0; i < nobj; i++)  // create_objects (src/lib/world.h:177-192): marshalling only
+    s->my_objects[i] = new Object(c->obj_off[i], c->obj_num[i], s->triangle_area + c->obj_off[i],
+                                  s->accumulated_triangle_area + c->obj_off[i]);
+  bool any = false;
+  for (int i = 0; i < nt; i++) {  // the tail of create_world (src/lib/world.h:236-246)
+    s->triangle_area[i] = c->my_geom[i]->get_area();
+    if (c->my_geom[i]->is_sub_surface_scattering()) {
+      s->my_objects[c->obj_idx[i]]->set_as_sub_surface_scattering(pts);
+      any = true;
+    }
+  }
+  if (!any) { delete s; return; }
+  s->pt_offset_array = new int[nobj];
+  s->num_pt_array = new int[nobj];
+  launch_1d(1, 1, [&] {
+    compute_num_sss_objects(&s->num_sss_objects, s->my_objects, s->pt_offset_array,
+                            s->num_pt_array, nobj, pts);
+  });
+  int n = pts * s->num_sss_objects;
+  s->num_sss_points = n;
+  s->sss_pts = new Point *[std::max(1, n)];
+  launch_1d(nobj, 1, [&] { allocate_pts_sss(s->my_objects, s->sss_pts, s->pt_offset_array, nobj); });
+  s->rand_state_sss = new curandState[std::max(1, n)];
+  launch_1d(std::max(1, n), 1, [&] { init_curand_state(n, s->rand_state_sss); });
+  for (int i = 0; i < nobj; i++) {
+    if (!s->my_objects[i]->sub_surface_scattering) continue;
+    for (int idx = 0; idx < pts; idx++) {
+      // one launch per point: the kernel's thread 0 sees rand_state[0] = state[idx] and
+      // writes point_array[pt_offset[i] + 0]
+      launch_1d(1, 1, [&] {
+        create_sss_pts(s->my_objects, c->my_geom, s->sss_pts + idx, s->pt_offset_array,
+                       s->rand_state_sss + idx, i, pts);
+      });
+    }
+  }
+  launch_1d(nobj, 1, [&] { compute_object_boundaries_batch(s->my_objects, nobj); });
+  launch_1d(nt + 1, 1, [&] { compute_pts_morton_code_batch(s->my_objects, s->sss_pts, n); });
+  for (int i = 0; i < nobj; i++)
+    std::stable_sort(s->sss_pts + s->pt_offset_array[i],
+                     s->sss_pts + s->pt_offset_array[i] + s->num_pt_array[i],
+                     [](Point *a, Point *b) {
+                       return a->bounding_box->morton_code < b->bounding_box->morton_code;
+                     });
+  launch_1d(1, 1, [&] { compute_sss_pts_offset(s->my_objects, nobj); });
+  s->node_list = new Node *[std::max(1, n - s->num_sss_objects)];
+  s->leaf_list = new Node *[std::max(1, n)];
+  for (int i = 0; i < nobj; i++)
+    launch_1d(std::max(1, n), 1, [&] {
+      build_sss_pts_leaf_list(s->leaf_list, s->sss_pts, s->my_objects, i, s->pt_offset_array);
+    });
+  for (int i = 0; i < nobj; i++)
+    launch_1d(std::max(1, n), 1,
+              [&] { build_sss_pts_node_list(s->node_list, s->my_objects, i); });
+  s->morton = new unsigned int[std::max(1, n)];
+  launch_1d(std::max(1, n), 1, [&] { extract_sss_morton_code_list(s->sss_pts, s->morton, n); });
+  for (int i = 0; i < nobj; i++)
+    launch_1d(std::max(1, n), 1, [&] {
+      set_pts_sss_node_relationship(s->node_list, s->leaf_list, s->morton, s->my_objects, i);
+    });
+  launch_1d(std::max(1, n), 1,
+            [&] { compute_node_bounding_boxes(s->leaf_list, s->node_list, n); });
+  c->sss = s;
+}
+
+// do_sss_first_pass (src/main.cu:1213-1232, pathtracing.h:202-249) over all points, threaded
+static void sss_first_pass(RefCtx *c, int nthreads) {
+  Sss *s = c->sss;
+  if (!s || s->first_pass_done) return;
+  const GptParams &p = c->params;
+  vec3 sky(p.sky_emission[0], p.sky_emission[1], p.sky_emission[2]);
+  int n = s->num_sss_points;
+  std::atomic<int> next(0);
+  auto work = [&] {
+    shim_blockDim = dim3(1, 1, 1);
+    shim_threadIdx = {0, 0, 0};
+    for (;;) {
+      int k = next.fetch_add(64);
+      if (k >= n) break;
+      for (int q = k; q < std::min(n, k + 64); q++) {
+        shim_blockIdx = {(unsigned)q, 0, 0};
+        do_sss_first_pass(s->sss_pts, n, p.pathtracing_sample_size, p.pathtracing_level, sky,
+                          c->bg_h, c->bg_w, c->bg_r.data(), c->bg_g.data(), c->bg_b.data(),
+                          c->main_bvh.node_list, s->rand_state_sss, c->light_bvh.geom,
+                          c->light_bvh.node_list, c->light_bvh.leaf_list, c->light_bvh.n,
+                          p.hittable_pdf_weight);
+      }
+    }
+    shim_blockIdx = {0, 0, 0};
+  };
+  if (nthreads <= 1) work();
+  else {
+    std::vector<std::thread> th;
+    for (int k = 0; k < nthreads; k++) th.emplace_back(work);
+    for (auto &x : th) x.join();
+  }
+  s->first_pass_done = true;
+}
+
 extern "C" {
 
 int ref_create(RefCtx **out) {
@@ -225,6 +351,10 @@ int ref_set_mesh(RefCtx *c, const GptMesh *m) {
   cpi(c->t3, m->tex_3_idx);
   cpi(c->mat_idx, m->material_idx);
   cpi(c->obj_idx, m->triangle_object_idx);
+  c->num_objects = m->num_objects;
+  c->obj_num.assign(m->object_num_primitives, m->object_num_primitives + m->num_objects);
+  c->obj_off.assign(m->object_primitive_offset_idx,
+                    m->object_primitive_offset_idx + m->num_objects);
   c->num_triangles = nt;
   c->num_vertices = m->num_vertices;
   c->have_mesh = true;
@@ -347,6 +477,9 @@ int ref_build(RefCtx *c) {
     sum_up_tangent_and_bitangent(tangent.data(), bitangent.data(), geom, nt);
   });
   launch_1d(nt, 1, [&] { assign_tangent(tangent.data(), geom, nt); });
+
+  // SSS objects / points / per-object point trees  src/main.cu:555-824 (before the sort)
+  sss_prepare(c);
 
   // main BVH  src/main.cu:826-918
   c->main_bvh.n = nt;
@@ -582,6 +715,10 @@ int ref_render_pathtrace_window(RefCtx *c, float *out_rgb, int row0, int row1, i
   col1 = std::min(col1, W);
   std::atomic<int> next_row(row0);
   std::atomic<unsigned long long> total_rays(0);
+  g_counted_root = nullptr;
+  sss_first_pass(c, nthreads);  // src/main.cu:1213-1232 (not part of the timed "Rendering")
+  Object **objs = c->sss ? c->sss->my_objects : nullptr;
+  Node **sss_nodes = c->sss ? c->sss->node_list : nullptr;
   g_counted_root = c->main_bvh.node_list[0];
   auto t0 = std::chrono::steady_clock::now();
   auto work = [&] {
@@ -597,7 +734,7 @@ int ref_render_pathtrace_window(RefCtx *c, float *out_rgb, int row0, int row1, i
         path_tracing_render(fb.data(), c->my_camera, rs.data(), p.pathtracing_sample_size,
                             p.pathtracing_level, p.dof_sample_size, sky, c->bg_h, c->bg_w,
                             c->bg_r.data(), c->bg_g.data(), c->bg_b.data(),
-                            c->main_bvh.node_list, nullptr, nullptr,
+                            c->main_bvh.node_list, objs, sss_nodes,
                             c->light_bvh.node_list, c->light_bvh.leaf_list,
                             c->light_bvh.geom, c->light_bvh.n, p.hittable_pdf_weight);
         float *o = out_rgb + 3 * ((size_t)i * W + j);
@@ -620,6 +757,26 @@ int ref_render_pathtrace_window(RefCtx *c, float *out_rgb, int row0, int row1, i
 }
 
 unsigned long long ref_last_rays(RefCtx *c) { return c->last_rays; }
+
+// SSS points in tree (sorted) order: object index + 12 floats (location, filter, normal,
+// colour after the first pass).  *count = number of points; arrays may be NULL.
+int ref_sss_export_points(RefCtx *c, int run_first_pass, int32_t *object_idx, float *rec12,
+                          int64_t *count, int nthreads) {
+  if (!c->sss) { *count = 0; return GPT_OK; }
+  Sss *s = c->sss;
+  if (run_first_pass) sss_first_pass(c, nthreads);
+  *count = s->num_sss_points;
+  for (int i = 0; i < s->num_sss_points; i++) {
+    Point *p = s->sss_pts[i];
+    if (object_idx) object_idx[i] = p->object_idx;
+    if (rec12) {
+      const vec3 *v[4] = {&p->location, &p->filter, &p->normal, &p->color};
+      for (int a = 0; a < 4; a++)
+        for (int b = 0; b < 3; b++) rec12[12 * (size_t)i + 3 * a + b] = (*v[a])[b];
+    }
+  }
+  return GPT_OK;
+}
 
 }  // extern "C"
 

@@ -180,3 +180,16 @@ class RefReplay:
         _check(self.lib.ref_sppm_resolve(self.ctx, C.c_int(ref_mode), C.c_int(passes),
                                          cabi.fptr(out)))
         return out
+
+    # -- SSS pre-pass (src/main.cu:555-824, 1213-1232) -------------------------------------
+    def sss_export_points(self, first_pass=True, nthreads=None) -> dict:
+        n = C.c_int64()
+        nt = C.c_int(nthreads or os.cpu_count() or 1)
+        _check(self.lib.ref_sss_export_points(self.ctx, 0, None, None, C.byref(n), nt))
+        obj = np.zeros(n.value, np.int32)
+        rec = np.zeros((n.value, 12), np.float32)
+        if n.value:
+            _check(self.lib.ref_sss_export_points(self.ctx, int(first_pass), cabi.iptr(obj),
+                                                  cabi.fptr(rec), C.byref(n), nt))
+        return dict(object_idx=obj, loc=rec[:, 0:3], filter=rec[:, 3:6], normal=rec[:, 6:9],
+                    color=rec[:, 9:12], rec=rec)
