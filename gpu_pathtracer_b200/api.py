@@ -27,7 +27,8 @@ gpt_rebuild_main_bvh gpt_export_triangles gpt_bvh_num_leaves gpt_export_bvh gpt_
 gpt_trace_device gpt_trace_count_device gpt_render_pathtrace gpt_render_pathtrace_device
 gpt_sppm_init gpt_sppm_pass gpt_sppm_flux_device gpt_sppm_update gpt_sppm_resolve
 gpt_sppm_stats gpt_sppm_export_hit_points gpt_sppm_export_photons gpt_sppm_import_photons
-gpt_sppm_pass_stages gpt_sppm_import_hit_points gpt_sss_export_points gpt_stats
+gpt_sppm_pass_stages gpt_sppm_import_hit_points gpt_sss_export_points gpt_tonemap_u8 gpt_write_ppm_u8
+gpt_save_image gpt_sppm_debug_image gpt_sss_debug_image gpt_stats
 gpt_synchronize gpt_set_profiling""".split()
 
 
@@ -36,6 +37,17 @@ class GptError(RuntimeError):
 
 
 _lib = None
+
+
+def write_ppm_u8(path: str, rgb_u8: np.ndarray):
+    """ASCII PPM byte-identical to the reference's save_image (host only, no GPU needed)."""
+    lib = load_library()
+    rgb_u8 = np.ascontiguousarray(rgb_u8, dtype=np.uint8)
+    h, w = rgb_u8.shape[:2]
+    rc = lib.gpt_write_ppm_u8(path.encode(), rgb_u8.ctypes.data_as(C.POINTER(C.c_uint8)),
+                              C.c_int32(w), C.c_int32(h))
+    if rc != 0:
+        raise GptError(f"gpt_write_ppm_u8 failed with {rc}")
 
 
 def load_library():
@@ -183,6 +195,32 @@ class PathTracer:
     def render_pathtrace_device(self, d_out: int, rank: int = 0, nranks: int = 1):
         self._check(self.lib.gpt_render_pathtrace_device(self.ctx, C.c_void_p(d_out),
                                                          C.c_int(rank), C.c_int(nranks)))
+
+    # -- output stage (src/util/image_util.h:50-72) and debug splats -------------------------
+    def tonemap_u8(self, rgb: np.ndarray) -> np.ndarray:
+        rgb = np.ascontiguousarray(rgb, dtype=np.float32)
+        out = np.zeros(rgb.shape, np.uint8)
+        self._check(self.lib.gpt_tonemap_u8(self.ctx, cabi.fptr(rgb), C.c_int64(rgb.size),
+                                            out.ctypes.data_as(C.POINTER(C.c_uint8))))
+        return out
+
+    def save_image(self, rgb: np.ndarray, path: str):
+        rgb = np.ascontiguousarray(rgb, dtype=np.float32)
+        h, w = rgb.shape[:2]
+        self._check(self.lib.gpt_save_image(self.ctx, cabi.fptr(rgb), C.c_int32(w), C.c_int32(h),
+                                            path.encode()))
+
+    def sppm_debug_image(self, which: int) -> np.ndarray:
+        cam = self.scene.camera
+        out = np.zeros((cam["height"], cam["width"], 3), np.float32)
+        self._check(self.lib.gpt_sppm_debug_image(self.ctx, C.c_int(which), cabi.fptr(out)))
+        return out
+
+    def sss_debug_image(self) -> np.ndarray:
+        cam = self.scene.camera
+        out = np.zeros((cam["height"], cam["width"], 3), np.float32)
+        self._check(self.lib.gpt_sss_debug_image(self.ctx, cabi.fptr(out)))
+        return out
 
     # -- SSS (src/main.cu:642-824, 1213-1232) ---------------------------------------------
     def sss_export_points(self, first_pass: bool = True) -> dict:

@@ -247,6 +247,17 @@ int gpt_sppm_import_photons(gpt_ctx *ctx, const int32_t *kind, const float *rec1
 int gpt_sppm_import_hit_points(gpt_ctx *ctx, const float *loc_radius,
                                const float *normal_vradius, const float *filter);
 
+/* ---- output stage: replaces save_image (src/util/image_util.h:50-72) ----
+ * display transform (int)(255 * clamp(0, 1, sqrt(c))) of n_values host floats */
+int gpt_tonemap_u8(gpt_ctx *ctx, const float *rgb, int64_t n_values, uint8_t *out);
+/* ASCII PPM exactly as save_image writes it: "P3\nW H\n255\n", then "r g b " per pixel */
+int gpt_write_ppm_u8(const char *path, const uint8_t *rgb_u8, int32_t width, int32_t height);
+int gpt_save_image(gpt_ctx *ctx, const float *rgb, int32_t width, int32_t height, const char *path);
+/* ---- debug splats (8 f-4): create_point_image (point_operations.h:19-75).  which: 0 = SPPM
+ * hit points (colour = filter), 1 = surface photons, 2 = volume photons of the last pass. */
+int gpt_sppm_debug_image(gpt_ctx *ctx, int which, float *out_rgb);
+int gpt_sss_debug_image(gpt_ctx *ctx, float *out_rgb);
+
 /* Profiling switches for the NEXT renders (never on in a timed headline run):
  *   time_stages  - bracket every trace / shade launch with CUDA events (fills
  *                  trace_kernel_ms / shade_kernel_ms)

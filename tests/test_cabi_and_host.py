@@ -89,3 +89,18 @@ def test_ray_sets():
     e = rays.edge_case_rays(sc, 512)
     assert (e[:, 4:7] == 0).any()                            # axis-aligned directions present
     assert np.array_equal(rays.random_rays(100, seed=3), rays.random_rays(100, seed=3))
+
+
+def test_write_ppm_matches_save_image_format(tmp_path):
+    """gpt_write_ppm_u8 writes the bytes the reference's save_image writes
+    (src/util/image_util.h:50-72): header, then "r g b " per pixel, no line breaks."""
+    import numpy as np
+    from gpu_pathtracer_b200 import api
+    rng = np.random.default_rng(3)
+    img = rng.integers(0, 256, size=(7, 5, 3), dtype=np.uint8)
+    img[0, 0] = (0, 9, 10)
+    img[0, 1] = (99, 100, 255)
+    path = str(tmp_path / "a.ppm")
+    api.write_ppm_u8(path, img)
+    want = "P3\n5 7\n255\n" + "".join(f"{int(v)} " for v in img.reshape(-1))
+    assert open(path, "rb").read() == want.encode()
