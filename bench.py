@@ -28,7 +28,8 @@ def parse():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="C2", choices=["C1", "C2", "small"])
+    ap.add_argument("--workload", default="C2", choices=["C1", "C2", "C4", "small"])
+    ap.add_argument("--photons", type=int, default=0, help="C4: photons per pass override")
     ap.add_argument("--mode", default="auto", choices=["auto", "trace", "render"])
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel")
     ap.add_argument("--cpu-budget-s", type=float, default=15.0)
@@ -139,6 +140,11 @@ def reference_window(sc, budget_s: float, nthreads: int):
 def run_reference(args, rank, world):
     """--impl reference: the reference's own CPU code on all host cores (rank 0 only)."""
     if rank != 0:
+        return
+    if args.workload == "C4":
+        print(json.dumps({"impl": "reference", "unavailable":
+                          "the reference arm is wired for the headline workload (C2); SPPM is "
+                          "compared in tools/run_reference_cuda_sppm.py and tests/test_gpu_sppm.py"}))
         return
     sc = make_workload(args.workload, args.spp)
     cores = os.cpu_count() or 1
@@ -317,6 +323,141 @@ def run_ours(args, rank, world, local_rank):
     print(json.dumps(line), flush=True)
 
 
+def run_sppm(args, rank, world, local_rank):
+    """--workload C4: stochastic progressive photon mapping, 10 M photons per pass, 1080p.  A
+    step = one SPPM pass (photon trace of this rank's photon range, photon trees, eye pass,
+    gather, the NCCL all-reduce of the per-hit-point accumulators when N > 1, update)."""
+    import torch
+    import torch.distributed as dist
+    from gpu_pathtracer_b200 import scene as S
+    from gpu_pathtracer_b200.api import PathTracer
+    from gpu_pathtracer_b200.parallel import allreduce_flux, device_tensor, photon_range
+
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    photons = args.photons or 10_000_000
+    sc = S.make_scene("C4", photons=photons, passes=args.warmup + args.steps)
+    pt = PathTracer(sc, device=local_rank)
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
+    pt.set_stream(stream.cuda_stream)
+    pt.build()
+    pt.sppm_init()
+    b, e = photon_range(photons, rank, world)
+    ptr, nfl = pt.sppm_flux_device()
+    flux = device_tensor(ptr, nfl, dev)
+    flush = torch.empty(L2_FLUSH_BYTES // 4, dtype=torch.float32, device=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def one_pass(p):
+        pt.sppm_pass(p, b, e)
+        r = pt.stats()["rays_traced"]
+        if world > 1:
+            allreduce_flux(flux)
+            stream.synchronize()
+        pt.sppm_update(p)
+        return r
+
+    for p in range(args.warmup):
+        flush.zero_()
+        one_pass(p)
+    barrier()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    evs, rays, launches = [], 0, 0
+    for k in range(args.steps):
+        flush.zero_()
+        a_, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a_.record(stream)
+        rays += one_pass(args.warmup + k)
+        b_.record(stream)
+        launches += pt.stats()["kernel_launches"] + 1
+        evs.append((a_, b_))
+    barrier()
+    total_ms = float(sum(x.elapsed_time(y) for x, y in evs))
+    clocks = sampler.stop() if sampler else None
+    # stage times + visit counts of one more pass (not timed)
+    p_extra = args.warmup + args.steps
+    stage = {}
+    pt.set_profiling(count_visits=True)
+    v_int = v_leaf = prof_rays = 0
+    for name, mask in (("photon", 1), ("eye", 2), ("gather", 4)):
+        pt.sppm_pass_stages(p_extra, mask, b, e)
+        st = pt.stats()
+        stage[name] = st["render_ms"]
+        if name == "photon":
+            v_int, v_leaf, prof_rays = st["internal_visits"], st["leaf_tests"], st["rays_traced"]
+    pt.set_profiling()
+    pt.sppm_pass_stages(p_extra, 1, b, e)
+    photon_ms = pt.stats()["render_ms"]
+    stats = pt.sppm_stats()
+    # e2e: host scene in, host frame out, for `steps` passes
+    barrier()
+    t0 = time.perf_counter()
+    pt.set_scene(sc)
+    pt.build()
+    pt.sppm_init()
+    e2e_rays = pt.stats()["rays_traced"]
+    for p in range(args.steps):
+        e2e_rays += one_pass(p)
+    img = pt.sppm_resolve(0, args.steps)
+    barrier()
+    e2e_ms = (time.perf_counter() - t0) * 1e3
+    t = torch.tensor([total_ms, e2e_ms], dtype=torch.float64, device=dev)
+    tot = torch.tensor([float(rays), float(e2e_rays)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    total_ms, e2e_ms = t.tolist()
+    rays_all, e2e_rays_all = tot.tolist()
+    if rank != 0:
+        return
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    ms_per_step = total_ms / args.steps
+    alg = 48.0 * prof_rays + 64.0 * v_int + 48.0 * v_leaf + 52.0 * (stats["n_surface"] + stats["n_volume"])
+    achieved = alg / (photon_ms * 1e-3) / 1e9 if photon_ms > 0 else 0.0
+    H, W = sc.camera["height"], sc.camera["width"]
+    line = {
+        "metric": "Mrays/s", "value": rays_all / (total_ms * 1e-3) / 1e6, "unit": "Mrays/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {
+            "workload": f"C4: SPPM, {sc.num_triangles} triangles (room + glass sphere + fog box), "
+                        f"{W}x{H}, {photons} photons per pass",
+            "step": "one SPPM pass: photon trace + photon LBVHs + eye pass + gather (+ NCCL "
+                    "all-reduce of 8 floats per pixel when N > 1) + update",
+            "rays": "closest-hit traversals of the main BVH: photon, eye, direct-light and "
+                    "visibility rays",
+            "cache": "L2 flushed (512 MiB write) between timed steps",
+            "sharding": "scene + eye pass replicated, photons split by index range",
+            "rank0_stage_ms": stage, "photons_stored": [stats["n_surface"], stats["n_volume"]],
+            "mean_radius": stats["mean_radius"],
+        },
+        "gpu_launches": int(launches),
+        "e2e": {"value": e2e_rays_all / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s",
+                "h2d_bytes_per_step": scene_bytes(sc) // max(1, args.steps),
+                "d2h_bytes_per_step": H * W * 12 // max(1, args.steps),
+                "what": "gpt_set_* + gpt_build + gpt_sppm_init + passes + gpt_sppm_resolve, host "
+                        "arrays in, host frame out"},
+        "roofline": {"bound": "hbm", "kernel": "k_photon_trace", "achieved": achieved, "peak": peak,
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                     "algorithmic_bytes_per_launch": alg, "avg_launch_ms": photon_ms,
+                     "note": "photon stage = k_photon_trace + compaction + two photon LBVH builds",
+                     "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback"},
+        "clocks": clocks,
+    }
+    print(json.dumps(line), flush=True)
+
+
 def main():
     args = parse()
     rank = int(os.environ.get("RANK", "0"))
@@ -332,7 +473,10 @@ def main():
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", rank=rank, world_size=world)
     try:
-        run_ours(args, rank, world, local_rank)
+        if args.workload == "C4":
+            run_sppm(args, rank, world, local_rank)
+        else:
+            run_ours(args, rank, world, local_rank)
     finally:
         if world > 1:
             import torch.distributed as dist

@@ -198,5 +198,6 @@ void gpt_sss_mark_first_pass_done(gpt_ctx *ctx);                     // sss.cu
 // stable LSD radix sort of (key, value) pairs on key bits [0, nbits)   // lbvh.cu
 int gpt_radix_sort_pairs(gpt_ctx *ctx, uint32_t *keys, int *vals, uint32_t *keys_alt,
                          int *vals_alt, uint32_t *block_hist, int n, int nbits,
-                         uint32_t **keys_out, int **vals_out);
+                         uint32_t **keys_out, int **vals_out,
+                         const int *d_n = nullptr);  // d_n: exact count on the device (n = bound)
 int gpt_radix_hist_entries(int n);

@@ -107,8 +107,9 @@ k_morton(const float *__restrict__ aabb, const int *__restrict__ prim_list, int 
 //        -> k_sort_scatter (stable ranks via __match_any_sync + per-warp running counters).
 __global__ void __launch_bounds__(SORT_THREADS)
 k_sort_hist(const uint32_t *__restrict__ keys, int n, int shift, uint32_t mask,
-            uint32_t *__restrict__ block_hist, int nblocks) {
+            uint32_t *__restrict__ block_hist, int nblocks, const int *__restrict__ d_n) {
   __shared__ uint32_t h[256];
+  if (d_n) n = min(n, __ldg(d_n));  // n is only an upper bound: the exact count is on the device
   h[threadIdx.x] = 0;
   __syncthreads();
   int base = blockIdx.x * SORT_TILE;
@@ -148,8 +149,10 @@ __global__ void __launch_bounds__(1024) k_sort_scan(uint32_t *data, int m) {
 __global__ void __launch_bounds__(SORT_THREADS)
 k_sort_scatter(const uint32_t *__restrict__ keys, const int *__restrict__ vals, int n,
                int shift, uint32_t mask, const uint32_t *__restrict__ block_hist, int nblocks,
-               uint32_t *__restrict__ keys_out, int *__restrict__ vals_out) {
+               uint32_t *__restrict__ keys_out, int *__restrict__ vals_out,
+               const int *__restrict__ d_n) {
   __shared__ uint32_t cnt[SORT_WARPS][256];  // running / total count per warp and digit
+  if (d_n) n = min(n, __ldg(d_n));
   int w = threadIdx.x >> 5, l = threadIdx.x & 31;
   for (int d = threadIdx.x; d < SORT_WARPS * 256; d += SORT_THREADS) (&cnt[0][0])[d] = 0;
   __syncthreads();
@@ -342,7 +345,7 @@ int gpt_radix_hist_entries(int n) {
 
 int gpt_radix_sort_pairs(gpt_ctx *ctx, uint32_t *keys, int *vals, uint32_t *keys_alt,
                          int *vals_alt, uint32_t *block_hist, int n, int nbits,
-                         uint32_t **keys_out, int **vals_out) {
+                         uint32_t **keys_out, int **vals_out, const int *d_n) {
   int nblocks = (n + SORT_TILE - 1) / SORT_TILE;
   if (nblocks < 1) nblocks = 1;
   uint32_t *ka = keys, *kb = keys_alt;
@@ -350,12 +353,12 @@ int gpt_radix_sort_pairs(gpt_ctx *ctx, uint32_t *keys, int *vals, uint32_t *keys
   for (int shift = 0; shift < nbits; shift += 8) {
     int bits = nbits - shift < 8 ? nbits - shift : 8;
     uint32_t mask = (1u << bits) - 1u;
-    k_sort_hist<<<nblocks, SORT_THREADS, 0, ctx->stream>>>(ka, n, shift, mask, block_hist, nblocks);
+    k_sort_hist<<<nblocks, SORT_THREADS, 0, ctx->stream>>>(ka, n, shift, mask, block_hist, nblocks, d_n);
     GPT_LAUNCH_CHECK(ctx);
     k_sort_scan<<<1, 1024, 0, ctx->stream>>>(block_hist, 256 * nblocks);
     GPT_LAUNCH_CHECK(ctx);
     k_sort_scatter<<<nblocks, SORT_THREADS, 0, ctx->stream>>>(ka, va, n, shift, mask, block_hist,
-                                                             nblocks, kb, vb);
+                                                             nblocks, kb, vb, d_n);
     GPT_LAUNCH_CHECK(ctx);
     uint32_t *tk = ka; ka = kb; kb = tk;
     int *tv = va; va = vb; vb = tv;

@@ -25,7 +25,8 @@ struct RenderCtx {
   int light_n = 0;
   uint32_t *rng_init = nullptr;   // cached curand_init states for (width, height, rank set)
   int rng_w = 0, rng_h = 0, rng_rank = -1, rng_nranks = 0;
-  int *h_counts = nullptr;        // pinned
+  int *h_counts = nullptr;        // pinned ring: RING x 4 ints (queue lengths + error flag)
+  cudaEvent_t ring_ev[4] = {nullptr, nullptr, nullptr, nullptr};
   uint32_t *sort_key = nullptr, *sort_key_alt = nullptr, *sort_hist = nullptr;
   int *sort_val = nullptr, *sort_val_alt = nullptr;
   float *d_fb = nullptr;          // internal framebuffer for the host API
@@ -283,8 +284,9 @@ __global__ void __launch_bounds__(PT_BLOCK)
 k_pt_shade(PathState ps, RenderParams p, const int *__restrict__ queue,
            const int *__restrict__ count, int *next_queue, int *next_count, SceneDev sc,
            TexAtlas atlas, const float4 *__restrict__ main_tris, LightTree lt, float *fb,
-           int *error_flag) {
+           int *error_flag, unsigned long long *ray_counter) {
   int a = blockIdx.x * blockDim.x + threadIdx.x;
+  if (a == 0) atomicAdd(ray_counter, (unsigned long long)*count);  // rays traced this iteration
   bool alive = false;
   int s = -1;
   if (a < *count) {
@@ -486,7 +488,11 @@ static int reserve_paths(gpt_ctx *ctx, RenderCtx *rc, int n) {
   GPT_TRY(gpt_alloc(ctx, &rc->sort_val, N));
   GPT_TRY(gpt_alloc(ctx, &rc->sort_val_alt, N));
   GPT_TRY(gpt_alloc(ctx, &rc->sort_hist, (size_t)gpt_radix_hist_entries(n)));
-  if (!rc->h_counts) GPT_CUDA(ctx, cudaMallocHost((void **)&rc->h_counts, 4 * sizeof(int)));
+  if (!rc->h_counts) {
+    GPT_CUDA(ctx, cudaMallocHost((void **)&rc->h_counts, 4 * 4 * sizeof(int)));
+    for (int k = 0; k < 4; k++)
+      GPT_CUDA(ctx, cudaEventCreateWithFlags(&rc->ring_ev[k], cudaEventDisableTiming));
+  }
   ps.capacity = n;
   rc->rng_w = rc->rng_h = 0;  // cached states are gone
   return GPT_OK;
@@ -619,8 +625,26 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
     }
     return cudaEventRecord(rc->events[nev++], st);
   };
-  long long max_iters = (long long)p.sample_size * p.dof_size * p.level + 8;
-  for (long long it = 0; active > 0 && it < max_iters; it++) {
+  // The host runs LAG iterations ahead of the device: the queue length it sizes the grids
+  // with is the (exact) length from LAG iterations earlier -- an upper bound, because slots only
+  // ever leave the queue -- read back through a ring of pinned slots, so no iteration waits for
+  // a device->host round trip.  Every kernel takes the exact length from device memory.
+  constexpr int RING = 4, LAG = 2;
+  unsigned long long *ray_counter = ctx->d_counters + 6;
+  GPT_CUDA(ctx, cudaMemsetAsync(ray_counter, 0, sizeof(unsigned long long), st));
+  long long max_iters = (long long)p.sample_size * p.dof_size * p.level + 8 + LAG;
+  int cur_of[RING] = {0, 0, 0, 0};
+  bool list_overflow = false;
+  long long it = 0;
+  for (; it < max_iters; it++) {
+    if (it >= LAG) {
+      int slot = (int)((it - LAG) % RING);
+      GPT_CUDA(ctx, cudaEventSynchronize(rc->ring_ev[slot]));
+      const int *h = rc->h_counts + 4 * slot;
+      active = h[cur_of[slot]];
+      if (h[2]) list_overflow = true;
+      if (active == 0 || list_overflow) break;
+    }
     int grid = (active + PT_BLOCK - 1) / PT_BLOCK;
     GPT_CUDA(ctx, cudaMemsetAsync(ps.counts + (cur ^ 1), 0, sizeof(int), st));
     GPT_CUDA(ctx, cudaMemsetAsync(next_ray, 0, sizeof(int), st));
@@ -642,21 +666,30 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
     uint32_t *sk = nullptr;
     int *sorted_slots = nullptr;
     GPT_TRY(gpt_radix_sort_pairs(ctx, rc->sort_key, rc->sort_val, rc->sort_key_alt, rc->sort_val_alt,
-                                 rc->sort_hist, active, 7, &sk, &sorted_slots));
+                                 rc->sort_hist, active, 7, &sk, &sorted_slots, ps.counts + cur));
     k_pt_shade<<<grid, PT_BLOCK, 0, st>>>(ps, p, sorted_slots, ps.counts + cur, ps.queue[cur ^ 1],
                                          ps.counts + (cur ^ 1), ctx->scene, atlas, mb.tris, lt,
-                                         d_fb, ps.counts + 2);
+                                         d_fb, ps.counts + 2, ray_counter);
     GPT_LAUNCH_CHECK(ctx);
     GPT_CUDA(ctx, stamp());
-    rays += (uint64_t)active;
-    shades += (uint64_t)active;
-    GPT_CUDA(ctx, cudaMemcpyAsync(rc->h_counts, ps.counts, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
-    GPT_CUDA(ctx, cudaStreamSynchronize(st));
     cur ^= 1;
-    active = rc->h_counts[cur];
-    if (rc->h_counts[2])
-      return gpt_fail(ctx, GPT_E_UNSUPPORTED, "nested-dielectric list deeper than 12", __FILE__, __LINE__);
+    int slot = (int)(it % RING);
+    cur_of[slot] = cur;  // which of counts[0..1] is the length of the queue the NEXT iteration reads
+    GPT_CUDA(ctx, cudaMemcpyAsync(rc->h_counts + 4 * slot, ps.counts, 4 * sizeof(int),
+                                  cudaMemcpyDeviceToHost, st));
+    GPT_CUDA(ctx, cudaEventRecord(rc->ring_ev[slot], st));
   }
+  {  // drain: final queue length, error flag, exact ray count
+    GPT_CUDA(ctx, cudaMemcpyAsync(rc->h_counts, ps.counts, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    unsigned long long h_rays = 0;
+    GPT_CUDA(ctx, cudaMemcpyAsync(&h_rays, ray_counter, sizeof(h_rays), cudaMemcpyDeviceToHost, st));
+    GPT_CUDA(ctx, cudaStreamSynchronize(st));
+    active = rc->h_counts[cur];
+    if (rc->h_counts[2]) list_overflow = true;
+    rays = shades = h_rays;
+  }
+  if (list_overflow)
+    return gpt_fail(ctx, GPT_E_UNSUPPORTED, "nested-dielectric list deeper than 12", __FILE__, __LINE__);
   GPT_CUDA(ctx, cudaEventRecord(ctx->ev1, st));
   GPT_CUDA(ctx, cudaEventSynchronize(ctx->ev1));
   float ms = 0.f;
@@ -700,6 +733,8 @@ void gpt_render_free(gpt_ctx *ctx) {
                rc->sort_key_alt, rc->sort_hist, rc->sort_val, rc->sort_val_alt};
   for (void *q : p) cudaFree(q);
   if (rc->h_counts) cudaFreeHost(rc->h_counts);
+  for (int k = 0; k < 4; k++)
+    if (rc->ring_ev[k]) cudaEventDestroy(rc->ring_ev[k]);
   for (cudaEvent_t e : rc->events) cudaEventDestroy(e);
   delete rc;
   ctx->render_state = nullptr;

@@ -54,8 +54,9 @@ struct SppmScene {
   SceneDev sc;
   TexAtlas atlas;
   LightTree lt;
-  unsigned long long *counters;  // [2] main-BVH rays, [3] stack overflow
+  unsigned long long *counters;  // [0] V_int [1] V_leaf (profiling) [2] main-BVH rays, [3] stack overflow
   int *error_flag;               // nested-dielectric list overflow
+  int count_visits;              // profiling: count V_int / V_leaf of the main-BVH traversals
 };
 
 // hit_record (primitive.h:111-119): persistent across traversals -- a miss only resets t.
@@ -85,8 +86,13 @@ static __device__ __noinline__ bool trace_surf(const SppmScene &S, const TreeRef
                                                Tracer &T, V3 o, V3 dir, SurfRec &rec) {
   RaySetup r = make_ray(o.x, o.y, o.z, dir.x, dir.y, dir.z);
   int overflow = 0;
-  HitResult h = trace_ray<false>(tr.nodes, tr.tris, tr.parent_leaf, r, INFINITY, T.stack, SP_BLOCK,
-                                 nullptr, nullptr, &overflow);
+  HitResult h;
+  if (S.count_visits && is_main)
+    h = trace_ray<true>(tr.nodes, tr.tris, tr.parent_leaf, r, INFINITY, T.stack, SP_BLOCK,
+                        S.counters, S.counters + 1, &overflow);
+  else
+    h = trace_ray<false>(tr.nodes, tr.tris, tr.parent_leaf, r, INFINITY, T.stack, SP_BLOCK,
+                         nullptr, nullptr, &overflow);
   if (overflow) atomicExch(S.counters + 3, 1ull);
   if (is_main) T.nrays++;
   rec.t = INFINITY;
@@ -937,6 +943,7 @@ static int make_scene_view(gpt_ctx *ctx, SppmCtx *sx, SppmScene &S) {
   S.lt = LightTree{lb.nodes, lb.tris, lb.parent_leaf, sx->leaf_info, sx->node_info, lb.n};
   S.counters = ctx->d_counters;
   S.error_flag = sx->d_counts + 2;
+  S.count_visits = ctx->prof_count_visits ? 1 : 0;
   return GPT_OK;
 }
 
@@ -1003,6 +1010,8 @@ static int sppm_collect_rays(gpt_ctx *ctx, SppmCtx *sx) {
   GPT_CUDA(ctx, cudaMemcpyAsync(c, ctx->d_counters, sizeof(c), cudaMemcpyDeviceToHost, ctx->stream));
   GPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   ctx->stats.rays_traced = c[2];
+  ctx->stats.internal_visits = c[0];
+  ctx->stats.leaf_tests = c[1];
   sx->rays_total += c[2];
   if (c[3]) return gpt_fail(ctx, GPT_E_INVALID, "traversal stack overflow", __FILE__, __LINE__);
   return GPT_OK;
