@@ -29,7 +29,7 @@ gpt_sppm_init gpt_sppm_pass gpt_sppm_flux_device gpt_sppm_update gpt_sppm_resolv
 gpt_sppm_stats gpt_sppm_export_hit_points gpt_sppm_export_photons gpt_sppm_import_photons
 gpt_sppm_pass_stages gpt_sppm_import_hit_points gpt_sss_export_points gpt_tonemap_u8 gpt_write_ppm_u8
 gpt_save_image gpt_sppm_debug_image gpt_sss_debug_image gpt_stats
-gpt_synchronize gpt_set_profiling""".split()
+gpt_synchronize gpt_set_profiling gpt_set_wavefront_groups""".split()
 
 
 class GptError(RuntimeError):
@@ -119,6 +119,9 @@ class PathTracer:
     def rebuild_main_bvh(self) -> float:
         self._check(self.lib.gpt_rebuild_main_bvh(self.ctx))
         return self.stats()["build_ms"]
+
+    def set_wavefront_groups(self, groups=0):
+        self._check(self.lib.gpt_set_wavefront_groups(self.ctx, C.c_int(int(groups))))
 
     def set_profiling(self, time_stages=False, count_visits=False):
         self._check(self.lib.gpt_set_profiling(self.ctx, C.c_int(int(time_stages)),

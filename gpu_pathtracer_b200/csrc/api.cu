@@ -421,6 +421,12 @@ int gpt_set_profiling(gpt_ctx *ctx, int time_stages, int count_visits) {
   return GPT_OK;
 }
 
+int gpt_set_wavefront_groups(gpt_ctx *ctx, int groups) {
+  if (!ctx || groups < 0 || groups > 8) return GPT_E_INVALID;
+  ctx->wavefront_groups = groups;
+  return GPT_OK;
+}
+
 int gpt_stats(gpt_ctx *ctx, GptStats *out) {
   if (!ctx || !out) return GPT_E_INVALID;
   *out = ctx->stats;

@@ -108,6 +108,7 @@ struct gpt_ctx {
   std::vector<int> obj_num, obj_off;         // object_num_primitives / object_primitive_offset_idx
   uint64_t launches = 0;                     // kernels launched since last reset
   bool prof_time_stages = false, prof_count_visits = false;
+  int wavefront_groups = 0;  // 0 = automatic (render.cu)
 };
 
 // ---- error plumbing --------------------------------------------------------------------

@@ -25,8 +25,15 @@ struct RenderCtx {
   int light_n = 0;
   uint32_t *rng_init = nullptr;   // cached curand_init states for (width, height, rank set)
   int rng_w = 0, rng_h = 0, rng_rank = -1, rng_nranks = 0;
-  int *h_counts = nullptr;        // pinned ring: RING x 4 ints (queue lengths + error flag)
-  cudaEvent_t ring_ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  // Independent wavefront groups (slot ranges), each on its own stream with its own queues,
+  // counters and read-back ring, so the tail of one group's trace overlaps the others' work.
+  static constexpr int MAX_GROUPS = 8, RING = 4;
+  int *h_counts = nullptr;        // pinned: MAX_GROUPS x RING x 4 ints (queue lengths + error flag)
+  cudaEvent_t ring_ev[MAX_GROUPS][RING] = {};
+  cudaStream_t gstream[MAX_GROUPS] = {};
+  cudaEvent_t fork_ev = nullptr, join_ev[MAX_GROUPS] = {};
+  int *next_ray = nullptr;        // MAX_GROUPS ints: the persistent trace kernels' ray cursors
+  int hist_stride = 0;
   uint32_t *sort_key = nullptr, *sort_key_alt = nullptr, *sort_hist = nullptr;
   int *sort_val = nullptr, *sort_val_alt = nullptr;
   float *d_fb = nullptr;          // internal framebuffer for the host API
@@ -482,16 +489,24 @@ static int reserve_paths(gpt_ctx *ctx, RenderCtx *rc, int n) {
   GPT_TRY(gpt_alloc(ctx, &ps.cam, 2 * N));
   GPT_TRY(gpt_alloc(ctx, &ps.queue[0], N));
   GPT_TRY(gpt_alloc(ctx, &ps.queue[1], N));
-  GPT_TRY(gpt_alloc(ctx, &ps.counts, (size_t)4));
+  GPT_TRY(gpt_alloc(ctx, &ps.counts, (size_t)4 * RenderCtx::MAX_GROUPS));
+  GPT_TRY(gpt_alloc(ctx, &rc->next_ray, (size_t)RenderCtx::MAX_GROUPS));
   GPT_TRY(gpt_alloc(ctx, &rc->sort_key, N));
   GPT_TRY(gpt_alloc(ctx, &rc->sort_key_alt, N));
   GPT_TRY(gpt_alloc(ctx, &rc->sort_val, N));
   GPT_TRY(gpt_alloc(ctx, &rc->sort_val_alt, N));
-  GPT_TRY(gpt_alloc(ctx, &rc->sort_hist, (size_t)gpt_radix_hist_entries(n)));
+  rc->hist_stride = gpt_radix_hist_entries(n);
+  GPT_TRY(gpt_alloc(ctx, &rc->sort_hist, (size_t)rc->hist_stride * RenderCtx::MAX_GROUPS));
   if (!rc->h_counts) {
-    GPT_CUDA(ctx, cudaMallocHost((void **)&rc->h_counts, 4 * 4 * sizeof(int)));
-    for (int k = 0; k < 4; k++)
-      GPT_CUDA(ctx, cudaEventCreateWithFlags(&rc->ring_ev[k], cudaEventDisableTiming));
+    GPT_CUDA(ctx, cudaMallocHost((void **)&rc->h_counts,
+                                 RenderCtx::MAX_GROUPS * RenderCtx::RING * 4 * sizeof(int)));
+    GPT_CUDA(ctx, cudaEventCreateWithFlags(&rc->fork_ev, cudaEventDisableTiming));
+    for (int g = 0; g < RenderCtx::MAX_GROUPS; g++) {
+      GPT_CUDA(ctx, cudaStreamCreateWithFlags(&rc->gstream[g], cudaStreamNonBlocking));
+      GPT_CUDA(ctx, cudaEventCreateWithFlags(&rc->join_ev[g], cudaEventDisableTiming));
+      for (int k = 0; k < RenderCtx::RING; k++)
+        GPT_CUDA(ctx, cudaEventCreateWithFlags(&rc->ring_ev[g][k], cudaEventDisableTiming));
+    }
   }
   ps.capacity = n;
   rc->rng_w = rc->rng_h = 0;  // cached states are gone
@@ -595,15 +610,11 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
   if (!sss_pass)
     GPT_CUDA(ctx, cudaMemcpyAsync(ps.rng, rc->rng_init, sizeof(uint32_t) * 8 * (size_t)n,
                                   cudaMemcpyDeviceToDevice, st));
-  int init_counts[4] = {n, 0, 0, 0};
-  GPT_CUDA(ctx, cudaMemcpyAsync(ps.counts, init_counts, sizeof(init_counts), cudaMemcpyHostToDevice, st));
   if (sss_pass)
     k_sss_start<<<(n + PT_BLOCK - 1) / PT_BLOCK, PT_BLOCK, 0, st>>>(ps, p, n);
   else
     k_pt_start<<<(n + PT_BLOCK - 1) / PT_BLOCK, PT_BLOCK, 0, st>>>(ps, p, n, d_fb);
   GPT_LAUNCH_CHECK(ctx);
-  int active = n, cur = 0;
-  int *next_ray = reinterpret_cast<int *>(ctx->d_counters + 4);
   static int trace_grid = 0;
   if (!trace_grid) {
     int sms = 148, per_sm = 4;
@@ -625,67 +636,137 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
     }
     return cudaEventRecord(rc->events[nev++], st);
   };
-  // The host runs LAG iterations ahead of the device: the queue length it sizes the grids
-  // with is the (exact) length from LAG iterations earlier -- an upper bound, because slots only
-  // ever leave the queue -- read back through a ring of pinned slots, so no iteration waits for
-  // a device->host round trip.  Every kernel takes the exact length from device memory.
-  constexpr int RING = 4, LAG = 2;
+  // ---- wavefront groups -------------------------------------------------------------------
+  // Slots are cut into G contiguous ranges that run their trace -> sort -> shade iterations
+  // independently on their own streams (a pixel never interacts with another pixel).  Inside
+  // a group the host runs LAG iterations ahead of the device: the queue length it sizes the
+  // grids with is the exact length from LAG iterations earlier -- an upper bound, because
+  // slots only ever leave a queue -- read back through a ring of pinned slots, so no
+  // iteration waits for a device->host round trip.  Kernels take the exact length from device
+  // memory.  Stage timing (profiling) needs one stream, so it forces G = 1.
+  constexpr int RING = RenderCtx::RING, LAG = 2;
+  int G = 1;
+  {
+    static int env_groups = -1;
+    if (env_groups < 0) {
+      const char *e = getenv("GPT_WAVEFRONT_GROUPS");
+      env_groups = e ? atoi(e) : 0;
+    }
+    G = ctx->wavefront_groups > 0 ? ctx->wavefront_groups
+        : env_groups > 0        ? env_groups
+                                : (n >= (1 << 16) ? 4 : 1);
+    if (G > RenderCtx::MAX_GROUPS) G = RenderCtx::MAX_GROUPS;
+    if (timing || G < 1) G = 1;
+  }
+  struct Group {
+    int s0, n, active, cur;
+    int cur_of[RenderCtx::RING];
+    long long it;
+    bool done;
+  };
+  Group grp[RenderCtx::MAX_GROUPS];
+  int h_init[4 * RenderCtx::MAX_GROUPS] = {0};
+  for (int g = 0; g < G; g++) {
+    // group boundaries on multiples of 1024 slots (= one 32x32 tile) so warps stay tile rows
+    long long lo = (long long)n * g / G, hi = (long long)n * (g + 1) / G;
+    if (g > 0) lo = (lo + 1023) / 1024 * 1024;
+    if (g < G - 1) hi = (hi + 1023) / 1024 * 1024;
+    if (lo > n) lo = n;
+    if (hi > n) hi = n;
+    grp[g] = Group{(int)lo, (int)(hi - lo), (int)(hi - lo), 0, {0, 0, 0, 0}, 0, hi <= lo};
+    h_init[4 * g] = grp[g].n;
+  }
+  GPT_CUDA(ctx, cudaMemcpyAsync(ps.counts, h_init, sizeof(int) * 4 * G, cudaMemcpyHostToDevice, st));
   unsigned long long *ray_counter = ctx->d_counters + 6;
   GPT_CUDA(ctx, cudaMemsetAsync(ray_counter, 0, sizeof(unsigned long long), st));
-  long long max_iters = (long long)p.sample_size * p.dof_size * p.level + 8 + LAG;
-  int cur_of[RING] = {0, 0, 0, 0};
+  GPT_CUDA(ctx, cudaEventRecord(rc->fork_ev, st));
+  for (int g = 0; g < G; g++)
+    if (G > 1) GPT_CUDA(ctx, cudaStreamWaitEvent(rc->gstream[g], rc->fork_ev, 0));
+  const long long max_iters = (long long)p.sample_size * p.dof_size * p.level + 8 + LAG;
   bool list_overflow = false;
-  long long it = 0;
-  for (; it < max_iters; it++) {
-    if (it >= LAG) {
-      int slot = (int)((it - LAG) % RING);
-      GPT_CUDA(ctx, cudaEventSynchronize(rc->ring_ev[slot]));
-      const int *h = rc->h_counts + 4 * slot;
-      active = h[cur_of[slot]];
-      if (h[2]) list_overflow = true;
-      if (active == 0 || list_overflow) break;
+  int remaining = 0;
+  for (int g = 0; g < G; g++) remaining += grp[g].done ? 0 : 1;
+  cudaStream_t const caller_stream = ctx->stream;
+  int rc_err = GPT_OK;
+  while (remaining > 0 && rc_err == GPT_OK) {
+    for (int g = 0; g < G && rc_err == GPT_OK; g++) {
+      Group &q = grp[g];
+      if (q.done) continue;
+      cudaStream_t gs = G > 1 ? rc->gstream[g] : st;
+      int *h_ring = rc->h_counts + 4 * RING * g;
+      int *d_counts = ps.counts + 4 * g;
+      if (q.it >= LAG) {
+        int slot = (int)((q.it - LAG) % RING);
+        GPT_CUDA(ctx, cudaEventSynchronize(rc->ring_ev[g][slot]));
+        const int *h = h_ring + 4 * slot;
+        q.active = h[q.cur_of[slot]];
+        if (h[2]) list_overflow = true;
+      }
+      if (q.active == 0 || list_overflow || q.it >= max_iters) {
+        q.done = true;
+        remaining--;
+        continue;
+      }
+      int grid = (q.active + PT_BLOCK - 1) / PT_BLOCK;
+      int *next_ray = rc->next_ray + g;
+      GPT_CUDA(ctx, cudaMemsetAsync(d_counts + (q.cur ^ 1), 0, sizeof(int), gs));
+      GPT_CUDA(ctx, cudaMemsetAsync(next_ray, 0, sizeof(int), gs));
+      GPT_CUDA(ctx, stamp());
+      {
+        QueueSource qs{ps, ps.queue[q.cur] + q.s0, d_counts + q.cur, ctx->scene.shade,
+                       rc->sort_key + q.s0, rc->sort_val + q.s0};
+        int tgrid = grid < trace_grid ? grid : trace_grid;
+        if (counting)
+          k_pt_trace<true><<<tgrid, TP_BLOCK, 0, gs>>>(qs, mb.nodes, mb.tris, mb.parent_leaf,
+                                                      next_ray, ctx->d_counters);
+        else
+          k_pt_trace<false><<<tgrid, TP_BLOCK, 0, gs>>>(qs, mb.nodes, mb.tris, mb.parent_leaf,
+                                                       next_ray, ctx->d_counters);
+      }
+      GPT_LAUNCH_CHECK(ctx);
+      trace_launches++;
+      GPT_CUDA(ctx, stamp());
+      // stable 7-bit radix sort of the active slots by material (ties keep tile order)
+      uint32_t *sk = nullptr;
+      int *sorted_slots = nullptr;
+      ctx->stream = gs;  // the sort enqueues on ctx->stream
+      rc_err = gpt_radix_sort_pairs(ctx, rc->sort_key + q.s0, rc->sort_val + q.s0,
+                                    rc->sort_key_alt + q.s0, rc->sort_val_alt + q.s0,
+                                    rc->sort_hist + (size_t)rc->hist_stride * g, q.active, 7, &sk,
+                                    &sorted_slots, d_counts + q.cur);
+      ctx->stream = caller_stream;
+      if (rc_err != GPT_OK) break;
+      k_pt_shade<<<grid, PT_BLOCK, 0, gs>>>(ps, p, sorted_slots, d_counts + q.cur,
+                                           ps.queue[q.cur ^ 1] + q.s0, d_counts + (q.cur ^ 1),
+                                           ctx->scene, atlas, mb.tris, lt, d_fb, d_counts + 2,
+                                           ray_counter);
+      GPT_LAUNCH_CHECK(ctx);
+      GPT_CUDA(ctx, stamp());
+      q.cur ^= 1;
+      int slot = (int)(q.it % RING);
+      q.cur_of[slot] = q.cur;  // which of counts[0..1] the NEXT iteration's queue length is
+      GPT_CUDA(ctx, cudaMemcpyAsync(h_ring + 4 * slot, d_counts, 4 * sizeof(int),
+                                    cudaMemcpyDeviceToHost, gs));
+      GPT_CUDA(ctx, cudaEventRecord(rc->ring_ev[g][slot], gs));
+      q.it++;
     }
-    int grid = (active + PT_BLOCK - 1) / PT_BLOCK;
-    GPT_CUDA(ctx, cudaMemsetAsync(ps.counts + (cur ^ 1), 0, sizeof(int), st));
-    GPT_CUDA(ctx, cudaMemsetAsync(next_ray, 0, sizeof(int), st));
-    GPT_CUDA(ctx, stamp());
-    {
-      QueueSource qs{ps, ps.queue[cur], ps.counts + cur, ctx->scene.shade, rc->sort_key, rc->sort_val};
-      int tgrid = grid < trace_grid ? grid : trace_grid;
-      if (counting)
-        k_pt_trace<true><<<tgrid, TP_BLOCK, 0, st>>>(qs, mb.nodes, mb.tris, mb.parent_leaf, next_ray,
-                                                    ctx->d_counters);
-      else
-        k_pt_trace<false><<<tgrid, TP_BLOCK, 0, st>>>(qs, mb.nodes, mb.tris, mb.parent_leaf, next_ray,
-                                                     ctx->d_counters);
-    }
-    GPT_LAUNCH_CHECK(ctx);
-    trace_launches++;
-    GPT_CUDA(ctx, stamp());
-    // stable 7-bit radix sort of the active slots by material (ties keep tile order)
-    uint32_t *sk = nullptr;
-    int *sorted_slots = nullptr;
-    GPT_TRY(gpt_radix_sort_pairs(ctx, rc->sort_key, rc->sort_val, rc->sort_key_alt, rc->sort_val_alt,
-                                 rc->sort_hist, active, 7, &sk, &sorted_slots, ps.counts + cur));
-    k_pt_shade<<<grid, PT_BLOCK, 0, st>>>(ps, p, sorted_slots, ps.counts + cur, ps.queue[cur ^ 1],
-                                         ps.counts + (cur ^ 1), ctx->scene, atlas, mb.tris, lt,
-                                         d_fb, ps.counts + 2, ray_counter);
-    GPT_LAUNCH_CHECK(ctx);
-    GPT_CUDA(ctx, stamp());
-    cur ^= 1;
-    int slot = (int)(it % RING);
-    cur_of[slot] = cur;  // which of counts[0..1] is the length of the queue the NEXT iteration reads
-    GPT_CUDA(ctx, cudaMemcpyAsync(rc->h_counts + 4 * slot, ps.counts, 4 * sizeof(int),
-                                  cudaMemcpyDeviceToHost, st));
-    GPT_CUDA(ctx, cudaEventRecord(rc->ring_ev[slot], st));
   }
-  {  // drain: final queue length, error flag, exact ray count
-    GPT_CUDA(ctx, cudaMemcpyAsync(rc->h_counts, ps.counts, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
+  if (rc_err != GPT_OK) return rc_err;
+  int active = 0;
+  {  // join the groups; final queue lengths, error flags, exact ray count
+    for (int g = 0; g < G && G > 1; g++) {
+      GPT_CUDA(ctx, cudaEventRecord(rc->join_ev[g], rc->gstream[g]));
+      GPT_CUDA(ctx, cudaStreamWaitEvent(st, rc->join_ev[g], 0));
+    }
+    int h_fin[4 * RenderCtx::MAX_GROUPS];
+    GPT_CUDA(ctx, cudaMemcpyAsync(h_fin, ps.counts, sizeof(int) * 4 * G, cudaMemcpyDeviceToHost, st));
     unsigned long long h_rays = 0;
     GPT_CUDA(ctx, cudaMemcpyAsync(&h_rays, ray_counter, sizeof(h_rays), cudaMemcpyDeviceToHost, st));
     GPT_CUDA(ctx, cudaStreamSynchronize(st));
-    active = rc->h_counts[cur];
-    if (rc->h_counts[2]) list_overflow = true;
+    for (int g = 0; g < G; g++) {
+      active += h_fin[4 * g + grp[g].cur];
+      if (h_fin[4 * g + 2]) list_overflow = true;
+    }
     rays = shades = h_rays;
   }
   if (list_overflow)
@@ -733,8 +814,14 @@ void gpt_render_free(gpt_ctx *ctx) {
                rc->sort_key_alt, rc->sort_hist, rc->sort_val, rc->sort_val_alt};
   for (void *q : p) cudaFree(q);
   if (rc->h_counts) cudaFreeHost(rc->h_counts);
-  for (int k = 0; k < 4; k++)
-    if (rc->ring_ev[k]) cudaEventDestroy(rc->ring_ev[k]);
+  if (rc->fork_ev) cudaEventDestroy(rc->fork_ev);
+  for (int g = 0; g < RenderCtx::MAX_GROUPS; g++) {
+    if (rc->gstream[g]) cudaStreamDestroy(rc->gstream[g]);
+    if (rc->join_ev[g]) cudaEventDestroy(rc->join_ev[g]);
+    for (int k = 0; k < RenderCtx::RING; k++)
+      if (rc->ring_ev[g][k]) cudaEventDestroy(rc->ring_ev[g][k]);
+  }
+  cudaFree(rc->next_ray);
   for (cudaEvent_t e : rc->events) cudaEventDestroy(e);
   delete rc;
   ctx->render_state = nullptr;

@@ -264,6 +264,11 @@ int gpt_sss_debug_image(gpt_ctx *ctx, float *out_rgb);
  *   count_visits - count V_int / V_leaf of the main-BVH traversals (fills internal_visits /
  *                  leaf_tests) */
 int gpt_set_profiling(gpt_ctx *ctx, int time_stages, int count_visits);
+/* Number of independent wavefront groups (1..8) the path tracer cuts a rank's pixels into, each
+ * on its own stream; 0 = automatic (4 for frames of >= 65536 pixels per rank, else 1; the
+ * environment variable GPT_WAVEFRONT_GROUPS overrides the automatic choice).  The image does
+ * not depend on it: a pixel's samples never interact with another pixel's. */
+int gpt_set_wavefront_groups(gpt_ctx *ctx, int groups);
 int gpt_stats(gpt_ctx *ctx, GptStats *out);
 int gpt_synchronize(gpt_ctx *ctx);
 

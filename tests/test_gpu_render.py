@@ -93,6 +93,25 @@ def test_tile_sharded_render_is_bit_identical():
         assert np.array_equal(fb.cpu().numpy().view(np.uint32), full.view(np.uint32)), nranks
 
 
+def test_wavefront_groups_do_not_change_the_image():
+    """The frame is cut into 1..8 independent wavefront groups on separate streams; every group
+    count gives the same image and the same ray count, bit for bit (mixed materials so the
+    groups drain at different iterations)."""
+    from gpu_pathtracer_b200.api import PathTracer
+    sc = S.make_scene("small", n=20, width=200, height=136, spp=3, level=6)
+    pt = PathTracer(sc)
+    pt.build()
+    pt.set_wavefront_groups(1)
+    base = pt.render_pathtrace()
+    rays = pt.stats()["rays_traced"]
+    for g in (2, 3, 4, 8):
+        pt.set_wavefront_groups(g)
+        img = pt.render_pathtrace()
+        assert np.array_equal(img.view(np.uint32), base.view(np.uint32)), g
+        assert pt.stats()["rays_traced"] == rays, g
+    pt.set_wavefront_groups(0)
+
+
 def test_against_reference_cuda_binary_8bit():
     """The reference's OWN CUDA build (sm_100, -fmad=false parity flags; oracle/_ref/
     gpu_path_tracing_100_nofma, built by `make -C oracle refcuda` from the unmodified sources +
