@@ -29,7 +29,9 @@ gpt_sppm_init gpt_sppm_pass gpt_sppm_flux_device gpt_sppm_update gpt_sppm_resolv
 gpt_sppm_stats gpt_sppm_export_hit_points gpt_sppm_export_photons gpt_sppm_import_photons
 gpt_sppm_pass_stages gpt_sppm_import_hit_points gpt_sss_export_points gpt_tonemap_u8 gpt_write_ppm_u8
 gpt_save_image gpt_sppm_debug_image gpt_sss_debug_image gpt_stats
-gpt_synchronize gpt_set_profiling gpt_set_wavefront_groups""".split()
+gpt_synchronize gpt_set_profiling gpt_set_wavefront_groups
+gpt_scene_files_parse gpt_scene_files_view gpt_scene_files_material_name
+gpt_scene_files_texture_name gpt_scene_files_free gpt_load_scene_files""".split()
 
 
 class GptError(RuntimeError):
@@ -65,6 +67,19 @@ def load_library():
     lib.gpt_destroy.restype = None
     _lib = lib
     return lib
+
+
+def load_scene_files(master_path: str, threads: int = 0, reader=None) -> Scene:
+    """The scene packer (gpt_scene_files_parse): master file + OBJ + MTL + textures -> Scene.
+    Host work inside libgpt.so; needs no GPU.  ``reader(user, path, h*, w*, rgb**)`` decodes
+    image formats the library does not (JPEG: the host's libjpeg)."""
+    lib = load_library()
+    lib.gpt_scene_files_free.restype = None
+    h, v = cabi.parse_scene_files(lib, "gpt_", master_path, threads, reader)
+    try:
+        return cabi.scene_from_view(lib, "gpt_", h, v)
+    finally:
+        lib.gpt_scene_files_free(h)
 
 
 class PathTracer:
@@ -106,6 +121,18 @@ class PathTracer:
     def set_scene(self, scene: Scene):
         self.scene = scene
         cabi.upload_scene(self.lib, "gpt_", self.ctx, scene, self._check)
+
+    def load_files(self, master_path: str, threads: int = 0, reader=None):
+        """Parses the reference's input files and uploads them in one go (main.cu:165-640):
+        gpt_scene_files_parse + gpt_load_scene_files, no numpy round trip of the mesh."""
+        self.lib.gpt_scene_files_free.restype = None
+        h, v = cabi.parse_scene_files(self.lib, "gpt_", master_path, threads, reader)
+        try:
+            self._check(self.lib.gpt_load_scene_files(self.ctx, h))
+            self.scene = cabi.scene_from_view(self.lib, "gpt_", h, v)
+        finally:
+            self.lib.gpt_scene_files_free(h)
+        return self.scene
 
     def set_params(self, **kw):
         self.scene.params.update(kw)

@@ -137,3 +137,93 @@ def upload_scene(lib, prefix: str, ctx, scene: Scene, check):
                               C.c_int32(b["height"]), C.c_int32(b["width"])))
     check(g("set_camera")(ctx, C.byref(cam)))
     check(g("set_params")(ctx, C.byref(par)))
+
+
+# ---- scene packer (include/gpt.h "scene packer") -------------------------------------------
+class GptSceneFilesView(C.Structure):
+    _fields_ = [("mesh", GptMesh), ("materials", GptMaterials), ("camera", GptCamera),
+                ("params", GptParams),
+                ("tex_r", PF), ("tex_g", PF), ("tex_b", PF), ("texture_length", C.c_int64),
+                ("bg_r", PF), ("bg_g", PF), ("bg_b", PF),
+                ("bg_height", C.c_int32), ("bg_width", C.c_int32),
+                ("num_textures", C.c_int32),
+                ("texture_offset", PI), ("texture_height", PI), ("texture_width", PI),
+                ("input_folder_path", C.c_char_p), ("obj_filename", C.c_char_p),
+                ("texture_bg_path", C.c_char_p), ("image_output_path", C.c_char_p),
+                ("ppm_image_output_iteration", C.c_int32),
+                ("parse_ms", C.c_double), ("obj_parse_ms", C.c_double),
+                ("obj_bytes", C.c_int64), ("threads", C.c_int32)]
+
+
+IMAGE_READER = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_char_p, PI, PI,
+                           C.POINTER(C.POINTER(C.c_uint8)))
+
+
+def _np(ptr, n, dtype):
+    if n == 0:
+        return np.zeros(0, dtype)
+    return np.ctypeslib.as_array(ptr, shape=(n,)).astype(dtype, copy=True)
+
+
+def scene_from_view(lib, prefix: str, handle, v: GptSceneFilesView) -> Scene:
+    """Copies a parsed scene (ours or the reference loader's) out of C memory into a Scene."""
+    m, q = v.mesh, v.materials
+    sizes = dict(x=m.num_vertices, y=m.num_vertices, z=m.num_vertices,
+                 x_norm=m.num_normals, y_norm=m.num_normals, z_norm=m.num_normals,
+                 x_tex=m.num_texcoords, y_tex=m.num_texcoords,
+                 object_num_primitives=m.num_objects, object_primitive_offset_idx=m.num_objects)
+    mesh = {n: _np(getattr(m, n), sizes[n], np.float32) for n in MESH_FLOAT}
+    for n in MESH_INT:
+        mesh[n] = _np(getattr(m, n), sizes.get(n, m.num_triangles), np.int32)
+    name = getattr(lib, prefix + "scene_files_material_name")
+    name.restype = C.c_char_p
+    tname = getattr(lib, prefix + "scene_files_texture_name")
+    tname.restype = C.c_char_p
+    mats = {"num_materials": int(q.num_materials),
+            "material_names": [name(handle, C.c_int32(i)).decode() for i in range(q.num_materials)]}
+    for n in MAT_FLOAT_FIELDS:
+        mats[n] = _np(getattr(q, n), q.num_materials, np.float32)
+    for n in MAT_INT_FIELDS:
+        mats[n] = _np(getattr(q, n), q.num_materials, np.int32)
+    for c in "rgb":
+        mats["tex_" + c] = _np(getattr(v, "tex_" + c), v.texture_length, np.float32)
+    mats["texture_names"] = [tname(handle, C.c_int32(i)).decode() for i in range(v.num_textures)]
+    for n in ("texture_offset", "texture_height", "texture_width"):
+        mats[n] = _np(getattr(v, n), v.num_textures, np.int32)
+    mats["images"] = []
+    nbg = v.bg_height * v.bg_width
+    bg = dict(r=_np(v.bg_r, nbg, np.float32), g=_np(v.bg_g, nbg, np.float32),
+              b=_np(v.bg_b, nbg, np.float32), height=int(v.bg_height), width=int(v.bg_width))
+    c = v.camera
+    cam = dict(eye=tuple(c.eye), center=tuple(c.center), up=tuple(c.up), fovy=c.fovy,
+               width=c.width, height=c.height, aperture=c.aperture, focus_dist=c.focus_dist)
+    par = {n: getattr(v.params, n) for n, _ in GptParams._fields_ if n != "sky_emission"}
+    par["sky_emission"] = tuple(v.params.sky_emission)
+    sc = Scene(mesh=mesh, materials=mats, camera=cam, params=par, bg=bg,
+               name=(v.obj_filename or b"scene").decode())
+    sc.files = dict(input_folder_path=(v.input_folder_path or b"").decode(),
+                    obj_filename=(v.obj_filename or b"").decode(),
+                    texture_bg_path=(v.texture_bg_path or b"").decode(),
+                    image_output_path=(v.image_output_path or b"").decode(),
+                    ppm_image_output_iteration=int(v.ppm_image_output_iteration),
+                    parse_ms=float(v.parse_ms), obj_parse_ms=float(v.obj_parse_ms),
+                    obj_bytes=int(v.obj_bytes), threads=int(v.threads))
+    return sc
+
+
+def parse_scene_files(lib, prefix: str, master_path: str, threads: int = 0, reader=None):
+    """<prefix>scene_files_parse -> (handle, view).  The caller frees the handle."""
+    err = C.create_string_buffer(1024)
+    h = C.c_void_p()
+    if prefix == "gpt_":
+        cb = IMAGE_READER(reader) if reader is not None else C.cast(None, IMAGE_READER)
+        rc = lib.gpt_scene_files_parse(master_path.encode(), C.c_int(threads), cb, None,
+                                       C.byref(h), err, C.c_int(len(err)))
+    else:
+        rc = getattr(lib, prefix + "scene_files_parse")(master_path.encode(), C.byref(h), err,
+                                                       C.c_int(len(err)))
+    if rc != 0:
+        raise ValueError(f"scene loader: {err.value.decode(errors='replace')}")
+    v = GptSceneFilesView()
+    getattr(lib, prefix + "scene_files_view")(h, C.byref(v))
+    return h, v

@@ -290,6 +290,7 @@ class Scene:
     bg: dict = field(default_factory=lambda: dict(
         r=np.ones(1, F32), g=np.ones(1, F32), b=np.ones(1, F32), height=1, width=1))
     name: str = "scene"
+    files: dict = field(default_factory=dict)  # paths + parse timings when loaded from files
 
     @property
     def num_triangles(self) -> int:

@@ -141,6 +141,53 @@ int gpt_set_background(gpt_ctx *ctx, const float *r, const float *g, const float
 int gpt_set_camera(gpt_ctx *ctx, const GptCamera *cam);
 int gpt_set_params(gpt_ctx *ctx, const GptParams *params);
 
+/* ---- scene packer: replaces the host loaders of src/main.cu:165-471 --------------------------
+ *      (InputParam::extract_parameters input_param.h:36-122, extract_material_file_names /
+ *      extract_material_data / extract_num_elements / extract_triangle_data
+ *      read_file_util.h:125-655, extract_image_resource_requirement / extract_textures
+ *      read_image_util.h:47-176).  Host work: the OBJ file is mapped once and parsed by
+ *      `threads` host threads (0 = all cores) in two passes (count, scan, fill); the SoA it
+ *      produces is value-identical to the reference loader's (deviations: loader.cu header). */
+
+/* Decodes `path` into 8-bit RGB scan lines, top to bottom, in a malloc()ed buffer the library
+ * frees; returns 0 on success.  This is where the host's libjpeg goes (the reference reads JPEG
+ * through external/libjpeg_cpp/jpeg.h); with reader == NULL the built-in readers accept the raw
+ * "GPTIMG <w> <h>\n<rgb bytes>" container and binary PPM (P6). */
+typedef int (*gpt_image_reader)(void *user, const char *path, int32_t *height, int32_t *width,
+                                uint8_t **rgb);
+
+typedef struct gpt_scene_files gpt_scene_files;
+
+/* Borrowed pointers into a parsed scene; valid until gpt_scene_files_free. */
+typedef struct GptSceneFilesView {
+  GptMesh mesh;
+  GptMaterials materials;
+  GptCamera camera;
+  GptParams params;
+  const float *tex_r, *tex_g, *tex_b; /* planar atlas, texel 0 = the white default */
+  int64_t texture_length;
+  const float *bg_r, *bg_g, *bg_b;
+  int32_t bg_height, bg_width;
+  int32_t num_textures;               /* atlas entries incl. the default */
+  const int32_t *texture_offset, *texture_height, *texture_width;
+  const char *input_folder_path, *obj_filename, *texture_bg_path, *image_output_path;
+  int32_t ppm_image_output_iteration;
+  double parse_ms;                    /* whole gpt_scene_files_parse                      */
+  double obj_parse_ms;                /* OBJ + MTL + textures                             */
+  int64_t obj_bytes;
+  int32_t threads;                    /* host threads the OBJ passes actually used        */
+} GptSceneFilesView;
+
+/* Needs no GPU.  On failure returns GPT_E_INVALID and writes the reason into err. */
+int gpt_scene_files_parse(const char *master_file_path, int threads, gpt_image_reader reader,
+                          void *reader_user, gpt_scene_files **out, char *err, int err_len);
+int gpt_scene_files_view(const gpt_scene_files *s, GptSceneFilesView *view);
+const char *gpt_scene_files_material_name(const gpt_scene_files *s, int32_t i);
+const char *gpt_scene_files_texture_name(const gpt_scene_files *s, int32_t i);
+void gpt_scene_files_free(gpt_scene_files *s);
+/* gpt_set_mesh + _materials + _textures + _background + _camera + _params from a parsed scene */
+int gpt_load_scene_files(gpt_ctx *ctx, const gpt_scene_files *s);
+
 /* ---- build: replaces create_world's derived data (triangle.h:254-321), tangents
  *      (triangle_operations.h:18-61) and the three LBVH builds (src/main.cu:826-1197) --- */
 int gpt_build(gpt_ctx *ctx);

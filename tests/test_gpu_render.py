@@ -138,3 +138,21 @@ def test_against_reference_cuda_binary_8bit():
     equal = (ours == ref).mean()
     print(f"8-bit agreement with the reference CUDA binary: {equal:.5f}")
     assert equal >= 0.995, equal
+
+
+def test_scene_loaded_from_files_renders_the_same_image(tmp_path):
+    """f-2 end to end: write_scene_files -> gpt_scene_files_parse -> gpt_load_scene_files ->
+    build -> render is bit-identical to the render of the in-memory scene (the loader's extra
+    Default_123 material at slot 0 is unused)."""
+    from gpu_pathtracer_b200.api import PathTracer
+    sc = S.make_scene("small", n=20, width=96, height=64, spp=2, level=5, textured=True)
+    pt = PathTracer(sc)
+    pt.build()
+    want = pt.render_pathtrace()
+    master = S.write_scene_files(sc, str(tmp_path), "files")
+    pf = PathTracer()
+    loaded = pf.load_files(master, threads=2)
+    assert loaded.num_triangles == sc.num_triangles
+    pf.build()
+    got = pf.render_pathtrace()
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
