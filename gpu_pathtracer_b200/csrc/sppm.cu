@@ -37,6 +37,7 @@
 #include <vector>
 
 #include "integrator.cuh"
+#include "trace_persistent.cuh"
 
 namespace {
 
@@ -80,6 +81,27 @@ struct Tracer {
   unsigned nrays;   // closest-hit traversals of the MAIN BVH by this thread
 };
 
+// hit_record fill of Triangle::hit (triangle.h:399-405) from a closest-hit result; a miss only
+// resets t (the record persists across traversals).
+__device__ __forceinline__ bool fill_surf(const SppmScene &S, const TreeRef &tr, float t, int leaf,
+                                          int prim, float b1, float b2, float b3, V3 dir,
+                                          SurfRec &rec) {
+  rec.t = INFINITY;
+  if (leaf < 0) return false;
+  const float4 *tp = tr.tris + 3 * (size_t)leaf;
+  float4 t0 = __ldg(tp), t1 = __ldg(tp + 1), t2 = __ldg(tp + 2);
+  TriShade ts = load_tri_shade(S.sc.shade, prim);
+  const MaterialDev &m = S.sc.mats[ts.mat];
+  rec.t = t;
+  rec.point = b1 * V3{t0.x, t0.y, t0.z} + b2 * V3{t0.w, t1.x, t1.y} + b3 * V3{t1.z, t1.w, t2.x};
+  rec.u = b1 * ts.u1 + b2 * ts.u2 + b3 * ts.u3;
+  rec.v = b1 * ts.v1 + b2 * ts.v2 + b3 * ts.v3;
+  rec.normal = shading_normal(ts, m, S.atlas, b1, b2, b3);
+  rec.mat = ts.mat;
+  rec.in_dir = dir;
+  return true;
+}
+
 // traverse_bvh (bvh_traversal.h:12-84) + hit_record fill of Triangle::hit (triangle.h:399-405).
 // `dir` must already be the Ray's unit direction.
 static __device__ __noinline__ bool trace_surf(const SppmScene &S, const TreeRef &tr, bool is_main,
@@ -95,20 +117,7 @@ static __device__ __noinline__ bool trace_surf(const SppmScene &S, const TreeRef
                          nullptr, nullptr, &overflow);
   if (overflow) atomicExch(S.counters + 3, 1ull);
   if (is_main) T.nrays++;
-  rec.t = INFINITY;
-  if (h.leaf < 0) return false;
-  const float4 *tp = tr.tris + 3 * (size_t)h.leaf;
-  float4 t0 = __ldg(tp), t1 = __ldg(tp + 1), t2 = __ldg(tp + 2);
-  TriShade ts = load_tri_shade(S.sc.shade, h.prim);
-  const MaterialDev &m = S.sc.mats[ts.mat];
-  rec.t = h.t;
-  rec.point = h.b1 * V3{t0.x, t0.y, t0.z} + h.b2 * V3{t0.w, t1.x, t1.y} + h.b3 * V3{t1.z, t1.w, t2.x};
-  rec.u = h.b1 * ts.u1 + h.b2 * ts.u2 + h.b3 * ts.u3;
-  rec.v = h.b1 * ts.v1 + h.b2 * ts.v2 + h.b3 * ts.v3;
-  rec.normal = shading_normal(ts, m, S.atlas, h.b1, h.b2, h.b3);
-  rec.mat = ts.mat;
-  rec.in_dir = dir;
-  return true;
+  return fill_surf(S, tr, h.t, h.leaf, h.prim, h.b1, h.b2, h.b3, dir, rec);
 }
 
 // rearrange_material_list (material_list_operations.h:43-59)
@@ -355,6 +364,345 @@ k_photon_trace(SppmScene S, PhotonParams pp, uint32_t *rng_state, float4 *raw, u
   unsigned tot = T.nrays;
   for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
   if ((threadIdx.x & 31) == 0 && tot) atomicAdd(S.counters + 2, (unsigned long long)tot);
+}
+
+// ---- photon pass as a wavefront ------------------------------------------------------------------
+// The same photon_pass, cut at its closest-hit traversals of the main BVH: k_photon_step runs a
+// photon's logic up to the next ray it needs (or to its end), parks the live state in HBM (16
+// float4 = 8 whole sectors per photon) and queues the ray; k_ph_trace answers all queued rays with
+// the persistent, ray-refilling traversal the path tracer uses; the next k_photon_step resumes
+// every photon where it stopped.  One thread-per-photon megakernel (k_photon_trace above, kept as
+// the bit-exact cross-check, GPT_SPPM_MEGAKERNEL=1) leaves most lanes idle: photons end after
+// 1..max_bounce(+scatter events) rays, and its three traversal call sites serialise.
+struct PhotonWave {
+  float4 *state;   // 16 per photon
+  float4 *rays;    // 2 per photon: {o, tmax} {unit d, -}
+  float4 *hits;    // 2 per photon: {t, leaf, prim, -} {b1, b2, b3, -}
+  int *queue[2];
+  int *counts;     // [0] [1] queue lengths, [2] the trace kernel's ray cursor
+  uint32_t *key, *key_alt;  // coherence sort of the traced queue: (resume point, hit material)
+  int *val, *val_alt;
+};
+
+struct PhotonRaySource {
+  const int *queue;
+  const int *qcount;
+  const float4 *rays;
+  float4 *hits;
+  const float4 *shade;  // per-triangle shading records (material id in s6.y)
+  uint32_t *sort_key;   // out: key of queue entry i
+  int *sort_val;        // out: its slot
+  __device__ int count() const { return *qcount; }
+  __device__ void load(int i, float4 &o, float4 &d) const {
+    int s = queue[i];
+    o = rays[2 * (size_t)s];
+    d = rays[2 * (size_t)s + 1];
+  }
+  __device__ void store(int i, const TraceLane &l) const {
+    int s = queue[i];
+    hits[2 * (size_t)s] = make_float4(l.t, __int_as_float(l.leaf), __int_as_float(l.prim), 0.f);
+    hits[2 * (size_t)s + 1] = make_float4(l.b1, l.b2, l.b3, 0.f);
+    // photons that will run the same code in k_photon_step become neighbours: same resume point
+    // (stored by the step in the ray's spare word), same material at the hit
+    uint32_t key = 63u;
+    if (l.leaf >= 0) key = (uint32_t)__float_as_int(__ldg(&shade[7 * (size_t)l.prim + 6].y)) & 63u;
+    key |= (uint32_t)__float_as_int(rays[2 * (size_t)s + 1].w) << 6;
+    sort_key[i] = key;
+    sort_val[i] = s;
+  }
+};
+
+template <bool COUNT>
+__global__ void __launch_bounds__(TP_BLOCK, TP_MINBLOCKS)
+k_ph_trace(PhotonRaySource src, const float4 *__restrict__ nodes, const float4 *__restrict__ tris,
+           const int *__restrict__ parent_leaf, int *next_ray, unsigned long long *counters) {
+  __shared__ int stack[TP_STACK_SMEM * TP_BLOCK];
+  trace_persistent<COUNT>(nodes, tris, parent_leaf, src, next_ray, stack, counters);
+}
+
+enum { PH_NEW = 0, PH_MEDIUM = 1, PH_SURFACE = 2 };  // where a photon resumes
+
+struct PhotonLive {
+  Rng G, L;
+  SurfRec rec, recm;
+  V3 refk, color, prev, ro, rd;
+  float mean_color, d;
+  int num_bounce, medium, guard, resume;
+  bool hit, in_medium, scattered_in_medium, dcs, scattered_now, have_trace, ref_diffuse;
+  MatList list;
+};
+
+__device__ __forceinline__ void rng_bare(Rng &r) {
+  r.s.boxmuller_flag = 0;
+  r.s.boxmuller_flag_double = 0;
+  r.s.boxmuller_extra = 0.f;
+  r.s.boxmuller_extra_double = 0.0;
+}
+
+__device__ __forceinline__ void photon_save(const PhotonLive &p, float4 *st) {
+  auto F = [](uint32_t u) { return __uint_as_float(u); };
+  auto I = [](int i) { return __int_as_float(i); };
+  const Rng &G = p.G, &L = p.L;
+  st[0] = make_float4(F(G.s.d), F(G.s.v[0]), F(G.s.v[1]), F(G.s.v[2]));
+  st[1] = make_float4(F(G.s.v[3]), F(G.s.v[4]), F(L.s.d), F(L.s.v[0]));
+  st[2] = make_float4(F(L.s.v[1]), F(L.s.v[2]), F(L.s.v[3]), F(L.s.v[4]));
+  const SurfRec &a = p.rec, &b = p.recm;
+  st[3] = make_float4(a.t, a.point.x, a.point.y, a.point.z);
+  st[4] = make_float4(a.normal.x, a.normal.y, a.normal.z, a.u);
+  st[5] = make_float4(a.v, I(a.mat), a.in_dir.x, a.in_dir.y);
+  st[6] = make_float4(a.in_dir.z, b.t, b.point.x, b.point.y);
+  st[7] = make_float4(b.point.z, b.normal.x, b.normal.y, b.normal.z);
+  st[8] = make_float4(b.u, b.v, I(b.mat), b.in_dir.x);
+  st[9] = make_float4(b.in_dir.y, b.in_dir.z, p.refk.x, p.refk.y);
+  st[10] = make_float4(p.refk.z, p.color.x, p.color.y, p.color.z);
+  st[11] = make_float4(p.mean_color, p.prev.x, p.prev.y, p.prev.z);
+  st[12] = make_float4(p.ro.x, p.ro.y, p.ro.z, p.d);
+  st[13] = make_float4(p.rd.x, p.rd.y, p.rd.z, I(p.num_bounce));
+  int flags = (p.hit ? 1 : 0) | (p.in_medium ? 2 : 0) | (p.scattered_in_medium ? 4 : 0) |
+              (p.dcs ? 8 : 0) | (p.scattered_now ? 16 : 0) | (p.have_trace ? 32 : 0) |
+              (p.ref_diffuse ? 64 : 0) | (p.resume << 8);
+  st[14] = make_float4(I(p.medium), I(p.guard), I(flags), I(p.list.len));
+  uint32_t w[3];
+#pragma unroll
+  for (int k = 0; k < 3; k++)
+    w[k] = (uint32_t)p.list.id[4 * k] | ((uint32_t)p.list.id[4 * k + 1] << 8) |
+           ((uint32_t)p.list.id[4 * k + 2] << 16) | ((uint32_t)p.list.id[4 * k + 3] << 24);
+  st[15] = make_float4(F(w[0]), F(w[1]), F(w[2]), 0.f);
+}
+
+__device__ __forceinline__ void photon_load(PhotonLive &p, const float4 *st) {
+  auto U = [](float f) { return __float_as_uint(f); };
+  auto I = [](float f) { return __float_as_int(f); };
+  float4 q[16];
+#pragma unroll
+  for (int k = 0; k < 16; k++) q[k] = st[k];
+  Rng &G = p.G, &L = p.L;
+  G.s.d = U(q[0].x); G.s.v[0] = U(q[0].y); G.s.v[1] = U(q[0].z); G.s.v[2] = U(q[0].w);
+  G.s.v[3] = U(q[1].x); G.s.v[4] = U(q[1].y); L.s.d = U(q[1].z); L.s.v[0] = U(q[1].w);
+  L.s.v[1] = U(q[2].x); L.s.v[2] = U(q[2].y); L.s.v[3] = U(q[2].z); L.s.v[4] = U(q[2].w);
+  rng_bare(G);
+  rng_bare(L);
+  SurfRec &a = p.rec, &b = p.recm;
+  a.t = q[3].x; a.point = V3{q[3].y, q[3].z, q[3].w};
+  a.normal = V3{q[4].x, q[4].y, q[4].z}; a.u = q[4].w;
+  a.v = q[5].x; a.mat = I(q[5].y); a.in_dir = V3{q[5].z, q[5].w, q[6].x};
+  b.t = q[6].y; b.point = V3{q[6].z, q[6].w, q[7].x};
+  b.normal = V3{q[7].y, q[7].z, q[7].w};
+  b.u = q[8].x; b.v = q[8].y; b.mat = I(q[8].z); b.in_dir = V3{q[8].w, q[9].x, q[9].y};
+  p.refk = V3{q[9].z, q[9].w, q[10].x};
+  p.color = V3{q[10].y, q[10].z, q[10].w};
+  p.mean_color = q[11].x; p.prev = V3{q[11].y, q[11].z, q[11].w};
+  p.ro = V3{q[12].x, q[12].y, q[12].z}; p.d = q[12].w;
+  p.rd = V3{q[13].x, q[13].y, q[13].z}; p.num_bounce = I(q[13].w);
+  p.medium = I(q[14].x); p.guard = I(q[14].y);
+  int flags = I(q[14].z);
+  p.list.len = I(q[14].w);
+  p.hit = flags & 1; p.in_medium = flags & 2; p.scattered_in_medium = flags & 4;
+  p.dcs = flags & 8; p.scattered_now = flags & 16; p.have_trace = flags & 32;
+  p.ref_diffuse = flags & 64; p.resume = (flags >> 8) & 3;
+  uint32_t w[3] = {U(q[15].x), U(q[15].y), U(q[15].z)};
+#pragma unroll
+  for (int k = 0; k < 12; k++) p.list.id[k] = (unsigned char)((w[k >> 2] >> (8 * (k & 3))) & 255u);
+}
+
+// One step of photon_pass (photon_pass.h:97-237) for queue entry a: from where the photon stopped
+// to its next main-BVH ray (returns true: ray in W.rays, state parked) or to its end (false:
+// record written).  The statements and their order are those of k_photon_trace.
+template <bool FIRST>
+__global__ void __launch_bounds__(SP_BLOCK)
+k_photon_step(SppmScene S, PhotonParams pp, PhotonWave W, int cur, const int *__restrict__ slots,
+              uint32_t *rng_state, float4 *raw, uint32_t *kind) {
+  __shared__ int stack_mem[FIRST ? SP_STACK * SP_BLOCK : 1];  // init_material_list's traversals
+  const int a = blockIdx.x * blockDim.x + threadIdx.x;
+  const int n = FIRST ? pp.count : W.counts[cur];
+  if (!FIRST && a == 0) atomicAdd(S.counters + 2, (unsigned long long)n);  // rays just traced
+  bool emit = false;
+  int s = -1;
+  if (a < n) {
+    s = FIRST ? a : slots[a];
+    Tracer T{stack_mem + threadIdx.x, 0u};
+    PhotonLive p;
+    PhotonOut out;
+    out.kind = 2;
+    out.loc = V3{INFINITY, INFINITY, INFINITY};
+    out.prev = out.dir = out.color = V3{0.f, 0.f, 0.f};
+    RefRec ref;
+    bool sss = false, finished = false;
+    int resume;
+    if (FIRST) {
+      resume = PH_NEW;
+      rng_load(p.G, rng_state, s, pp.count);
+      p.L = p.G;
+      for (int k = 0; k < pp.pass; k++) (void)rng_uniform(p.L);
+      const float max_energy = __ldg(pp.cdf + pp.nlight - 1);
+      int li = pick_light(pp.cdf, pp.nlight, rng_uniform(p.L));
+      surf_init(p.rec);
+      {
+        const float4 *tp = S.lt.tris + 3 * (size_t)li;
+        float4 t0 = __ldg(tp), t1 = __ldg(tp + 1), t2 = __ldg(tp + 2);
+        int prim = __float_as_int(t2.z);
+        TriShade ts = load_tri_shade(S.sc.shade, prim);
+        float r1 = rng_uniform(p.L), r2 = rng_uniform(p.L);
+        float u = 1.f - powf(r1, .5f);
+        float v = r2 * powf(r1, .5f);
+        float w = 1.f - u - v;
+        p.rec.point = (u * V3{t0.x, t0.y, t0.z} + v * V3{t0.w, t1.x, t1.y}) + w * V3{t1.z, t1.w, t2.x};
+        p.rec.normal = unit((u * ts.n1 + v * ts.n2) + w * ts.n3);
+        p.rec.u = (u * ts.u1 + v * ts.u2) + w * ts.u3;
+        p.rec.v = (u * ts.v1 + v * ts.v2) + w * ts.v3;
+        p.rec.mat = ts.mat;
+        Frame f = frame_from_z(p.rec.normal);
+        V3 rd = frame_to_world(f, sample_hemisphere(p.L));
+        p.rec.in_dir = unit(-rd);
+      }
+      p.color = mat_emission(S.atlas, S.sc.mats[p.rec.mat], p.rec.u, p.rec.v);
+      p.color = p.color * (max_energy / ((p.color.x + p.color.y + p.color.z) / 3.f));
+      p.mean_color = (p.color.x + p.color.y + p.color.z) / 3.f;
+      (void)generate_dir(V3{0.f, 0.f, 0.f}, p.rec.normal, 2, 1.f, p.L);
+      p.prev = p.rec.point;
+#pragma unroll
+      for (int k = 0; k < MATLIST_MAX; k++) p.list.id[k] = MAT_AIR;
+      p.list.len = 0;
+      surf_init(p.recm);
+      p.refk = V3{0.f, 0.f, 0.f};
+      p.ref_diffuse = false;
+      p.ro = p.rd = V3{0.f, 0.f, 0.f};
+      p.d = 0.f;
+      p.num_bounce = -1;
+      p.medium = MAT_AIR;
+      p.guard = 0;
+      p.hit = p.in_medium = p.scattered_in_medium = p.dcs = false;
+      p.scattered_now = p.have_trace = false;
+    } else {
+      photon_load(p, W.state + 16 * (size_t)s);
+      resume = p.resume;
+      float4 h0 = W.hits[2 * (size_t)s], h1 = W.hits[2 * (size_t)s + 1];
+      float4 rdv = W.rays[2 * (size_t)s + 1];
+      SurfRec &target = resume == PH_MEDIUM ? p.recm : p.rec;
+      p.hit = fill_surf(S, S.main_t, h0.x, __float_as_int(h0.y), __float_as_int(h0.z), h1.x, h1.y,
+                        h1.z, V3{rdv.x, rdv.y, rdv.z}, target);
+    }
+    ref.k = p.refk;
+    ref.diffuse = p.ref_diffuse;
+    ref.reflected = ref.refracted = ref.false_hit = ref.entering = ref.bent = false;
+    ref.n = 1.f; ref.perfect = V3{1.f, 0.f, 0.f};
+    ref.dir = V3{1.f, 0.f, 0.f}; ref.filter = ref.filter2 = V3{0.f, 0.f, 0.f};
+    ref.next_material = MAT_AIR;
+    V3 ray_o = V3{0.f, 0.f, 0.f}, ray_d = V3{1.f, 0.f, 0.f};
+    bool in_medium_walk = resume == PH_MEDIUM;
+    while (true) {
+      if (!in_medium_walk) {
+        // ---- loop head (photon_pass.h:141) ----
+        if (!((p.hit && p.num_bounce < pp.max_bounce) || p.num_bounce < 0)) {
+          finished = true;
+          break;
+        }
+        p.scattered_now = false;
+        p.have_trace = false;
+        p.num_bounce++;
+        // only a photon's first step can be at bounce 0 (resumed photons are at >= 1)
+        if (FIRST && p.num_bounce <= 0) init_material_list(S, T, p.list, p.rec.point, p.rec.normal, p.L);
+        check_next_path<true>(S.sc.mats, S.atlas, p.rec.mat, p.rec.in_dir, p.rec.normal, p.rec.u,
+                              p.rec.v, p.list, ref, sss, p.G, false);
+        if (p.num_bounce > 0) rearrange_list(S, p.list, p.rec.mat, ref);
+        p.in_medium = entering_medium(S, ref, p.in_medium, p.medium);
+      }
+      if (in_medium_walk || !ref.false_hit) {
+        if (in_medium_walk || (p.in_medium && !p.dcs && p.medium != MAT_AIR)) {
+          const MaterialDev &md = S.sc.mats[p.medium];
+          if (!in_medium_walk) {
+            p.ro = p.rec.point;
+            p.rd = ref.dir;
+            p.d = -logf(rng_uniform(p.L)) / md.extinction_coef;
+            p.guard = 0;
+            ray_o = p.ro; ray_d = p.rd;
+            p.resume = PH_MEDIUM;
+            emit = true;
+            break;
+          }
+          in_medium_walk = false;
+          p.have_trace = true;
+          if (p.d - p.recm.t < GPT_SMALL && p.guard++ < 4096) {
+            p.scattered_in_medium = true;
+            p.scattered_now = true;
+            float rn = rng_uniform(p.L);
+            if (rn < md.scattering_prob) {
+              out.kind = 1;
+              out.prev = p.prev;
+              out.loc = p.ro + p.d * p.rd;
+              out.color = p.color;
+              out.dir = p.recm.in_dir;
+              finished = true;
+              break;
+            }
+            V3 nd = new_scattering_direction(md, p.rd, p.L);
+            p.d = -logf(rng_uniform(p.L)) / md.extinction_coef;
+            p.ro = p.ro + p.d * p.rd;
+            p.rd = unit(nd);
+            p.prev = p.recm.point;
+            ray_o = p.ro; ray_d = p.rd;
+            p.resume = PH_MEDIUM;
+            emit = true;
+            break;
+          }
+          p.dcs = true;
+          if (p.scattered_now) p.rec = p.recm;
+        }
+        if (!p.scattered_now && p.num_bounce > 0) {
+          float rn = rng_uniform(p.L);
+          float refl = fmaxf(fmaxf(ref.k.x, ref.k.y), ref.k.z);
+          if (rn > refl) {
+            if (ref.diffuse && (p.num_bounce > 1 || p.scattered_in_medium)) {
+              out.kind = 0;
+              out.prev = p.prev;
+              out.loc = p.rec.point;
+              out.color = p.color;
+              out.dir = p.rec.in_dir;
+            }
+            finished = true;
+            break;
+          }
+          p.color = ref.k * p.color;
+          float mean_tmp = (p.color.x + p.color.y + p.color.z) / 3.f;
+          p.color = p.color * (p.mean_color / mean_tmp);
+          p.dcs = false;
+        }
+      }
+      if (!p.scattered_now) {
+        p.prev = p.rec.point;
+        if (p.have_trace) {  // the reference re-traces the identical ray (photon_pass.h:230-233)
+          p.rec = p.recm;
+        } else {
+          ray_o = p.rec.point; ray_d = ref.dir;
+          p.resume = PH_SURFACE;
+          emit = true;
+          break;
+        }
+      }
+    }
+    if (emit) {
+      p.refk = ref.k;
+      p.ref_diffuse = ref.diffuse;
+      W.rays[2 * (size_t)s] = make_float4(ray_o.x, ray_o.y, ray_o.z, INFINITY);
+      W.rays[2 * (size_t)s + 1] = make_float4(ray_d.x, ray_d.y, ray_d.z, __int_as_float(p.resume));
+      photon_save(p, W.state + 16 * (size_t)s);
+    } else {
+      (void)finished;
+      rng_store(p.G, rng_state, s, pp.count);
+      raw[3 * (size_t)s] = make_float4(out.loc.x, out.loc.y, out.loc.z, out.prev.x);
+      raw[3 * (size_t)s + 1] = make_float4(out.prev.y, out.prev.z, out.dir.x, out.dir.y);
+      raw[3 * (size_t)s + 2] = make_float4(out.dir.z, out.color.x, out.color.y, out.color.z);
+      kind[s] = (uint32_t)out.kind;
+    }
+  }
+  // warp-aggregated append to the next queue
+  unsigned m = __ballot_sync(0xffffffffu, emit);
+  if (m) {
+    int lane = threadIdx.x & 31, leader = __ffs(m) - 1, base = 0;
+    if (lane == leader) base = atomicAdd(W.counts + (FIRST ? 0 : (cur ^ 1)), __popc(m));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (emit) W.queue[FIRST ? 0 : (cur ^ 1)][base + __popc(m & ((1u << lane) - 1u))] = s;
+  }
 }
 
 __global__ void __launch_bounds__(256) k_iota(int *v, int n) {
@@ -901,6 +1249,7 @@ struct SppmCtx {
   float4 *leaf_surf = nullptr, *leaf_vol = nullptr, *spheres = nullptr;
   BvhDev surf_bvh, vol_bvh;
   int n_surf = 0, n_vol = 0;
+  PhotonWave wave{};               // wavefront photon pass: parked state, rays, hits, queues
   float *cdf = nullptr;
   int cdf_n = 0;
   int *d_counts = nullptr;        // [0] n_surf [1] n_surf + n_vol [2] error flag
@@ -984,6 +1333,16 @@ static int sppm_reserve_photons(gpt_ctx *ctx, SppmCtx *sx, long long first, int 
     GPT_TRY(gpt_alloc(ctx, &sx->leaf_surf, 3 * N));
     GPT_TRY(gpt_alloc(ctx, &sx->leaf_vol, 3 * N));
     GPT_TRY(gpt_alloc(ctx, &sx->spheres, 2 * N));
+    GPT_TRY(gpt_alloc(ctx, &sx->wave.state, 16 * N));
+    GPT_TRY(gpt_alloc(ctx, &sx->wave.rays, 2 * N));
+    GPT_TRY(gpt_alloc(ctx, &sx->wave.hits, 2 * N));
+    GPT_TRY(gpt_alloc(ctx, &sx->wave.queue[0], N));
+    GPT_TRY(gpt_alloc(ctx, &sx->wave.queue[1], N));
+    GPT_TRY(gpt_alloc(ctx, &sx->wave.key, N));
+    GPT_TRY(gpt_alloc(ctx, &sx->wave.key_alt, N));
+    GPT_TRY(gpt_alloc(ctx, &sx->wave.val, N));
+    GPT_TRY(gpt_alloc(ctx, &sx->wave.val_alt, N));
+    if (!sx->wave.counts) GPT_TRY(gpt_alloc(ctx, &sx->wave.counts, (size_t)4));
     sx->ph_capacity = count;
     sx->ph_first = -1;
   }
@@ -1038,7 +1397,9 @@ void gpt_sppm_free(gpt_ctx *ctx) {
                sx->rng_pix, sx->rng_ph, sx->raw, sx->kind, sx->kind_alt, sx->hist, sx->idx,
                sx->idx_alt, sx->aabb, sx->leaf_surf, sx->leaf_vol, sx->spheres, sx->cdf,
                sx->d_counts, sx->d_mean, sx->d_stat, sx->d_out, sx->leaf_info, sx->node_info,
-               sx->node_energy, sx->lt_flags};
+               sx->node_energy, sx->lt_flags, sx->wave.state, sx->wave.rays, sx->wave.hits,
+               sx->wave.queue[0], sx->wave.queue[1], sx->wave.counts, sx->wave.key,
+               sx->wave.key_alt, sx->wave.val, sx->wave.val_alt};
   for (void *q : p) cudaFree(q);
   gpt_lbvh_free(sx->surf_bvh);
   gpt_lbvh_free(sx->vol_bvh);
@@ -1092,6 +1453,68 @@ int gpt_sppm_init(gpt_ctx *ctx) {
 
 // gather_recorded_photons (photon_pass.h:19-47) as a stable partition by kind (photon order is
 // kept inside each kind), then the two photon trees (src/main.cu:1576-1752).
+// photon_pass<<<ppm_num_photon_per_pass, 1>>> (src/main.cu:1496): the wavefront by default, the
+// one-thread-per-photon megakernel when GPT_SPPM_MEGAKERNEL=1 (cross-check; identical records).
+static int photon_stage(gpt_ctx *ctx, SppmCtx *sx, const SppmScene &S, const PhotonParams &pp) {
+  cudaStream_t st = ctx->stream;
+  const int count = pp.count;
+  static int mega = -1;
+  if (mega < 0) {
+    const char *e = getenv("GPT_SPPM_MEGAKERNEL");
+    mega = (e && atoi(e) != 0) ? 1 : 0;
+  }
+  if (mega) {
+    k_photon_trace<<<(count + SP_BLOCK - 1) / SP_BLOCK, SP_BLOCK, 0, st>>>(S, pp, sx->rng_ph, sx->raw,
+                                                                        sx->kind);
+    GPT_LAUNCH_CHECK(ctx);
+    return GPT_OK;
+  }
+  static int trace_grid = 0;
+  if (!trace_grid) {
+    int sms = 148, per_sm = 4;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ph_trace<false>, TP_BLOCK, 0);
+    trace_grid = sms * (per_sm > 0 ? per_sm : 1);
+  }
+  PhotonWave &W = sx->wave;
+  BvhDev &mb = ctx->bvh[GPT_BVH_MAIN];
+  GPT_CUDA(ctx, cudaMemsetAsync(W.counts, 0, 4 * sizeof(int), st));
+  k_photon_step<true><<<(count + SP_BLOCK - 1) / SP_BLOCK, SP_BLOCK, 0, st>>>(S, pp, W, 0, nullptr,
+                                                                             sx->rng_ph, sx->raw, sx->kind);
+  GPT_LAUNCH_CHECK(ctx);
+  int cur = 0;
+  // every photon ends after at most max_bounce surface events + 4096 scatter events per bounce
+  for (long long it = 0; it < 4100LL * (pp.max_bounce + 2); it++) {
+    int h[2];
+    GPT_CUDA(ctx, cudaMemcpyAsync(h, W.counts, sizeof(h), cudaMemcpyDeviceToHost, st));
+    GPT_CUDA(ctx, cudaStreamSynchronize(st));
+    const int n = h[cur];
+    if (n == 0) return GPT_OK;
+    GPT_CUDA(ctx, cudaMemsetAsync(W.counts + (cur ^ 1), 0, sizeof(int), st));
+    GPT_CUDA(ctx, cudaMemsetAsync(W.counts + 2, 0, sizeof(int), st));
+    PhotonRaySource src{W.queue[cur], W.counts + cur, W.rays, W.hits, ctx->scene.shade, W.key, W.val};
+    int grid = (n + TP_BLOCK - 1) / TP_BLOCK;
+    if (grid > trace_grid) grid = trace_grid;
+    if (S.count_visits)
+      k_ph_trace<true><<<grid, TP_BLOCK, 0, st>>>(src, mb.nodes, mb.tris, mb.parent_leaf, W.counts + 2,
+                                                 ctx->d_counters);
+    else
+      k_ph_trace<false><<<grid, TP_BLOCK, 0, st>>>(src, mb.nodes, mb.tris, mb.parent_leaf, W.counts + 2,
+                                                  ctx->d_counters);
+    GPT_LAUNCH_CHECK(ctx);
+    // stable 8-bit radix sort of the traced photons by (resume point, hit material)
+    uint32_t *sk = nullptr;
+    int *sorted_slots = nullptr;
+    GPT_TRY(gpt_radix_sort_pairs(ctx, W.key, W.val, W.key_alt, W.val_alt, sx->hist, n, 8, &sk,
+                                 &sorted_slots, W.counts + cur));
+    k_photon_step<false><<<(n + SP_BLOCK - 1) / SP_BLOCK, SP_BLOCK, 0, st>>>(S, pp, W, cur, sorted_slots,
+                                                                            sx->rng_ph, sx->raw, sx->kind);
+    GPT_LAUNCH_CHECK(ctx);
+    cur ^= 1;
+  }
+  return gpt_fail(ctx, GPT_E_INVALID, "photon wavefront did not drain", __FILE__, __LINE__);
+}
+
 static int sppm_build_trees(gpt_ctx *ctx, SppmCtx *sx, int count) {
   cudaStream_t st = ctx->stream;
   GPT_CUDA(ctx, cudaMemsetAsync(sx->d_counts, 0, 2 * sizeof(int), st));
@@ -1163,9 +1586,7 @@ int gpt_sppm_pass_stages(gpt_ctx *ctx, int pass, int64_t photon_begin, int64_t p
       pp.count = count;
       pp.cdf = sx->cdf;
       pp.nlight = ctx->bvh[GPT_BVH_LIGHT].n;
-      int grid = (count + SP_BLOCK - 1) / SP_BLOCK;
-      k_photon_trace<<<grid, SP_BLOCK, 0, st>>>(S, pp, sx->rng_ph, sx->raw, sx->kind);
-      GPT_LAUNCH_CHECK(ctx);
+      GPT_TRY(photon_stage(ctx, sx, S, pp));
       GPT_TRY(sppm_build_trees(ctx, sx, count));
     }
   }
