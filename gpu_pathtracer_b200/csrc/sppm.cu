@@ -378,8 +378,9 @@ struct PhotonWave {
   float4 *state;   // 16 per photon
   float4 *rays;    // 2 per photon: {o, tmax} {unit d, -}
   float4 *hits;    // 2 per photon: {t, leaf, prim, -} {b1, b2, b3, -}
-  int *queue[2];
-  int *counts;     // [0] [1] queue lengths, [2] the trace kernel's ray cursor
+  int *queue[2];   // photons waiting for a main-BVH ray
+  int *iqueue[2];  // photons waiting for a transparent-BVH ray (init_material_list)
+  int *counts;     // [0] [1] queue lengths, [2] trace cursor; [3] [4] [5] same for iqueue
   uint32_t *key, *key_alt;  // coherence sort of the traced queue: (resume point, hit material)
   int *val, *val_alt;
 };
@@ -390,7 +391,7 @@ struct PhotonRaySource {
   const float4 *rays;
   float4 *hits;
   const float4 *shade;  // per-triangle shading records (material id in s6.y)
-  uint32_t *sort_key;   // out: key of queue entry i
+  uint32_t *sort_key;   // out: key of queue entry i (already offset for this queue)
   int *sort_val;        // out: its slot
   __device__ int count() const { return *qcount; }
   __device__ void load(int i, float4 &o, float4 &d) const {
@@ -420,7 +421,7 @@ k_ph_trace(PhotonRaySource src, const float4 *__restrict__ nodes, const float4 *
   trace_persistent<COUNT>(nodes, tris, parent_leaf, src, next_ray, stack, counters);
 }
 
-enum { PH_NEW = 0, PH_MEDIUM = 1, PH_SURFACE = 2 };  // where a photon resumes
+enum { PH_NEW = 0, PH_MEDIUM = 1, PH_SURFACE = 2, PH_INIT = 3 };  // where a photon resumes
 
 struct PhotonLive {
   Rng G, L;
@@ -505,22 +506,17 @@ __device__ __forceinline__ void photon_load(PhotonLive &p, const float4 *st) {
   for (int k = 0; k < 12; k++) p.list.id[k] = (unsigned char)((w[k >> 2] >> (8 * (k & 3))) & 255u);
 }
 
-// One step of photon_pass (photon_pass.h:97-237) for queue entry a: from where the photon stopped
-// to its next main-BVH ray (returns true: ray in W.rays, state parked) or to its end (false:
-// record written).  The statements and their order are those of k_photon_trace.
+// One step of photon_pass (photon_pass.h:97-237) for photon slot s: from where the photon stopped
+// to the next ray it needs -- returns 1: a main-BVH ray, 2: a transparent-BVH ray of
+// init_material_list (material_list_operations.h:61-92); the ray is in W.rays and the state is
+// parked -- or to its end (returns 0: record written).  The statements and their order are those
+// of k_photon_trace.
 template <bool FIRST>
-__global__ void __launch_bounds__(SP_BLOCK)
-k_photon_step(SppmScene S, PhotonParams pp, PhotonWave W, int cur, const int *__restrict__ slots,
-              uint32_t *rng_state, float4 *raw, uint32_t *kind) {
-  __shared__ int stack_mem[FIRST ? SP_STACK * SP_BLOCK : 1];  // init_material_list's traversals
-  const int a = blockIdx.x * blockDim.x + threadIdx.x;
-  const int n = FIRST ? pp.count : W.counts[cur];
-  if (!FIRST && a == 0) atomicAdd(S.counters + 2, (unsigned long long)n);  // rays just traced
-  bool emit = false;
-  int s = -1;
-  if (a < n) {
-    s = FIRST ? a : slots[a];
-    Tracer T{stack_mem + threadIdx.x, 0u};
+__device__ __forceinline__ int photon_step_one(const SppmScene &S, const PhotonParams &pp,
+                                               const PhotonWave &W, int s, uint32_t *rng_state,
+                                               float4 *raw, uint32_t *kind) {
+  int emit = 0;
+  {
     PhotonLive p;
     PhotonOut out;
     out.kind = 2;
@@ -529,6 +525,7 @@ k_photon_step(SppmScene S, PhotonParams pp, PhotonWave W, int cur, const int *__
     RefRec ref;
     bool sss = false, finished = false;
     int resume;
+    V3 ray_o = V3{0.f, 0.f, 0.f}, ray_d = V3{1.f, 0.f, 0.f};
     if (FIRST) {
       resume = PH_NEW;
       rng_load(p.G, rng_state, s, pp.count);
@@ -573,14 +570,39 @@ k_photon_step(SppmScene S, PhotonParams pp, PhotonWave W, int cur, const int *__
       p.guard = 0;
       p.hit = p.in_medium = p.scattered_in_medium = p.dcs = false;
       p.scattered_now = p.have_trace = false;
+      if (S.transp_t.n >= 2) {  // init_material_list: walk back from 999 units along the normal
+        p.d = 999.f;            // (t of the reference's loop, kept in the free-flight slot)
+        ray_o = p.rec.point + p.d * p.rec.normal;
+        ray_d = unit(-p.rec.normal);
+        p.resume = PH_INIT;
+        emit = 2;
+      }
     } else {
       photon_load(p, W.state + 16 * (size_t)s);
       resume = p.resume;
       float4 h0 = W.hits[2 * (size_t)s], h1 = W.hits[2 * (size_t)s + 1];
       float4 rdv = W.rays[2 * (size_t)s + 1];
-      SurfRec &target = resume == PH_MEDIUM ? p.recm : p.rec;
-      p.hit = fill_surf(S, S.main_t, h0.x, __float_as_int(h0.y), __float_as_int(h0.z), h1.x, h1.y,
-                        h1.z, V3{rdv.x, rdv.y, rdv.z}, target);
+      SurfRec &target = resume == PH_SURFACE ? p.rec : p.recm;
+      p.hit = fill_surf(S, resume == PH_INIT ? S.transp_t : S.main_t, h0.x, __float_as_int(h0.y),
+                        __float_as_int(h0.z), h1.x, h1.y, h1.z, V3{rdv.x, rdv.y, rdv.z}, target);
+      if (resume == PH_INIT) {
+        if (p.hit && p.d - p.recm.t > GPT_SMALL && p.guard++ < 4096) {
+          p.d -= p.recm.t;
+          RefRec iref;
+          bool isss;
+          check_next_path<true>(S.sc.mats, S.atlas, p.recm.mat, p.recm.in_dir, p.recm.normal,
+                                p.recm.u, p.recm.v, p.list, iref, isss, p.L, true);
+          rearrange_list(S, p.list, p.recm.mat, iref);
+          ray_o = p.recm.point;
+          ray_d = unit(-p.rec.normal);
+          emit = 2;
+        } else {  // the walk is over: the loop proper starts with fresh records
+          surf_init(p.recm);
+          p.hit = false;
+          p.guard = 0;
+          p.d = 0.f;
+        }
+      }
     }
     ref.k = p.refk;
     ref.diffuse = p.ref_diffuse;
@@ -588,9 +610,8 @@ k_photon_step(SppmScene S, PhotonParams pp, PhotonWave W, int cur, const int *__
     ref.n = 1.f; ref.perfect = V3{1.f, 0.f, 0.f};
     ref.dir = V3{1.f, 0.f, 0.f}; ref.filter = ref.filter2 = V3{0.f, 0.f, 0.f};
     ref.next_material = MAT_AIR;
-    V3 ray_o = V3{0.f, 0.f, 0.f}, ray_d = V3{1.f, 0.f, 0.f};
     bool in_medium_walk = resume == PH_MEDIUM;
-    while (true) {
+    while (emit == 0) {
       if (!in_medium_walk) {
         // ---- loop head (photon_pass.h:141) ----
         if (!((p.hit && p.num_bounce < pp.max_bounce) || p.num_bounce < 0)) {
@@ -600,8 +621,7 @@ k_photon_step(SppmScene S, PhotonParams pp, PhotonWave W, int cur, const int *__
         p.scattered_now = false;
         p.have_trace = false;
         p.num_bounce++;
-        // only a photon's first step can be at bounce 0 (resumed photons are at >= 1)
-        if (FIRST && p.num_bounce <= 0) init_material_list(S, T, p.list, p.rec.point, p.rec.normal, p.L);
+        // (init_material_list of bounce 0 has already run as the PH_INIT steps)
         check_next_path<true>(S.sc.mats, S.atlas, p.rec.mat, p.rec.in_dir, p.rec.normal, p.rec.u,
                               p.rec.v, p.list, ref, sss, p.G, false);
         if (p.num_bounce > 0) rearrange_list(S, p.list, p.rec.mat, ref);
@@ -617,7 +637,7 @@ k_photon_step(SppmScene S, PhotonParams pp, PhotonWave W, int cur, const int *__
             p.guard = 0;
             ray_o = p.ro; ray_d = p.rd;
             p.resume = PH_MEDIUM;
-            emit = true;
+            emit = 1;
             break;
           }
           in_medium_walk = false;
@@ -642,7 +662,7 @@ k_photon_step(SppmScene S, PhotonParams pp, PhotonWave W, int cur, const int *__
             p.prev = p.recm.point;
             ray_o = p.ro; ray_d = p.rd;
             p.resume = PH_MEDIUM;
-            emit = true;
+            emit = 1;
             break;
           }
           p.dcs = true;
@@ -675,7 +695,7 @@ k_photon_step(SppmScene S, PhotonParams pp, PhotonWave W, int cur, const int *__
         } else {
           ray_o = p.rec.point; ray_d = ref.dir;
           p.resume = PH_SURFACE;
-          emit = true;
+          emit = 1;
           break;
         }
       }
@@ -695,13 +715,38 @@ k_photon_step(SppmScene S, PhotonParams pp, PhotonWave W, int cur, const int *__
       kind[s] = (uint32_t)out.kind;
     }
   }
-  // warp-aggregated append to the next queue
-  unsigned m = __ballot_sync(0xffffffffu, emit);
-  if (m) {
-    int lane = threadIdx.x & 31, leader = __ffs(m) - 1, base = 0;
-    if (lane == leader) base = atomicAdd(W.counts + (FIRST ? 0 : (cur ^ 1)), __popc(m));
-    base = __shfl_sync(0xffffffffu, base, leader);
-    if (emit) W.queue[FIRST ? 0 : (cur ^ 1)][base + __popc(m & ((1u << lane) - 1u))] = s;
+  return emit;
+}
+
+// Persistent over the (sorted) slot list: a thread's local-memory frame is reused from photon to
+// photon instead of one frame per photon going out to HBM.  n = n_init + n_main entries.
+template <bool FIRST>
+__global__ void __launch_bounds__(SP_BLOCK)
+k_photon_step(SppmScene S, PhotonParams pp, PhotonWave W, int cur, const int *__restrict__ slots,
+              int n, int n_main, uint32_t *rng_state, float4 *raw, uint32_t *kind) {
+  if (!FIRST && blockIdx.x == 0 && threadIdx.x == 0)
+    atomicAdd(S.counters + 2, (unsigned long long)n_main);  // main-BVH rays just traced
+  const int lane = threadIdx.x & 31;
+  const int nxt = FIRST ? 0 : (cur ^ 1);
+  for (int base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x) {
+    const int a = base + threadIdx.x;
+    int s = -1, emit = 0;
+    if (a < n) {
+      s = FIRST ? a : slots[a];
+      emit = photon_step_one<FIRST>(S, pp, W, s, rng_state, raw, kind);
+    }
+    // warp-aggregated append to the next main / init queue
+#pragma unroll
+    for (int q = 1; q <= 2; q++) {
+      unsigned m = __ballot_sync(0xffffffffu, emit == q);
+      if (m) {
+        int leader = __ffs(m) - 1, at = 0;
+        int *cnt = W.counts + (q == 1 ? nxt : 3 + nxt);
+        if (lane == leader) at = atomicAdd(cnt, __popc(m));
+        at = __shfl_sync(0xffffffffu, at, leader);
+        if (emit == q) (q == 1 ? W.queue[nxt] : W.iqueue[nxt])[at + __popc(m & ((1u << lane) - 1u))] = s;
+      }
+    }
   }
 }
 
@@ -1338,11 +1383,13 @@ static int sppm_reserve_photons(gpt_ctx *ctx, SppmCtx *sx, long long first, int 
     GPT_TRY(gpt_alloc(ctx, &sx->wave.hits, 2 * N));
     GPT_TRY(gpt_alloc(ctx, &sx->wave.queue[0], N));
     GPT_TRY(gpt_alloc(ctx, &sx->wave.queue[1], N));
+    GPT_TRY(gpt_alloc(ctx, &sx->wave.iqueue[0], N));
+    GPT_TRY(gpt_alloc(ctx, &sx->wave.iqueue[1], N));
     GPT_TRY(gpt_alloc(ctx, &sx->wave.key, N));
     GPT_TRY(gpt_alloc(ctx, &sx->wave.key_alt, N));
     GPT_TRY(gpt_alloc(ctx, &sx->wave.val, N));
     GPT_TRY(gpt_alloc(ctx, &sx->wave.val_alt, N));
-    if (!sx->wave.counts) GPT_TRY(gpt_alloc(ctx, &sx->wave.counts, (size_t)4));
+    if (!sx->wave.counts) GPT_TRY(gpt_alloc(ctx, &sx->wave.counts, (size_t)8));
     sx->ph_capacity = count;
     sx->ph_first = -1;
   }
@@ -1398,7 +1445,8 @@ void gpt_sppm_free(gpt_ctx *ctx) {
                sx->idx_alt, sx->aabb, sx->leaf_surf, sx->leaf_vol, sx->spheres, sx->cdf,
                sx->d_counts, sx->d_mean, sx->d_stat, sx->d_out, sx->leaf_info, sx->node_info,
                sx->node_energy, sx->lt_flags, sx->wave.state, sx->wave.rays, sx->wave.hits,
-               sx->wave.queue[0], sx->wave.queue[1], sx->wave.counts, sx->wave.key,
+               sx->wave.queue[0], sx->wave.queue[1], sx->wave.iqueue[0], sx->wave.iqueue[1],
+               sx->wave.counts, sx->wave.key,
                sx->wave.key_alt, sx->wave.val, sx->wave.val_alt};
   for (void *q : p) cudaFree(q);
   gpt_lbvh_free(sx->surf_bvh);
@@ -1476,39 +1524,62 @@ static int photon_stage(gpt_ctx *ctx, SppmCtx *sx, const SppmScene &S, const Pho
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ph_trace<false>, TP_BLOCK, 0);
     trace_grid = sms * (per_sm > 0 ? per_sm : 1);
   }
+  static int step_grid[2] = {0, 0};
+  if (!step_grid[0]) {
+    int sms = 148, per_sm = 4;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_photon_step<false>, SP_BLOCK, 0);
+    step_grid[0] = sms * (per_sm > 0 ? per_sm : 1);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_photon_step<true>, SP_BLOCK, 0);
+    step_grid[1] = sms * (per_sm > 0 ? per_sm : 1);
+  }
   PhotonWave &W = sx->wave;
-  BvhDev &mb = ctx->bvh[GPT_BVH_MAIN];
-  GPT_CUDA(ctx, cudaMemsetAsync(W.counts, 0, 4 * sizeof(int), st));
-  k_photon_step<true><<<(count + SP_BLOCK - 1) / SP_BLOCK, SP_BLOCK, 0, st>>>(S, pp, W, 0, nullptr,
-                                                                             sx->rng_ph, sx->raw, sx->kind);
-  GPT_LAUNCH_CHECK(ctx);
+  BvhDev &mb = ctx->bvh[GPT_BVH_MAIN], &tb = ctx->bvh[GPT_BVH_TRANSPARENT];
+  GPT_CUDA(ctx, cudaMemsetAsync(W.counts, 0, 8 * sizeof(int), st));
+  {
+    int grid = (count + SP_BLOCK - 1) / SP_BLOCK;
+    if (grid > step_grid[1]) grid = step_grid[1];
+    k_photon_step<true><<<grid, SP_BLOCK, 0, st>>>(S, pp, W, 0, nullptr, count, 0, sx->rng_ph, sx->raw,
+                                                   sx->kind);
+    GPT_LAUNCH_CHECK(ctx);
+  }
   int cur = 0;
-  // every photon ends after at most max_bounce surface events + 4096 scatter events per bounce
-  for (long long it = 0; it < 4100LL * (pp.max_bounce + 2); it++) {
-    int h[2];
-    GPT_CUDA(ctx, cudaMemcpyAsync(h, W.counts, sizeof(h), cudaMemcpyDeviceToHost, st));
-    GPT_CUDA(ctx, cudaStreamSynchronize(st));
-    const int n = h[cur];
-    if (n == 0) return GPT_OK;
-    GPT_CUDA(ctx, cudaMemsetAsync(W.counts + (cur ^ 1), 0, sizeof(int), st));
-    GPT_CUDA(ctx, cudaMemsetAsync(W.counts + 2, 0, sizeof(int), st));
-    PhotonRaySource src{W.queue[cur], W.counts + cur, W.rays, W.hits, ctx->scene.shade, W.key, W.val};
+  auto trace = [&](const BvhDev &tree, const int *queue, int *qcount, int *cursor, int n, int offset,
+                   bool count_visits) -> int {
+    PhotonRaySource src{queue, qcount, W.rays, W.hits, ctx->scene.shade, W.key + offset, W.val + offset};
     int grid = (n + TP_BLOCK - 1) / TP_BLOCK;
     if (grid > trace_grid) grid = trace_grid;
-    if (S.count_visits)
-      k_ph_trace<true><<<grid, TP_BLOCK, 0, st>>>(src, mb.nodes, mb.tris, mb.parent_leaf, W.counts + 2,
+    if (count_visits)
+      k_ph_trace<true><<<grid, TP_BLOCK, 0, st>>>(src, tree.nodes, tree.tris, tree.parent_leaf, cursor,
                                                  ctx->d_counters);
     else
-      k_ph_trace<false><<<grid, TP_BLOCK, 0, st>>>(src, mb.nodes, mb.tris, mb.parent_leaf, W.counts + 2,
+      k_ph_trace<false><<<grid, TP_BLOCK, 0, st>>>(src, tree.nodes, tree.tris, tree.parent_leaf, cursor,
                                                   ctx->d_counters);
     GPT_LAUNCH_CHECK(ctx);
+    return GPT_OK;
+  };
+  // every photon ends after at most max_bounce surface events + 4096 scatter events per bounce
+  // (+ 4096 steps of the initial walk)
+  for (long long it = 0; it < 4100LL * (pp.max_bounce + 3); it++) {
+    int h[8];
+    GPT_CUDA(ctx, cudaMemcpyAsync(h, W.counts, sizeof(h), cudaMemcpyDeviceToHost, st));
+    GPT_CUDA(ctx, cudaStreamSynchronize(st));
+    const int n_main = h[cur], n_init = h[3 + cur], n = n_main + n_init;
+    if (n == 0) return GPT_OK;
+    int zero_at[4] = {cur ^ 1, 2, 3 + (cur ^ 1), 5};
+    for (int z : zero_at) GPT_CUDA(ctx, cudaMemsetAsync(W.counts + z, 0, sizeof(int), st));
+    // keys / slots of the init queue land in [0, n_init), those of the main queue behind them
+    if (n_init) GPT_TRY(trace(tb, W.iqueue[cur], W.counts + 3 + cur, W.counts + 5, n_init, 0, false));
+    if (n_main) GPT_TRY(trace(mb, W.queue[cur], W.counts + cur, W.counts + 2, n_main, n_init, S.count_visits));
     // stable 8-bit radix sort of the traced photons by (resume point, hit material)
     uint32_t *sk = nullptr;
     int *sorted_slots = nullptr;
     GPT_TRY(gpt_radix_sort_pairs(ctx, W.key, W.val, W.key_alt, W.val_alt, sx->hist, n, 8, &sk,
-                                 &sorted_slots, W.counts + cur));
-    k_photon_step<false><<<(n + SP_BLOCK - 1) / SP_BLOCK, SP_BLOCK, 0, st>>>(S, pp, W, cur, sorted_slots,
-                                                                            sx->rng_ph, sx->raw, sx->kind);
+                                 &sorted_slots, nullptr));
+    int grid = (n + SP_BLOCK - 1) / SP_BLOCK;
+    if (grid > step_grid[0]) grid = step_grid[0];
+    k_photon_step<false><<<grid, SP_BLOCK, 0, st>>>(S, pp, W, cur, sorted_slots, n, n_main, sx->rng_ph,
+                                                    sx->raw, sx->kind);
     GPT_LAUNCH_CHECK(ctx);
     cur ^= 1;
   }
