@@ -259,6 +259,7 @@ struct QueueSource {
   const float4 *shade;   // per-triangle shading records (material id in s6.y)
   uint32_t *sort_key;    // out: shade-coherence key of queue entry i (material, 127 = miss)
   int *sort_val;         // out: its slot
+  int loc_bits, loc_shift;  // minor key: the hit leaf's top loc_bits bits (Morton order = place)
   __device__ int count() const { return *qcount; }
   __device__ void load(int i, float4 &o, float4 &d) const {
     int s = queue[i];
@@ -272,8 +273,13 @@ struct QueueSource {
     // Key for the material sort that precedes shade: paths that will run the same BSDF code
     // become neighbours, which is what keeps warps converged (and the instruction cache warm)
     // in k_pt_shade.
-    uint32_t key = 127u;
-    if (l.leaf >= 0) key = (uint32_t)__float_as_int(__ldg(&shade[7 * (size_t)l.prim + 6].y)) & 127u;
+    // ... and, within a material, paths that hit the same part of the scene: their textures /
+    // shading records share cache lines, and the rays they spawn start close together, which
+    // is what the NEXT trace wants (shade appends to the next queue in this order).
+    uint32_t key = 127u << loc_bits;
+    if (l.leaf >= 0)
+      key = (((uint32_t)__float_as_int(__ldg(&shade[7 * (size_t)l.prim + 6].y)) & 127u) << loc_bits) |
+            ((uint32_t)l.leaf >> loc_shift);
     sort_key[i] = key;
     sort_val[i] = s;
   }
@@ -292,11 +298,15 @@ k_pt_shade(PathState ps, RenderParams p, const int *__restrict__ queue,
            const int *__restrict__ count, int *next_queue, int *next_count, SceneDev sc,
            TexAtlas atlas, const float4 *__restrict__ main_tris, LightTree lt, float *fb,
            int *error_flag, unsigned long long *ray_counter) {
-  int a = blockIdx.x * blockDim.x + threadIdx.x;
-  if (a == 0) atomicAdd(ray_counter, (unsigned long long)*count);  // rays traced this iteration
+  const int n = *count;
+  if (blockIdx.x == 0 && threadIdx.x == 0)
+    atomicAdd(ray_counter, (unsigned long long)n);  // rays traced this iteration
+  // grid-stride only when the host caps the grid (GPT_SHADE_WAVES, an experiment; off by default)
+  for (int base_a = blockIdx.x * blockDim.x; base_a < n; base_a += gridDim.x * blockDim.x) {
+  const int a = base_a + threadIdx.x;
   bool alive = false;
   int s = -1;
-  if (a < *count) {
+  if (a < n) {
     s = queue[a];
     alive = true;
     float4 ro = ps.rays[2 * (size_t)s], rdv = ps.rays[2 * (size_t)s + 1];
@@ -434,6 +444,7 @@ k_pt_shade(PathState ps, RenderParams p, const int *__restrict__ queue,
     if (lane == leader) base = atomicAdd(next_count, __popc(ballot));
     base = __shfl_sync(0xffffffffu, base, leader);
     if (alive) next_queue[base + __popc(ballot & ((1u << lane) - 1u))] = s;
+  }
   }
 }
 
@@ -622,6 +633,17 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pt_trace<false>, TP_BLOCK, 0);
     trace_grid = sms * (per_sm > 0 ? per_sm : 1);
   }
+  static int shade_grid = 0;
+  if (!shade_grid) {
+    int sms = 148, per_sm = 4;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pt_shade, PT_BLOCK, 0);
+    // measured on C2: capping the grid at 1-2 resident waves is 25-30 % SLOWER (shade 34.5 ->
+    // 44.4 ms @16 spp), so by default every path vertex gets its own thread
+    const char *e = getenv("GPT_SHADE_WAVES");
+    int waves = e ? atoi(e) : 0;
+    shade_grid = waves > 0 ? sms * (per_sm > 0 ? per_sm : 1) * waves : 0x7fffffff;
+  }
   uint64_t rays = 0, shades = 0, trace_launches = 0;
   const bool timing = ctx->prof_time_stages, counting = ctx->prof_count_visits;
   size_t nev = 0;
@@ -657,6 +679,22 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
                                 : (n >= (1 << 16) ? 4 : 1);
     if (G > RenderCtx::MAX_GROUPS) G = RenderCtx::MAX_GROUPS;
     if (timing || G < 1) G = 1;
+  }
+  // spatial minor key of the coherence sort: top bits of the hit leaf's Morton-sorted position
+  int loc_bits = 0, loc_shift = 31;  // measured on C2: trace -7 % at 17 bits, but the extra sort passes cost more (default off)
+  {
+    static int env_loc = -1;
+    if (env_loc < 0) {
+      const char *e = getenv("GPT_SORT_LOC_BITS");
+      env_loc = e ? atoi(e) : 0;
+      if (env_loc < 0 || env_loc > 17) env_loc = 0;
+    }
+    loc_bits = env_loc;
+    int leaf_bits = 1;
+    while ((1 << leaf_bits) < mb.n) leaf_bits++;
+    if (loc_bits > leaf_bits) loc_bits = leaf_bits;
+    loc_shift = leaf_bits - loc_bits;
+    if (loc_bits == 0) loc_shift = 31;
   }
   struct Group {
     int s0, n, active, cur;
@@ -714,7 +752,7 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
       GPT_CUDA(ctx, stamp());
       {
         QueueSource qs{ps, ps.queue[q.cur] + q.s0, d_counts + q.cur, ctx->scene.shade,
-                       rc->sort_key + q.s0, rc->sort_val + q.s0};
+                       rc->sort_key + q.s0, rc->sort_val + q.s0, loc_bits, loc_shift};
         int tgrid = grid < trace_grid ? grid : trace_grid;
         if (counting)
           k_pt_trace<true><<<tgrid, TP_BLOCK, 0, gs>>>(qs, mb.nodes, mb.tris, mb.parent_leaf,
@@ -732,11 +770,11 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
       ctx->stream = gs;  // the sort enqueues on ctx->stream
       rc_err = gpt_radix_sort_pairs(ctx, rc->sort_key + q.s0, rc->sort_val + q.s0,
                                     rc->sort_key_alt + q.s0, rc->sort_val_alt + q.s0,
-                                    rc->sort_hist + (size_t)rc->hist_stride * g, q.active, 7, &sk,
+                                    rc->sort_hist + (size_t)rc->hist_stride * g, q.active, 7 + loc_bits, &sk,
                                     &sorted_slots, d_counts + q.cur);
       ctx->stream = caller_stream;
       if (rc_err != GPT_OK) break;
-      k_pt_shade<<<grid, PT_BLOCK, 0, gs>>>(ps, p, sorted_slots, d_counts + q.cur,
+      k_pt_shade<<<grid < shade_grid ? grid : shade_grid, PT_BLOCK, 0, gs>>>(ps, p, sorted_slots, d_counts + q.cur,
                                            ps.queue[q.cur ^ 1] + q.s0, d_counts + (q.cur ^ 1),
                                            ctx->scene, atlas, mb.tris, lt, d_fb, d_counts + 2,
                                            ray_counter);

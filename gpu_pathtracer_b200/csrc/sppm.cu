@@ -1532,6 +1532,10 @@ static int photon_stage(gpt_ctx *ctx, SppmCtx *sx, const SppmScene &S, const Pho
     step_grid[0] = sms * (per_sm > 0 ? per_sm : 1);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_photon_step<true>, SP_BLOCK, 0);
     step_grid[1] = sms * (per_sm > 0 ? per_sm : 1);
+    const char *e = getenv("GPT_PHOTON_WAVES");
+    int waves = e ? atoi(e) : 1;
+    if (waves <= 0) step_grid[0] = step_grid[1] = 0x7fffffff;
+    else { step_grid[0] *= waves; step_grid[1] *= waves; }
   }
   PhotonWave &W = sx->wave;
   BvhDev &mb = ctx->bvh[GPT_BVH_MAIN], &tb = ctx->bvh[GPT_BVH_TRANSPARENT];
