@@ -448,10 +448,11 @@ def run_sppm(args, rank, world, local_rank):
                 "d2h_bytes_per_step": H * W * 12 // max(1, args.steps),
                 "what": "gpt_set_* + gpt_build + gpt_sppm_init + passes + gpt_sppm_resolve, host "
                         "arrays in, host frame out"},
-        "roofline": {"bound": "hbm", "kernel": "k_photon_trace", "achieved": achieved, "peak": peak,
+        "roofline": {"bound": "hbm", "kernel": "photon stage: k_photon_step + k_ph_trace", "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": achieved / peak, "traffic": None,
                      "algorithmic_bytes_per_launch": alg, "avg_launch_ms": photon_ms,
-                     "note": "photon stage = k_photon_trace + compaction + two photon LBVH builds",
+                     "note": "photon stage = wavefront photon trace (k_photon_step, k_ph_trace, coherence sort) "
+                             "+ compaction + two photon LBVH builds",
                      "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback"},
         "clocks": clocks,
     }
