@@ -383,13 +383,15 @@ def run_sppm(args, rank, world, local_rank):
     p_extra = args.warmup + args.steps
     stage = {}
     pt.set_profiling(count_visits=True)
-    v_int = v_leaf = prof_rays = 0
+    v_int = v_leaf = prof_rays = eye_rays = 0
     for name, mask in (("photon", 1), ("eye", 2), ("gather", 4)):
         pt.sppm_pass_stages(p_extra, mask, b, e)
         st = pt.stats()
         stage[name] = st["render_ms"]
         if name == "photon":
             v_int, v_leaf, prof_rays = st["internal_visits"], st["leaf_tests"], st["rays_traced"]
+        if name == "eye":
+            eye_rays = st["rays_traced"]
     pt.set_profiling()
     pt.sppm_pass_stages(p_extra, 1, b, e)
     photon_ms = pt.stats()["render_ms"]
@@ -400,7 +402,7 @@ def run_sppm(args, rank, world, local_rank):
     pt.set_scene(sc)
     pt.build()
     pt.sppm_init()
-    e2e_rays = pt.stats()["rays_traced"]
+    e2e_rays = init_rays = pt.stats()["rays_traced"]
     for p in range(args.steps):
         e2e_rays += one_pass(p)
     img = pt.sppm_resolve(0, args.steps)
@@ -413,6 +415,9 @@ def run_sppm(args, rank, world, local_rank):
         dist.all_reduce(tot, op=dist.ReduceOp.SUM)
     total_ms, e2e_ms = t.tolist()
     rays_all, e2e_rays_all = tot.tolist()
+    # the eye pass is replicated on every rank: its rays are counted ONCE, not once per rank
+    rays_all -= (world - 1) * eye_rays * args.steps
+    e2e_rays_all -= (world - 1) * (init_rays + eye_rays * args.steps)
     if rank != 0:
         return
     peaks = {}
@@ -436,7 +441,7 @@ def run_sppm(args, rank, world, local_rank):
             "step": "one SPPM pass: photon trace + photon LBVHs + eye pass + gather (+ NCCL "
                     "all-reduce of 8 floats per pixel when N > 1) + update",
             "rays": "closest-hit traversals of the main BVH: photon, eye, direct-light and "
-                    "visibility rays",
+                    "visibility rays (the replicated eye pass counted once)",
             "cache": "L2 flushed (512 MiB write) between timed steps",
             "sharding": "scene + eye pass replicated, photons split by index range",
             "rank0_stage_ms": stage, "photons_stored": [stats["n_surface"], stats["n_volume"]],
