@@ -14,6 +14,7 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--nranks", type=int, default=4)
 ap.add_argument("--spp", type=int, default=16)
 ap.add_argument("--workload", default="C2")
+ap.add_argument("--only-rank0", action="store_true")
 a = ap.parse_args()
 sc = S.make_scene(a.workload, spp=a.spp)
 pt = PathTracer(sc)
@@ -21,7 +22,7 @@ pt.build()
 fb = torch.zeros((sc.camera["height"], sc.camera["width"], 3), dtype=torch.float32, device="cuda")
 out = []
 for nr in sorted({1, a.nranks}):
-    for r in range(nr):
+    for r in range(1 if a.only_rank0 else nr):
         for timing in (False, True):
             pt.set_profiling(time_stages=timing)
             for _ in range(2):
