@@ -307,7 +307,12 @@ def run_ours(args, rank, world, local_rank):
                         "with host arrays in, host frame out"},
         "roofline": {"bound": "hbm", "kernel": "k_pt_trace",
                      "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None,
+                     "frac": achieved / peak,
+                     # physical DRAM bytes per launch: ncu --set full on this kernel at C2
+                     # (profiles/r01d_k_pt_trace_raw.csv: 52.9 MB read + 2.6 MB write per
+                     # 518 400-ray launch = 107 B per ray), scaled to this run's rays per launch
+                     "traffic": (107.0 * rays / max(1, n_trace)) if args.workload == "C2" else None,
+                     "traffic_source": "ncu r01d capture, 107 B/ray (C2 only)",
                      "launches": int(n_trace),
                      "algorithmic_bytes_per_launch": alg_bytes / n_trace,
                      "avg_launch_ms": trace_ms / n_trace,

@@ -298,15 +298,11 @@ k_pt_shade(PathState ps, RenderParams p, const int *__restrict__ queue,
            const int *__restrict__ count, int *next_queue, int *next_count, SceneDev sc,
            TexAtlas atlas, const float4 *__restrict__ main_tris, LightTree lt, float *fb,
            int *error_flag, unsigned long long *ray_counter) {
-  const int n = *count;
-  if (blockIdx.x == 0 && threadIdx.x == 0)
-    atomicAdd(ray_counter, (unsigned long long)n);  // rays traced this iteration
-  // grid-stride only when the host caps the grid (GPT_SHADE_WAVES, an experiment; off by default)
-  for (int base_a = blockIdx.x * blockDim.x; base_a < n; base_a += gridDim.x * blockDim.x) {
-  const int a = base_a + threadIdx.x;
+  int a = blockIdx.x * blockDim.x + threadIdx.x;
+  if (a == 0) atomicAdd(ray_counter, (unsigned long long)*count);  // rays traced this iteration
   bool alive = false;
   int s = -1;
-  if (a < n) {
+  if (a < *count) {
     s = queue[a];
     alive = true;
     float4 ro = ps.rays[2 * (size_t)s], rdv = ps.rays[2 * (size_t)s + 1];
@@ -444,7 +440,6 @@ k_pt_shade(PathState ps, RenderParams p, const int *__restrict__ queue,
     if (lane == leader) base = atomicAdd(next_count, __popc(ballot));
     base = __shfl_sync(0xffffffffu, base, leader);
     if (alive) next_queue[base + __popc(ballot & ((1u << lane) - 1u))] = s;
-  }
   }
 }
 
@@ -633,17 +628,6 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pt_trace<false>, TP_BLOCK, 0);
     trace_grid = sms * (per_sm > 0 ? per_sm : 1);
   }
-  static int shade_grid = 0;
-  if (!shade_grid) {
-    int sms = 148, per_sm = 4;
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pt_shade, PT_BLOCK, 0);
-    // measured on C2: capping the grid at 1-2 resident waves is 25-30 % SLOWER (shade 34.5 ->
-    // 44.4 ms @16 spp), so by default every path vertex gets its own thread
-    const char *e = getenv("GPT_SHADE_WAVES");
-    int waves = e ? atoi(e) : 0;
-    shade_grid = waves > 0 ? sms * (per_sm > 0 ? per_sm : 1) * waves : 0x7fffffff;
-  }
   uint64_t rays = 0, shades = 0, trace_launches = 0;
   const bool timing = ctx->prof_time_stages, counting = ctx->prof_count_visits;
   size_t nev = 0;
@@ -774,7 +758,7 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
                                     &sorted_slots, d_counts + q.cur);
       ctx->stream = caller_stream;
       if (rc_err != GPT_OK) break;
-      k_pt_shade<<<grid < shade_grid ? grid : shade_grid, PT_BLOCK, 0, gs>>>(ps, p, sorted_slots, d_counts + q.cur,
+      k_pt_shade<<<grid, PT_BLOCK, 0, gs>>>(ps, p, sorted_slots, d_counts + q.cur,
                                            ps.queue[q.cur ^ 1] + q.s0, d_counts + (q.cur ^ 1),
                                            ctx->scene, atlas, mb.tris, lt, d_fb, d_counts + 2,
                                            ray_counter);
