@@ -122,27 +122,52 @@ k_sort_hist(const uint32_t *__restrict__ keys, int n, int shift, uint32_t mask,
   block_hist[(size_t)threadIdx.x * nblocks + blockIdx.x] = h[threadIdx.x];
 }
 
-// single-block exclusive scan of m counters (m = 256 * nblocks)
+// single-block exclusive scan of the m = (digits of this pass) * nblocks counters, in tiles of
+// 4096: coalesced 16-byte loads, warp-shuffle scans, one running carry
 __global__ void __launch_bounds__(1024) k_sort_scan(uint32_t *data, int m) {
-  __shared__ uint32_t part[1024];
-  int t = threadIdx.x;
-  int chunk = (m + 1023) / 1024;
-  int lo = t * chunk, hi = min(m, lo + chunk);
-  uint32_t s = 0;
-  for (int i = lo; i < hi; i++) s += data[i];
-  part[t] = s;
-  __syncthreads();
-  for (int o = 1; o < 1024; o <<= 1) {
-    uint32_t v = (t >= o) ? part[t - o] : 0;
+  __shared__ uint32_t wsum[32];
+  const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+  uint32_t carry = 0;
+  for (int base = 0; base < m; base += 4096) {
+    const int i = base + 4 * t;
+    uint32_t v0 = 0, v1 = 0, v2 = 0, v3 = 0;
+    if (i + 3 < m) {
+      uint4 q = *reinterpret_cast<const uint4 *>(data + i);
+      v0 = q.x; v1 = q.y; v2 = q.z; v3 = q.w;
+    } else {
+      if (i < m) v0 = data[i];
+      if (i + 1 < m) v1 = data[i + 1];
+      if (i + 2 < m) v2 = data[i + 2];
+    }
+    const uint32_t s = v0 + v1 + v2 + v3;
+    uint32_t x = s;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+      if (lane >= o) x += y;
+    }
+    if (lane == 31) wsum[w] = x;
     __syncthreads();
-    part[t] += v;
+    if (w == 0) {
+      uint32_t y = wsum[lane];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        uint32_t z = __shfl_up_sync(0xffffffffu, y, o);
+        if (lane >= o) y += z;
+      }
+      wsum[lane] = y;
+    }
     __syncthreads();
-  }
-  uint32_t run = part[t] - s;
-  for (int i = lo; i < hi; i++) {
-    uint32_t v = data[i];
-    data[i] = run;
-    run += v;
+    uint32_t p = carry + (w > 0 ? wsum[w - 1] : 0u) + (x - s);
+    if (i + 3 < m) {
+      *reinterpret_cast<uint4 *>(data + i) = make_uint4(p, p + v0, p + v0 + v1, p + v0 + v1 + v2);
+    } else {
+      if (i < m) data[i] = p;
+      if (i + 1 < m) data[i + 1] = p + v0;
+      if (i + 2 < m) data[i + 2] = p + v0 + v1;
+    }
+    carry += wsum[31];
+    __syncthreads();
   }
 }
 
@@ -355,7 +380,8 @@ int gpt_radix_sort_pairs(gpt_ctx *ctx, uint32_t *keys, int *vals, uint32_t *keys
     uint32_t mask = (1u << bits) - 1u;
     k_sort_hist<<<nblocks, SORT_THREADS, 0, ctx->stream>>>(ka, n, shift, mask, block_hist, nblocks, d_n);
     GPT_LAUNCH_CHECK(ctx);
-    k_sort_scan<<<1, 1024, 0, ctx->stream>>>(block_hist, 256 * nblocks);
+    // digit-major layout: only the digits this pass can produce need scanning
+    k_sort_scan<<<1, 1024, 0, ctx->stream>>>(block_hist, (int)(mask + 1) * nblocks);
     GPT_LAUNCH_CHECK(ctx);
     k_sort_scatter<<<nblocks, SORT_THREADS, 0, ctx->stream>>>(ka, va, n, shift, mask, block_hist,
                                                              nblocks, kb, vb, d_n);
