@@ -1107,19 +1107,37 @@ k_eye_pass(SppmScene S, EyeParams ep, HitPoints hp, const uint32_t *__restrict__
 // compute_average_radius (ray_tracing_pass.h:416-436): serial fp32 sum in pixel order, then
 // assign_radius_to_invalid_hit_points gives EVERY hit point that mean (src/main.cu:1353).
 // One warp streams the radii (coalesced), lane order = pixel order, lane 0 carries the sum.
-__global__ void k_mean_radius_serial(const float4 *__restrict__ loc, int P, float *out) {
-  int lane = threadIdx.x;
+// The sum is a chain of P dependent fp32 adds in pixel order; everything else is taken off that
+// chain: 7 warps stage the next tile of radii into shared memory (coalesced) while thread 0 adds
+// the current one.
+constexpr int MR_TILE = 2048;
+__global__ void __launch_bounds__(256) k_mean_radius_serial(const float4 *__restrict__ loc, int P, float *out) {
+  __shared__ float tile[2][MR_TILE];
+  const int t = threadIdx.x;
   float sum = 0.f;
   int valid = 0;
-  for (int base = 0; base < P; base += 32) {
-    int i = base + lane;
-    float r = i < P ? loc[i].w : INFINITY;
-    for (int k = 0; k < 32; k++) {
-      float rk = __shfl_sync(0xffffffffu, r, k);
-      if (!isinf(rk)) { valid++; sum += rk; }
+  auto stage = [&](int buf, int base) {
+    if (t >= 32)
+      for (int k = t - 32; k < MR_TILE; k += 224) {
+        int i = base + k;
+        tile[buf][k] = i < P ? loc[i].w : INFINITY;
+      }
+  };
+  stage(0, 0);
+  __syncthreads();
+  int buf = 0;
+  for (int base = 0; base < P; base += MR_TILE, buf ^= 1) {
+    stage(buf ^ 1, base + MR_TILE);
+    if (t == 0) {
+#pragma unroll 16
+      for (int k = 0; k < MR_TILE; k++) {
+        float r = tile[buf][k];
+        if (!isinf(r)) { valid++; sum += r; }
+      }
     }
+    __syncthreads();
   }
-  if (lane == 0) { out[0] = sum / (float)valid; out[1] = (float)valid; }
+  if (t == 0) { out[0] = sum / (float)valid; out[1] = (float)valid; }
 }
 __global__ void __launch_bounds__(256)
 k_assign_radius(HitPoints hp, const float *__restrict__ mean) {
@@ -1476,7 +1494,7 @@ int gpt_sppm_init(gpt_ctx *ctx) {
   sx->n_surf = sx->n_vol = 0;
   GPT_CUDA(ctx, cudaEventRecord(ctx->ev0, st));
   GPT_TRY(eye_pass(ctx, sx, S, 0, true));
-  k_mean_radius_serial<<<1, 32, 0, st>>>(sx->hp.loc, sx->P, sx->d_mean);
+  k_mean_radius_serial<<<1, 256, 0, st>>>(sx->hp.loc, sx->P, sx->d_mean);
   GPT_LAUNCH_CHECK(ctx);
   k_assign_radius<<<(sx->P + 255) / 256, 256, 0, st>>>(sx->hp, sx->d_mean);
   GPT_LAUNCH_CHECK(ctx);
@@ -1506,12 +1524,8 @@ int gpt_sppm_init(gpt_ctx *ctx) {
 static int photon_stage(gpt_ctx *ctx, SppmCtx *sx, const SppmScene &S, const PhotonParams &pp) {
   cudaStream_t st = ctx->stream;
   const int count = pp.count;
-  static int mega = -1;
-  if (mega < 0) {
-    const char *e = getenv("GPT_SPPM_MEGAKERNEL");
-    mega = (e && atoi(e) != 0) ? 1 : 0;
-  }
-  if (mega) {
+  const char *mega_env = getenv("GPT_SPPM_MEGAKERNEL");  // read per call: tests flip it
+  if (mega_env && atoi(mega_env) != 0) {
     k_photon_trace<<<(count + SP_BLOCK - 1) / SP_BLOCK, SP_BLOCK, 0, st>>>(S, pp, sx->rng_ph, sx->raw,
                                                                         sx->kind);
     GPT_LAUNCH_CHECK(ctx);

@@ -176,3 +176,29 @@ def test_multi_rank_photon_split_sums_to_single_rank():
     got = parts[0] + parts[1]
     assert np.array_equal(got[:, 3], want[:, 3])
     assert np.allclose(got[:, :3], want[:, :3], rtol=1e-4, atol=1e-4)
+
+
+def test_wavefront_photon_pass_equals_the_megakernel(monkeypatch):
+    """The photon pass runs as a wavefront (k_photon_step / k_ph_trace / coherence sort); the
+    one-thread-per-photon megakernel it replaced is kept as a cross-check.  Same photons, bit for
+    bit, over two passes (the per-photon RNG state carries over), and the same ray count."""
+    from gpu_pathtracer_b200.api import PathTracer
+    sc = S.make_scene("C4", width=64, height=48)
+    sc.params["ppm_num_photon_per_pass"] = 30000
+    out = {}
+    for mode in ("0", "1"):
+        monkeypatch.setenv("GPT_SPPM_MEGAKERNEL", mode)
+        pt = PathTracer(sc)
+        pt.build()
+        pt.sppm_init()
+        recs = []
+        for ps in range(2):
+            pt.sppm_pass_stages(ps, 1, 0, 30000)
+            ph = pt.sppm_export_photons()
+            recs.append((ph["kind"].copy(), ph["rec"].copy(), pt.stats()["rays_traced"]))
+        out[mode] = recs
+    for (k0, r0, n0), (k1, r1, n1) in zip(out["0"], out["1"]):
+        assert n0 == n1 and n0 > 30000
+        assert np.array_equal(k0, k1)
+        assert np.array_equal(r0.view(np.uint32), r1.view(np.uint32))
+        assert (k0 == 1).sum() > 100 and (k0 == 0).sum() > 1000  # volume and surface photons
