@@ -28,7 +28,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="C2", choices=["C1", "C2", "C4", "small"])
+    ap.add_argument("--workload", default="C2", choices=["C1", "C2", "C3", "C4", "C5", "small"])
     ap.add_argument("--photons", type=int, default=0, help="C4: photons per pass override")
     ap.add_argument("--mode", default="auto", choices=["auto", "trace", "render"])
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel")
@@ -43,6 +43,10 @@ def make_workload(name: str, spp: int = 0):
         sc = S.make_scene("C2")
     elif name == "C1":
         sc = S.make_scene("C1")
+    elif name == "C3":
+        sc = S.make_scene("C3")
+    elif name == "C5":  # 10 M triangles + fog + SSS at 4K (BASELINE config 5; pass --spp to shorten)
+        sc = S.make_scene("C5")
     else:
         sc = S.make_scene("small", n=64, width=256, height=256)
     if spp:

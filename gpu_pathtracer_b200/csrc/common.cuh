@@ -185,6 +185,12 @@ struct SssTree {           // per scene OBJECT; n == 0 for objects without sub-s
   const float4 *leaf;      // 2 float4 per point in leaf order: (location, -) (colour, -)
   int n;
   int pad;
+  // search structure (ours): an LBVH of the same points keyed by their TRUE Morton codes;
+  // spos[j] = (location, VISIT position of the point in the reference walk) of search leaf j;
+  // visit[k] = leaf-order index of the k-th point the reference walk would test
+  const float4 *snodes;
+  const float4 *spos;
+  const int *visit;
 };
 struct SssView {
   const SssTree *trees;    // device, one per object; nullptr when the scene has no SSS points
@@ -192,6 +198,10 @@ struct SssView {
   float4 *leaf;            // all trees' leaf records, tree order (colour written by the first pass)
   const uint32_t *rng;     // rand_state_sss, 6 planes of stride npoints
   int npoints;
+  // pool of private candidate bitmaps for sss_lookup (one bit per point of an object)
+  uint32_t *bm_pool;
+  int *bm_busy;
+  int bm_n, bm_words;
 };
 int gpt_sss_prepare(gpt_ctx *ctx);                                   // sss.cu
 bool gpt_sss_view(gpt_ctx *ctx, SssView *out, bool *first_pass_done);  // sss.cu

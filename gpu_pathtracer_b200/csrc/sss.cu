@@ -25,7 +25,8 @@ namespace {
 
 struct SssObj {
   int obj = 0, tri_off = 0, tri_num = 0, pt_off = 0;
-  BvhDev bvh;
+  BvhDev bvh;      // the reference's tree (degenerate keys, see k_sss_morton)
+  BvhDev search;   // same points, true Morton keys: finds the candidates of a lookup fast
 };
 
 struct SssCtx {
@@ -38,6 +39,15 @@ struct SssCtx {
   uint32_t *keys = nullptr;
   int *obj_flag = nullptr;
   SssTree *trees = nullptr;    // device, one per scene object
+  float4 *spos = nullptr;      // npoints: (location, leaf-order index) per search leaf
+  int *rank = nullptr;         // pts scratch: creation index -> leaf-order index
+  int *leafpos = nullptr;      // pts scratch: leaf-order index -> position in the reference walk
+  int *visit = nullptr;        // npoints: position in the walk -> leaf-order index, per object
+  uint32_t *vkeys = nullptr, *vkeys_alt = nullptr, *vhist = nullptr;  // pts scratch (rank sort)
+  int *vvals = nullptr, *vvals_alt = nullptr;
+  uint32_t *bm_pool = nullptr;
+  int *bm_busy = nullptr;
+  int bm_n = 0, bm_words = 0;
   bool first_pass_done = false;
 };
 
@@ -49,16 +59,37 @@ k_obj_flags(const float4 *__restrict__ shade, int n, int *flag) {
   if (__float_as_int(s6.z) & GPT_TRI_SSS) flag[__float_as_int(s6.w)] = 1;
 }
 
-// Object::compute_accummulated_triangle_area (object.h:104-112): serial fp32 prefix per object
-__global__ void k_area_cdf(const float4 *__restrict__ shade, const int *__restrict__ off,
-                           const int *__restrict__ num, int nobj, float *cdf) {
-  int o = blockIdx.x * blockDim.x + threadIdx.x;
-  if (o >= nobj) return;
-  float acc = 0.f;
-  for (int i = off[o]; i < off[o] + num[o]; i++) {
-    float a = __ldg(&shade[7 * (size_t)i + 3].w);
-    acc += (a == a ? a : 0.f);
-    cdf[i] = acc;
+// Object::compute_accummulated_triangle_area (object.h:104-112): serial fp32 prefix per object.
+// Only the SSS objects' tables are ever read (create_sss_pts), so only those are computed: one
+// block per SSS object; the block stages a tile of areas, thread 0 runs the dependent adds over
+// shared memory, the block writes the tile back.  (One thread walking a 10 M-triangle terrain
+// through global memory was 3.9 s of C5's build.)
+constexpr int CDF_TILE = 2048;
+__global__ void __launch_bounds__(256)
+k_area_cdf(const float4 *__restrict__ shade, const int *__restrict__ off,
+           const int *__restrict__ num, float *cdf) {
+  __shared__ float tile[CDF_TILE];
+  __shared__ float carry;
+  const int first = off[blockIdx.x], count = num[blockIdx.x];
+  if (threadIdx.x == 0) carry = 0.f;
+  for (int base = 0; base < count; base += CDF_TILE) {
+    const int m = min(CDF_TILE, count - base);
+    for (int k = threadIdx.x; k < m; k += blockDim.x) {
+      float a = __ldg(&shade[7 * (size_t)(first + base + k) + 3].w);
+      tile[k] = (a == a ? a : 0.f);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float acc = carry;
+      for (int k = 0; k < m; k++) {
+        acc += tile[k];
+        tile[k] = acc;
+      }
+      carry = acc;
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < m; k += blockDim.x) cdf[first + base + k] = tile[k];
+    __syncthreads();
   }
 }
 
@@ -172,9 +203,10 @@ extern "C" void gpt_sss_free(gpt_ctx *ctx) {
   if (!ctx || !ctx->sss_state) return;
   SssCtx *sx = sss_of(ctx);
   void *p[] = {sx->cdf, sx->rng, sx->pts_created, sx->pts, sx->leaf, sx->aabb, sx->keys,
-               sx->obj_flag, sx->trees};
+               sx->obj_flag, sx->trees, sx->spos, sx->rank, sx->bm_pool, sx->bm_busy,
+               sx->leafpos, sx->visit, sx->vkeys, sx->vkeys_alt, sx->vhist, sx->vvals, sx->vvals_alt};
   for (void *q : p) cudaFree(q);
-  for (SssObj &o : sx->objs) gpt_lbvh_free(o.bvh);
+  for (SssObj &o : sx->objs) { gpt_lbvh_free(o.bvh); gpt_lbvh_free(o.search); }
   delete sx;
   ctx->sss_state = nullptr;
 }
@@ -187,12 +219,49 @@ bool gpt_sss_view(gpt_ctx *ctx, SssView *out, bool *first_pass_done) {
   out->leaf = sx->leaf;
   out->rng = sx->rng;
   out->npoints = sx->npoints;
+  out->bm_pool = sx->bm_pool;
+  out->bm_busy = sx->bm_busy;
+  out->bm_n = sx->bm_n;
+  out->bm_words = sx->bm_words;
   if (first_pass_done) *first_pass_done = sx->first_pass_done;
   return true;
 }
 
 void gpt_sss_mark_first_pass_done(gpt_ctx *ctx) {
   if (sss_of(ctx)) sss_of(ctx)->first_pass_done = true;
+}
+
+// The reference walk (bvh_traversal_pts.h) tests a node's leaf children when it visits the node,
+// left before right, and visits nodes in left-first preorder: leaf_visit_rank (trace_core.cuh)
+// is that order.  Sorting the leaves by it gives every point its position in the walk.
+__global__ void __launch_bounds__(256)
+k_sss_visit_keys(const float4 *__restrict__ nodes, const int *__restrict__ parent_leaf, int n,
+                 uint32_t *keys, int *vals) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  keys[i] = (uint32_t)leaf_visit_rank(nodes, parent_leaf, i);
+  vals[i] = i;
+}
+__global__ void __launch_bounds__(256)
+k_sss_invert(const int *__restrict__ order, int n, int *pos) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < n) pos[order[k]] = k;
+}
+// leaf-order index of every point (inverse of the reference tree's sorted_prim) ...
+__global__ void __launch_bounds__(256)
+k_sss_rank(const int *__restrict__ sorted_prim, int n, int *rank) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) rank[sorted_prim[i]] = i;
+}
+// ... and the search tree's leaf records: location + where the point sits in the reference order
+__global__ void __launch_bounds__(256)
+k_sss_spos(const float4 *__restrict__ created, const int *__restrict__ search_sorted,
+           const int *__restrict__ rank, const int *__restrict__ leafpos, int n, float4 *spos) {
+  int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  int p = search_sorted[j];
+  float4 a = created[3 * (size_t)p];
+  spos[j] = make_float4(a.x, a.y, a.z, __int_as_float(leafpos[rank[p]]));
 }
 
 int gpt_sss_prepare(gpt_ctx *ctx) {
@@ -239,7 +308,7 @@ int gpt_sss_prepare(gpt_ctx *ctx) {
   }
   GPT_TRY(gpt_upload(ctx, &d_tab, tab.data(), tab.size()));
   GPT_TRY(gpt_alloc(ctx, &sx->cdf, (size_t)sc.ntri));
-  k_area_cdf<<<(nobj + 63) / 64, 64, 0, st>>>(sc.shade, d_tab, d_tab + nobj, nobj, sx->cdf);
+  k_area_cdf<<<nsss, 256, 0, st>>>(sc.shade, d_tab + 2 * nobj, d_tab + 2 * nobj + nsss, sx->cdf);
   GPT_LAUNCH_CHECK(ctx);
   GPT_TRY(gpt_alloc(ctx, &sx->rng, 6 * (size_t)np));
   k_sss_rng_init<<<(np + 127) / 128, 128, 0, st>>>(sx->rng, np);
@@ -249,6 +318,15 @@ int gpt_sss_prepare(gpt_ctx *ctx) {
   GPT_TRY(gpt_alloc(ctx, &sx->leaf, 2 * (size_t)np));
   GPT_TRY(gpt_alloc(ctx, &sx->aabb, 6 * (size_t)np));
   GPT_TRY(gpt_alloc(ctx, &sx->keys, (size_t)np));
+  GPT_TRY(gpt_alloc(ctx, &sx->spos, (size_t)np));
+  GPT_TRY(gpt_alloc(ctx, &sx->rank, (size_t)pts));
+  GPT_TRY(gpt_alloc(ctx, &sx->leafpos, (size_t)pts));
+  GPT_TRY(gpt_alloc(ctx, &sx->visit, (size_t)np));
+  GPT_TRY(gpt_alloc(ctx, &sx->vkeys, (size_t)pts));
+  GPT_TRY(gpt_alloc(ctx, &sx->vkeys_alt, (size_t)pts));
+  GPT_TRY(gpt_alloc(ctx, &sx->vvals, (size_t)pts));
+  GPT_TRY(gpt_alloc(ctx, &sx->vvals_alt, (size_t)pts));
+  GPT_TRY(gpt_alloc(ctx, &sx->vhist, (size_t)gpt_radix_hist_entries(pts)));
   TexAtlas atlas{sc.tex_r, sc.tex_g, sc.tex_b};
   const int *d_soff = d_tab + 2 * nobj, *d_snum = d_soff + nsss, *d_poff = d_snum + nsss;
   k_sss_points<<<(pts + 127) / 128, 128, 0, st>>>(sc, atlas, sx->cdf, d_soff, d_snum, d_poff, nsss,
@@ -267,8 +345,41 @@ int gpt_sss_prepare(gpt_ctx *ctx) {
                                                  sx->pts + 3 * (size_t)so.pt_off,
                                                  sx->leaf + 2 * (size_t)so.pt_off);
     GPT_LAUNCH_CHECK(ctx);
-    trees[so.obj] = SssTree{so.bvh.nodes, sx->leaf + 2 * (size_t)so.pt_off, pts, 0};
+    // the search structure: same boxes, the builder's own (true) Morton codes
+    GPT_TRY(gpt_lbvh_build_boxes(ctx, so.search, sx->aabb + 6 * (size_t)so.pt_off, nullptr, pts, false,
+                                 nullptr));
+    k_sss_rank<<<(pts + 255) / 256, 256, 0, st>>>(so.bvh.sorted_prim, pts, sx->rank);
+    GPT_LAUNCH_CHECK(ctx);
+    // positions in the reference walk: sort the leaves by visit rank (< 2 * pts)
+    k_sss_visit_keys<<<(pts + 255) / 256, 256, 0, st>>>(so.bvh.nodes, so.bvh.parent_leaf, pts, sx->vkeys,
+                                                       sx->vvals);
+    GPT_LAUNCH_CHECK(ctx);
+    int vbits = 1;
+    while ((1ll << vbits) < 2ll * pts) vbits++;
+    uint32_t *ko = nullptr;
+    int *order = nullptr;
+    GPT_TRY(gpt_radix_sort_pairs(ctx, sx->vkeys, sx->vvals, sx->vkeys_alt, sx->vvals_alt, sx->vhist, pts,
+                                 vbits, &ko, &order, nullptr));
+    GPT_CUDA(ctx, cudaMemcpyAsync(sx->visit + so.pt_off, order, sizeof(int) * (size_t)pts,
+                                  cudaMemcpyDeviceToDevice, st));
+    k_sss_invert<<<(pts + 255) / 256, 256, 0, st>>>(sx->visit + so.pt_off, pts, sx->leafpos);
+    GPT_LAUNCH_CHECK(ctx);
+    k_sss_spos<<<(pts + 255) / 256, 256, 0, st>>>(sx->pts_created + 3 * (size_t)so.pt_off,
+                                                 so.search.sorted_prim, sx->rank, sx->leafpos, pts,
+                                                 sx->spos + so.pt_off);
+    GPT_LAUNCH_CHECK(ctx);
+    trees[so.obj] = SssTree{so.bvh.nodes, sx->leaf + 2 * (size_t)so.pt_off, pts, 0,
+                            so.search.nodes, sx->spos + so.pt_off, sx->visit + so.pt_off};
   }
+  // candidate bitmaps: one bit per point; enough of them for every resident shade thread to hold
+  // one (148 SMs x 640 threads) at 1.4x for the probing, within 2 GB
+  sx->bm_words = (((pts + 31) / 32) + 3) & ~3;  // whole 16-byte groups
+  sx->bm_n = (int)std::min<size_t>(131072, ((size_t)2 << 30) / (4 * (size_t)sx->bm_words));
+  if (sx->bm_n < 1) sx->bm_n = 1;
+  GPT_TRY(gpt_alloc(ctx, &sx->bm_pool, (size_t)sx->bm_n * sx->bm_words));
+  GPT_TRY(gpt_alloc(ctx, &sx->bm_busy, (size_t)sx->bm_n));
+  GPT_CUDA(ctx, cudaMemsetAsync(sx->bm_pool, 0, sizeof(uint32_t) * (size_t)sx->bm_n * sx->bm_words, st));
+  GPT_CUDA(ctx, cudaMemsetAsync(sx->bm_busy, 0, sizeof(int) * (size_t)sx->bm_n, st));
   GPT_TRY(gpt_upload(ctx, &sx->trees, trees.data(), trees.size()));
   GPT_CUDA(ctx, cudaStreamSynchronize(st));
   cudaFree(d_tab);

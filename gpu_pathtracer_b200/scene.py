@@ -498,7 +498,36 @@ def sppm_scene(cells: int = 91, width: int = 1920, height: int = 1080, photons: 
     return Scene(mb.finish(), mats.finish(), cam, par, name=name)
 
 
+def big_scene(n: int = 2237, width: int = 3840, height: int = 2160, spp: int = 256,
+              level: int = 5, sss_pts: int = 100000, name: str = "C5") -> Scene:
+    """Config 5: terrain-10M (n = 2237 -> 9 999 392 triangles) + a fog box + one sub-surface
+    scattering object (path_length .3, sss_pts_per_object 1e5), 4K.  The BVH (1.1 GB) no
+    longer fits the L2, so traversal is HBM-bound here."""
+    mats = MaterialBuilder()
+    m_terrain = mats.add("terrain", kd=(0.7, 0.65, 0.55))
+    m_floor = mats.add("floor", kd=(0.5, 0.5, 0.5))
+    m_fog = mats.add("fog", t_r=1.0, n_i=1.0, n_s=1e6, priority=3, scattering_coef=0.05,
+                     absorption_coef=0.01, g=0.3)
+    m_wax = mats.add("wax", kd=(0.8, 0.55, 0.4), path_length=0.3)
+    m_light = mats.add("light", ke=(15.0, 15.0, 15.0))
+    mb = MeshBuilder()
+    v, f, nrm, uv = terrain(n, 1984)
+    mb.add(v, f, m_terrain, normals=nrm, uvs=uv)
+    v2, f2, uv2 = quad((-12, -2.0, -12), (-12, -2.0, 12), (12, -2.0, 12), (12, -2.0, -12))
+    mb.add(v2, f2, m_floor, uvs=uv2)
+    bv, bf = box((-6.0, 1.5, -6.0), (5.0, 3.0, 5.0))
+    mb.add(bv, bf, m_fog)
+    sv, sf, sn = icosphere((3.0, 3.2, 1.0), 1.4, 4)
+    mb.add(sv, sf, m_wax, normals=sn)
+    _add_lights(mb, m_light)
+    return Scene(mb.finish(), mats.finish(), default_camera(width, height),
+                 default_params(pathtracing_sample_size=spp, pathtracing_level=level,
+                                sss_pts_per_object=sss_pts), name=name)
+
+
 def make_scene(kind: str, **kw) -> Scene:
+    if kind in ("C5", "big"):
+        return big_scene(**kw)
     if kind in ("C4", "sppm"):
         return sppm_scene(**kw)
     if kind in ("C1", "terrain"):

@@ -55,3 +55,20 @@ def test_render_with_sss_lookup(pair):
     assert abs(got.mean() - want.mean()) <= 5e-3 * want.mean()
     # the SSS objects are in view: some pixels must come straight from the point cloud
     assert np.isfinite(got).all()
+
+
+def test_fast_lookup_equals_the_reference_walk(monkeypatch):
+    """sss_lookup finds the points of a lookup with a second LBVH (true Morton keys) and adds
+    them up in the reference tree's leaf order via a bitmap scan; GPT_SSS_DEBUG_MODE=1 walks the
+    reference's own (degenerate) tree instead.  Same terms in the same order: the images are
+    bit-identical."""
+    from gpu_pathtracer_b200.api import PathTracer
+    sc = S.make_scene("small", n=16, width=128, height=96, spp=2, level=4, sss_pts=3000)
+    imgs = {}
+    for mode in ("0", "1"):
+        monkeypatch.setenv("GPT_SSS_DEBUG_MODE", mode)
+        pt = PathTracer(sc)
+        pt.build()
+        imgs[mode] = pt.render_pathtrace()
+    assert np.array_equal(imgs["0"].view(np.uint32), imgs["1"].view(np.uint32))
+    assert np.isfinite(imgs["0"]).all() and imgs["0"].max() > 0
