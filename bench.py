@@ -124,17 +124,20 @@ def reference_window(sc, budget_s: float, nthreads: int):
     ref = RefReplay(sc)
     H, W = sc.camera["height"], sc.camera["width"]
     rays, ms, rows_done = 0, 0.0, 0
-    # rows around the image centre (terrain + spheres), full width strips of 2 rows at a time
-    order = [H // 2 + (k // 2) * (1 if k % 2 == 0 else -1) - (0 if k % 2 == 0 else 1)
-             for k in range(H)]
+    # horizontal strips around the image centre (terrain + spheres), alternating below / above;
+    # a strip has one row per host thread, because the replay hands out work by rows
+    strip = max(1, nthreads)
     cols = (W // 4, 3 * W // 4)
     k = 0
-    while ms < budget_s * 1e3 and k < len(order):
-        r = order[k]
-        ref.render_pathtrace(window=(r, r + 1, cols[0], cols[1]), nthreads=nthreads)
+    while ms < budget_s * 1e3:
+        off = (k // 2) * strip
+        r0 = H // 2 + off if k % 2 == 0 else H // 2 - off - strip
+        if r0 < 0 or r0 + strip > H:
+            break
+        ref.render_pathtrace(window=(r0, r0 + strip, cols[0], cols[1]), nthreads=nthreads)
         rays += ref.render_rays
         ms += ref.render_ms
-        rows_done += 1
+        rows_done += strip
         k += 1
     return dict(mrays=rays / ms / 1e3, rays=rays, ms=ms,
                 sample=f"{rows_done} image rows x columns [{cols[0]},{cols[1]}) around the centre "
