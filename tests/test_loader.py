@@ -247,3 +247,100 @@ def test_parallel_obj_parse_is_thread_count_invariant(tmp_path):
     for sym in ("gpt_scene_files_parse", "gpt_scene_files_view", "gpt_scene_files_free",
                 "gpt_load_scene_files", "gpt_scene_files_material_name"):
         assert hasattr(lib, sym)
+
+
+def _random_case(rng, d):
+    """A random but well-formed OBJ + 1-2 MTL files using every construct the loaders know:
+    polygons of 3-6 corners in the four corner forms, optional vn / vt, several usemtl runs,
+    odd whitespace, CRLF, numbers in every spelling stof accepts."""
+    def num(lo=-50.0, hi=50.0):
+        v = rng.uniform(lo, hi)
+        form = rng.integers(0, 6)
+        if form == 0:
+            return "%.9g" % np.float32(v)
+        if form == 1:
+            return "%d" % int(v)
+        if form == 2:
+            return "%.3e" % v
+        if form == 3:
+            return ("+" if v >= 0 else "") + "%.4f" % v
+        if form == 4:
+            return ("%.5f" % (v / 100.0)).replace("0.", ".", 1)
+        return "%.12f" % v
+    sep = lambda: rng.choice([" ", "  ", "\t", " \t "])
+    eol = rng.choice(["\n", "\r\n"])
+    nv, nn, nt = int(rng.integers(4, 40)), int(rng.integers(0, 8)), int(rng.integers(0, 8))
+    mats = ["m%d" % i for i in range(int(rng.integers(1, 5)))]
+    files = ["a.mtl"] + (["b.mtl"] if rng.random() < 0.5 else [])
+    tex = []
+    for fi, fn in enumerate(files):
+        with open(d + fn, "w", newline="") as f:
+            if fi == 1 and rng.random() < 0.5:
+                f.write("Ks" + sep() + " ".join(num(0, 1) for _ in range(3)) + eol)
+            for m in (mats if fi == 0 else ["x%d" % i for i in range(int(rng.integers(1, 3)))]):
+                f.write("newmtl" + sep() + m + eol)
+                for key in ("Ka", "Kd", "Ks", "Ke", "Tf"):
+                    if rng.random() < 0.6:
+                        f.write(key + sep() + sep().join(num(0, 2) for _ in range(3)) + eol)
+                for key, lo, hi in (("d", -0.5, 1.5), ("Tr", -0.5, 1.5), ("Ns", -10, 2e6), ("Ni", 0, 3),
+                                    ("path_length", 0, 1), ("scattering_coef", 0, 1),
+                                    ("absorption_coef", 0, 1), ("g", -1, 1)):
+                    if rng.random() < 0.4:
+                        f.write(key + sep() + num(lo, hi) + eol)
+                if rng.random() < 0.4:
+                    f.write("priority" + sep() + str(int(rng.integers(-9, 9))) + eol)
+                for key in ("map_Kd", "map_Ks", "map_Ke", "map_Ns"):
+                    if rng.random() < 0.25:
+                        name = "t%d.img" % int(rng.integers(0, 3))
+                        tex.append(name)
+                        f.write(key + sep() + name + eol)
+                if rng.random() < 0.25:
+                    name = "t%d.img" % int(rng.integers(0, 3))
+                    tex.append(name)
+                    f.write("map_Bump -bm " + num(0, 1) + " " + name + eol)
+                f.write(eol)
+    for name in set(tex):
+        _write_img(d + name, int(rng.integers(1, 6)), int(rng.integers(1, 6)), int(rng.integers(1 << 30)))
+    _write_img(d + "bg.img", int(rng.integers(1, 4)), int(rng.integers(1, 4)), 7)
+    with open(d + "r.obj", "w", newline="") as f:
+        f.write("# generated" + eol + "mtllib " + " ".join(files) + eol)
+        for _ in range(nv):
+            f.write("v" + sep() + sep().join(num() for _ in range(3)) + eol)
+        for _ in range(nn):
+            f.write("vn" + sep() + sep().join(num(-1, 1) for _ in range(3)) + eol)
+        for _ in range(nt):
+            f.write("vt" + sep() + sep().join(num(0, 1) for _ in range(2)) + eol)
+        f.write(eol + "o thing" + eol + "s off" + eol)
+        for _ in range(int(rng.integers(1, 6))):
+            f.write("usemtl" + sep() + str(rng.choice(mats)) + eol)
+            for _ in range(int(rng.integers(0, 12))):
+                k = int(rng.integers(3, 7))
+                form = int(rng.integers(0, 4))
+                if form in (1, 3) and nt == 0:
+                    form = 0
+                if form in (2, 3) and nn == 0:
+                    form = 0
+                corners = []
+                for _ in range(k):
+                    p = int(rng.integers(1, nv + 1))
+                    t = int(rng.integers(1, max(nt, 1) + 1))
+                    n = int(rng.integers(1, max(nn, 1) + 1))
+                    corners.append(["%d" % p, "%d/%d" % (p, t), "%d//%d" % (p, n),
+                                    "%d/%d/%d" % (p, t, n)][form])
+                f.write(rng.choice(["f", "  f"]) + sep() + sep().join(corners) + rng.choice(["", " "]) + eol)
+    with open(d + "m.txt", "w") as f:
+        f.write(f"input_folder_path\t{d}\nobj_filename\tr.obj\ntexture_bg_path\tbg.img\n"
+                f"image_width\t{int(rng.integers(1, 99))}\nimage_height\t{int(rng.integers(1, 99))}\n"
+                f"aperture\t{num(-1, 1)}\ndof_sample_size\t{int(rng.integers(1, 9))}\n"
+                f"fovy\t{num(10, 90)}\neye_x\t{num()}\nrender_mode\t{int(rng.integers(1, 3))}\n")
+    return d + "m.txt"
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_loader_matches_the_reference_loader_on_random_files(tmp_path, seed):
+    rng = np.random.default_rng(1984 + seed)
+    d = os.path.join(str(tmp_path), "")
+    master = _random_case(rng, d)
+    want = _ref_load(master)
+    got = load_scene_files(master, threads=int(rng.integers(1, 4)))
+    _assert_same_scene(got, want)
