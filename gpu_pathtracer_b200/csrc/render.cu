@@ -730,6 +730,11 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
     int sms = 148, per_sm = 4;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pt_trace<false>, TP_BLOCK, 0);
+    // GPT_TRACE_BLOCKS_PER_SM < occupancy leaves room for another group's shade / sort blocks to
+    // run beside a persistent trace kernel instead of after it (experiment knob)
+    const char *e = getenv("GPT_TRACE_BLOCKS_PER_SM");
+    int cap = e ? atoi(e) : 0;
+    if (cap > 0 && cap < per_sm) per_sm = cap;
     trace_grid = sms * (per_sm > 0 ? per_sm : 1);
   }
   uint64_t rays = 0, shades = 0, trace_launches = 0;

@@ -120,6 +120,24 @@ static __device__ __noinline__ bool trace_surf(const SppmScene &S, const TreeRef
   return fill_surf(S, tr, h.t, h.leaf, h.prim, h.b1, h.b2, h.b3, dir, rec);
 }
 
+// visibility rays only ask "how far is the first hit": the traversal without the hit-record fill
+static __device__ __noinline__ bool trace_t(const SppmScene &S, const TreeRef &tr, Tracer &T, V3 o,
+                                            V3 dir, float &t) {
+  RaySetup r = make_ray(o.x, o.y, o.z, dir.x, dir.y, dir.z);
+  int overflow = 0;
+  HitResult h;
+  if (S.count_visits)
+    h = trace_ray<true>(tr.nodes, tr.tris, tr.parent_leaf, r, INFINITY, T.stack, SP_BLOCK,
+                        S.counters, S.counters + 1, &overflow);
+  else
+    h = trace_ray<false>(tr.nodes, tr.tris, tr.parent_leaf, r, INFINITY, T.stack, SP_BLOCK,
+                         nullptr, nullptr, &overflow);
+  if (overflow) atomicExch(S.counters + 3, 1ull);
+  T.nrays++;
+  t = h.leaf < 0 ? INFINITY : h.t;
+  return h.leaf >= 0;
+}
+
 // rearrange_material_list (material_list_operations.h:43-59)
 __device__ __forceinline__ void rearrange_list(const SppmScene &S, MatList &l, int mat,
                                                const RefRec &ref) {
@@ -1209,10 +1227,9 @@ k_gather(SppmScene S, PhotonTree st, HitPoints hp) {
             if (dist(c, V3{a.x, a.y, a.z}) <= r) {  // BoundingSphere::is_inside
               float4 b = __ldg(ph + 1), d = __ldg(ph + 2);
               V3 rd = V3{a.w, b.x, b.y} - c;  // prev_location - hit point
-              SurfRec rec;
-              rec.t = INFINITY;
-              bool gh = trace_surf(S, S.main_t, true, T, c, unit(rd), rec);
-              if (gh && rec.t > length(rd)) {
+              float tv;
+              bool gh = trace_t(S, S.main_t, T, c, unit(rd), tv);
+              if (gh && tv > length(rd)) {
                 count++;
                 float f = fmaxf(0.0f, dot(nrm, -V3{b.z, b.w, d.x}));
                 flux = flux + f * V3{d.y, d.z, d.w};
