@@ -28,11 +28,13 @@ struct RenderCtx {
   // Independent wavefront groups (slot ranges), each on its own stream with its own queues,
   // counters and read-back ring, so the tail of one group's trace overlaps the others' work.
   static constexpr int MAX_GROUPS = 8, RING = 4;
-  int *h_counts = nullptr;        // pinned: MAX_GROUPS x RING x 4 ints (queue lengths + error flag)
+  // per group, 8 ints on the device: [0..2] queue lengths in rotation (read / append / being
+  // zeroed), [3] the trace kernel's ray cursor, [4] error flag
+  static constexpr int CNT = 8;
+  int *h_counts = nullptr;        // pinned: MAX_GROUPS x RING x CNT ints
   cudaEvent_t ring_ev[MAX_GROUPS][RING] = {};
   cudaStream_t gstream[MAX_GROUPS] = {};
   cudaEvent_t fork_ev = nullptr, join_ev[MAX_GROUPS] = {};
-  int *next_ray = nullptr;        // MAX_GROUPS ints: the persistent trace kernels' ray cursors
   int hist_stride = 0;
   uint32_t *sort_key = nullptr, *sort_key_alt = nullptr, *sort_hist = nullptr;
   int *sort_val = nullptr, *sort_val_alt = nullptr;
@@ -241,7 +243,12 @@ static __device__ __noinline__ V3 sss_lookup_ref_walk(const SssTree &t, V3 c, fl
 // that walk in a private bitmap, then add them up by scanning the bitmap in increasing order.  Same terms, same order, same result; ~100x fewer node visits.  The bitmap comes
 // from a pool (probe + atomicCAS); with the pool exhausted the reference walk above runs.
 __device__ int g_sss_debug_mode = 0;  // 0 fast, 1 reference walk, 2 skip (timing experiments)
-static __device__ __noinline__ V3 sss_lookup(const SssView &sv, const SssTree &t, V3 c, float r,
+struct BitmapPool {  // by value: a reference into the kernel parameters would be spilled
+  uint32_t *bm_pool;
+  int *bm_busy;
+  int bm_n, bm_words;
+};
+static __device__ __noinline__ V3 sss_lookup(BitmapPool sv, const SssTree &t, V3 c, float r,
                                              bool &found) {
   found = false;
   if (t.n < 2) return V3{0.f, 0.f, 0.f};
@@ -396,9 +403,15 @@ __global__ void __launch_bounds__(PT_BLOCK)
 k_pt_shade(PathState ps, RenderParams p, const int *__restrict__ queue,
            const int *__restrict__ count, int *next_queue, int *next_count, SceneDev sc,
            TexAtlas atlas, const float4 *__restrict__ main_tris, LightTree lt, float *fb,
-           int *error_flag, unsigned long long *ray_counter) {
+           int *error_flag, unsigned long long *ray_counter, int *zero_a, int *zero_b) {
   int a = blockIdx.x * blockDim.x + threadIdx.x;
-  if (a == 0) atomicAdd(ray_counter, (unsigned long long)*count);  // rays traced this iteration
+  if (a == 0) {
+    atomicAdd(ray_counter, (unsigned long long)*count);  // rays traced this iteration
+    // nobody reads these two until the next iteration of this group: the queue length of the
+    // iteration after next, and the trace kernel's ray cursor (saves two memsets per iteration)
+    *zero_a = 0;
+    *zero_b = 0;
+  }
   bool alive = false;
   int s = -1;
   if (a < *count) {
@@ -441,7 +454,8 @@ k_pt_shade(PathState ps, RenderParams p, const int *__restrict__ queue,
                                 p.pdf_weight, rng);
       if (sss_hit) {  // return compute_color_sss(...): the sample IS the point-cloud estimate
         bool found;
-        V3 col = sss_lookup(p.sss, p.sss.trees[ts.obj], point, m.path_length, found);
+        V3 col = sss_lookup(BitmapPool{p.sss.bm_pool, p.sss.bm_busy, p.sss.bm_n, p.sss.bm_words},
+                            p.sss.trees[ts.obj], point, m.path_length, found);
         result = found ? col * mat_diffuse(atlas, m, u, v) : V3{0.f, 0.f, 0.f};
         done = true;
       }
@@ -594,8 +608,7 @@ static int reserve_paths(gpt_ctx *ctx, RenderCtx *rc, int n) {
   GPT_TRY(gpt_alloc(ctx, &ps.cam, 2 * N));
   GPT_TRY(gpt_alloc(ctx, &ps.queue[0], N));
   GPT_TRY(gpt_alloc(ctx, &ps.queue[1], N));
-  GPT_TRY(gpt_alloc(ctx, &ps.counts, (size_t)4 * RenderCtx::MAX_GROUPS));
-  GPT_TRY(gpt_alloc(ctx, &rc->next_ray, (size_t)RenderCtx::MAX_GROUPS));
+  GPT_TRY(gpt_alloc(ctx, &ps.counts, (size_t)RenderCtx::CNT * RenderCtx::MAX_GROUPS));
   GPT_TRY(gpt_alloc(ctx, &rc->sort_key, N));
   GPT_TRY(gpt_alloc(ctx, &rc->sort_key_alt, N));
   GPT_TRY(gpt_alloc(ctx, &rc->sort_val, N));
@@ -604,7 +617,7 @@ static int reserve_paths(gpt_ctx *ctx, RenderCtx *rc, int n) {
   GPT_TRY(gpt_alloc(ctx, &rc->sort_hist, (size_t)rc->hist_stride * RenderCtx::MAX_GROUPS));
   if (!rc->h_counts) {
     GPT_CUDA(ctx, cudaMallocHost((void **)&rc->h_counts,
-                                 RenderCtx::MAX_GROUPS * RenderCtx::RING * 4 * sizeof(int)));
+                                 RenderCtx::MAX_GROUPS * RenderCtx::RING * RenderCtx::CNT * sizeof(int)));
     GPT_CUDA(ctx, cudaEventCreateWithFlags(&rc->fork_ev, cudaEventDisableTiming));
     for (int g = 0; g < RenderCtx::MAX_GROUPS; g++) {
       GPT_CUDA(ctx, cudaStreamCreateWithFlags(&rc->gstream[g], cudaStreamNonBlocking));
@@ -789,14 +802,16 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
     loc_shift = leaf_bits - loc_bits;
     if (loc_bits == 0) loc_shift = 31;
   }
+  constexpr int CNT = RenderCtx::CNT;
   struct Group {
     int s0, n, active, cur;
+    int c;  // which of counts[0..2] holds the length of the queue being traced
     int cur_of[RenderCtx::RING];
     long long it;
     bool done;
   };
   Group grp[RenderCtx::MAX_GROUPS];
-  int h_init[4 * RenderCtx::MAX_GROUPS] = {0};
+  int h_init[RenderCtx::CNT * RenderCtx::MAX_GROUPS] = {0};
   for (int g = 0; g < G; g++) {
     // group boundaries on multiples of 1024 slots (= one 32x32 tile) so warps stay tile rows
     long long lo = (long long)n * g / G, hi = (long long)n * (g + 1) / G;
@@ -804,10 +819,11 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
     if (g < G - 1) hi = (hi + 1023) / 1024 * 1024;
     if (lo > n) lo = n;
     if (hi > n) hi = n;
-    grp[g] = Group{(int)lo, (int)(hi - lo), (int)(hi - lo), 0, {0, 0, 0, 0}, 0, hi <= lo};
-    h_init[4 * g] = grp[g].n;
+    grp[g] = Group{(int)lo, (int)(hi - lo), (int)(hi - lo), 0, 0, {0, 0, 0, 0}, 0, hi <= lo};
+    h_init[CNT * g] = grp[g].n;
   }
-  GPT_CUDA(ctx, cudaMemcpyAsync(ps.counts, h_init, sizeof(int) * 4 * G, cudaMemcpyHostToDevice, st));
+  GPT_CUDA(ctx, cudaMemcpyAsync(ps.counts, h_init, sizeof(int) * CNT * G, cudaMemcpyHostToDevice, st));
+
   unsigned long long *ray_counter = ctx->d_counters + 6;
   GPT_CUDA(ctx, cudaMemsetAsync(ray_counter, 0, sizeof(unsigned long long), st));
   GPT_CUDA(ctx, cudaEventRecord(rc->fork_ev, st));
@@ -824,14 +840,14 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
       Group &q = grp[g];
       if (q.done) continue;
       cudaStream_t gs = G > 1 ? rc->gstream[g] : st;
-      int *h_ring = rc->h_counts + 4 * RING * g;
-      int *d_counts = ps.counts + 4 * g;
+      int *h_ring = rc->h_counts + CNT * RING * g;
+      int *d_counts = ps.counts + CNT * g;
       if (q.it >= LAG) {
         int slot = (int)((q.it - LAG) % RING);
         GPT_CUDA(ctx, cudaEventSynchronize(rc->ring_ev[g][slot]));
-        const int *h = h_ring + 4 * slot;
+        const int *h = h_ring + CNT * slot;
         q.active = h[q.cur_of[slot]];
-        if (h[2]) list_overflow = true;
+        if (h[4]) list_overflow = true;
       }
       if (q.active == 0 || list_overflow || q.it >= max_iters) {
         q.done = true;
@@ -839,12 +855,12 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
         continue;
       }
       int grid = (q.active + PT_BLOCK - 1) / PT_BLOCK;
-      int *next_ray = rc->next_ray + g;
-      GPT_CUDA(ctx, cudaMemsetAsync(d_counts + (q.cur ^ 1), 0, sizeof(int), gs));
-      GPT_CUDA(ctx, cudaMemsetAsync(next_ray, 0, sizeof(int), gs));
+      int *next_ray = d_counts + 3;
+      const int c0 = q.c, c1 = (q.c + 1) % 3, c2 = (q.c + 2) % 3;
+      uint32_t *hist = rc->sort_hist + (size_t)rc->hist_stride * g;
       GPT_CUDA(ctx, stamp());
       {
-        QueueSource qs{ps, ps.queue[q.cur] + q.s0, d_counts + q.cur, ctx->scene.shade,
+        QueueSource qs{ps, ps.queue[q.cur] + q.s0, d_counts + c0, ctx->scene.shade,
                        rc->sort_key + q.s0, rc->sort_val + q.s0, loc_bits, loc_shift};
         int tgrid = grid < trace_grid ? grid : trace_grid;
         if (counting)
@@ -863,20 +879,20 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
       ctx->stream = gs;  // the sort enqueues on ctx->stream
       rc_err = gpt_radix_sort_pairs(ctx, rc->sort_key + q.s0, rc->sort_val + q.s0,
                                     rc->sort_key_alt + q.s0, rc->sort_val_alt + q.s0,
-                                    rc->sort_hist + (size_t)rc->hist_stride * g, q.active, 7 + loc_bits, &sk,
-                                    &sorted_slots, d_counts + q.cur);
+                                    hist, q.active, 7 + loc_bits, &sk, &sorted_slots, d_counts + c0);
       ctx->stream = caller_stream;
       if (rc_err != GPT_OK) break;
-      k_pt_shade<<<grid, PT_BLOCK, 0, gs>>>(ps, p, sorted_slots, d_counts + q.cur,
-                                           ps.queue[q.cur ^ 1] + q.s0, d_counts + (q.cur ^ 1),
-                                           ctx->scene, atlas, mb.tris, lt, d_fb, d_counts + 2,
-                                           ray_counter);
+      k_pt_shade<<<grid, PT_BLOCK, 0, gs>>>(ps, p, sorted_slots, d_counts + c0,
+                                           ps.queue[q.cur ^ 1] + q.s0, d_counts + c1,
+                                           ctx->scene, atlas, mb.tris, lt, d_fb, d_counts + 4,
+                                           ray_counter, d_counts + c2, d_counts + 3);
       GPT_LAUNCH_CHECK(ctx);
       GPT_CUDA(ctx, stamp());
       q.cur ^= 1;
+      q.c = c1;
       int slot = (int)(q.it % RING);
-      q.cur_of[slot] = q.cur;  // which of counts[0..1] the NEXT iteration's queue length is
-      GPT_CUDA(ctx, cudaMemcpyAsync(h_ring + 4 * slot, d_counts, 4 * sizeof(int),
+      q.cur_of[slot] = q.c;  // which of counts[0..2] the NEXT iteration's queue length is
+      GPT_CUDA(ctx, cudaMemcpyAsync(h_ring + CNT * slot, d_counts, CNT * sizeof(int),
                                     cudaMemcpyDeviceToHost, gs));
       GPT_CUDA(ctx, cudaEventRecord(rc->ring_ev[g][slot], gs));
       q.it++;
@@ -889,14 +905,14 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
       GPT_CUDA(ctx, cudaEventRecord(rc->join_ev[g], rc->gstream[g]));
       GPT_CUDA(ctx, cudaStreamWaitEvent(st, rc->join_ev[g], 0));
     }
-    int h_fin[4 * RenderCtx::MAX_GROUPS];
-    GPT_CUDA(ctx, cudaMemcpyAsync(h_fin, ps.counts, sizeof(int) * 4 * G, cudaMemcpyDeviceToHost, st));
+    int h_fin[RenderCtx::CNT * RenderCtx::MAX_GROUPS];
+    GPT_CUDA(ctx, cudaMemcpyAsync(h_fin, ps.counts, sizeof(int) * CNT * G, cudaMemcpyDeviceToHost, st));
     unsigned long long h_rays = 0;
     GPT_CUDA(ctx, cudaMemcpyAsync(&h_rays, ray_counter, sizeof(h_rays), cudaMemcpyDeviceToHost, st));
     GPT_CUDA(ctx, cudaStreamSynchronize(st));
     for (int g = 0; g < G; g++) {
-      active += h_fin[4 * g + grp[g].cur];
-      if (h_fin[4 * g + 2]) list_overflow = true;
+      active += h_fin[CNT * g + grp[g].c];
+      if (h_fin[CNT * g + 4]) list_overflow = true;
     }
     rays = shades = h_rays;
   }
@@ -952,7 +968,6 @@ void gpt_render_free(gpt_ctx *ctx) {
     for (int k = 0; k < RenderCtx::RING; k++)
       if (rc->ring_ev[g][k]) cudaEventDestroy(rc->ring_ev[g][k]);
   }
-  cudaFree(rc->next_ray);
   for (cudaEvent_t e : rc->events) cudaEventDestroy(e);
   delete rc;
   ctx->render_state = nullptr;
