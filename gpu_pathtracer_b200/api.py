@@ -216,9 +216,15 @@ class PathTracer:
         return self.stats()
 
     # -- render -------------------------------------------------------------------------
-    def render_pathtrace(self) -> np.ndarray:
+    def render_pathtrace(self, out: np.ndarray | None = None) -> np.ndarray:
+        """Full frame into a host array (``out``: float32 [H, W, 3], C order; page-locked
+        memory makes the read-back a plain DMA).  Every pixel is written."""
         cam = self.scene.camera
-        out = np.zeros((cam["height"], cam["width"], 3), np.float32)
+        shape = (cam["height"], cam["width"], 3)
+        if out is None:
+            out = np.empty(shape, np.float32)
+        elif out.shape != shape:
+            raise ValueError(f"out must be float32 {shape}, got {out.dtype} {out.shape}")
         self._check(self.lib.gpt_render_pathtrace(self.ctx, cabi.fptr(out)))
         return out
 

@@ -35,6 +35,13 @@ int gpt_create(int device, gpt_ctx **out) {
     return GPT_E_CUDA;
   }
   cudaMemset(ctx->d_counters, 0, 8 * sizeof(unsigned long long));
+  {  // gpt_alloc (common.cuh): keep freed blocks in the pool instead of returning them to the OS
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+      uint64_t keep = UINT64_MAX;
+      cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    }
+  }
   ctx->stream = ctx->own_stream;
   ctx->params.render_mode = 1;
   ctx->params.pathtracing_sample_size = 1;
@@ -48,11 +55,11 @@ void gpt_render_free(gpt_ctx *ctx);  // render.cu
 void gpt_sppm_free(gpt_ctx *ctx);    // sppm.cu
 void gpt_sss_free(gpt_ctx *ctx);     // sss.cu
 
-static void free_scene(SceneDev &s) {
+static void free_scene(gpt_ctx *ctx, SceneDev &s) {
   void *ptrs[] = {s.x, s.y, s.z, s.xn, s.yn, s.zn, s.xt, s.yt, s.p1, s.p2, s.p3, s.n1, s.n2,
                   s.n3, s.t1, s.t2, s.t3, s.mat_idx, s.obj_idx, s.tolerance, s.aabb, s.normal,
                   s.energy, s.shade, s.vtangent};
-  for (void *p : ptrs) cudaFree(p);
+  for (void *p : ptrs) gpt_free(ctx, p);
   MaterialDev *mats = s.mats;
   float *tr = s.tex_r, *tg = s.tex_g, *tb = s.tex_b, *br = s.bg_r, *bg = s.bg_g, *bb = s.bg_b;
   int nmat = s.nmat, bh = s.bg_h, bw = s.bg_w;
@@ -70,12 +77,12 @@ void gpt_destroy(gpt_ctx *ctx) {
   gpt_render_free(ctx);
   gpt_sppm_free(ctx);
   gpt_sss_free(ctx);
-  for (int k = 0; k < 3; k++) gpt_lbvh_free(ctx->bvh[k]);
+  for (int k = 0; k < 3; k++) gpt_lbvh_free(ctx, ctx->bvh[k]);
   SceneDev &s = ctx->scene;
-  free_scene(s);
-  cudaFree(s.mats); cudaFree(s.tex_r); cudaFree(s.tex_g); cudaFree(s.tex_b);
-  cudaFree(s.bg_r); cudaFree(s.bg_g); cudaFree(s.bg_b);
-  cudaFree(ctx->d_counters);
+  free_scene(ctx, s);
+  gpt_free(ctx, s.mats); gpt_free(ctx, s.tex_r); gpt_free(ctx, s.tex_g); gpt_free(ctx, s.tex_b);
+  gpt_free(ctx, s.bg_r); gpt_free(ctx, s.bg_g); gpt_free(ctx, s.bg_b);
+  cudaFree(ctx->d_counters);  // plain cudaMalloc in gpt_create
   cudaEventDestroy(ctx->ev0);
   cudaEventDestroy(ctx->ev1);
   cudaStreamDestroy(ctx->own_stream);
@@ -86,7 +93,10 @@ const char *gpt_last_error(const gpt_ctx *ctx) { return ctx ? ctx->err.c_str() :
 
 int gpt_set_stream(gpt_ctx *ctx, uint64_t cuda_stream) {
   if (!ctx) return GPT_E_INVALID;
-  ctx->stream = cuda_stream ? reinterpret_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
+  cudaStream_t next = cuda_stream ? reinterpret_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
+  // allocations and frees are ordered on ctx->stream: drain the old one before switching
+  if (next != ctx->stream) GPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  ctx->stream = next;
   return GPT_OK;
 }
 
@@ -100,7 +110,7 @@ int gpt_set_mesh(gpt_ctx *ctx, const GptMesh *m) {
   if (!ctx || !m || m->num_triangles < 0) return GPT_E_INVALID;
   GPT_CUDA(ctx, cudaSetDevice(ctx->device));
   SceneDev &s = ctx->scene;
-  free_scene(s);
+  free_scene(ctx, s);
   ctx->built = false;
   s.nv = m->num_vertices; s.nvn = m->num_normals; s.nvt = m->num_texcoords;
   s.ntri = m->num_triangles; s.nobj = m->num_objects;
@@ -367,7 +377,7 @@ int gpt_trace_count_device(gpt_ctx *ctx, int which, const void *d_rays, int64_t 
     cudaMemcpyAsync(c, ctx->d_counters, sizeof(c), cudaMemcpyDeviceToHost, ctx->stream);
     cudaStreamSynchronize(ctx->stream);
   }
-  cudaFree(hits);
+  gpt_free(ctx, hits);
   GPT_TRY(rc);
   ctx->stats.internal_visits = c[0];
   ctx->stats.leaf_tests = c[1];
@@ -396,8 +406,8 @@ int gpt_trace(gpt_ctx *ctx, int which, const float *rays, int64_t n, int32_t *le
     if (cudaMemcpyAsync(h.data(), d_hits, 32 * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) { rc = GPT_E_CUDA; break; }
     rc = check_overflow(ctx);
   } while (0);
-  cudaFree(d_rays);
-  cudaFree(d_hits);
+  gpt_free(ctx, d_rays);
+  gpt_free(ctx, d_hits);
   GPT_TRY(rc);
   float ms = 0.f;
   cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1);

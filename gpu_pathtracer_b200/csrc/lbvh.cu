@@ -394,10 +394,10 @@ int gpt_radix_sort_pairs(gpt_ctx *ctx, uint32_t *keys, int *vals, uint32_t *keys
   return GPT_OK;
 }
 
-void gpt_lbvh_free(BvhDev &b) {
-  cudaFree(b.nodes); cudaFree(b.tris); cudaFree(b.parent_leaf); cudaFree(b.morton);
-  cudaFree(b.sorted_prim); cudaFree(b.prim_list); cudaFree(b.world_enc);
-  cudaFree(b.keys_alt); cudaFree(b.vals_alt); cudaFree(b.block_hist); cudaFree(b.flags);
+void gpt_lbvh_free(gpt_ctx *ctx, BvhDev &b) {
+  gpt_free(ctx, b.nodes); gpt_free(ctx, b.tris); gpt_free(ctx, b.parent_leaf); gpt_free(ctx, b.morton);
+  gpt_free(ctx, b.sorted_prim); gpt_free(ctx, b.prim_list); gpt_free(ctx, b.world_enc);
+  gpt_free(ctx, b.keys_alt); gpt_free(ctx, b.vals_alt); gpt_free(ctx, b.block_hist); gpt_free(ctx, b.flags);
   b = BvhDev();
 }
 
@@ -406,7 +406,7 @@ static int lbvh_reserve(gpt_ctx *ctx, BvhDev &b, int n, bool with_tris) {
   if (n < b.capacity) n = b.capacity;
   int *keep = b.prim_list;
   b.prim_list = nullptr;
-  gpt_lbvh_free(b);
+  gpt_lbvh_free(ctx, b);
   b.prim_list = keep;
   size_t N = (size_t)n;
   GPT_TRY(gpt_alloc(ctx, &b.nodes, 4 * N));
@@ -503,14 +503,14 @@ int gpt_collect_subset(gpt_ctx *ctx, int flag_mask, int **d_list, int *count) {
   GPT_CUDA(ctx, cudaMemcpyAsync(&c, d_count, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
   GPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   *count = c;
-  if (*d_list) { cudaFree(*d_list); *d_list = nullptr; }
+  if (*d_list) { gpt_free(ctx, *d_list); *d_list = nullptr; }
   GPT_TRY(gpt_alloc(ctx, d_list, (size_t)(c > 0 ? c : 1)));
   if (c > 0)
     GPT_CUDA(ctx, cudaMemcpyAsync(*d_list, vo, sizeof(int) * (size_t)c,
                                   cudaMemcpyDeviceToDevice, ctx->stream));
   GPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  cudaFree(keys); cudaFree(keys_alt); cudaFree(vals); cudaFree(vals_alt); cudaFree(hist);
-  cudaFree(d_count);
+  gpt_free(ctx, keys); gpt_free(ctx, keys_alt); gpt_free(ctx, vals); gpt_free(ctx, vals_alt); gpt_free(ctx, hist);
+  gpt_free(ctx, d_count);
   return GPT_OK;
 }
 
@@ -552,6 +552,6 @@ int gpt_lbvh_export(gpt_ctx *ctx, int which, uint32_t *morton, int32_t *sorted_t
       world_aabb[2 * a + 1] = dec_f32(we[3 + a]) + GPT_SMALL;
     }
   }
-  cudaFree(d_i); cudaFree(d_f);
+  gpt_free(ctx, d_i); gpt_free(ctx, d_f);
   return GPT_OK;
 }

@@ -78,8 +78,8 @@ extern "C" int gpt_splat_device(gpt_ctx *ctx, const float *d_loc, int loc_stride
   GPT_CUDA(ctx, cudaMemcpyAsync(out_rgb_host, d_out, sizeof(float) * 3 * (size_t)P,
                                 cudaMemcpyDeviceToHost, st));
   GPT_CUDA(ctx, cudaStreamSynchronize(st));
-  cudaFree(d_win);
-  cudaFree(d_out);
+  gpt_free(ctx, d_win);
+  gpt_free(ctx, d_out);
   return GPT_OK;
 }
 
@@ -100,8 +100,8 @@ int gpt_tonemap_u8(gpt_ctx *ctx, const float *rgb, int64_t n_values, uint8_t *ou
   GPT_LAUNCH_CHECK(ctx);
   GPT_CUDA(ctx, cudaMemcpyAsync(out, d_out, (size_t)n_values, cudaMemcpyDeviceToHost, st));
   GPT_CUDA(ctx, cudaStreamSynchronize(st));
-  cudaFree(d_in);
-  cudaFree(d_out);
+  gpt_free(ctx, d_in);
+  gpt_free(ctx, d_out);
   return GPT_OK;
 }
 

@@ -189,6 +189,6 @@ int gpt_preprocess(gpt_ctx *ctx) {
   k_assign_tangent<<<grid, 256, 0, ctx->stream>>>(s);
   GPT_LAUNCH_CHECK(ctx);
   GPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  cudaFree(keys); cudaFree(keys_alt); cudaFree(vals); cudaFree(vals_alt); cudaFree(hist);
+  gpt_free(ctx, keys); gpt_free(ctx, keys_alt); gpt_free(ctx, vals); gpt_free(ctx, vals_alt); gpt_free(ctx, hist);
   return GPT_OK;
 }

@@ -959,7 +959,7 @@ void gpt_render_free(gpt_ctx *ctx) {
                ps.queue[0], ps.queue[1], ps.counts, rc->leaf_info, rc->node_info,
                rc->node_energy, rc->lt_flags, rc->rng_init, rc->d_fb, rc->sort_key,
                rc->sort_key_alt, rc->sort_hist, rc->sort_val, rc->sort_val_alt};
-  for (void *q : p) cudaFree(q);
+  for (void *q : p) gpt_free(ctx, q);
   if (rc->h_counts) cudaFreeHost(rc->h_counts);
   if (rc->fork_ev) cudaEventDestroy(rc->fork_ev);
   for (int g = 0; g < RenderCtx::MAX_GROUPS; g++) {

@@ -1483,9 +1483,9 @@ void gpt_sppm_free(gpt_ctx *ctx) {
                sx->wave.queue[0], sx->wave.queue[1], sx->wave.iqueue[0], sx->wave.iqueue[1],
                sx->wave.counts, sx->wave.key,
                sx->wave.key_alt, sx->wave.val, sx->wave.val_alt};
-  for (void *q : p) cudaFree(q);
-  gpt_lbvh_free(sx->surf_bvh);
-  gpt_lbvh_free(sx->vol_bvh);
+  for (void *q : p) gpt_free(ctx, q);
+  gpt_lbvh_free(ctx, sx->surf_bvh);
+  gpt_lbvh_free(ctx, sx->vol_bvh);
   delete sx;
   ctx->sppm_state = nullptr;
 }

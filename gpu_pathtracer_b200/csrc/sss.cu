@@ -205,8 +205,8 @@ extern "C" void gpt_sss_free(gpt_ctx *ctx) {
   void *p[] = {sx->cdf, sx->rng, sx->pts_created, sx->pts, sx->leaf, sx->aabb, sx->keys,
                sx->obj_flag, sx->trees, sx->spos, sx->rank, sx->bm_pool, sx->bm_busy,
                sx->leafpos, sx->visit, sx->vkeys, sx->vkeys_alt, sx->vhist, sx->vvals, sx->vvals_alt};
-  for (void *q : p) cudaFree(q);
-  for (SssObj &o : sx->objs) { gpt_lbvh_free(o.bvh); gpt_lbvh_free(o.search); }
+  for (void *q : p) gpt_free(ctx, q);
+  for (SssObj &o : sx->objs) { gpt_lbvh_free(ctx, o.bvh); gpt_lbvh_free(ctx, o.search); }
   delete sx;
   ctx->sss_state = nullptr;
 }
@@ -382,7 +382,7 @@ int gpt_sss_prepare(gpt_ctx *ctx) {
   GPT_CUDA(ctx, cudaMemsetAsync(sx->bm_busy, 0, sizeof(int) * (size_t)sx->bm_n, st));
   GPT_TRY(gpt_upload(ctx, &sx->trees, trees.data(), trees.size()));
   GPT_CUDA(ctx, cudaStreamSynchronize(st));
-  cudaFree(d_tab);
+  gpt_free(ctx, d_tab);
   return GPT_OK;
 }
 

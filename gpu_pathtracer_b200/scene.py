@@ -296,6 +296,25 @@ class Scene:
     def num_triangles(self) -> int:
         return int(self.mesh["point_1_idx"].shape[0])
 
+    def pinned(self) -> "Scene":
+        """The same scene with every array in page-locked host memory, so that the uploads of
+        gpt_set_mesh / gpt_set_textures / gpt_set_background are real DMA transfers instead of
+        the driver's staged pageable copies (C2: 86 MB in 8.4 ms pageable).  The reference
+        keeps these arrays in cudaMallocManaged memory (src/main.cu:386-450); a host that
+        fills them for this library can allocate them page-locked the same way."""
+        import torch
+
+        def pin(v):
+            if not isinstance(v, np.ndarray) or v.size == 0:
+                return v
+            return torch.from_numpy(np.ascontiguousarray(v)).pin_memory().numpy()
+
+        return Scene(mesh={k: pin(v) for k, v in self.mesh.items()},
+                     materials={k: pin(v) for k, v in self.materials.items()},
+                     camera=dict(self.camera), params=dict(self.params),
+                     bg={k: pin(v) for k, v in self.bg.items()}, name=self.name,
+                     files=dict(self.files))
+
 
 def default_params(**kw) -> dict:
     p = dict(render_mode=1, pathtracing_sample_size=16, pathtracing_level=5,
