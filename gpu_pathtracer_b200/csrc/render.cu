@@ -391,12 +391,14 @@ struct QueueSource {
   }
 };
 
-template <bool COUNT>
+template <bool COUNT, bool COOP>
 __global__ void __launch_bounds__(TP_BLOCK, TP_MINBLOCKS)
 k_pt_trace(QueueSource src, const float4 *__restrict__ nodes, const float4 *__restrict__ tris,
            const int *__restrict__ parent_leaf, int *next_ray, unsigned long long *counters) {
   __shared__ int stack[TP_STACK_SMEM * TP_BLOCK];
-  trace_persistent<COUNT>(nodes, tris, parent_leaf, src, next_ray, stack, counters);
+  __shared__ int coop[COOP ? (TP_BLOCK / 32) * COOP_WARP_WORDS : 1];
+  trace_persistent<COUNT, QueueSource, COOP>(nodes, tris, parent_leaf, src, next_ray, stack,
+                                             counters, coop);
 }
 
 __global__ void __launch_bounds__(PT_BLOCK)
@@ -738,11 +740,21 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
   else
     k_pt_start<<<(n + PT_BLOCK - 1) / PT_BLOCK, PT_BLOCK, 0, st>>>(ps, p, n, d_fb);
   GPT_LAUNCH_CHECK(ctx);
+  // cooperative tail (trace_persistent.cuh): GPT_TRACE_COOP=0 switches it off
+  static int trace_coop = -1;
+  if (trace_coop < 0) {
+    const char *e = getenv("GPT_TRACE_COOP");
+    trace_coop = e ? (atoi(e) != 0) : 1;
+  }
+  const bool coop = trace_coop && mb.n < (1 << COOP_NODE_BITS);
   static int trace_grid = 0;
   if (!trace_grid) {
     int sms = 148, per_sm = 4;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pt_trace<false>, TP_BLOCK, 0);
+    if (trace_coop)
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pt_trace<false, true>, TP_BLOCK, 0);
+    else
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pt_trace<false, false>, TP_BLOCK, 0);
     // GPT_TRACE_BLOCKS_PER_SM < occupancy leaves room for another group's shade / sort blocks to
     // run beside a persistent trace kernel instead of after it (experiment knob)
     const char *e = getenv("GPT_TRACE_BLOCKS_PER_SM");
@@ -863,12 +875,10 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
         QueueSource qs{ps, ps.queue[q.cur] + q.s0, d_counts + c0, ctx->scene.shade,
                        rc->sort_key + q.s0, rc->sort_val + q.s0, loc_bits, loc_shift};
         int tgrid = grid < trace_grid ? grid : trace_grid;
-        if (counting)
-          k_pt_trace<true><<<tgrid, TP_BLOCK, 0, gs>>>(qs, mb.nodes, mb.tris, mb.parent_leaf,
-                                                      next_ray, ctx->d_counters);
-        else
-          k_pt_trace<false><<<tgrid, TP_BLOCK, 0, gs>>>(qs, mb.nodes, mb.tris, mb.parent_leaf,
-                                                       next_ray, ctx->d_counters);
+        auto kern = counting ? (coop ? k_pt_trace<true, true> : k_pt_trace<true, false>)
+                             : (coop ? k_pt_trace<false, true> : k_pt_trace<false, false>);
+        kern<<<tgrid, TP_BLOCK, 0, gs>>>(qs, mb.nodes, mb.tris, mb.parent_leaf, next_ray,
+                                         ctx->d_counters);
       }
       GPT_LAUNCH_CHECK(ctx);
       trace_launches++;
@@ -876,8 +886,11 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
       // stable 7-bit radix sort of the active slots by material (ties keep tile order)
       uint32_t *sk = nullptr;
       int *sorted_slots = nullptr;
+      static int no_sort = -1;  // experiment knob: shade in queue order
+      if (no_sort < 0) { const char *e = getenv("GPT_NO_SORT"); no_sort = e ? atoi(e) : 0; }
       ctx->stream = gs;  // the sort enqueues on ctx->stream
-      rc_err = gpt_radix_sort_pairs(ctx, rc->sort_key + q.s0, rc->sort_val + q.s0,
+      if (no_sort) sorted_slots = rc->sort_val + q.s0;
+      else rc_err = gpt_radix_sort_pairs(ctx, rc->sort_key + q.s0, rc->sort_val + q.s0,
                                     rc->sort_key_alt + q.s0, rc->sort_val_alt + q.s0,
                                     hist, q.active, 7 + loc_bits, &sk, &sorted_slots, d_counts + c0);
       ctx->stream = caller_stream;

@@ -40,16 +40,221 @@ struct TraceLane {
   unsigned neg;    // bit a set: 1/d[a] < 0 -> the "near" bound of that axis is the box max
 };
 
+
+// ---- cooperative tail -----------------------------------------------------------------
+// A launch ends when its slowest ray ends, and a ray is a chain of dependent node steps of
+// ~0.5-0.7 us each.  On a 1/8-frame shard every ray of the queue is in flight at once, so the
+// launch time IS that one chain (ncu / shard_time: ~250 us of a 310 us iteration), and the
+// 320 dependent iterations of a 64-spp frame are what bounds strong scaling.  So, once the
+// queue is exhausted and a warp is down to <= COOP_SLOTS live rays, the warp stops walking
+// them one lane each: the pending nodes of ALL its live rays (current node + stack entries)
+// go into one warp-wide work list in shared memory, and every round each lane pops one entry,
+// tests that node's two children against ITS ray, tests leaves, and pushes the children that
+// pass.  Closest hit with the visit-rank tie-break does not depend on the visit order (the
+// parity argument in trace_core.cuh never uses it), so the result is bit-identical; culling
+// sees t_best of the round's start only, so a few more nodes are visited than in the ordered
+// walk, which the tail has idle lanes to pay for.
+#ifndef COOP_SLOTS_V
+#define COOP_SLOTS_V 16
+#endif
+constexpr int COOP_SLOTS = COOP_SLOTS_V;        // live rays a warp may take into the tail (<= 32)
+constexpr int COOP_LIST = 32 * TP_STACK_SMEM;   // work-list entries per warp (its share of the stack array)
+constexpr int COOP_RAY_WORDS = 18;
+constexpr int COOP_WARP_WORDS = COOP_RAY_WORDS * COOP_SLOTS;  // ray table; the list reuses the stack array
+constexpr int COOP_NODE_BITS = 27;              // entry = slot << 27 | node
+enum { CR_OX, CR_OY, CR_OZ, CR_IX, CR_IY, CR_IZ, CR_SX, CR_SY, CR_SZ, CR_KZNEG, CR_BEST, CR_T,
+       CR_LEAF, CR_B1, CR_B2, CR_B3, CR_PRIM, CR_RAY };
+
+template <bool COUNT, class Source>
+__device__ __forceinline__ void coop_finish(const float4 *__restrict__ nodes,
+                                         const float4 *__restrict__ tris,
+                                         const int *__restrict__ parent_leaf, Source &src,
+                                         const TraceLane &L, unsigned live, const int *stack,
+                                         int *sm, unsigned &vi, unsigned &vl) {
+  const unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  // The work list lives in the warp's own part of the traversal-stack array: 32 levels x 32
+  // lanes, entry i at level i / 32, column i % 32.  (A separate list costs shared memory that
+  // the unified L1 then lacks: 37 KB instead of 16 KB per block made the FULL-frame trace 12 %
+  // slower, with the tail code never even reached.)
+  int *const wbase = const_cast<int *>(stack) - lane;
+#define WL(i) wbase[((i) >> 5) * TP_BLOCK + ((i) & 31)]
+  float *rt = reinterpret_cast<float *>(sm);  // ray table [word][slot]
+  int *rti = sm;
+  const bool mine = (live >> lane) & 1u;
+  const int nslots = __popc(live);
+  const int slot0 = __popc(live & ((1u << lane) - 1u));
+  // ---- the live lanes' stacks, compacted in place level by level: the entries of level k
+  //      land at list positions < 32 (k + 1), i.e. in levels that were already read ----------
+  int cnt = 0;
+  {
+    int maxsp = mine ? L.sp : 0;
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) maxsp = max(maxsp, __shfl_xor_sync(FULL, maxsp, d));
+    const int tag = slot0 << COOP_NODE_BITS;
+    for (int k = 0; k <= maxsp; k++) {
+      // level sp of a lane = its current node (the most urgent entry, so the last one)
+      const bool has = mine && k <= L.sp;
+      int v = 0;
+      if (has) v = tag | (k < L.sp ? stack[k * TP_BLOCK] : L.node);
+      const unsigned hm = __ballot_sync(FULL, has);
+      __syncwarp();
+      if (has) WL(cnt + __popc(hm & ((1u << lane) - 1u))) = v;
+      cnt += __popc(hm);
+      __syncwarp();
+    }
+  }
+  if (mine) {
+    const int slot = slot0;
+    rt[CR_OX * COOP_SLOTS + slot] = L.ox; rt[CR_OY * COOP_SLOTS + slot] = L.oy;
+    rt[CR_OZ * COOP_SLOTS + slot] = L.oz; rt[CR_IX * COOP_SLOTS + slot] = L.ix;
+    rt[CR_IY * COOP_SLOTS + slot] = L.iy; rt[CR_IZ * COOP_SLOTS + slot] = L.iz;
+    rt[CR_SX * COOP_SLOTS + slot] = L.sx; rt[CR_SY * COOP_SLOTS + slot] = L.sy;
+    rt[CR_SZ * COOP_SLOTS + slot] = L.sz;
+    rti[CR_KZNEG * COOP_SLOTS + slot] = L.kz | (int)(L.neg << 2);
+    rt[CR_BEST * COOP_SLOTS + slot] = L.best; rt[CR_T * COOP_SLOTS + slot] = L.t;
+    rti[CR_LEAF * COOP_SLOTS + slot] = L.leaf; rt[CR_B1 * COOP_SLOTS + slot] = L.b1;
+    rt[CR_B2 * COOP_SLOTS + slot] = L.b2; rt[CR_B3 * COOP_SLOTS + slot] = L.b3;
+    rti[CR_PRIM * COOP_SLOTS + slot] = L.prim; rti[CR_RAY * COOP_SLOTS + slot] = L.ray;
+  }
+  __syncwarp();
+  // ---- rounds: every lane pops one (ray, node) entry ------------------------------------
+  while (cnt > 0) {
+    int m = cnt < 32 ? cnt : 32;
+    if (cnt > COOP_LIST - 128) m = 1;  // nearly full: depth-first with one lane, which cannot grow it by more than the tree depth
+    const bool has_e = lane < m;
+    const int e = has_e ? WL(cnt - 1 - lane) : 0;
+    cnt -= m;
+    __syncwarp();
+    int npush = 0, push_far = 0, push_near = 0, slot = 0;
+    bool cand = false;
+    float ct = 0.f, cb1 = 0.f, cb2 = 0.f, cb3 = 0.f, ctol = 0.f;
+    int cleaf = -1, cprim = -1;
+    if (has_e) {
+      slot = (int)((unsigned)e >> COOP_NODE_BITS);
+      const int node = e & ((1 << COOP_NODE_BITS) - 1);
+      RaySetup r;
+      r.ox = rt[CR_OX * COOP_SLOTS + slot]; r.oy = rt[CR_OY * COOP_SLOTS + slot];
+      r.oz = rt[CR_OZ * COOP_SLOTS + slot]; r.ix = rt[CR_IX * COOP_SLOTS + slot];
+      r.iy = rt[CR_IY * COOP_SLOTS + slot]; r.iz = rt[CR_IZ * COOP_SLOTS + slot];
+      r.sx = rt[CR_SX * COOP_SLOTS + slot]; r.sy = rt[CR_SY * COOP_SLOTS + slot];
+      r.sz = rt[CR_SZ * COOP_SLOTS + slot];
+      const int kzneg = rti[CR_KZNEG * COOP_SLOTS + slot];
+      r.kz = kzneg & 3;
+      const unsigned neg = (unsigned)kzneg >> 2;
+      float best = rt[CR_BEST * COOP_SLOTS + slot];
+      const float4 *q = nodes + 4 * (size_t)node;
+      float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3);
+      if (COUNT) vi++;
+      int cref[2] = {__float_as_int(q3.x), __float_as_int(q3.y)};
+      const bool nx = neg & 1u, ny = neg & 2u, nz = neg & 4u;
+      float xn[2] = {nx ? q0.y : q0.x, nx ? q1.w : q1.z}, xf[2] = {nx ? q0.x : q0.y, nx ? q1.z : q1.w};
+      float yn[2] = {ny ? q0.w : q0.z, ny ? q2.y : q2.x}, yf[2] = {ny ? q0.z : q0.w, ny ? q2.x : q2.y};
+      float zn[2] = {nz ? q1.y : q1.x, nz ? q2.w : q2.z}, zf[2] = {nz ? q1.x : q1.y, nz ? q2.z : q2.w};
+      bool go[2];
+      float tnear[2], tcull[2];
+#pragma unroll
+      for (int c = 0; c < 2; c++) {  // the same predicate, operation for operation, as the ordered walk
+        float txn = (xn[c] - r.ox) * r.ix, txx = (xf[c] - r.ox) * r.ix;
+        float tyn = (yn[c] - r.oy) * r.iy, tyx = (yf[c] - r.oy) * r.iy;
+        float tzn = (zn[c] - r.oz) * r.iz, tzx = (zf[c] - r.oz) * r.iz;
+        bool ok = (txn <= tyx) && (tyn <= txx);
+        float txyn = fmaxf(txn, tyn), txyx = fminf(txx, tyx);
+        ok = ok && (txyn <= tzx) && (tzn <= txyx);
+        float tn = r.kz == 0 ? txn : (r.kz == 1 ? tyn : tzn);
+        float tf = r.kz == 0 ? txx : (r.kz == 1 ? tyx : tzx);
+        float margin = 1e-5f * fmaxf(fabsf(tn), fabsf(tf));
+        tnear[c] = tn;
+        tcull[c] = tn - margin;
+        go[c] = ok && !(tf + margin < 0.f);
+      }
+      int lf0 = (go[0] && cref[0] < 0) ? ~cref[0] : -1, lf1 = (go[1] && cref[1] < 0) ? ~cref[1] : -1;
+      float lc0 = tcull[0], lc1 = tcull[1];
+      if (lf0 < 0) { lf0 = lf1; lc0 = lc1; lf1 = -1; }
+#pragma unroll 1
+      while (lf0 >= 0) {
+        if (!(lc0 > best)) {
+          const float4 *tp = tris + 3 * (size_t)lf0;
+          float4 t0 = __ldg(tp), t1 = __ldg(tp + 1), t2 = __ldg(tp + 2);
+          if (COUNT) vl++;
+          float t, b1, b2, b3;
+          if (tri_test(r, t0, t1, t2, t, b1, b2, b3)) {
+            if (!(t > best) && !(t < t2.y)) {
+              bool take = true;
+              if (cand && t == ct)  // the node's two leaves tie: the later one in reference order
+                take = leaf_visit_rank(nodes, parent_leaf, lf0) >
+                       leaf_visit_rank(nodes, parent_leaf, cleaf);
+              if (take) {
+                cand = true; ct = t; cb1 = b1; cb2 = b2; cb3 = b3; cleaf = lf0;
+                cprim = __float_as_int(t2.z); ctol = t2.y;
+                best = t;
+              }
+            }
+          }
+        }
+        lf0 = lf1; lc0 = lc1; lf1 = -1;
+      }
+      const bool gl = go[0] && cref[0] >= 0 && !(tcull[0] > best);
+      const bool gr = go[1] && cref[1] >= 0 && !(tcull[1] > best);
+      const bool lfirst = tnear[0] <= tnear[1];
+      npush = (gl ? 1 : 0) + (gr ? 1 : 0);
+      const int tag = slot << COOP_NODE_BITS;
+      if (gl && gr) { push_near = tag | (lfirst ? cref[0] : cref[1]); push_far = tag | (lfirst ? cref[1] : cref[0]); }
+      else if (npush) push_near = tag | (gl ? cref[0] : cref[1]);
+    }
+    // ---- append the children that passed (far below near: near is popped first) -----------
+    const unsigned m1 = __ballot_sync(FULL, npush >= 1), m2 = __ballot_sync(FULL, npush == 2);
+    const unsigned lt = (1u << lane) - 1u;
+    const int off = cnt + __popc(m1 & lt) + __popc(m2 & lt);
+    if (npush == 2) { WL(off) = push_far; WL(off + 1) = push_near; }
+    else if (npush == 1) WL(off) = push_near;
+    cnt += __popc(m1) + __popc(m2);
+    // ---- hits: merged one lane at a time into the ray's record (few per round) ------------
+    unsigned cm = __ballot_sync(FULL, cand);
+    while (cm) {
+      const int j = __ffs(cm) - 1;
+      cm &= cm - 1;
+      if (lane == j) {
+        const float best = rt[CR_BEST * COOP_SLOTS + slot];
+        if (!(ct > best) && !(ct < ctol)) {
+          bool take = true;
+          const int hleaf = rti[CR_LEAF * COOP_SLOTS + slot];
+          if (ct == rt[CR_T * COOP_SLOTS + slot] && hleaf >= 0)
+            take = leaf_visit_rank(nodes, parent_leaf, cleaf) >
+                   leaf_visit_rank(nodes, parent_leaf, hleaf);
+          if (take) {
+            rt[CR_T * COOP_SLOTS + slot] = ct; rti[CR_LEAF * COOP_SLOTS + slot] = cleaf;
+            rt[CR_B1 * COOP_SLOTS + slot] = cb1; rt[CR_B2 * COOP_SLOTS + slot] = cb2;
+            rt[CR_B3 * COOP_SLOTS + slot] = cb3; rti[CR_PRIM * COOP_SLOTS + slot] = cprim;
+            rt[CR_BEST * COOP_SLOTS + slot] = ct;
+          }
+        }
+      }
+      __syncwarp();
+    }
+    __syncwarp();
+  }
+  // ---- hand the records back ---------------------------------------------------------------
+  if (lane < nslots) {
+    TraceLane R = L;
+    R.t = rt[CR_T * COOP_SLOTS + lane]; R.leaf = rti[CR_LEAF * COOP_SLOTS + lane];
+    R.b1 = rt[CR_B1 * COOP_SLOTS + lane]; R.b2 = rt[CR_B2 * COOP_SLOTS + lane];
+    R.b3 = rt[CR_B3 * COOP_SLOTS + lane]; R.prim = rti[CR_PRIM * COOP_SLOTS + lane];
+    src.store(rti[CR_RAY * COOP_SLOTS + lane], R);
+  }
+#undef WL
+}
 // Source concept:
 //   int count() const;                       number of rays in the queue
 //   void load(int i, float4 &o, float4 &d);  ray i: {o, tmax}{unit d, -}
 //   void store(int i, const TraceLane &l);   hit record of ray i
-template <bool COUNT, class Source>
+template <bool COUNT, class Source, bool COOP = false>
 __device__ __forceinline__ void trace_persistent(const float4 *__restrict__ nodes,
                                                  const float4 *__restrict__ tris,
                                                  const int *__restrict__ parent_leaf,
                                                  Source src, int *next_ray, int *stack_smem,
-                                                 unsigned long long *counters) {
+                                                 unsigned long long *counters,
+                                                 int *coop_smem = nullptr) {
   const unsigned FULL = 0xffffffffu;
   const int lane = threadIdx.x & 31;
   const int n = src.count();
@@ -59,6 +264,7 @@ __device__ __forceinline__ void trace_persistent(const float4 *__restrict__ node
   L.ray = -1;
   unsigned vi = 0, vl = 0;
   bool exhausted = false;
+  unsigned coop_live = 0;
   while (true) {
     // ---- refill idle lanes -----------------------------------------------------------
     unsigned idle = __ballot_sync(FULL, L.ray < 0);
@@ -84,6 +290,20 @@ __device__ __forceinline__ void trace_persistent(const float4 *__restrict__ node
       }
     }
     if (__ballot_sync(FULL, L.ray >= 0) == 0) break;
+    if (COOP && exhausted) {
+      // the queue is empty and only a few long rays are left in this warp: leave the ordered
+      // walk and finish them with all 32 lanes (coop_finish, after this loop -- NOT called from
+      // inside it: a call here costs the hot loop 26 registers and 18 % of its speed)
+      coop_live = __ballot_sync(FULL, L.ray >= 0);
+      if (__popc(coop_live) <= COOP_SLOTS) {
+        // (a lane deeper than the shared-memory levels counts as too much)
+        int tot = L.ray >= 0 ? (L.sp < TP_STACK_SMEM ? 1 + L.sp : COOP_LIST) : 0;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) tot += __shfl_xor_sync(FULL, tot, d);
+        if (tot <= COOP_LIST - 128) break;  // else: very deep stacks, stay with the ordered walk
+      }
+      coop_live = 0;
+    }
     // ---- traverse until enough lanes have gone idle ------------------------------------
     // (postponing leaf tests into separate warp-wide "intersect rounds" was measured and was
     //  10-20 % SLOWER on C2 -- the extra rounds and votes cost more than the divergence they
@@ -181,8 +401,12 @@ __device__ __forceinline__ void trace_persistent(const float4 *__restrict__ node
       }
       unsigned nidle = __popc(__ballot_sync(FULL, L.ray < 0));
       if (nidle == 32 || (!exhausted && nidle >= TP_REFILL)) break;
+      if (COOP && exhausted && nidle >= 32 - COOP_SLOTS) break;
     }
   }
+  if (COOP && coop_live)
+    coop_finish<COUNT>(nodes, tris, parent_leaf, src, L, coop_live, stack,
+                       coop_smem + (threadIdx.x >> 5) * COOP_WARP_WORDS, vi, vl);
   if (COUNT) {
     atomicAdd(counters, (unsigned long long)vi);
     atomicAdd(counters + 1, (unsigned long long)vl);
