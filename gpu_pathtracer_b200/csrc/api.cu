@@ -437,6 +437,12 @@ int gpt_set_wavefront_groups(gpt_ctx *ctx, int groups) {
   return GPT_OK;
 }
 
+int gpt_set_trace_tail(gpt_ctx *ctx, int mode) {
+  if (!ctx || mode < -1 || mode > 1) return GPT_E_INVALID;
+  ctx->trace_tail = mode;
+  return GPT_OK;
+}
+
 int gpt_stats(gpt_ctx *ctx, GptStats *out) {
   if (!ctx || !out) return GPT_E_INVALID;
   *out = ctx->stats;

@@ -740,21 +740,14 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
   else
     k_pt_start<<<(n + PT_BLOCK - 1) / PT_BLOCK, PT_BLOCK, 0, st>>>(ps, p, n, d_fb);
   GPT_LAUNCH_CHECK(ctx);
-  // cooperative tail (trace_persistent.cuh): GPT_TRACE_COOP=0 switches it off
-  static int trace_coop = -1;
-  if (trace_coop < 0) {
-    const char *e = getenv("GPT_TRACE_COOP");
-    trace_coop = e ? (atoi(e) != 0) : 1;
-  }
-  const bool coop = trace_coop && mb.n < (1 << COOP_NODE_BITS);
+  const bool coop = gpt_trace_coop(ctx, mb);  // cooperative tail (trace_persistent.cuh)
   static int trace_grid = 0;
   if (!trace_grid) {
     int sms = 148, per_sm = 4;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
-    if (trace_coop)
-      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pt_trace<false, true>, TP_BLOCK, 0);
-    else
-      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pt_trace<false, false>, TP_BLOCK, 0);
+    // (the variant with the tail: 72 registers, 7 blocks per SM instead of 8 -- the grid size
+    //  is flat between 4 and 8, profiles/r01d_summary.md)
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pt_trace<false, true>, TP_BLOCK, 0);
     // GPT_TRACE_BLOCKS_PER_SM < occupancy leaves room for another group's shade / sort blocks to
     // run beside a persistent trace kernel instead of after it (experiment knob)
     const char *e = getenv("GPT_TRACE_BLOCKS_PER_SM");

@@ -431,12 +431,14 @@ struct PhotonRaySource {
   }
 };
 
-template <bool COUNT>
+template <bool COUNT, bool COOP>
 __global__ void __launch_bounds__(TP_BLOCK, TP_MINBLOCKS)
 k_ph_trace(PhotonRaySource src, const float4 *__restrict__ nodes, const float4 *__restrict__ tris,
            const int *__restrict__ parent_leaf, int *next_ray, unsigned long long *counters) {
   __shared__ int stack[TP_STACK_SMEM * TP_BLOCK];
-  trace_persistent<COUNT>(nodes, tris, parent_leaf, src, next_ray, stack, counters);
+  __shared__ int coop[COOP ? (TP_BLOCK / 32) * COOP_WARP_WORDS : 1];
+  trace_persistent<COUNT, PhotonRaySource, COOP>(nodes, tris, parent_leaf, src, next_ray, stack,
+                                                 counters, coop);
 }
 
 enum { PH_NEW = 0, PH_MEDIUM = 1, PH_SURFACE = 2, PH_INIT = 3 };  // where a photon resumes
@@ -1552,7 +1554,7 @@ static int photon_stage(gpt_ctx *ctx, SppmCtx *sx, const SppmScene &S, const Pho
   if (!trace_grid) {
     int sms = 148, per_sm = 4;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ph_trace<false>, TP_BLOCK, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ph_trace<false, true>, TP_BLOCK, 0);
     trace_grid = sms * (per_sm > 0 ? per_sm : 1);
   }
   static int step_grid[2] = {0, 0};
@@ -1584,12 +1586,11 @@ static int photon_stage(gpt_ctx *ctx, SppmCtx *sx, const SppmScene &S, const Pho
     PhotonRaySource src{queue, qcount, W.rays, W.hits, ctx->scene.shade, W.key + offset, W.val + offset};
     int grid = (n + TP_BLOCK - 1) / TP_BLOCK;
     if (grid > trace_grid) grid = trace_grid;
-    if (count_visits)
-      k_ph_trace<true><<<grid, TP_BLOCK, 0, st>>>(src, tree.nodes, tree.tris, tree.parent_leaf, cursor,
-                                                 ctx->d_counters);
-    else
-      k_ph_trace<false><<<grid, TP_BLOCK, 0, st>>>(src, tree.nodes, tree.tris, tree.parent_leaf, cursor,
-                                                  ctx->d_counters);
+    const bool coop = gpt_trace_coop(ctx, tree);
+    auto kern = count_visits ? (coop ? k_ph_trace<true, true> : k_ph_trace<true, false>)
+                             : (coop ? k_ph_trace<false, true> : k_ph_trace<false, false>);
+    kern<<<grid, TP_BLOCK, 0, st>>>(src, tree.nodes, tree.tris, tree.parent_leaf, cursor,
+                                    ctx->d_counters);
     GPT_LAUNCH_CHECK(ctx);
     return GPT_OK;
   };

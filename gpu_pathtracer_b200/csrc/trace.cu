@@ -1,9 +1,11 @@
 // trace.cu -- stand-alone closest-hit kernel over a ray queue (gpt_trace*).
 //
-// One thread per ray, 128-thread CTAs, traversal stack in shared memory laid out
+// Persistent warps with ray refill and a cooperative tail (trace_persistent.cuh), 128-thread CTAs, traversal stack in shared memory laid out
 // [level][thread] (bank-conflict free), nodes / triangles fetched as 16-byte words through
 // the read-only path.  Rays: 2 x float4 {ox,oy,oz,tmax}{dx,dy,dz,-}; hits: 2 x float4
 // {t, leaf, prim, -}{b1, b2, b3, -}.
+#include <cstdlib>
+
 #include "trace_persistent.cuh"
 
 namespace {
@@ -28,13 +30,15 @@ struct ArraySource {
   }
 };
 
-template <bool NORMALIZE, bool COUNT>
+template <bool NORMALIZE, bool COUNT, bool COOP>
 __global__ void __launch_bounds__(TP_BLOCK, TP_MINBLOCKS)
 k_trace(const float4 *__restrict__ nodes, const float4 *__restrict__ tris,
         const int *__restrict__ parent_leaf, ArraySource<NORMALIZE> src, int *next_ray,
         unsigned long long *counters) {
   __shared__ int stack[TP_STACK_SMEM * TP_BLOCK];
-  trace_persistent<COUNT>(nodes, tris, parent_leaf, src, next_ray, stack, counters);
+  __shared__ int coop[COOP ? (TP_BLOCK / 32) * COOP_WARP_WORDS : 1];
+  trace_persistent<COUNT, ArraySource<NORMALIZE>, COOP>(nodes, tris, parent_leaf, src, next_ray,
+                                                        stack, counters, coop);
 }
 
 template <class K>
@@ -48,6 +52,19 @@ int persistent_grid(K kernel) {
 
 }  // namespace
 
+// Whether the persistent trace kernels finish their last rays cooperatively
+// (trace_persistent.cuh): on unless gpt_set_trace_tail / GPT_TRACE_COOP=0 says otherwise, and
+// only while a node index fits the work-list entry.
+bool gpt_trace_coop(const gpt_ctx *ctx, const BvhDev &b) {
+  static int env = -1;
+  if (env < 0) {
+    const char *e = getenv("GPT_TRACE_COOP");
+    env = e ? (atoi(e) != 0) : 1;
+  }
+  int on = ctx->trace_tail >= 0 ? ctx->trace_tail : env;
+  return on && b.n < (1 << COOP_NODE_BITS);
+}
+
 int gpt_trace_launch(gpt_ctx *ctx, int which, const float4 *d_rays, int64_t n, float4 *d_hits,
                      bool normalize, bool count) {
   if (which < 0 || which > 2) return gpt_fail(ctx, GPT_E_INVALID, "bad BVH id", __FILE__, __LINE__);
@@ -60,16 +77,22 @@ int gpt_trace_launch(gpt_ctx *ctx, int which, const float4 *d_rays, int64_t n, f
   if (count) GPT_CUDA(ctx, cudaMemsetAsync(c, 0, 3 * sizeof(unsigned long long), ctx->stream));
   GPT_CUDA(ctx, cudaMemsetAsync(next_ray, 0, sizeof(int), ctx->stream));
   cudaStream_t st = ctx->stream;
-#define GPT_TRACE_LAUNCH(NORM, CNT)                                                        \
+  const bool coop = gpt_trace_coop(ctx, b);
+#define GPT_TRACE_LAUNCH(NORM, CNT, COOP)                                                  \
   do {                                                                                     \
-    static int grid = persistent_grid(k_trace<NORM, CNT>);                                 \
+    static int grid = persistent_grid(k_trace<NORM, CNT, COOP>);                           \
     long long need = (n + TP_BLOCK - 1) / TP_BLOCK;                                        \
     ArraySource<NORM> src{d_rays, d_hits, (int)n};                                         \
-    k_trace<NORM, CNT><<<(unsigned)(need < grid ? need : grid), TP_BLOCK, 0, st>>>(        \
+    k_trace<NORM, CNT, COOP><<<(unsigned)(need < grid ? need : grid), TP_BLOCK, 0, st>>>(  \
         b.nodes, b.tris, b.parent_leaf, src, next_ray, c);                                 \
   } while (0)
-  if (normalize) { if (count) GPT_TRACE_LAUNCH(true, true); else GPT_TRACE_LAUNCH(true, false); }
-  else { if (count) GPT_TRACE_LAUNCH(false, true); else GPT_TRACE_LAUNCH(false, false); }
+#define GPT_TRACE_LAUNCH2(NORM, CNT)                                                       \
+  do {                                                                                     \
+    if (coop) GPT_TRACE_LAUNCH(NORM, CNT, true); else GPT_TRACE_LAUNCH(NORM, CNT, false);  \
+  } while (0)
+  if (normalize) { if (count) GPT_TRACE_LAUNCH2(true, true); else GPT_TRACE_LAUNCH2(true, false); }
+  else { if (count) GPT_TRACE_LAUNCH2(false, true); else GPT_TRACE_LAUNCH2(false, false); }
+#undef GPT_TRACE_LAUNCH2
 #undef GPT_TRACE_LAUNCH
   GPT_LAUNCH_CHECK(ctx);
   return GPT_OK;

@@ -316,6 +316,14 @@ int gpt_set_profiling(gpt_ctx *ctx, int time_stages, int count_visits);
  * environment variable GPT_WAVEFRONT_GROUPS overrides the automatic choice).  The image does
  * not depend on it: a pixel's samples never interact with another pixel's. */
 int gpt_set_wavefront_groups(gpt_ctx *ctx, int groups);
+/* How the persistent trace kernels end a launch.  1: once the ray queue is empty and a warp is
+ * down to <= 16 live rays, the warp finishes them cooperatively -- their pending nodes go into
+ * one shared work list that all 32 lanes pop from -- instead of walking them one lane each
+ * (the chain of dependent node steps of the slowest ray is what a launch's tail, and with it
+ * strong scaling, is made of).  0: every ray stays on its lane.  -1 (default): on, unless the
+ * environment variable GPT_TRACE_COOP=0.  Hits are bit-identical either way: closest hit with
+ * the reference's visit-rank tie-break does not depend on the order nodes are visited in. */
+int gpt_set_trace_tail(gpt_ctx *ctx, int mode);
 int gpt_stats(gpt_ctx *ctx, GptStats *out);
 int gpt_synchronize(gpt_ctx *ctx);
 

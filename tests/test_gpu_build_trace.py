@@ -88,6 +88,54 @@ def test_trace_tmax_and_empty(pair):
     assert pt.trace(np.zeros((0, 8), np.float32))["t"].shape == (0,)
 
 
+def _doubled(sc):
+    """Every triangle twice (same vertices): each hit is an equal-t tie that only the
+    reference's visit rank decides."""
+    import copy
+    d = copy.deepcopy(sc)
+    m = d.mesh
+    for k in ("point_1_idx", "point_2_idx", "point_3_idx", "norm_1_idx", "norm_2_idx",
+              "norm_3_idx", "tex_1_idx", "tex_2_idx", "tex_3_idx", "material_idx"):
+        m[k] = np.concatenate([m[k], m[k]])
+    n2 = m["point_1_idx"].shape[0]
+    m["triangle_object_idx"] = np.zeros(n2, np.int32)
+    m["object_num_primitives"] = np.array([n2], np.int32)
+    m["object_primitive_offset_idx"] = np.array([0], np.int32)
+    return d
+
+
+@pytest.mark.parametrize("scene_kind", ["small", "doubled", "C1"])
+def test_trace_tail_modes_agree(scene_kind):
+    """The cooperative tail of the persistent trace (gpt_set_trace_tail) visits nodes in another
+    order than the per-lane walk; hits must be bit-identical, ties included, and equal to the
+    reference replay where that is affordable."""
+    from gpu_pathtracer_b200.api import PathTracer
+    sc = S.make_scene("C1") if scene_kind == "C1" else S.make_scene("small", n=40, textured=True)
+    if scene_kind == "doubled":
+        sc = _doubled(sc)
+    pt = PathTracer(sc)
+    pt.build()
+    # few rays per warp at the end of the queue AND long incoherent walks: 3 batch sizes
+    sets = [rays.random_rays(50000), rays.edge_case_rays(sc, 8192), rays.camera_rays(sc)[::3].copy(),
+            rays.random_rays(37)]
+    out = {}
+    for mode in (0, 1):
+        pt.set_trace_tail(mode)
+        trees = (cabi.GPT_BVH_MAIN,) if scene_kind == "C1" else (cabi.GPT_BVH_MAIN, cabi.GPT_BVH_TRANSPARENT)
+        out[mode] = [pt.trace(r, w) for r in sets for w in trees]
+    pt.set_trace_tail(-1)
+    for a, b in zip(out[0], out[1]):
+        for k in ("leaf_id", "tri_id", "t", "bary"):
+            _eq(a[k], b[k], f"{scene_kind} {k}")
+    assert any((a["tri_id"] >= 0).any() for a in out[1])
+    if scene_kind == "doubled":
+        from tests.refreplay import RefReplay
+        ref = RefReplay(sc)
+        want = ref.trace(sets[0], cabi.GPT_BVH_MAIN)
+        _eq(out[1][0]["leaf_id"], want["leaf_id"], "doubled vs replay leaf_id")
+        _eq(out[1][0]["t"], want["t"], "doubled vs replay t")
+
+
 def test_against_committed_golden_vectors():
     """Same checks against tests/golden/small_scene.npz (made from the reference's own
     headers by tests/golden/make_golden.py): needs no reference code at run time."""
