@@ -109,6 +109,7 @@ struct gpt_ctx {
   uint64_t launches = 0;                     // kernels launched since last reset
   bool prof_time_stages = false, prof_count_visits = false;
   int wavefront_groups = 0;  // 0 = automatic (render.cu)
+  int pipeline = -1;         // path tracer: 0 = rounds of launches, 1 = streaming (two persistent kernels), -1 = default (env GPT_PIPELINE, else by frame size)
   int trace_tail = -1;       // cooperative tail of the persistent trace: -1 = default (on, env GPT_TRACE_COOP), 0 off, 1 on
 };
 
@@ -221,4 +222,5 @@ int gpt_radix_sort_pairs(gpt_ctx *ctx, uint32_t *keys, int *vals, uint32_t *keys
                          uint32_t **keys_out, int **vals_out,
                          const int *d_n = nullptr);  // d_n: exact count on the device (n = bound)
 int gpt_radix_hist_entries(int n);
+int gpt_radix_sort_set_carveout(int percent);
 bool gpt_trace_coop(const gpt_ctx *ctx, const BvhDev &b);  // trace.cu

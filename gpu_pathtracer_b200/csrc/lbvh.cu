@@ -19,6 +19,11 @@ namespace {
 constexpr int SORT_THREADS = 256;
 constexpr int SORT_ITEMS = 16;                         // keys per thread
 constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;   // 4096 keys per block
+// Short inputs (the path tracer's per-group queues on a tile-sharded frame, 10^4..10^5 slots)
+// are latency: with 4096-key tiles 65 536 keys are 16 blocks whose threads walk 16 keys each,
+// 10 + 12 us for histogram + scatter.  Up to SORT_SMALL_N keys the tile is 1024 keys.
+constexpr int SORT_ITEMS_SMALL = 4;
+constexpr int SORT_SMALL_N = 1 << 18;
 constexpr int SORT_WARPS = SORT_THREADS / 32;
 
 // ---- world box ---------------------------------------------------------------------
@@ -105,6 +110,7 @@ k_morton(const float *__restrict__ aabb, const int *__restrict__ prim_list, int 
 // ---- stable LSD radix sort -------------------------------------------------------------
 // Pass = k_sort_hist (per-block digit counts, digit-major) -> k_sort_scan (exclusive scan)
 //        -> k_sort_scatter (stable ranks via __match_any_sync + per-warp running counters).
+template <int ITEMS>
 __global__ void __launch_bounds__(SORT_THREADS)
 k_sort_hist(const uint32_t *__restrict__ keys, int n, int shift, uint32_t mask,
             uint32_t *__restrict__ block_hist, int nblocks, const int *__restrict__ d_n) {
@@ -112,9 +118,9 @@ k_sort_hist(const uint32_t *__restrict__ keys, int n, int shift, uint32_t mask,
   if (d_n) n = min(n, __ldg(d_n));  // n is only an upper bound: the exact count is on the device
   h[threadIdx.x] = 0;
   __syncthreads();
-  int base = blockIdx.x * SORT_TILE;
+  int base = blockIdx.x * (SORT_THREADS * ITEMS);
 #pragma unroll
-  for (int k = 0; k < SORT_ITEMS; k++) {
+  for (int k = 0; k < ITEMS; k++) {
     int i = base + k * SORT_THREADS + threadIdx.x;
     if (i < n) atomicAdd(&h[(__ldg(keys + i) >> shift) & mask], 1u);
   }
@@ -171,6 +177,7 @@ __global__ void __launch_bounds__(1024) k_sort_scan(uint32_t *data, int m) {
   }
 }
 
+template <int ITEMS>
 __global__ void __launch_bounds__(SORT_THREADS)
 k_sort_scatter(const uint32_t *__restrict__ keys, const int *__restrict__ vals, int n,
                int shift, uint32_t mask, const uint32_t *__restrict__ block_hist, int nblocks,
@@ -182,12 +189,12 @@ k_sort_scatter(const uint32_t *__restrict__ keys, const int *__restrict__ vals, 
   for (int d = threadIdx.x; d < SORT_WARPS * 256; d += SORT_THREADS) (&cnt[0][0])[d] = 0;
   __syncthreads();
   // each warp owns a contiguous chunk of the tile, read 32 keys at a time in order
-  int wbase = blockIdx.x * SORT_TILE + w * (32 * SORT_ITEMS);
-  uint32_t key[SORT_ITEMS];
-  uint16_t rank[SORT_ITEMS];
+  int wbase = blockIdx.x * (SORT_THREADS * ITEMS) + w * (32 * ITEMS);
+  uint32_t key[ITEMS];
+  uint16_t rank[ITEMS];
   uint32_t lt = (1u << l) - 1u;
 #pragma unroll
-  for (int k = 0; k < SORT_ITEMS; k++) {
+  for (int k = 0; k < ITEMS; k++) {
     int i = wbase + k * 32 + l;
     bool ok = i < n;
     key[k] = ok ? __ldg(keys + i) : 0xffffffffu;
@@ -213,7 +220,7 @@ k_sort_scatter(const uint32_t *__restrict__ keys, const int *__restrict__ vals, 
   }
   __syncthreads();
 #pragma unroll
-  for (int k = 0; k < SORT_ITEMS; k++) {
+  for (int k = 0; k < ITEMS; k++) {
     int i = wbase + k * 32 + l;
     if (i < n) {
       uint32_t d = (key[k] >> shift) & mask;
@@ -363,28 +370,50 @@ k_export(const float4 *__restrict__ nodes, const int *__restrict__ parent_leaf,
 
 }  // namespace
 
+// All three sort kernels ask for this L1 / shared-memory split (percent of the maximum shared
+// memory); render.cu gives every kernel of its rounds the same one, so that blocks of different
+// wavefront groups can share an SM (the split of an SM only changes while the SM is empty).
+int gpt_radix_sort_set_carveout(int percent) {
+  cudaError_t e = cudaFuncSetAttribute(k_sort_hist<SORT_ITEMS>, cudaFuncAttributePreferredSharedMemoryCarveout, percent);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_sort_hist<SORT_ITEMS_SMALL>, cudaFuncAttributePreferredSharedMemoryCarveout, percent);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_sort_scan, cudaFuncAttributePreferredSharedMemoryCarveout, percent);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_sort_scatter<SORT_ITEMS>, cudaFuncAttributePreferredSharedMemoryCarveout, percent);
+  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_sort_scatter<SORT_ITEMS_SMALL>, cudaFuncAttributePreferredSharedMemoryCarveout, percent);
+  return e == cudaSuccess ? GPT_OK : GPT_E_CUDA;
+}
+
+static int sort_tile_of(int n) { return SORT_THREADS * (n <= SORT_SMALL_N ? SORT_ITEMS_SMALL : SORT_ITEMS); }
+
+// counters a sort of up to n keys needs -- and of ANY shorter input (the path tracer sorts its
+// shrinking queues with the buffer of the first round), whichever tile that one uses
 int gpt_radix_hist_entries(int n) {
-  int nblocks = (n + SORT_TILE - 1) / SORT_TILE;
+  int small_n = n < SORT_SMALL_N ? n : SORT_SMALL_N;
+  int a = (small_n + SORT_THREADS * SORT_ITEMS_SMALL - 1) / (SORT_THREADS * SORT_ITEMS_SMALL);
+  int b = (n + SORT_TILE - 1) / SORT_TILE;
+  int nblocks = a > b ? a : b;
   return 256 * (nblocks > 0 ? nblocks : 1);
 }
 
 int gpt_radix_sort_pairs(gpt_ctx *ctx, uint32_t *keys, int *vals, uint32_t *keys_alt,
                          int *vals_alt, uint32_t *block_hist, int n, int nbits,
                          uint32_t **keys_out, int **vals_out, const int *d_n) {
-  int nblocks = (n + SORT_TILE - 1) / SORT_TILE;
+  const int tile = sort_tile_of(n);
+  const bool small = tile != SORT_TILE;
+  int nblocks = (n + tile - 1) / tile;
   if (nblocks < 1) nblocks = 1;
   uint32_t *ka = keys, *kb = keys_alt;
   int *va = vals, *vb = vals_alt;
   for (int shift = 0; shift < nbits; shift += 8) {
     int bits = nbits - shift < 8 ? nbits - shift : 8;
     uint32_t mask = (1u << bits) - 1u;
-    k_sort_hist<<<nblocks, SORT_THREADS, 0, ctx->stream>>>(ka, n, shift, mask, block_hist, nblocks, d_n);
+    if (small) k_sort_hist<SORT_ITEMS_SMALL><<<nblocks, SORT_THREADS, 0, ctx->stream>>>(ka, n, shift, mask, block_hist, nblocks, d_n);
+    else k_sort_hist<SORT_ITEMS><<<nblocks, SORT_THREADS, 0, ctx->stream>>>(ka, n, shift, mask, block_hist, nblocks, d_n);
     GPT_LAUNCH_CHECK(ctx);
     // digit-major layout: only the digits this pass can produce need scanning
     k_sort_scan<<<1, 1024, 0, ctx->stream>>>(block_hist, (int)(mask + 1) * nblocks);
     GPT_LAUNCH_CHECK(ctx);
-    k_sort_scatter<<<nblocks, SORT_THREADS, 0, ctx->stream>>>(ka, va, n, shift, mask, block_hist,
-                                                             nblocks, kb, vb, d_n);
+    if (small) k_sort_scatter<SORT_ITEMS_SMALL><<<nblocks, SORT_THREADS, 0, ctx->stream>>>(ka, va, n, shift, mask, block_hist, nblocks, kb, vb, d_n);
+    else k_sort_scatter<SORT_ITEMS><<<nblocks, SORT_THREADS, 0, ctx->stream>>>(ka, va, n, shift, mask, block_hist, nblocks, kb, vb, d_n);
     GPT_LAUNCH_CHECK(ctx);
     uint32_t *tk = ka; ka = kb; kb = tk;
     int *tv = va; va = vb; vb = tv;

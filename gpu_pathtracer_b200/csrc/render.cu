@@ -8,6 +8,8 @@
 //   k_pt_shade  material decision, light sampling + MIS, throughput update, next ray or next
 //               sample (ray-gen is folded into shade), warp-aggregated queue compaction
 #include <cmath>
+#include <cstdio>
+#include <cstring>
 #include <vector>
 
 #include "integrator.cuh"
@@ -16,6 +18,13 @@
 namespace {
 
 constexpr int PT_BLOCK = 128;
+#ifndef GPT_ROUNDS_CARVEOUT_KB_DEFAULT
+#define GPT_ROUNDS_CARVEOUT_KB_DEFAULT 0
+#endif
+// frames of at most this many slots per rank use the streaming pipeline by default
+#ifndef GPT_STREAM_AUTO_MAX_SLOTS
+#define GPT_STREAM_AUTO_MAX_SLOTS 0
+#endif
 
 struct RenderCtx {
   PathState ps{};
@@ -38,6 +47,8 @@ struct RenderCtx {
   int hist_stride = 0;
   uint32_t *sort_key = nullptr, *sort_key_alt = nullptr, *sort_hist = nullptr;
   int *sort_val = nullptr, *sort_val_alt = nullptr;
+  int *sq_cells = nullptr, *sq_ctl = nullptr;  // streaming pipeline: 9 rings + control words
+  int sq_capacity = 0;                         // cells per ring
   float *d_fb = nullptr;          // internal framebuffer for the host API
   size_t fb_capacity = 0;
   std::vector<cudaEvent_t> events;  // profiling only
@@ -144,7 +155,7 @@ __device__ __forceinline__ V3 sky_color(const RenderParams &p, V3 dir) {
   return p.sky * V3{__ldg(p.bg_r + idx), __ldg(p.bg_g + idx), __ldg(p.bg_b + idx)};
 }
 
-__device__ __forceinline__ void start_sample(PathState &ps, int slot, V3 o, V3 d) {
+__device__ __forceinline__ void start_sample(const PathState &ps, int slot, V3 o, V3 d) {
   ps.rays[2 * (size_t)slot] = make_float4(o.x, o.y, o.z, INFINITY);
   ps.rays[2 * (size_t)slot + 1] = make_float4(d.x, d.y, d.z, 0.f);
   MatList l;
@@ -401,6 +412,147 @@ k_pt_trace(QueueSource src, const float4 *__restrict__ nodes, const float4 *__re
                                              counters, coop);
 }
 
+// One path vertex: the slot's hit is shaded and the slot either gets its next ray (returns
+// true: it goes back to the trace stage) or its pixel is finished (false).  ASYNC = the
+// streaming pipeline: a slot's state is written by whichever SM had it last while THIS kernel
+// runs, so it is read around the (incoherent) L1.
+#define PS_LD(ptr) (ASYNC ? __ldcg(ptr) : *(ptr))
+template <bool ASYNC>
+__device__ __forceinline__ bool shade_slot(const PathState &ps, const RenderParams &p, int s,
+                                           const SceneDev &sc, const TexAtlas &atlas,
+                                           const float4 *__restrict__ main_tris,
+                                           const LightTree &lt, float *fb, int *error_flag) {
+  bool alive = true;
+  float4 rdv = PS_LD(ps.rays + 2 * (size_t)s + 1);
+  float4 h0 = PS_LD(ps.hits + 2 * (size_t)s), h1 = PS_LD(ps.hits + 2 * (size_t)s + 1);
+  float4 mk = PS_LD(ps.ma + 2 * (size_t)s), ac = PS_LD(ps.ma + 2 * (size_t)s + 1);
+  V3 dir = V3{rdv.x, rdv.y, rdv.z};
+  V3 mask = V3{mk.x, mk.y, mk.z}, acc = V3{ac.x, ac.y, ac.z};
+  int bounce = __float_as_int(mk.w), sidx = __float_as_int(ac.w);
+  int leaf = __float_as_int(h0.y);
+  Rng rng;
+  rng_load_packed<ASYNC>(rng, ps.rng, s);
+  bool done = false;
+  V3 result = V3{0.f, 0.f, 0.f};
+  if (leaf >= 0) {
+    int prim = __float_as_int(h0.z);
+    float b1 = h1.x, b2 = h1.y, b3 = h1.z;
+    const float4 *tp = main_tris + 3 * (size_t)leaf;
+    float4 t0 = __ldg(tp), t1 = __ldg(tp + 1), t2 = __ldg(tp + 2);
+    TriShade ts = load_tri_shade(sc.shade, prim);
+    const MaterialDev &m = sc.mats[ts.mat];
+    // hit_record (triangle.h:399-405)
+    V3 point = b1 * V3{t0.x, t0.y, t0.z} + b2 * V3{t0.w, t1.x, t1.y} + b3 * V3{t1.z, t1.w, t2.x};
+    float u = b1 * ts.u1 + b2 * ts.u2 + b3 * ts.u3;
+    float v = b1 * ts.v1 + b2 * ts.v2 + b3 * ts.v3;
+    V3 normal = shading_normal(ts, m, atlas, b1, b2, b3);
+    MatList list;
+    matlist_unpack(list, PS_LD(reinterpret_cast<const uint4 *>(ps.cm + 2 * (size_t)s + 1)));
+    RefRec ref;
+    ref.reflected = false; ref.refracted = false; ref.diffuse = false;
+    ref.n = 1.f; ref.k = V3{0.f, 0.f, 0.f}; ref.perfect = V3{1.f, 0.f, 0.f}; ref.bent = false;
+    bool sss = false;
+    check_next_path<false>(sc.mats, atlas, ts.mat, dir, normal, u, v, list, ref, sss, rng, false);
+    float factor = 1.f;
+    const bool sss_hit = sss && p.use_sss;  // `sss && !sss_first_pass` (pathtracing.h:129-142)
+    if (!ref.false_hit && !sss_hit)
+      factor = change_ref_ray(lt, sc.shade, sc.mats, atlas, point, normal, dir, ref,
+                              p.pdf_weight, rng);
+    if (sss_hit) {  // return compute_color_sss(...): the sample IS the point-cloud estimate
+      bool found;
+      V3 col = sss_lookup(BitmapPool{p.sss.bm_pool, p.sss.bm_busy, p.sss.bm_n, p.sss.bm_words},
+                          p.sss.trees[ts.obj], point, m.path_length, found);
+      result = found ? col * mat_diffuse(atlas, m, u, v) : V3{0.f, 0.f, 0.f};
+      done = true;
+    }
+    // material list bookkeeping (pathtracing.h:144-162)
+    bool ok = true;
+    if ((ref.false_hit || ref.refracted) && ref.entering) ok = matlist_add(list, ts.mat);
+    else if ((ref.false_hit || ref.refracted) && !ref.entering) matlist_remove(list, ts.mat);
+    if (!ok && !sss_hit) *error_flag = 1;
+    matlist_store(reinterpret_cast<uint4 *>(ps.cm + 2 * (size_t)s + 1), list);
+    if (!ref.false_hit && !sss_hit) {
+      V3 add = de_nan(mask * mat_emission(atlas, m, u, v));
+      acc = acc + add;
+      if (factor > 0.f) {
+        mask = mask * (ref.filter * clamp_lohi(0.f, .9999f, factor));
+      } else {
+        done = true;
+        result = acc;
+      }
+    }
+    if (!done) {
+      bounce++;
+      if (bounce >= p.level) {
+        done = true;
+        result = acc;
+      } else {
+        ps.rays[2 * (size_t)s] = make_float4(point.x, point.y, point.z, INFINITY);
+        ps.rays[2 * (size_t)s + 1] = make_float4(ref.dir.x, ref.dir.y, ref.dir.z, 0.f);
+        ps.ma[2 * (size_t)s] = make_float4(mask.x, mask.y, mask.z, __int_as_float(bounce));
+        ps.ma[2 * (size_t)s + 1] = make_float4(acc.x, acc.y, acc.z, __int_as_float(sidx));
+      }
+    }
+  } else {
+    V3 sky = sky_color(p, dir);
+    result = bounce < 1 ? sky : acc + mask * sky;
+    done = true;
+  }
+  if (done) {
+    float4 cl = PS_LD(ps.cm + 2 * (size_t)s);
+    V3 color = V3{cl.x, cl.y, cl.z} + de_nan(result);
+    int k = __float_as_int(cl.w);
+    sidx++;
+    V3 o, d;
+    bool finished = false;
+    if (p.mode == 1) {
+      // do_sss_first_pass: every sample draws a fresh cosine-hemisphere ray at the point
+      if (sidx >= p.sample_size) {
+        finished = true;
+      } else {
+        float4 co = PS_LD(ps.cam + 2 * (size_t)s), cn = PS_LD(ps.cam + 2 * (size_t)s + 1);
+        o = V3{co.x, co.y, co.z};
+        d = generate_dir(V3{0.f, 0.f, 0.f}, V3{cn.x, cn.y, cn.z}, 0, 1.f, rng);
+      }
+    } else if (sidx >= p.sample_size) {
+      sidx = 0;
+      k++;
+      if (k >= p.dof_size) {
+        finished = true;
+      } else {
+        int pix = ps.pixel[s];
+        camera_ray(p.cam, pix / p.cam.width + .5f, pix % p.cam.width + .5f, rng, o, d);
+        ps.cam[2 * (size_t)s] = make_float4(o.x, o.y, o.z, 0.f);
+        ps.cam[2 * (size_t)s + 1] = make_float4(d.x, d.y, d.z, 0.f);
+      }
+    } else {
+      float4 co = PS_LD(ps.cam + 2 * (size_t)s), cd = PS_LD(ps.cam + 2 * (size_t)s + 1);
+      o = V3{co.x, co.y, co.z};
+      d = V3{cd.x, cd.y, cd.z};
+    }
+    if (finished && p.mode == 1) {
+      // color *= (1.0 / sample_size); color *= filter; point -> assign_color(color)
+      float4 pa = __ldg(p.sss.pts + 3 * (size_t)s), pb = __ldg(p.sss.pts + 3 * (size_t)s + 1);
+      V3 out = (color * p.inv_samples) * V3{pa.w, pb.x, pb.y};
+      p.sss.leaf[2 * (size_t)s + 1] = make_float4(out.x, out.y, out.z, 0.f);
+      alive = false;
+    } else if (finished) {
+      int pix = ps.pixel[s];
+      V3 out = color * p.inv_samples;
+      fb[3 * (size_t)pix] = out.x; fb[3 * (size_t)pix + 1] = out.y; fb[3 * (size_t)pix + 2] = out.z;
+      alive = false;
+    } else {
+      ps.cm[2 * (size_t)s] = make_float4(color.x, color.y, color.z, __int_as_float(k));
+      ps.ma[2 * (size_t)s] = make_float4(1.f, 1.f, 1.f, __int_as_float(0));
+      ps.ma[2 * (size_t)s + 1] = make_float4(0.f, 0.f, 0.f, __int_as_float(sidx));
+      start_sample(ps, s, o, d);
+    }
+  }
+  rng_store_packed(rng, ps.rng, s);
+  return alive;
+}
+#undef PS_LD
+
 __global__ void __launch_bounds__(PT_BLOCK)
 k_pt_shade(PathState ps, RenderParams p, const int *__restrict__ queue,
            const int *__restrict__ count, int *next_queue, int *next_count, SceneDev sc,
@@ -418,133 +570,7 @@ k_pt_shade(PathState ps, RenderParams p, const int *__restrict__ queue,
   int s = -1;
   if (a < *count) {
     s = queue[a];
-    alive = true;
-    float4 ro = ps.rays[2 * (size_t)s], rdv = ps.rays[2 * (size_t)s + 1];
-    float4 h0 = ps.hits[2 * (size_t)s], h1 = ps.hits[2 * (size_t)s + 1];
-    float4 mk = ps.ma[2 * (size_t)s], ac = ps.ma[2 * (size_t)s + 1];
-    V3 dir = V3{rdv.x, rdv.y, rdv.z};
-    V3 mask = V3{mk.x, mk.y, mk.z}, acc = V3{ac.x, ac.y, ac.z};
-    int bounce = __float_as_int(mk.w), sidx = __float_as_int(ac.w);
-    int leaf = __float_as_int(h0.y);
-    Rng rng;
-    rng_load_packed(rng, ps.rng, s);
-    bool done = false;
-    V3 result = V3{0.f, 0.f, 0.f};
-    if (leaf >= 0) {
-      int prim = __float_as_int(h0.z);
-      float b1 = h1.x, b2 = h1.y, b3 = h1.z;
-      const float4 *tp = main_tris + 3 * (size_t)leaf;
-      float4 t0 = __ldg(tp), t1 = __ldg(tp + 1), t2 = __ldg(tp + 2);
-      TriShade ts = load_tri_shade(sc.shade, prim);
-      const MaterialDev &m = sc.mats[ts.mat];
-      // hit_record (triangle.h:399-405)
-      V3 point = b1 * V3{t0.x, t0.y, t0.z} + b2 * V3{t0.w, t1.x, t1.y} + b3 * V3{t1.z, t1.w, t2.x};
-      float u = b1 * ts.u1 + b2 * ts.u2 + b3 * ts.u3;
-      float v = b1 * ts.v1 + b2 * ts.v2 + b3 * ts.v3;
-      V3 normal = shading_normal(ts, m, atlas, b1, b2, b3);
-      MatList list;
-      matlist_load(list, reinterpret_cast<const uint4 *>(ps.cm + 2 * (size_t)s + 1));
-      RefRec ref;
-      ref.reflected = false; ref.refracted = false; ref.diffuse = false;
-      ref.n = 1.f; ref.k = V3{0.f, 0.f, 0.f}; ref.perfect = V3{1.f, 0.f, 0.f}; ref.bent = false;
-      bool sss = false;
-      check_next_path<false>(sc.mats, atlas, ts.mat, dir, normal, u, v, list, ref, sss, rng, false);
-      float factor = 1.f;
-      const bool sss_hit = sss && p.use_sss;  // `sss && !sss_first_pass` (pathtracing.h:129-142)
-      if (!ref.false_hit && !sss_hit)
-        factor = change_ref_ray(lt, sc.shade, sc.mats, atlas, point, normal, dir, ref,
-                                p.pdf_weight, rng);
-      if (sss_hit) {  // return compute_color_sss(...): the sample IS the point-cloud estimate
-        bool found;
-        V3 col = sss_lookup(BitmapPool{p.sss.bm_pool, p.sss.bm_busy, p.sss.bm_n, p.sss.bm_words},
-                            p.sss.trees[ts.obj], point, m.path_length, found);
-        result = found ? col * mat_diffuse(atlas, m, u, v) : V3{0.f, 0.f, 0.f};
-        done = true;
-      }
-      // material list bookkeeping (pathtracing.h:144-162)
-      bool ok = true;
-      if ((ref.false_hit || ref.refracted) && ref.entering) ok = matlist_add(list, ts.mat);
-      else if ((ref.false_hit || ref.refracted) && !ref.entering) matlist_remove(list, ts.mat);
-      if (!ok && !sss_hit) *error_flag = 1;
-      matlist_store(reinterpret_cast<uint4 *>(ps.cm + 2 * (size_t)s + 1), list);
-      if (!ref.false_hit && !sss_hit) {
-        V3 add = de_nan(mask * mat_emission(atlas, m, u, v));
-        acc = acc + add;
-        if (factor > 0.f) {
-          mask = mask * (ref.filter * clamp_lohi(0.f, .9999f, factor));
-        } else {
-          done = true;
-          result = acc;
-        }
-      }
-      if (!done) {
-        bounce++;
-        if (bounce >= p.level) {
-          done = true;
-          result = acc;
-        } else {
-          ps.rays[2 * (size_t)s] = make_float4(point.x, point.y, point.z, INFINITY);
-          ps.rays[2 * (size_t)s + 1] = make_float4(ref.dir.x, ref.dir.y, ref.dir.z, 0.f);
-          ps.ma[2 * (size_t)s] = make_float4(mask.x, mask.y, mask.z, __int_as_float(bounce));
-          ps.ma[2 * (size_t)s + 1] = make_float4(acc.x, acc.y, acc.z, __int_as_float(sidx));
-        }
-      }
-    } else {
-      V3 sky = sky_color(p, dir);
-      result = bounce < 1 ? sky : acc + mask * sky;
-      done = true;
-    }
-    if (done) {
-      float4 cl = ps.cm[2 * (size_t)s];
-      V3 color = V3{cl.x, cl.y, cl.z} + de_nan(result);
-      int k = __float_as_int(cl.w);
-      sidx++;
-      V3 o, d;
-      bool finished = false;
-      if (p.mode == 1) {
-        // do_sss_first_pass: every sample draws a fresh cosine-hemisphere ray at the point
-        if (sidx >= p.sample_size) {
-          finished = true;
-        } else {
-          float4 co = ps.cam[2 * (size_t)s], cn = ps.cam[2 * (size_t)s + 1];
-          o = V3{co.x, co.y, co.z};
-          d = generate_dir(V3{0.f, 0.f, 0.f}, V3{cn.x, cn.y, cn.z}, 0, 1.f, rng);
-        }
-      } else if (sidx >= p.sample_size) {
-        sidx = 0;
-        k++;
-        if (k >= p.dof_size) {
-          finished = true;
-        } else {
-          int pix = ps.pixel[s];
-          camera_ray(p.cam, pix / p.cam.width + .5f, pix % p.cam.width + .5f, rng, o, d);
-          ps.cam[2 * (size_t)s] = make_float4(o.x, o.y, o.z, 0.f);
-          ps.cam[2 * (size_t)s + 1] = make_float4(d.x, d.y, d.z, 0.f);
-        }
-      } else {
-        float4 co = ps.cam[2 * (size_t)s], cd = ps.cam[2 * (size_t)s + 1];
-        o = V3{co.x, co.y, co.z};
-        d = V3{cd.x, cd.y, cd.z};
-      }
-      if (finished && p.mode == 1) {
-        // color *= (1.0 / sample_size); color *= filter; point -> assign_color(color)
-        float4 pa = __ldg(p.sss.pts + 3 * (size_t)s), pb = __ldg(p.sss.pts + 3 * (size_t)s + 1);
-        V3 out = (color * p.inv_samples) * V3{pa.w, pb.x, pb.y};
-        p.sss.leaf[2 * (size_t)s + 1] = make_float4(out.x, out.y, out.z, 0.f);
-        alive = false;
-      } else if (finished) {
-        int pix = ps.pixel[s];
-        V3 out = color * p.inv_samples;
-        fb[3 * (size_t)pix] = out.x; fb[3 * (size_t)pix + 1] = out.y; fb[3 * (size_t)pix + 2] = out.z;
-        alive = false;
-      } else {
-        ps.cm[2 * (size_t)s] = make_float4(color.x, color.y, color.z, __int_as_float(k));
-        ps.ma[2 * (size_t)s] = make_float4(1.f, 1.f, 1.f, __int_as_float(0));
-        ps.ma[2 * (size_t)s + 1] = make_float4(0.f, 0.f, 0.f, __int_as_float(sidx));
-        start_sample(ps, s, o, d);
-      }
-    }
-    rng_store_packed(rng, ps.rng, s);
+    alive = shade_slot<false>(ps, p, s, sc, atlas, main_tris, lt, fb, error_flag);
   }
   // warp-aggregated compaction of the surviving slots into the next queue
   unsigned ballot = __ballot_sync(0xffffffffu, alive);
@@ -556,6 +582,221 @@ k_pt_shade(PathState ps, RenderParams p, const int *__restrict__ queue,
     base = __shfl_sync(0xffffffffu, base, leader);
     if (alive) next_queue[base + __popc(ballot & ((1u << lane) - 1u))] = s;
   }
+}
+
+
+// ---- streaming pipeline (barrier-free wavefront) ------------------------------------------------
+// The iteration loop above makes a frame a chain of dof x spp x level DEPENDENT rounds of
+// launches, and each round lasts as long as its slowest ray + the latency of a sort + of one
+// shade wave, however few rays it carries: fine for a whole frame on one GPU (groups overlap the
+// rounds), but it is what bounds a tile-sharded frame (1/8 of 1080p: ~250 us a round, SMs 40 %
+// idle).  Here the two stages are two PERSISTENT kernels running side by side, and a slot moves
+// between them through rings in HBM the moment it is ready:
+//   ray ring      shade -> trace   slots whose next ray is written
+//   hit rings[8]  trace -> shade   slots whose hit record is written, one ring per material
+//                                  class (ring 7 = miss), so a shade warp pops 32 slots that run
+//                                  the same BSDF code -- the coherence sort, without the sort
+// A pixel's chain is now the sum of ITS OWN ray and shade latencies, not of every round's
+// maxima.  Pixels never interact and a pixel's samples stay sequential on its own RNG stream,
+// so the frame is bit-identical to the iteration loop's (test).
+// Ring protocol: a cell holds a slot index or -1.  Producers take a position with atomicAdd on
+// the ring's tail, make their state writes visible (__threadfence) and store the slot into
+// the cell; the consumer that owns the position spins until the cell is >= 0, empties it, and
+// reads the slot's state around L1 (ld.cg).  Ray-ring positions are handed out unconditionally
+// (a trace lane holds at most one and polls it between traversal steps); hit-ring positions
+// only below the tail (CAS), because a shade warp must not commit to a material that may
+// never come.  Rings hold >= 2 n cells for n slots, and a producer waits for its cell to be
+// empty, so a wrap-around can never overwrite a slot.
+constexpr int SQ_RINGS = 8;    // material classes (7 = miss)
+constexpr int SQ_SUB = 16;     // sub-rings per class: producers and consumers of different SMs use
+                               // different counters (ONE head per class was measured: 1184 shade
+                               // warps serialised on it, 70 Mrays/s)
+constexpr int SQ_NR = SQ_RINGS * SQ_SUB;
+enum { SQ_RAY_HEAD = 0, SQ_RAY_TAIL = 8, SQ_DONE = 16, SQ_ABORT = 24, SQ_ERR = 32,
+       SQ_RING0 = 40, SQ_WORDS = 40 + 24 * SQ_NR };
+// per hit ring r: head (next position to hand to a consumer), tail (next position to hand to a
+// producer), credits (published cells not yet promised to a consumer), one 32-byte sector each
+__device__ __forceinline__ int sq_head(int r) { return SQ_RING0 + 24 * r; }
+__device__ __forceinline__ int sq_tail(int r) { return SQ_RING0 + 24 * r + 8; }
+__device__ __forceinline__ int sq_credits(int r) { return SQ_RING0 + 24 * r + 16; }
+struct StreamQ {
+  int *ray_ring;   // cells
+  int *hit_ring;   // SQ_NR x hit_cells
+  int *ctl;        // SQ_WORDS ints
+  int mask;        // cells - 1
+  int hit_mask;    // hit_cells - 1
+  int n;           // slots = pixels to finish
+};
+__device__ __forceinline__ int ld_volatile(const int *p) { return *reinterpret_cast<const volatile int *>(p); }
+__device__ __forceinline__ void st_volatile(int *p, int v) { *reinterpret_cast<volatile int *>(p) = v; }
+// store slot s at an already reserved position of a ring (the caller fenced its state writes)
+__device__ __forceinline__ void ring_put(int *cells, int mask, int pos, int s, int *ctl) {
+  int *c = cells + (pos & mask);
+  int spins = 0;
+  while (ld_volatile(c) >= 0) {  // a full lap behind an unread cell: wait, never overwrite
+    __nanosleep(100);
+    if (++spins > (1 << 24)) { atomicExch(ctl + SQ_ABORT, 1); break; }
+  }
+  st_volatile(c, s);
+}
+
+struct StreamSource {
+  PathState ps;
+  StreamQ q;
+  const float4 *shade;
+  __device__ int reserve(int cnt) const { return atomicAdd(q.ctl + SQ_RAY_HEAD, cnt); }
+  __device__ int poll(int pos) const {
+    int *c = q.ray_ring + (pos & q.mask);
+    int v = ld_volatile(c);
+    if (v >= 0) {
+      st_volatile(c, -1);
+      __threadfence();
+    }
+    return v;
+  }
+  __device__ void load(int s, float4 &o, float4 &d) const {
+    o = __ldcg(ps.rays + 2 * (size_t)s);
+    d = __ldcg(ps.rays + 2 * (size_t)s + 1);
+  }
+  // a finished ray: the record goes out at once (fire and forget); the slot itself is handed to
+  // the shade kernel later, by the whole warp (publish), and the return value says to which ring
+  __device__ int store(int s, const TraceLane &l) const {
+    __stcg(ps.hits + 2 * (size_t)s, make_float4(l.t, __int_as_float(l.leaf), __int_as_float(l.prim), 0.f));
+    __stcg(ps.hits + 2 * (size_t)s + 1, make_float4(l.b1, l.b2, l.b3, 0.f));
+    int m = SQ_RINGS - 1;  // miss
+    if (l.leaf >= 0) m = (__float_as_int(__ldg(&shade[7 * (size_t)l.prim + 6].y)) & 127) % (SQ_RINGS - 1);
+    return m * SQ_SUB + (int)(blockIdx.x % SQ_SUB);
+  }
+  // called by all 32 lanes; lanes with slot >= 0 hand it to ring r
+  __device__ void publish(int slot, int r) const {
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    __threadfence();  // hit records before the cells
+    const unsigned has = __ballot_sync(FULL, slot >= 0);
+    if (slot >= 0) {
+      const unsigned peers = __match_any_sync(has, r);
+      const int leader = __ffs(peers) - 1, cnt = __popc(peers);
+      int base = 0;
+      if (lane == leader) base = atomicAdd(q.ctl + sq_tail(r), cnt);
+      base = __shfl_sync(peers, base, leader);
+      ring_put(q.hit_ring + (size_t)r * (q.hit_mask + 1), q.hit_mask,
+               base + __popc(peers & ((1u << lane) - 1u)), slot, q.ctl);
+      __threadfence();  // cells before the credits
+      __syncwarp(peers);
+      if (lane == leader) atomicAdd(q.ctl + sq_credits(r), cnt);
+    }
+  }
+  __device__ bool finished() const {
+    return ld_volatile(q.ctl + SQ_DONE) >= q.n || ld_volatile(q.ctl + SQ_ABORT) != 0;
+  }
+  __device__ void abort() const { atomicExch(q.ctl + SQ_ABORT, 1); }
+};
+
+__global__ void __launch_bounds__(256) k_stream_init(StreamQ q) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t cells = (size_t)q.mask + 1, hit_total = (size_t)SQ_NR * ((size_t)q.hit_mask + 1);
+  if (i < cells) q.ray_ring[i] = i < (size_t)q.n ? (int)i : -1;
+  if (i < hit_total) q.hit_ring[i] = -1;
+  if (i < SQ_WORDS) q.ctl[i] = i == SQ_RAY_TAIL ? q.n : 0;
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(TP_BLOCK, TP_MINBLOCKS)
+k_pt_trace_stream(StreamSource src, const float4 *__restrict__ nodes,
+                  const float4 *__restrict__ tris, const int *__restrict__ parent_leaf,
+                  unsigned long long *counters) {
+  __shared__ int stack[TP_STACK_SMEM * TP_BLOCK];
+  trace_stream<COUNT, StreamSource>(nodes, tris, parent_leaf, src, stack, counters);
+}
+
+__global__ void __launch_bounds__(PT_BLOCK)
+k_pt_shade_stream(PathState ps, RenderParams p, StreamQ q, SceneDev sc, TexAtlas atlas,
+                  const float4 *__restrict__ main_tris, LightTree lt, float *fb,
+                  unsigned long long *ray_counter) {
+  const unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const size_t hit_cells = (size_t)q.hit_mask + 1;
+  // the four sub-rings this warp looks at first; lanes = 4 sub-rings x 8 classes
+  int home = ((blockIdx.x * (PT_BLOCK / 32) + (threadIdx.x >> 5)) * 4) % SQ_SUB;
+  unsigned shaded = 0;
+  int misses = 0;
+  long long idle_since = 0;
+  while (true) {
+    // ---- pick a ring: a full warp's worth wins, else the longest ------------------------------
+    const int r_of_lane = (lane & 7) * SQ_SUB + (home + (lane >> 3)) % SQ_SUB;
+    const int credits = ld_volatile(q.ctl + sq_credits(r_of_lane));
+    const unsigned full = __ballot_sync(FULL, credits >= 32);
+    int src_lane;
+    if (full) {
+      src_lane = __ffs(full) - 1;
+    } else {
+      int best = credits, bl = lane;
+#pragma unroll
+      for (int d = 16; d > 0; d >>= 1) {
+        int ob = __shfl_xor_sync(FULL, best, d), ol = __shfl_xor_sync(FULL, bl, d);
+        if (ob > best || (ob == best && ol < bl)) { best = ob; bl = ol; }
+      }
+      src_lane = bl;
+    }
+    const int r = __shfl_sync(FULL, r_of_lane, src_lane);
+    int take = __shfl_sync(FULL, credits, src_lane);
+    take = take > 32 ? 32 : take;
+    int h = -1;
+    if (take > 0 && lane == 0) {
+      // semaphore try-wait: credits are cells that ARE published, so positions promised against
+      // them exist (head never passes tail); an overdraft is put back
+      if (atomicAdd(q.ctl + sq_credits(r), -take) >= take) h = atomicAdd(q.ctl + sq_head(r), take);
+      else atomicAdd(q.ctl + sq_credits(r), take);
+    }
+    h = __shfl_sync(FULL, h, 0);
+    if (h < 0) {
+      home = (home + 4) % SQ_SUB;
+      if (++misses < SQ_SUB / 4) continue;  // look at the other sub-rings first
+      misses = 0;
+      if (ld_volatile(q.ctl + SQ_DONE) >= q.n || ld_volatile(q.ctl + SQ_ABORT) != 0) break;
+      const long long now = clock64();
+      if (idle_since == 0) idle_since = now;
+      if (now - idle_since > TS_WATCHDOG_CYCLES) {
+        atomicExch(q.ctl + SQ_ABORT, 1);
+        break;
+      }
+      __nanosleep(100);
+      continue;
+    }
+    idle_since = 0;
+    misses = 0;
+    // ---- the slots at positions h .. h + take - 1 ------------------------------------------------
+    int s = -1;
+    if (lane < take) {
+      int *c = q.hit_ring + (size_t)r * hit_cells + ((h + lane) & q.hit_mask);
+      int spins = 0;
+      while ((s = ld_volatile(c)) < 0) {  // published out of order: its producer is a few instructions away
+        __nanosleep(20);
+        if (++spins > (1 << 24)) { atomicExch(q.ctl + SQ_ABORT, 1); break; }
+      }
+      if (s >= 0) st_volatile(c, -1);
+    }
+    __threadfence();
+    bool alive = false;
+    if (s >= 0) {
+      alive = shade_slot<true>(ps, p, s, sc, atlas, main_tris, lt, fb, q.ctl + SQ_ERR);
+      shaded++;
+    }
+    // ---- next ray -> ray ring; finished pixels -> the counter both kernels watch ----------------
+    __threadfence();
+    const unsigned am = __ballot_sync(FULL, alive), fm = __ballot_sync(FULL, s >= 0 && !alive);
+    if (am) {
+      const int leader = __ffs(am) - 1;
+      int base = 0;
+      if (lane == leader) base = atomicAdd(q.ctl + SQ_RAY_TAIL, __popc(am));
+      base = __shfl_sync(FULL, base, leader);
+      if (alive) ring_put(q.ray_ring, q.mask, base + __popc(am & ((1u << lane) - 1u)), s, q.ctl);
+    }
+    if (fm && lane == __ffs(fm) - 1) atomicAdd(q.ctl + SQ_DONE, __popc(fm));
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) shaded += __shfl_xor_sync(FULL, shaded, d);
+  if (lane == 0 && shaded) atomicAdd(ray_counter, (unsigned long long)shaded);
 }
 
 }  // namespace
@@ -682,6 +923,7 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
   } else if (new_map) {
     px = tile_pixels(W, H, rank, nranks);
     n = (int)px.size();
+    if (n == 0) return GPT_OK;  // more ranks than tiles: nothing to render here
     GPT_TRY(reserve_paths(ctx, rc, n));
     GPT_CUDA(ctx, cudaMemcpyAsync(rc->ps.pixel, px.data(), sizeof(int) * (size_t)n,
                                   cudaMemcpyHostToDevice, ctx->stream));
@@ -755,6 +997,29 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
     if (cap > 0 && cap < per_sm) per_sm = cap;
     trace_grid = sms * (per_sm > 0 ? per_sm : 1);
   }
+  {
+    // One L1 / shared-memory split for every kernel of a round: an SM's split only changes
+    // while the SM is empty, so a shade or sort block (little or no shared memory) and a trace
+    // block (16 KB of stacks) of two different groups could otherwise never share an SM, and
+    // the groups overlapped only SM by SM.  GPT_ROUNDS_CARVEOUT_KB=0 leaves the driver's choice.
+    static int carve_done = 0;
+    if (!carve_done) {
+      carve_done = 1;
+      const char *e = getenv("GPT_ROUNDS_CARVEOUT_KB");
+      int kb = e ? atoi(e) : GPT_ROUNDS_CARVEOUT_KB_DEFAULT;
+      if (kb > 0) {
+        int pct = (kb * 100 + 227) / 228;
+        if (pct > 100) pct = 100;
+        GPT_CUDA(ctx, cudaFuncSetAttribute(k_pt_trace<false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+        GPT_CUDA(ctx, cudaFuncSetAttribute(k_pt_trace<false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+        GPT_CUDA(ctx, cudaFuncSetAttribute(k_pt_trace<true, false>, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+        GPT_CUDA(ctx, cudaFuncSetAttribute(k_pt_trace<true, true>, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+        GPT_CUDA(ctx, cudaFuncSetAttribute(k_pt_shade, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
+        if (gpt_radix_sort_set_carveout(pct) != GPT_OK)
+          return gpt_fail(ctx, GPT_E_CUDA, "cudaFuncSetAttribute(carveout) failed", __FILE__, __LINE__);
+      }
+    }
+  }
   uint64_t rays = 0, shades = 0, trace_launches = 0;
   const bool timing = ctx->prof_time_stages, counting = ctx->prof_count_visits;
   size_t nev = 0;
@@ -769,6 +1034,119 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
     }
     return cudaEventRecord(rc->events[nev++], st);
   };
+  // ---- which pipeline ------------------------------------------------------------------------
+  int pipeline = ctx->pipeline;
+  if (pipeline < 0) {
+    static int env_pipe = -2;
+    if (env_pipe == -2) {
+      const char *e = getenv("GPT_PIPELINE");
+      env_pipe = !e ? -1 : (!strcmp(e, "stream") || !strcmp(e, "1")) ? 1 : 0;
+    }
+    pipeline = env_pipe >= 0 ? env_pipe : (n <= GPT_STREAM_AUTO_MAX_SLOTS ? 1 : 0);
+  }
+  if (sss_pass || timing) pipeline = 0;  // the SSS first pass and stage timing use the rounds
+  if (pipeline == 1) {
+    // ---- streaming pipeline: two persistent kernels side by side (see k_pt_shade_stream) ------
+    int cells = 1024;
+    while (cells < 2 * n) cells <<= 1;
+    const int hit_cells = cells / 4;  // per sub-ring: >= n / 2 slots of ONE class from ONE sixteenth of the trace blocks
+    if (cells > rc->sq_capacity) {
+      GPT_TRY(gpt_alloc(ctx, &rc->sq_cells, (size_t)cells + (size_t)SQ_NR * hit_cells));
+      GPT_TRY(gpt_alloc(ctx, &rc->sq_ctl, (size_t)SQ_WORDS));
+      rc->sq_capacity = cells;
+    }
+    StreamQ q{rc->sq_cells, rc->sq_cells + cells, rc->sq_ctl, cells - 1, hit_cells - 1, n};
+    k_stream_init<<<(unsigned)(((size_t)SQ_NR * hit_cells + 255) / 256), 256, 0, st>>>(q);
+    GPT_LAUNCH_CHECK(ctx);
+    unsigned long long *ray_counter = ctx->d_counters + 6;
+    GPT_CUDA(ctx, cudaMemsetAsync(ray_counter, 0, sizeof(unsigned long long), st));
+    static int bt = 0, bs = 0, sms = 148;
+    if (!bt) {
+      // CUDA loads a kernel's code lazily at its first launch, and that load synchronises with
+      // the kernels already running: the second kernel of the pair would wait for the first,
+      // which waits for it.  Load all of them before the first pair goes out.
+      cudaFuncAttributes fa;
+      GPT_CUDA(ctx, cudaFuncGetAttributes(&fa, k_pt_shade_stream));
+      GPT_CUDA(ctx, cudaFuncGetAttributes(&fa, k_pt_trace_stream<false>));
+      GPT_CUDA(ctx, cudaFuncGetAttributes(&fa, k_pt_trace_stream<true>));
+      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
+      const char *e1 = getenv("GPT_STREAM_TRACE_BLOCKS"), *e2 = getenv("GPT_STREAM_SHADE_BLOCKS");
+      bs = e2 ? atoi(e2) : 2;
+      bt = e1 ? atoi(e1) : 3;
+      if (bt < 1) bt = 1;
+      if (bs < 1) bs = 1;
+      // Both kernels must be able to share an SM, and an SM's L1 / shared-memory split can only
+      // change while the SM is empty: a shade block (no shared memory) that configures an SM
+      // for "all L1" would lock the trace blocks (16 KB of traversal stacks each) out of it for
+      // as long as it runs -- for ever (seen: the watchdog fired as soon as shade covered every
+      // SM).  So all three ask for the same split: the smallest one that holds bt trace blocks.
+      static const int cfg_kb[] = {8, 16, 32, 64, 100, 132, 164, 196, 228};
+      int need_kb = bt * (TP_STACK_SMEM * TP_BLOCK * 4 / 1024 + 1), pick = 228;
+      for (int c : cfg_kb)
+        if (c >= need_kb) { pick = c; break; }
+      const int carve = (pick * 100 + 227) / 228;
+      GPT_CUDA(ctx, cudaFuncSetAttribute(k_pt_shade_stream, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
+      GPT_CUDA(ctx, cudaFuncSetAttribute(k_pt_trace_stream<false>, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
+      GPT_CUDA(ctx, cudaFuncSetAttribute(k_pt_trace_stream<true>, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
+    }
+    const int need = (n + TP_BLOCK - 1) / TP_BLOCK;
+    const int tgrid = std::min(sms * bt, need), sgrid = std::min(sms * bs, need);
+    GPT_CUDA(ctx, cudaEventRecord(rc->fork_ev, st));
+    GPT_CUDA(ctx, cudaStreamWaitEvent(rc->gstream[0], rc->fork_ev, 0));
+    GPT_CUDA(ctx, cudaStreamWaitEvent(rc->gstream[1], rc->fork_ev, 0));
+    StreamSource src{ps, q, ctx->scene.shade};
+    // shade first: it has the larger local-memory frame, and a launch that makes the driver
+    // grow the local-memory pool waits for every running kernel -- behind a persistent trace
+    // kernel that itself waits for shade, that is a deadlock (seen: the watchdog fired)
+    k_pt_shade_stream<<<sgrid, PT_BLOCK, 0, rc->gstream[1]>>>(ps, p, q, ctx->scene, atlas, mb.tris, lt, d_fb, ray_counter);
+    GPT_LAUNCH_CHECK(ctx);
+    if (counting)
+      k_pt_trace_stream<true><<<tgrid, TP_BLOCK, 0, rc->gstream[0]>>>(src, mb.nodes, mb.tris, mb.parent_leaf, ctx->d_counters);
+    else
+      k_pt_trace_stream<false><<<tgrid, TP_BLOCK, 0, rc->gstream[0]>>>(src, mb.nodes, mb.tris, mb.parent_leaf, ctx->d_counters);
+    GPT_LAUNCH_CHECK(ctx);
+    for (int g = 0; g < 2; g++) {
+      GPT_CUDA(ctx, cudaEventRecord(rc->join_ev[g], rc->gstream[g]));
+      GPT_CUDA(ctx, cudaStreamWaitEvent(st, rc->join_ev[g], 0));
+    }
+    int h_ctl[SQ_WORDS];
+    unsigned long long h_rays = 0;
+    GPT_CUDA(ctx, cudaMemcpyAsync(h_ctl, q.ctl, sizeof(h_ctl), cudaMemcpyDeviceToHost, st));
+    GPT_CUDA(ctx, cudaMemcpyAsync(&h_rays, ray_counter, sizeof(h_rays), cudaMemcpyDeviceToHost, st));
+    GPT_CUDA(ctx, cudaEventRecord(ctx->ev1, st));
+    GPT_CUDA(ctx, cudaEventSynchronize(ctx->ev1));
+    float ms = 0.f;
+    GPT_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+    ctx->stats.render_ms = ms;
+    ctx->stats.rays_traced = h_rays;
+    ctx->stats.shade_events = h_rays;
+    ctx->stats.kernel_launches = ctx->launches;
+    ctx->stats.trace_launches = 1;
+    if (counting) {
+      unsigned long long c[4];
+      GPT_CUDA(ctx, cudaMemcpy(c, ctx->d_counters, sizeof(c), cudaMemcpyDeviceToHost));
+      ctx->stats.internal_visits = c[0];
+      ctx->stats.leaf_tests = c[1];
+    }
+    if (h_ctl[SQ_ERR])
+      return gpt_fail(ctx, GPT_E_UNSUPPORTED, "nested-dielectric list deeper than 12", __FILE__, __LINE__);
+    if (h_ctl[SQ_ABORT] || h_ctl[SQ_DONE] != n) {
+      static char msg[512];
+      int o = snprintf(msg, sizeof(msg), "streaming pipeline stalled: abort %d, done %d of %d, ray ring %d/%d, hit rings",
+                       h_ctl[SQ_ABORT], h_ctl[SQ_DONE], n, h_ctl[SQ_RAY_HEAD], h_ctl[SQ_RAY_TAIL]);
+      for (int m = 0; m < SQ_RINGS && o < (int)sizeof(msg) - 48; m++) {
+        long long hd = 0, tl = 0, cr = 0;
+        for (int k = 0; k < SQ_SUB; k++) {
+          int r = m * SQ_SUB + k;
+          hd += h_ctl[SQ_RING0 + 24 * r]; tl += h_ctl[SQ_RING0 + 24 * r + 8]; cr += h_ctl[SQ_RING0 + 24 * r + 16];
+        }
+        o += snprintf(msg + o, sizeof(msg) - o, " %lld/%lld(%lld)", hd, tl, cr);
+      }
+      snprintf(msg + o, sizeof(msg) - o, " (%.1f ms)", ms);
+      return gpt_fail(ctx, GPT_E_INVALID, msg, __FILE__, __LINE__);
+    }
+    return GPT_OK;
+  }
   // ---- wavefront groups -------------------------------------------------------------------
   // Slots are cut into G contiguous ranges that run their trace -> sort -> shade iterations
   // independently on their own streams (a pixel never interacts with another pixel).  Inside
@@ -964,7 +1342,7 @@ void gpt_render_free(gpt_ctx *ctx) {
   void *p[] = {ps.pixel, ps.rng, ps.rays, ps.hits, ps.ma, ps.cm, ps.cam,
                ps.queue[0], ps.queue[1], ps.counts, rc->leaf_info, rc->node_info,
                rc->node_energy, rc->lt_flags, rc->rng_init, rc->d_fb, rc->sort_key,
-               rc->sort_key_alt, rc->sort_hist, rc->sort_val, rc->sort_val_alt};
+               rc->sort_key_alt, rc->sort_hist, rc->sort_val, rc->sort_val_alt, rc->sq_cells, rc->sq_ctl};
   for (void *q : p) gpt_free(ctx, q);
   if (rc->h_counts) cudaFreeHost(rc->h_counts);
   if (rc->fork_ev) cudaEventDestroy(rc->fork_ev);

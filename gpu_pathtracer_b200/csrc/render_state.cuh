@@ -38,10 +38,10 @@ __device__ __forceinline__ void matlist_store(uint4 *dst, const MatList &l) {
   w[3] = (uint32_t)l.len;
   *dst = make_uint4(w[0], w[1], w[2], w[3]);
 }
-__device__ __forceinline__ void matlist_load(MatList &l, const uint4 *src) {
-  uint4 q = *src;
+__device__ __forceinline__ void matlist_unpack(MatList &l, uint4 q) {
   uint32_t w[3] = {q.x, q.y, q.z};
 #pragma unroll
   for (int i = 0; i < MATLIST_MAX; i++) l.id[i] = (unsigned char)((w[i >> 2] >> (8 * (i & 3))) & 0xff);
   l.len = (int)q.w;
 }
+__device__ __forceinline__ void matlist_load(MatList &l, const uint4 *src) { matlist_unpack(l, *src); }

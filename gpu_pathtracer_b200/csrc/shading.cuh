@@ -37,9 +37,10 @@ __device__ __forceinline__ void rng_store(const Rng &r, uint32_t *st, size_t slo
 }
 // packed variant: 8 words per slot (one 32-byte sector), for state that is visited in random
 // slot order
-__device__ __forceinline__ void rng_load_packed(Rng &r, const uint32_t *__restrict__ st, size_t slot) {
+template <bool AROUND_L1 = false>
+__device__ __forceinline__ void rng_load_packed(Rng &r, const uint32_t *st, size_t slot) {
   const uint4 *p = reinterpret_cast<const uint4 *>(st + 8 * slot);
-  uint4 a = p[0], b = p[1];
+  uint4 a = AROUND_L1 ? __ldcg(p) : p[0], b = AROUND_L1 ? __ldcg(p + 1) : p[1];
   r.s.d = a.x; r.s.v[0] = a.y; r.s.v[1] = a.z; r.s.v[2] = a.w; r.s.v[3] = b.x; r.s.v[4] = b.y;
   r.s.boxmuller_flag = 0;
   r.s.boxmuller_flag_double = 0;

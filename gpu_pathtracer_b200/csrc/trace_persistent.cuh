@@ -244,6 +244,102 @@ __device__ __forceinline__ void coop_finish(const float4 *__restrict__ nodes,
   }
 #undef WL
 }
+// One step of the ordered walk for a lane that holds a ray: test the two children of L.node,
+// test leaves where they are found, descend / push / pop.  Returns true when the walk is over
+// (the caller stores the record).
+template <bool COUNT>
+__device__ __forceinline__ bool tp_step(const float4 *__restrict__ nodes,
+                                        const float4 *__restrict__ tris,
+                                        const int *__restrict__ parent_leaf, TraceLane &L,
+                                        int *stack, int *spill, unsigned long long *counters,
+                                        unsigned &vi, unsigned &vl) {
+    const float4 *q = nodes + 4 * (size_t)L.node;
+    float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3);
+    if (COUNT) vi++;
+    int cref[2] = {__float_as_int(q3.x), __float_as_int(q3.y)};
+    // near / far bound per axis from the sign of 1/d
+    const bool nx = L.neg & 1u, ny = L.neg & 2u, nz = L.neg & 4u;
+    float xn[2] = {nx ? q0.y : q0.x, nx ? q1.w : q1.z}, xf[2] = {nx ? q0.x : q0.y, nx ? q1.z : q1.w};
+    float yn[2] = {ny ? q0.w : q0.z, ny ? q2.y : q2.x}, yf[2] = {ny ? q0.z : q0.w, ny ? q2.x : q2.y};
+    float zn[2] = {nz ? q1.y : q1.x, nz ? q2.w : q2.z}, zf[2] = {nz ? q1.x : q1.y, nz ? q2.z : q2.w};
+    bool go[2];
+    float tnear[2], tcull[2];
+#pragma unroll
+    for (int c = 0; c < 2; c++) {
+      float txn = (xn[c] - L.ox) * L.ix, txx = (xf[c] - L.ox) * L.ix;
+      float tyn = (yn[c] - L.oy) * L.iy, tyx = (yf[c] - L.oy) * L.iy;
+      float tzn = (zn[c] - L.oz) * L.iz, tzx = (zf[c] - L.oz) * L.iz;
+      bool ok = (txn <= tyx) && (tyn <= txx);
+      float txyn = fmaxf(txn, tyn), txyx = fminf(txx, tyx);
+      ok = ok && (txyn <= tzx) && (tzn <= txyx);
+      float tn = L.kz == 0 ? txn : (L.kz == 1 ? tyn : tzn);
+      float tf = L.kz == 0 ? txx : (L.kz == 1 ? tyx : tzx);
+      float margin = 1e-5f * fmaxf(fabsf(tn), fabsf(tf));
+      tnear[c] = tn;
+      tcull[c] = tn - margin;
+      go[c] = ok && !(tf + margin < 0.f);
+    }
+    // Leaves: the two children's tests share ONE copy of the intersection code (a leaf on
+    // either side of any lane runs in the same round), instead of two unrolled copies that
+    // each execute with ~2 of 32 lanes (ncu r01b: 37 % of issued instructions).
+    int lf0 = (go[0] && cref[0] < 0) ? ~cref[0] : -1, lf1 = (go[1] && cref[1] < 0) ? ~cref[1] : -1;
+    float lc0 = tcull[0], lc1 = tcull[1];
+    if (lf0 < 0) { lf0 = lf1; lc0 = lc1; lf1 = -1; }
+#pragma unroll 1
+    while (lf0 >= 0) {
+      if (!(lc0 > L.best)) {
+        const float4 *tp = tris + 3 * (size_t)lf0;
+        float4 t0 = __ldg(tp), t1 = __ldg(tp + 1), t2 = __ldg(tp + 2);
+        if (COUNT) vl++;
+        RaySetup r;
+        r.ox = L.ox; r.oy = L.oy; r.oz = L.oz; r.sx = L.sx; r.sy = L.sy; r.sz = L.sz; r.kz = L.kz;
+        float t, b1, b2, b3;
+        if (tri_test(r, t0, t1, t2, t, b1, b2, b3)) {
+          if (!(t > L.best) && !(t < t2.y)) {
+            bool take = true;
+            if (t == L.t && L.leaf >= 0)
+              take = leaf_visit_rank(nodes, parent_leaf, lf0) >
+                     leaf_visit_rank(nodes, parent_leaf, L.leaf);
+            if (take) {
+              L.t = t; L.leaf = lf0; L.b1 = b1; L.b2 = b2; L.b3 = b3;
+              L.prim = __float_as_int(t2.z);
+              L.best = t;
+            }
+          }
+        }
+      }
+      lf0 = lf1; lc0 = lc1; lf1 = -1;
+    }
+    // Internal children, written to compile into predicated code rather than a three-way
+    // divergent branch (push / step / pop): near child first, far child pushed.
+    const bool gl = go[0] && cref[0] >= 0 && !(tcull[0] > L.best);
+    const bool gr = go[1] && cref[1] >= 0 && !(tcull[1] > L.best);
+    const bool both = gl && gr, any = gl || gr;
+    const bool lfirst = tnear[0] <= tnear[1];
+    const int nearc = (gl && (!gr || lfirst)) ? cref[0] : cref[1];
+    const int farc = lfirst ? cref[1] : cref[0];
+    if (both && L.sp < TP_STACK_SMEM) stack[L.sp * TP_BLOCK] = farc;
+#if TP_PREFETCH
+    if (both && farc >= 0) {
+      const float4 *fq = nodes + 4 * (size_t)farc;
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(fq));
+    }
+#endif
+    if (both && L.sp >= TP_STACK_SMEM) {  // rare: deeper than the shared-memory levels
+      if (L.sp < TRACE_STACK) spill[L.sp - TP_STACK_SMEM] = farc;
+      else atomicExch(counters + 3, 1ull);
+    }
+    if (both && L.sp < TRACE_STACK) L.sp++;
+    const bool finished = !any && L.sp == 0;
+    if (any) {
+      L.node = nearc;
+    } else if (L.sp > 0) {
+      L.sp--;
+      L.node = L.sp < TP_STACK_SMEM ? stack[L.sp * TP_BLOCK] : spill[L.sp - TP_STACK_SMEM];
+    }
+    return finished;
+}
+
 // Source concept:
 //   int count() const;                       number of rays in the queue
 //   void load(int i, float4 &o, float4 &d);  ray i: {o, tmax}{unit d, -}
@@ -310,91 +406,7 @@ __device__ __forceinline__ void trace_persistent(const float4 *__restrict__ node
     //  remove with one triangle per leaf -- so leaves are tested where they are found.)
     while (true) {
       if (L.ray >= 0) {
-        const float4 *q = nodes + 4 * (size_t)L.node;
-        float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3);
-        if (COUNT) vi++;
-        int cref[2] = {__float_as_int(q3.x), __float_as_int(q3.y)};
-        // near / far bound per axis from the sign of 1/d
-        const bool nx = L.neg & 1u, ny = L.neg & 2u, nz = L.neg & 4u;
-        float xn[2] = {nx ? q0.y : q0.x, nx ? q1.w : q1.z}, xf[2] = {nx ? q0.x : q0.y, nx ? q1.z : q1.w};
-        float yn[2] = {ny ? q0.w : q0.z, ny ? q2.y : q2.x}, yf[2] = {ny ? q0.z : q0.w, ny ? q2.x : q2.y};
-        float zn[2] = {nz ? q1.y : q1.x, nz ? q2.w : q2.z}, zf[2] = {nz ? q1.x : q1.y, nz ? q2.z : q2.w};
-        bool go[2];
-        float tnear[2], tcull[2];
-#pragma unroll
-        for (int c = 0; c < 2; c++) {
-          float txn = (xn[c] - L.ox) * L.ix, txx = (xf[c] - L.ox) * L.ix;
-          float tyn = (yn[c] - L.oy) * L.iy, tyx = (yf[c] - L.oy) * L.iy;
-          float tzn = (zn[c] - L.oz) * L.iz, tzx = (zf[c] - L.oz) * L.iz;
-          bool ok = (txn <= tyx) && (tyn <= txx);
-          float txyn = fmaxf(txn, tyn), txyx = fminf(txx, tyx);
-          ok = ok && (txyn <= tzx) && (tzn <= txyx);
-          float tn = L.kz == 0 ? txn : (L.kz == 1 ? tyn : tzn);
-          float tf = L.kz == 0 ? txx : (L.kz == 1 ? tyx : tzx);
-          float margin = 1e-5f * fmaxf(fabsf(tn), fabsf(tf));
-          tnear[c] = tn;
-          tcull[c] = tn - margin;
-          go[c] = ok && !(tf + margin < 0.f);
-        }
-        // Leaves: the two children's tests share ONE copy of the intersection code (a leaf on
-        // either side of any lane runs in the same round), instead of two unrolled copies that
-        // each execute with ~2 of 32 lanes (ncu r01b: 37 % of issued instructions).
-        int lf0 = (go[0] && cref[0] < 0) ? ~cref[0] : -1, lf1 = (go[1] && cref[1] < 0) ? ~cref[1] : -1;
-        float lc0 = tcull[0], lc1 = tcull[1];
-        if (lf0 < 0) { lf0 = lf1; lc0 = lc1; lf1 = -1; }
-#pragma unroll 1
-        while (lf0 >= 0) {
-          if (!(lc0 > L.best)) {
-            const float4 *tp = tris + 3 * (size_t)lf0;
-            float4 t0 = __ldg(tp), t1 = __ldg(tp + 1), t2 = __ldg(tp + 2);
-            if (COUNT) vl++;
-            RaySetup r;
-            r.ox = L.ox; r.oy = L.oy; r.oz = L.oz; r.sx = L.sx; r.sy = L.sy; r.sz = L.sz; r.kz = L.kz;
-            float t, b1, b2, b3;
-            if (tri_test(r, t0, t1, t2, t, b1, b2, b3)) {
-              if (!(t > L.best) && !(t < t2.y)) {
-                bool take = true;
-                if (t == L.t && L.leaf >= 0)
-                  take = leaf_visit_rank(nodes, parent_leaf, lf0) >
-                         leaf_visit_rank(nodes, parent_leaf, L.leaf);
-                if (take) {
-                  L.t = t; L.leaf = lf0; L.b1 = b1; L.b2 = b2; L.b3 = b3;
-                  L.prim = __float_as_int(t2.z);
-                  L.best = t;
-                }
-              }
-            }
-          }
-          lf0 = lf1; lc0 = lc1; lf1 = -1;
-        }
-        // Internal children, written to compile into predicated code rather than a three-way
-        // divergent branch (push / step / pop): near child first, far child pushed.
-        const bool gl = go[0] && cref[0] >= 0 && !(tcull[0] > L.best);
-        const bool gr = go[1] && cref[1] >= 0 && !(tcull[1] > L.best);
-        const bool both = gl && gr, any = gl || gr;
-        const bool lfirst = tnear[0] <= tnear[1];
-        const int nearc = (gl && (!gr || lfirst)) ? cref[0] : cref[1];
-        const int farc = lfirst ? cref[1] : cref[0];
-        if (both && L.sp < TP_STACK_SMEM) stack[L.sp * TP_BLOCK] = farc;
-#if TP_PREFETCH
-        if (both && farc >= 0) {
-          const float4 *fq = nodes + 4 * (size_t)farc;
-          asm volatile("prefetch.global.L2 [%0];" ::"l"(fq));
-        }
-#endif
-        if (both && L.sp >= TP_STACK_SMEM) {  // rare: deeper than the shared-memory levels
-          if (L.sp < TRACE_STACK) spill[L.sp - TP_STACK_SMEM] = farc;
-          else atomicExch(counters + 3, 1ull);
-        }
-        if (both && L.sp < TRACE_STACK) L.sp++;
-        const bool finished = !any && L.sp == 0;
-        if (any) {
-          L.node = nearc;
-        } else if (L.sp > 0) {
-          L.sp--;
-          L.node = L.sp < TP_STACK_SMEM ? stack[L.sp * TP_BLOCK] : spill[L.sp - TP_STACK_SMEM];
-        }
-        if (finished) {
+        if (tp_step<COUNT>(nodes, tris, parent_leaf, L, stack, spill, counters, vi, vl)) {
           src.store(L.ray, L);
           L.ray = -1;
         }
@@ -407,6 +419,108 @@ __device__ __forceinline__ void trace_persistent(const float4 *__restrict__ node
   if (COOP && coop_live)
     coop_finish<COUNT>(nodes, tris, parent_leaf, src, L, coop_live, stack,
                        coop_smem + (threadIdx.x >> 5) * COOP_WARP_WORDS, vi, vl);
+  if (COUNT) {
+    atomicAdd(counters, (unsigned long long)vi);
+    atomicAdd(counters + 1, (unsigned long long)vl);
+  }
+}
+
+// ---- streaming trace (the path tracer's barrier-free pipeline, render.cu) -----------------
+// The same ordered walk, fed from a RING that the shade kernel fills while this kernel runs:
+// there is no "end of the queue", so there is no tail to wait for.  An idle lane reserves the
+// next ring position (warp-aggregated atomicAdd on the ring's head) and polls that cell between
+// traversal steps until a slot appears in it; a finished ray is handed to the shade kernel by
+// the source's store().  The launch ends when the source says every pixel is finished.
+// Source concept:
+//   int  reserve(int cnt);                    first of cnt consecutive ring positions
+//   int  poll(int pos);                       slot published at that position, or -1 (not yet)
+//   void load(int slot, float4 &o, float4 &d);
+//   int  store(int slot, const TraceLane &l); writes the hit record, returns the ring it goes to
+//   void publish(int slot, int ring);         warp-wide: lanes with slot >= 0 hand it over
+//   bool finished();                          every pixel done (or the pipeline was aborted)
+//   void abort();
+// Handing a slot over costs a fence and two atomics, i.e. several round trips to L2 during
+// which the whole warp stands still; so a finished lane keeps its slot until the warp comes
+// back to the refill point (>= TS_REFILL lanes without a ray, or a poll of reserved cells is
+// due) and the warp publishes all of them together, one atomic per ring.
+constexpr int TS_POLL_STEPS = 8;                          // steps between polls of reserved cells
+#ifndef TS_REFILL_V
+#define TS_REFILL_V 12
+#endif
+constexpr int TS_REFILL = TS_REFILL_V;                    // lanes without a ray that end a traversal stretch
+constexpr long long TS_WATCHDOG_CYCLES = 20000000000ll;   // ~10 s without any ray: give up loudly
+template <bool COUNT, class Source>
+__device__ __forceinline__ void trace_stream(const float4 *__restrict__ nodes,
+                                             const float4 *__restrict__ tris,
+                                             const int *__restrict__ parent_leaf, Source src,
+                                             int *stack_smem, unsigned long long *counters) {
+  const unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  int *stack = stack_smem + threadIdx.x;
+  int spill[TRACE_STACK - TP_STACK_SMEM];
+  TraceLane L;
+  L.ray = -1;
+  int pend = -1;      // ring position this lane has reserved and is waiting on
+  int fin_slot = -1;  // finished, not yet handed to the shade kernel
+  int fin_ring = 0;
+  unsigned vi = 0, vl = 0;
+  long long idle_since = 0;
+  while (true) {
+    if (__ballot_sync(FULL, fin_slot >= 0)) {
+      src.publish(fin_slot, fin_ring);
+      fin_slot = -1;
+    }
+    const unsigned want = __ballot_sync(FULL, L.ray < 0 && pend < 0);
+    const unsigned busy = __ballot_sync(FULL, L.ray >= 0);
+    if (want && (__popc(want) >= TS_REFILL || busy == 0)) {
+      const int cnt = __popc(want), leader = __ffs(want) - 1;
+      int base = 0;
+      if (lane == leader) base = src.reserve(cnt);
+      base = __shfl_sync(FULL, base, leader);
+      if (L.ray < 0 && pend < 0) pend = base + __popc(want & ((1u << lane) - 1u));
+    }
+    if (pend >= 0) {
+      const int slot = src.poll(pend);
+      if (slot >= 0) {
+        float4 ro, rd;
+        src.load(slot, ro, rd);
+        RaySetup r = make_ray(ro.x, ro.y, ro.z, rd.x, rd.y, rd.z);
+        L.ox = r.ox; L.oy = r.oy; L.oz = r.oz; L.ix = r.ix; L.iy = r.iy; L.iz = r.iz;
+        L.sx = r.sx; L.sy = r.sy; L.sz = r.sz; L.kz = r.kz;
+        L.neg = (r.ix < 0.f ? 1u : 0u) | (r.iy < 0.f ? 2u : 0u) | (r.iz < 0.f ? 4u : 0u);
+        L.best = ro.w;
+        L.t = INFINITY; L.leaf = -1; L.prim = -1; L.b1 = L.b2 = L.b3 = 0.f;
+        L.node = 0; L.sp = 0;
+        L.ray = slot;
+        pend = -1;
+      }
+    }
+    if (__ballot_sync(FULL, L.ray >= 0) == 0) {
+      // nothing to walk: either the frame is over or the shade kernel has not produced yet
+      if (src.finished()) break;
+      const long long now = clock64();
+      if (idle_since == 0) idle_since = now;
+      if (now - idle_since > TS_WATCHDOG_CYCLES) {
+        src.abort();
+        break;
+      }
+      __nanosleep(100);
+      continue;
+    }
+    idle_since = 0;
+    int steps = __ballot_sync(FULL, pend >= 0) ? TS_POLL_STEPS : (1 << 30);
+    while (true) {
+      if (L.ray >= 0) {
+        if (tp_step<COUNT>(nodes, tris, parent_leaf, L, stack, spill, counters, vi, vl)) {
+          fin_ring = src.store(L.ray, L);
+          fin_slot = L.ray;
+          L.ray = -1;
+        }
+      }
+      const int nwant = __popc(__ballot_sync(FULL, L.ray < 0 && pend < 0));
+      if (nwant >= TS_REFILL || --steps <= 0) break;
+    }
+  }
   if (COUNT) {
     atomicAdd(counters, (unsigned long long)vi);
     atomicAdd(counters + 1, (unsigned long long)vl);

@@ -324,6 +324,18 @@ int gpt_set_wavefront_groups(gpt_ctx *ctx, int groups);
  * environment variable GPT_TRACE_COOP=0.  Hits are bit-identical either way: closest hit with
  * the reference's visit-rank tie-break does not depend on the order nodes are visited in. */
 int gpt_set_trace_tail(gpt_ctx *ctx, int mode);
+/* How gpt_render_pathtrace* runs path_tracing_render's dof x spp x level loop
+ * (src/render/pathtracing.h:251-305).
+ *   0 "rounds":  one round of launches (trace, material sort, shade) per bounce of every pixel,
+ *                in 1..8 independent groups (gpt_set_wavefront_groups).
+ *   1 "stream":  two persistent kernels, trace and shade, run side by side for the whole frame
+ *                and hand pixel slots to each other through rings in device memory (one ring
+ *                per material class towards shade), so no pixel waits for another pixel's ray.
+ *  -1 (default): environment variable GPT_PIPELINE ("rounds" / "stream"), else chosen by the
+ *                number of pixels this rank renders.
+ * The frame and the ray count are bit-identical either way: pixels never interact, and a
+ * pixel's samples stay sequential on its own RNG stream. */
+int gpt_set_pipeline(gpt_ctx *ctx, int mode);
 int gpt_stats(gpt_ctx *ctx, GptStats *out);
 int gpt_synchronize(gpt_ctx *ctx);
 

@@ -112,6 +112,39 @@ def test_wavefront_groups_do_not_change_the_image():
     pt.set_wavefront_groups(0)
 
 
+def test_streaming_pipeline_is_bit_identical():
+    """gpt_set_pipeline(1): trace and shade as two persistent kernels exchanging pixel slots
+    through rings (per-material rings towards shade) instead of rounds of launches.  Same frame
+    and same ray count, bit for bit: on the small scene with glass (nested material lists), on
+    C2's mixed materials with textures, with depth of field (dof x spp samples per pixel), for
+    a frame smaller than one block and for tile-sharded ranks."""
+    import torch
+    from gpu_pathtracer_b200.api import PathTracer
+    scenes = (S.make_scene("small", n=20, width=200, height=136, spp=3, level=6),
+              S.make_scene("small", n=12, width=9, height=7, spp=2, level=3),
+              S.make_scene("C2", n=60, width=160, height=96, spp=2, tex=64, n_spheres=8),
+              S.make_scene("C3", width=96, height=64, spp=2, dof=2, level=6))
+    for sc in scenes:
+        pt = PathTracer(sc)
+        pt.build()
+        pt.set_pipeline("rounds")
+        base = pt.render_pathtrace()
+        rays = pt.stats()["rays_traced"]
+        assert rays > 0
+        pt.set_pipeline("stream")
+        for _ in range(2):
+            img = pt.render_pathtrace()
+            assert np.array_equal(img.view(np.uint32), base.view(np.uint32)), sc.name
+            assert pt.stats()["rays_traced"] == rays, sc.name
+        h, w = base.shape[:2]
+        fb = torch.zeros((h, w, 3), dtype=torch.float32, device="cuda")
+        for r in range(3):
+            pt.render_pathtrace_device(fb.data_ptr(), r, 3)
+        pt.synchronize()
+        assert np.array_equal(fb.cpu().numpy().view(np.uint32), base.view(np.uint32)), sc.name
+        pt.set_pipeline("default")
+
+
 def test_against_reference_cuda_binary_8bit():
     """The reference's OWN CUDA build (sm_100, -fmad=false parity flags; oracle/_ref/
     gpu_path_tracing_100_nofma, built by `make -C oracle refcuda` from the unmodified sources +
