@@ -32,6 +32,8 @@ def parse():
     ap.add_argument("--photons", type=int, default=0, help="C4: photons per pass override")
     ap.add_argument("--mode", default="auto", choices=["auto", "trace", "render"])
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel")
+    ap.add_argument("--pipeline", default="default", choices=["default", "rounds", "stream"],
+                    help="gpt_set_pipeline: rounds of launches / two persistent kernels")
     ap.add_argument("--cpu-budget-s", type=float, default=15.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -200,6 +202,7 @@ def run_ours(args, rank, world, local_rank):
     sc = make_workload(args.workload, args.spp)
     H, W = sc.camera["height"], sc.camera["width"]
     pt = PathTracer(sc, device=local_rank)
+    pt.set_pipeline(args.pipeline)
     # a real (non-legacy) stream: the library launches on it and the events below time it
     stream = torch.cuda.Stream(device=dev)
     torch.cuda.set_stream(stream)
@@ -305,6 +308,7 @@ def run_ours(args, rank, world, local_rank):
                     "reference's traverse_bvh(node_list[0]) call count",
             "cache": "L2 flushed (512 MiB write) between timed steps",
             "sharding": "scene replicated, 32x32 pixel tiles dealt round-robin to ranks",
+            "pipeline": {"default": "rounds (library default)"}.get(args.pipeline, args.pipeline),
             "spp_per_s": spp_total / (ms_per_step * 1e-3),
             "rays_per_frame": rays_all,
             "lbvh_build_ms": build_ms, "build_all_ms": build_stats["build_all_ms"],
@@ -322,10 +326,10 @@ def run_ours(args, rank, world, local_rank):
                      "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak,
                      # physical DRAM bytes per launch: ncu --set full on this kernel at C2
-                     # (profiles/r01d_k_pt_trace_raw.csv: 52.9 MB read + 2.6 MB write per
+                     # (profiles/r01g_k_pt_trace_raw.csv: 50.4-55.3 MB read + 2.7-3.3 MB write per
                      # 518 400-ray launch = 107 B per ray), scaled to this run's rays per launch
                      "traffic": (107.0 * rays / max(1, n_trace)) if args.workload == "C2" else None,
-                     "traffic_source": "ncu r01d capture, 107 B/ray (C2 only)",
+                     "traffic_source": "ncu r01g capture, 102-113 B/ray (C2 only)",
                      "launches": int(n_trace),
                      "algorithmic_bytes_per_launch": alg_bytes / n_trace,
                      "avg_launch_ms": trace_ms / n_trace,

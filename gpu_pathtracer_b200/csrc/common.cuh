@@ -222,5 +222,4 @@ int gpt_radix_sort_pairs(gpt_ctx *ctx, uint32_t *keys, int *vals, uint32_t *keys
                          uint32_t **keys_out, int **vals_out,
                          const int *d_n = nullptr);  // d_n: exact count on the device (n = bound)
 int gpt_radix_hist_entries(int n);
-int gpt_radix_sort_set_carveout(int percent);
 bool gpt_trace_coop(const gpt_ctx *ctx, const BvhDev &b);  // trace.cu

@@ -370,18 +370,6 @@ k_export(const float4 *__restrict__ nodes, const int *__restrict__ parent_leaf,
 
 }  // namespace
 
-// All three sort kernels ask for this L1 / shared-memory split (percent of the maximum shared
-// memory); render.cu gives every kernel of its rounds the same one, so that blocks of different
-// wavefront groups can share an SM (the split of an SM only changes while the SM is empty).
-int gpt_radix_sort_set_carveout(int percent) {
-  cudaError_t e = cudaFuncSetAttribute(k_sort_hist<SORT_ITEMS>, cudaFuncAttributePreferredSharedMemoryCarveout, percent);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_sort_hist<SORT_ITEMS_SMALL>, cudaFuncAttributePreferredSharedMemoryCarveout, percent);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_sort_scan, cudaFuncAttributePreferredSharedMemoryCarveout, percent);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_sort_scatter<SORT_ITEMS>, cudaFuncAttributePreferredSharedMemoryCarveout, percent);
-  if (e == cudaSuccess) e = cudaFuncSetAttribute(k_sort_scatter<SORT_ITEMS_SMALL>, cudaFuncAttributePreferredSharedMemoryCarveout, percent);
-  return e == cudaSuccess ? GPT_OK : GPT_E_CUDA;
-}
-
 static int sort_tile_of(int n) { return SORT_THREADS * (n <= SORT_SMALL_N ? SORT_ITEMS_SMALL : SORT_ITEMS); }
 
 // counters a sort of up to n keys needs -- and of ANY shorter input (the path tracer sorts its

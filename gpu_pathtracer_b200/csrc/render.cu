@@ -7,6 +7,7 @@
 //   k_pt_trace  closest hit of every active path's ray against the main BVH
 //   k_pt_shade  material decision, light sampling + MIS, throughput update, next ray or next
 //               sample (ray-gen is folded into shade), warp-aggregated queue compaction
+#include <chrono>
 #include <cmath>
 #include <cstdio>
 #include <cstring>
@@ -18,9 +19,6 @@
 namespace {
 
 constexpr int PT_BLOCK = 128;
-#ifndef GPT_ROUNDS_CARVEOUT_KB_DEFAULT
-#define GPT_ROUNDS_CARVEOUT_KB_DEFAULT 0
-#endif
 // frames of at most this many slots per rank use the streaming pipeline by default
 #ifndef GPT_STREAM_AUTO_MAX_SLOTS
 #define GPT_STREAM_AUTO_MAX_SLOTS 0
@@ -997,29 +995,6 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
     if (cap > 0 && cap < per_sm) per_sm = cap;
     trace_grid = sms * (per_sm > 0 ? per_sm : 1);
   }
-  {
-    // One L1 / shared-memory split for every kernel of a round: an SM's split only changes
-    // while the SM is empty, so a shade or sort block (little or no shared memory) and a trace
-    // block (16 KB of stacks) of two different groups could otherwise never share an SM, and
-    // the groups overlapped only SM by SM.  GPT_ROUNDS_CARVEOUT_KB=0 leaves the driver's choice.
-    static int carve_done = 0;
-    if (!carve_done) {
-      carve_done = 1;
-      const char *e = getenv("GPT_ROUNDS_CARVEOUT_KB");
-      int kb = e ? atoi(e) : GPT_ROUNDS_CARVEOUT_KB_DEFAULT;
-      if (kb > 0) {
-        int pct = (kb * 100 + 227) / 228;
-        if (pct > 100) pct = 100;
-        GPT_CUDA(ctx, cudaFuncSetAttribute(k_pt_trace<false, false>, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
-        GPT_CUDA(ctx, cudaFuncSetAttribute(k_pt_trace<false, true>, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
-        GPT_CUDA(ctx, cudaFuncSetAttribute(k_pt_trace<true, false>, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
-        GPT_CUDA(ctx, cudaFuncSetAttribute(k_pt_trace<true, true>, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
-        GPT_CUDA(ctx, cudaFuncSetAttribute(k_pt_shade, cudaFuncAttributePreferredSharedMemoryCarveout, pct));
-        if (gpt_radix_sort_set_carveout(pct) != GPT_OK)
-          return gpt_fail(ctx, GPT_E_CUDA, "cudaFuncSetAttribute(carveout) failed", __FILE__, __LINE__);
-      }
-    }
-  }
   uint64_t rays = 0, shades = 0, trace_launches = 0;
   const bool timing = ctx->prof_time_stages, counting = ctx->prof_count_visits;
   size_t nev = 0;
@@ -1155,7 +1130,18 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
   // slots only ever leave a queue -- read back through a ring of pinned slots, so no
   // iteration waits for a device->host round trip.  Kernels take the exact length from device
   // memory.  Stage timing (profiling) needs one stream, so it forces G = 1.
-  constexpr int RING = RenderCtx::RING, LAG = 2;
+  constexpr int RING = RenderCtx::RING;
+  static int LAG = 0;  // rounds the host runs ahead of the device (1 .. RING - 1), env GPT_HOST_LAG
+  static int host_prof = 0;
+  if (!LAG) {
+    const char *e = getenv("GPT_HOST_LAG");
+    LAG = e ? atoi(e) : 2;
+    if (LAG < 1) LAG = 1;
+    if (LAG > RING - 1) LAG = RING - 1;
+    host_prof = getenv("GPT_HOST_PROFILE") != nullptr;
+  }
+  double host_wait_s = 0.0;
+  const auto host_t0 = std::chrono::steady_clock::now();
   int G = 1;
   {
     static int env_groups = -1;
@@ -1227,7 +1213,13 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
       int *d_counts = ps.counts + CNT * g;
       if (q.it >= LAG) {
         int slot = (int)((q.it - LAG) % RING);
-        GPT_CUDA(ctx, cudaEventSynchronize(rc->ring_ev[g][slot]));
+        if (host_prof) {
+          const auto w0 = std::chrono::steady_clock::now();
+          GPT_CUDA(ctx, cudaEventSynchronize(rc->ring_ev[g][slot]));
+          host_wait_s += std::chrono::duration<double>(std::chrono::steady_clock::now() - w0).count();
+        } else {
+          GPT_CUDA(ctx, cudaEventSynchronize(rc->ring_ev[g][slot]));
+        }
         const int *h = h_ring + CNT * slot;
         q.active = h[q.cur_of[slot]];
         if (h[4]) list_overflow = true;
@@ -1245,7 +1237,8 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
       {
         QueueSource qs{ps, ps.queue[q.cur] + q.s0, d_counts + c0, ctx->scene.shade,
                        rc->sort_key + q.s0, rc->sort_val + q.s0, loc_bits, loc_shift};
-        int tgrid = grid < trace_grid ? grid : trace_grid;
+        const int tneed = (q.active + TP_BLOCK - 1) / TP_BLOCK;
+        int tgrid = tneed < trace_grid ? tneed : trace_grid;
         auto kern = counting ? (coop ? k_pt_trace<true, true> : k_pt_trace<true, false>)
                              : (coop ? k_pt_trace<false, true> : k_pt_trace<false, false>);
         kern<<<tgrid, TP_BLOCK, 0, gs>>>(qs, mb.nodes, mb.tris, mb.parent_leaf, next_ray,
@@ -1283,6 +1276,11 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
     }
   }
   if (rc_err != GPT_OK) return rc_err;
+  if (host_prof) {
+    const double loop_s = std::chrono::duration<double>(std::chrono::steady_clock::now() - host_t0).count();
+    fprintf(stderr, "[gpt host] G=%d LAG=%d: launch loop %.3f ms, of which %.3f ms waiting for queue lengths, %llu trace launches\n",
+            G, LAG, loop_s * 1e3, host_wait_s * 1e3, (unsigned long long)trace_launches);
+  }
   int active = 0;
   {  // join the groups; final queue lengths, error flags, exact ray count
     for (int g = 0; g < G && G > 1; g++) {

@@ -12,7 +12,10 @@
 #pragma once
 #include "trace_core.cuh"
 
-constexpr int TP_BLOCK = 128;
+#ifndef TP_BLOCK_V
+#define TP_BLOCK_V 128
+#endif
+constexpr int TP_BLOCK = TP_BLOCK_V;  // threads per persistent trace block (a block keeps its SM resources until its slowest warp ends)
 #ifndef TP_STACK_SMEM_V
 #define TP_STACK_SMEM_V 32
 #endif
