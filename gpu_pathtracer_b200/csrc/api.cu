@@ -449,6 +449,12 @@ int gpt_set_pipeline(gpt_ctx *ctx, int mode) {
   return GPT_OK;
 }
 
+int gpt_set_trace_leaf_batching(gpt_ctx *ctx, int mode) {
+  if (!ctx || mode < -1 || mode > 1) return GPT_E_INVALID;
+  ctx->trace_defer = mode;
+  return GPT_OK;
+}
+
 int gpt_stats(gpt_ctx *ctx, GptStats *out) {
   if (!ctx || !out) return GPT_E_INVALID;
   *out = ctx->stats;

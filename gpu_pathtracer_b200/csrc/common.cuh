@@ -110,6 +110,7 @@ struct gpt_ctx {
   bool prof_time_stages = false, prof_count_visits = false;
   int wavefront_groups = 0;  // 0 = automatic (render.cu)
   int pipeline = -1;         // path tracer: 0 = rounds of launches, 1 = streaming (two persistent kernels), -1 = default (env GPT_PIPELINE, else by frame size)
+  int trace_defer = -1;      // path tracer: batch the triangle tests of a warp (deferred leaf tests): -1 = default (on, env GPT_TRACE_DEFER), 0 off, 1 on
   int trace_tail = -1;       // cooperative tail of the persistent trace: -1 = default (on, env GPT_TRACE_COOP), 0 off, 1 on
 };
 

@@ -19,6 +19,9 @@
 namespace {
 
 constexpr int PT_BLOCK = 128;
+#ifndef GPT_TRACE_DEFER_DEFAULT
+#define GPT_TRACE_DEFER_DEFAULT 1
+#endif
 // frames of at most this many slots per rank use the streaming pipeline by default
 #ifndef GPT_STREAM_AUTO_MAX_SLOTS
 #define GPT_STREAM_AUTO_MAX_SLOTS 0
@@ -400,14 +403,15 @@ struct QueueSource {
   }
 };
 
-template <bool COUNT, bool COOP>
+template <bool COUNT, bool COOP, bool DEFER = false>
 __global__ void __launch_bounds__(TP_BLOCK, TP_MINBLOCKS)
 k_pt_trace(QueueSource src, const float4 *__restrict__ nodes, const float4 *__restrict__ tris,
            const int *__restrict__ parent_leaf, int *next_ray, unsigned long long *counters) {
   __shared__ int stack[TP_STACK_SMEM * TP_BLOCK];
   __shared__ int coop[COOP ? (TP_BLOCK / 32) * COOP_WARP_WORDS : 1];
-  trace_persistent<COUNT, QueueSource, COOP>(nodes, tris, parent_leaf, src, next_ray, stack,
-                                             counters, coop);
+  __shared__ int defer[DEFER ? 2 * DEFER_SLOTS * TP_BLOCK : 1];
+  trace_persistent<COUNT, QueueSource, COOP, DEFER>(nodes, tris, parent_leaf, src, next_ray,
+                                                    stack, counters, coop, defer);
 }
 
 // One path vertex: the slot's hit is shaded and the slot either gets its next ray (returns
@@ -981,6 +985,12 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
     k_pt_start<<<(n + PT_BLOCK - 1) / PT_BLOCK, PT_BLOCK, 0, st>>>(ps, p, n, d_fb);
   GPT_LAUNCH_CHECK(ctx);
   const bool coop = gpt_trace_coop(ctx, mb);  // cooperative tail (trace_persistent.cuh)
+  static int env_defer = -1;  // deferred leaf tests (trace_persistent.cuh), env GPT_TRACE_DEFER
+  if (env_defer < 0) {
+    const char *e = getenv("GPT_TRACE_DEFER");
+    env_defer = e ? (atoi(e) != 0) : GPT_TRACE_DEFER_DEFAULT;
+  }
+  const bool defer_leaves = ctx->trace_defer >= 0 ? ctx->trace_defer != 0 : env_defer != 0;
   static int trace_grid = 0;
   if (!trace_grid) {
     int sms = 148, per_sm = 4;
@@ -1241,6 +1251,9 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
         int tgrid = tneed < trace_grid ? tneed : trace_grid;
         auto kern = counting ? (coop ? k_pt_trace<true, true> : k_pt_trace<true, false>)
                              : (coop ? k_pt_trace<false, true> : k_pt_trace<false, false>);
+        if (defer_leaves)
+          kern = counting ? (coop ? k_pt_trace<true, true, true> : k_pt_trace<true, false, true>)
+                          : (coop ? k_pt_trace<false, true, true> : k_pt_trace<false, false, true>);
         kern<<<tgrid, TP_BLOCK, 0, gs>>>(qs, mb.nodes, mb.tris, mb.parent_leaf, next_ray,
                                          ctx->d_counters);
       }

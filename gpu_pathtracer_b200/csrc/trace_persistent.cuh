@@ -343,17 +343,153 @@ __device__ __forceinline__ bool tp_step(const float4 *__restrict__ nodes,
     return finished;
 }
 
+// ---- deferred leaf tests (DEFER) ----------------------------------------------------------
+// ncu (profiles/r01g_k_pt_trace, source page): 82 % of the node steps are followed by a pass of
+// the ~95-instruction triangle test with 2.9 of 32 lanes on -- 43 % of the loop's issue slots.
+// Here a step only QUEUES the leaves it finds, the walk goes on with the cull bound it has,
+// and the warp runs a test pass -- every lane with a queued leaf tests its newest one -- only
+// when some lane holds more than DEFER_MAX, and empties the queues when it returns to the
+// refill point.  Closest hit with the visit-rank tie-break does not depend on the order of
+// the tests (trace_core.cuh) and a stale bound only culls less (V_int 47.8 -> 49.2, V_leaf
+// 4.98 -> 5.13 on C2), so the hits are bit-identical; a lane whose walk is over waits
+// (L.node = -1) for its queue to drain.  C2: trace stage 32.8 -> 29.1 ms at 8 spp.
+#ifndef DEFER_MAX_V
+#define DEFER_MAX_V 4
+#endif
+#ifndef DEFER_LANES_V
+#define DEFER_LANES_V 33
+#endif
+constexpr int DEFER_MAX = DEFER_MAX_V;      // a lane may keep this many leaves queued between passes (2 more arrive per step at most)
+constexpr int DEFER_LANES = DEFER_LANES_V;  // ... and a pass also runs once this many lanes have one (33 = never)
+// The queue is a per-lane LIFO in shared memory ([slot][thread], like the stack): a push is two
+// predicated stores.  (A front-packed queue in registers was measured first: its select chains
+// cost every step what the batching saved.)
+constexpr int DEFER_SLOTS = DEFER_MAX_V + 2;
+struct LeafQueue {
+  int *qi;     // [slot * TP_BLOCK]: leaf
+  float *qc;   // [slot * TP_BLOCK]: cull bound
+  int cnt = 0;
+  __device__ __forceinline__ LeafQueue(int *smem) : qi(smem + threadIdx.x), qc(reinterpret_cast<float *>(smem + DEFER_SLOTS * TP_BLOCK + threadIdx.x)) {}
+  __device__ __forceinline__ void push(int lf, float lc) {
+    if (lf >= 0) {
+      qi[cnt * TP_BLOCK] = lf;
+      qc[cnt * TP_BLOCK] = lc;
+      cnt++;
+    }
+  }
+  __device__ __forceinline__ void pop(int &lf, float &lc) {
+    cnt--;
+    lf = qi[cnt * TP_BLOCK];
+    lc = qc[cnt * TP_BLOCK];
+  }
+};
+
+// the triangle test of one queued leaf (the body of tp_step's leaf loop, same operations)
+template <bool COUNT>
+__device__ __forceinline__ void tp_leaf_test(const float4 *__restrict__ nodes,
+                                             const float4 *__restrict__ tris,
+                                             const int *__restrict__ parent_leaf, TraceLane &L,
+                                             int lf0, float lc0, unsigned &vl) {
+      if (!(lc0 > L.best)) {
+      const float4 *tp = tris + 3 * (size_t)lf0;
+      float4 t0 = __ldg(tp), t1 = __ldg(tp + 1), t2 = __ldg(tp + 2);
+      if (COUNT) vl++;
+      RaySetup r;
+      r.ox = L.ox; r.oy = L.oy; r.oz = L.oz; r.sx = L.sx; r.sy = L.sy; r.sz = L.sz; r.kz = L.kz;
+      float t, b1, b2, b3;
+      if (tri_test(r, t0, t1, t2, t, b1, b2, b3)) {
+        if (!(t > L.best) && !(t < t2.y)) {
+          bool take = true;
+          if (t == L.t && L.leaf >= 0)
+            take = leaf_visit_rank(nodes, parent_leaf, lf0) >
+                   leaf_visit_rank(nodes, parent_leaf, L.leaf);
+          if (take) {
+            L.t = t; L.leaf = lf0; L.b1 = b1; L.b2 = b2; L.b3 = b3;
+            L.prim = __float_as_int(t2.z);
+            L.best = t;
+          }
+        }
+      }
+    }
+}
+
+// tp_step without its leaf tests: the leaves found go to (lfA, lcA), (lfB, lcB)
+template <bool COUNT>
+__device__ __forceinline__ bool tp_node_step(const float4 *__restrict__ nodes, TraceLane &L,
+                                             int *stack, int *spill,
+                                             unsigned long long *counters, unsigned &vi,
+                                             int &lfA, float &lcA, int &lfB, float &lcB) {
+    const float4 *q = nodes + 4 * (size_t)L.node;
+    float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3);
+    if (COUNT) vi++;
+    int cref[2] = {__float_as_int(q3.x), __float_as_int(q3.y)};
+    // near / far bound per axis from the sign of 1/d
+    const bool nx = L.neg & 1u, ny = L.neg & 2u, nz = L.neg & 4u;
+    float xn[2] = {nx ? q0.y : q0.x, nx ? q1.w : q1.z}, xf[2] = {nx ? q0.x : q0.y, nx ? q1.z : q1.w};
+    float yn[2] = {ny ? q0.w : q0.z, ny ? q2.y : q2.x}, yf[2] = {ny ? q0.z : q0.w, ny ? q2.x : q2.y};
+    float zn[2] = {nz ? q1.y : q1.x, nz ? q2.w : q2.z}, zf[2] = {nz ? q1.x : q1.y, nz ? q2.z : q2.w};
+    bool go[2];
+    float tnear[2], tcull[2];
+#pragma unroll
+    for (int c = 0; c < 2; c++) {
+      float txn = (xn[c] - L.ox) * L.ix, txx = (xf[c] - L.ox) * L.ix;
+      float tyn = (yn[c] - L.oy) * L.iy, tyx = (yf[c] - L.oy) * L.iy;
+      float tzn = (zn[c] - L.oz) * L.iz, tzx = (zf[c] - L.oz) * L.iz;
+      bool ok = (txn <= tyx) && (tyn <= txx);
+      float txyn = fmaxf(txn, tyn), txyx = fminf(txx, tyx);
+      ok = ok && (txyn <= tzx) && (tzn <= txyx);
+      float tn = L.kz == 0 ? txn : (L.kz == 1 ? tyn : tzn);
+      float tf = L.kz == 0 ? txx : (L.kz == 1 ? tyx : tzx);
+      float margin = 1e-5f * fmaxf(fabsf(tn), fabsf(tf));
+      tnear[c] = tn;
+      tcull[c] = tn - margin;
+      go[c] = ok && !(tf + margin < 0.f);
+    }
+    lfA = (go[0] && cref[0] < 0) ? ~cref[0] : -1;
+    lfB = (go[1] && cref[1] < 0) ? ~cref[1] : -1;
+    lcA = tcull[0]; lcB = tcull[1];
+    // Internal children, written to compile into predicated code rather than a three-way
+    // divergent branch (push / step / pop): near child first, far child pushed.
+    const bool gl = go[0] && cref[0] >= 0 && !(tcull[0] > L.best);
+    const bool gr = go[1] && cref[1] >= 0 && !(tcull[1] > L.best);
+    const bool both = gl && gr, any = gl || gr;
+    const bool lfirst = tnear[0] <= tnear[1];
+    const int nearc = (gl && (!gr || lfirst)) ? cref[0] : cref[1];
+    const int farc = lfirst ? cref[1] : cref[0];
+    if (both && L.sp < TP_STACK_SMEM) stack[L.sp * TP_BLOCK] = farc;
+#if TP_PREFETCH
+    if (both && farc >= 0) {
+      const float4 *fq = nodes + 4 * (size_t)farc;
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(fq));
+    }
+#endif
+    if (both && L.sp >= TP_STACK_SMEM) {  // rare: deeper than the shared-memory levels
+      if (L.sp < TRACE_STACK) spill[L.sp - TP_STACK_SMEM] = farc;
+      else atomicExch(counters + 3, 1ull);
+    }
+    if (both && L.sp < TRACE_STACK) L.sp++;
+    const bool finished = !any && L.sp == 0;
+    if (any) {
+      L.node = nearc;
+    } else if (L.sp > 0) {
+      L.sp--;
+      L.node = L.sp < TP_STACK_SMEM ? stack[L.sp * TP_BLOCK] : spill[L.sp - TP_STACK_SMEM];
+    }
+    return finished;
+}
+
 // Source concept:
 //   int count() const;                       number of rays in the queue
 //   void load(int i, float4 &o, float4 &d);  ray i: {o, tmax}{unit d, -}
 //   void store(int i, const TraceLane &l);   hit record of ray i
-template <bool COUNT, class Source, bool COOP = false>
+template <bool COUNT, class Source, bool COOP = false, bool DEFER = false>
 __device__ __forceinline__ void trace_persistent(const float4 *__restrict__ nodes,
                                                  const float4 *__restrict__ tris,
                                                  const int *__restrict__ parent_leaf,
                                                  Source src, int *next_ray, int *stack_smem,
                                                  unsigned long long *counters,
-                                                 int *coop_smem = nullptr) {
+                                                 int *coop_smem = nullptr,
+                                                 int *defer_smem = nullptr) {
   const unsigned FULL = 0xffffffffu;
   const int lane = threadIdx.x & 31;
   const int n = src.count();
@@ -407,16 +543,60 @@ __device__ __forceinline__ void trace_persistent(const float4 *__restrict__ node
     // (postponing leaf tests into separate warp-wide "intersect rounds" was measured and was
     //  10-20 % SLOWER on C2 -- the extra rounds and votes cost more than the divergence they
     //  remove with one triangle per leaf -- so leaves are tested where they are found.)
-    while (true) {
-      if (L.ray >= 0) {
-        if (tp_step<COUNT>(nodes, tris, parent_leaf, L, stack, spill, counters, vi, vl)) {
+    if constexpr (!DEFER) {
+      while (true) {
+        if (L.ray >= 0) {
+          if (tp_step<COUNT>(nodes, tris, parent_leaf, L, stack, spill, counters, vi, vl)) {
+            src.store(L.ray, L);
+            L.ray = -1;
+          }
+        }
+        unsigned nidle = __popc(__ballot_sync(FULL, L.ray < 0));
+        if (nidle == 32 || (!exhausted && nidle >= TP_REFILL)) break;
+        if (COOP && exhausted && nidle >= 32 - COOP_SLOTS) break;
+      }
+    } else {
+      LeafQueue Q(defer_smem);
+      while (true) {
+        if (L.ray >= 0 && L.node >= 0) {
+          int lfA, lfB;
+          float lcA, lcB;
+          if (tp_node_step<COUNT>(nodes, L, stack, spill, counters, vi, lfA, lcA, lfB, lcB))
+            L.node = -1;  // walk over; the record is stored once the queue is empty
+          Q.push(lfA, lcA);
+          Q.push(lfB, lcB);
+        }
+        bool pass = __ballot_sync(FULL, Q.cnt > DEFER_MAX) != 0;
+        if (DEFER_LANES <= 32 && !pass) pass = __popc(__ballot_sync(FULL, Q.cnt > 0)) >= DEFER_LANES;
+        while (pass) {
+          if (Q.cnt > 0) {
+            int lf;
+            float lc;
+            Q.pop(lf, lc);
+            tp_leaf_test<COUNT>(nodes, tris, parent_leaf, L, lf, lc, vl);
+          }
+          pass = __ballot_sync(FULL, Q.cnt > DEFER_MAX) != 0;
+        }
+        if (L.ray >= 0 && L.node < 0 && Q.cnt == 0) {
           src.store(L.ray, L);
           L.ray = -1;
         }
+        const int nwalk = __popc(__ballot_sync(FULL, L.ray >= 0 && L.node >= 0));
+        if (nwalk == 0 || (!exhausted && 32 - nwalk >= TP_REFILL)) break;
+        if (COOP && exhausted && nwalk <= COOP_SLOTS) break;
       }
-      unsigned nidle = __popc(__ballot_sync(FULL, L.ray < 0));
-      if (nidle == 32 || (!exhausted && nidle >= TP_REFILL)) break;
-      if (COOP && exhausted && nidle >= 32 - COOP_SLOTS) break;
+      while (__ballot_sync(FULL, Q.cnt > 0)) {  // back at the refill point with empty queues
+        if (Q.cnt > 0) {
+          int lf;
+          float lc;
+          Q.pop(lf, lc);
+          tp_leaf_test<COUNT>(nodes, tris, parent_leaf, L, lf, lc, vl);
+        }
+      }
+      if (L.ray >= 0 && L.node < 0) {
+        src.store(L.ray, L);
+        L.ray = -1;
+      }
     }
   }
   if (COOP && coop_live)

@@ -324,6 +324,15 @@ int gpt_set_wavefront_groups(gpt_ctx *ctx, int groups);
  * environment variable GPT_TRACE_COOP=0.  Hits are bit-identical either way: closest hit with
  * the reference's visit-rank tie-break does not depend on the order nodes are visited in. */
 int gpt_set_trace_tail(gpt_ctx *ctx, int mode);
+/* Path tracer's trace stage (traverse_bvh + Triangle::hit, src/model/bvh/bvh_traversal.h:12-84,
+ * src/model/geometry/triangle.h:343-408).  1: a traversal step only queues the leaves it finds
+ * (per-lane LIFO in shared memory) and the warp runs the triangle test for all its lanes
+ * together once a lane holds more than 4 -- the test is ~95 instructions and, done where the
+ * leaf is found, runs with ~3 of 32 lanes on.  0: every leaf is tested where it is found.
+ * -1 (default): on, unless the environment variable GPT_TRACE_DEFER=0.  Hits are bit-identical
+ * either way (closest hit with the reference's visit-rank tie-break does not depend on the
+ * order of the tests; a later test only means a looser cull bound in between). */
+int gpt_set_trace_leaf_batching(gpt_ctx *ctx, int mode);
 /* How gpt_render_pathtrace* runs path_tracing_render's dof x spp x level loop
  * (src/render/pathtracing.h:251-305).
  *   0 "rounds":  one round of launches (trace, material sort, shade) per bounce of every pixel,

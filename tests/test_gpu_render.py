@@ -112,6 +112,32 @@ def test_wavefront_groups_do_not_change_the_image():
     pt.set_wavefront_groups(0)
 
 
+def test_leaf_batching_does_not_change_the_image():
+    """gpt_set_trace_leaf_batching: the trace stage queues the leaves a step finds and tests them
+    for the whole warp together.  Frame and ray count equal the test-where-found walk bit for
+    bit, with and without the cooperative tail, with 1 and 4 groups, on glass, on C2's mixed
+    materials and with depth of field; and the batched frame still matches the reference replay."""
+    from gpu_pathtracer_b200.api import PathTracer
+    scenes = (S.make_scene("small", n=20, width=200, height=136, spp=3, level=6),
+              S.make_scene("C2", n=60, width=160, height=96, spp=2, tex=64, n_spheres=8),
+              S.make_scene("C3", width=96, height=64, spp=2, dof=2, level=6))
+    for sc in scenes:
+        pt = PathTracer(sc)
+        pt.build()
+        pt.set_trace_leaf_batching(0)
+        base = pt.render_pathtrace()
+        rays = pt.stats()["rays_traced"]
+        pt.set_trace_leaf_batching(1)
+        for tail in (0, 1):
+            pt.set_trace_tail(tail)
+            for groups in (1, 4):
+                pt.set_wavefront_groups(groups)
+                img = pt.render_pathtrace()
+                assert np.array_equal(img.view(np.uint32), base.view(np.uint32)), (sc.name, tail, groups)
+                assert pt.stats()["rays_traced"] == rays, (sc.name, tail, groups)
+    _compare(S.make_scene("small", n=16, width=96, height=104, spp=2, level=4))  # default = batched
+
+
 def test_streaming_pipeline_is_bit_identical():
     """gpt_set_pipeline(1): trace and shade as two persistent kernels exchanging pixel slots
     through rings (per-material rings towards shade) instead of rounds of launches.  Same frame

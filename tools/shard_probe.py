@@ -3,6 +3,7 @@ split of the C2 frame with 1, 2, 4, 8 wavefront groups, then once with stage tim
 Usage: PYTHONPATH=. python tools/shard_probe.py [--nranks 8] [--spp 16] [--groups 1,2,4,8]
        [--frames 1]  (--frames 1 --groups 4 --no-stage is the form to run under ncu)"""
 import argparse
+import hashlib
 import json
 import time
 
@@ -38,7 +39,8 @@ def run(nr, label):
     ms = (time.perf_counter() - t0) / a.frames * 1e3
     st = pt.stats()
     rec = {"nranks": nr, **label, "frame_ms": round(ms, 2), "rays": st["rays_traced"],
-           "Mrays_s": round(st["rays_traced"] / ms / 1e3, 1), "launches": st["kernel_launches"]}
+           "Mrays_s": round(st["rays_traced"] / ms / 1e3, 1), "launches": st["kernel_launches"],
+           "frame_sha1": hashlib.sha1(fb.cpu().numpy().tobytes()).hexdigest()[:12]}
     return rec, st
 
 
