@@ -224,3 +224,4 @@ int gpt_radix_sort_pairs(gpt_ctx *ctx, uint32_t *keys, int *vals, uint32_t *keys
                          const int *d_n = nullptr);  // d_n: exact count on the device (n = bound)
 int gpt_radix_hist_entries(int n);
 bool gpt_trace_coop(const gpt_ctx *ctx, const BvhDev &b);  // trace.cu
+bool gpt_trace_defer(const gpt_ctx *ctx);                   // trace.cu

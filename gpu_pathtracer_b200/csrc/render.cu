@@ -19,9 +19,6 @@
 namespace {
 
 constexpr int PT_BLOCK = 128;
-#ifndef GPT_TRACE_DEFER_DEFAULT
-#define GPT_TRACE_DEFER_DEFAULT 1
-#endif
 // frames of at most this many slots per rank use the streaming pipeline by default
 #ifndef GPT_STREAM_AUTO_MAX_SLOTS
 #define GPT_STREAM_AUTO_MAX_SLOTS 0
@@ -985,12 +982,7 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
     k_pt_start<<<(n + PT_BLOCK - 1) / PT_BLOCK, PT_BLOCK, 0, st>>>(ps, p, n, d_fb);
   GPT_LAUNCH_CHECK(ctx);
   const bool coop = gpt_trace_coop(ctx, mb);  // cooperative tail (trace_persistent.cuh)
-  static int env_defer = -1;  // deferred leaf tests (trace_persistent.cuh), env GPT_TRACE_DEFER
-  if (env_defer < 0) {
-    const char *e = getenv("GPT_TRACE_DEFER");
-    env_defer = e ? (atoi(e) != 0) : GPT_TRACE_DEFER_DEFAULT;
-  }
-  const bool defer_leaves = ctx->trace_defer >= 0 ? ctx->trace_defer != 0 : env_defer != 0;
+  const bool defer_leaves = gpt_trace_defer(ctx);  // deferred leaf tests (trace_persistent.cuh)
   static int trace_grid = 0;
   if (!trace_grid) {
     int sms = 148, per_sm = 4;

@@ -431,14 +431,15 @@ struct PhotonRaySource {
   }
 };
 
-template <bool COUNT, bool COOP>
+template <bool COUNT, bool COOP, bool DEFER = false>
 __global__ void __launch_bounds__(TP_BLOCK, TP_MINBLOCKS)
 k_ph_trace(PhotonRaySource src, const float4 *__restrict__ nodes, const float4 *__restrict__ tris,
            const int *__restrict__ parent_leaf, int *next_ray, unsigned long long *counters) {
   __shared__ int stack[TP_STACK_SMEM * TP_BLOCK];
   __shared__ int coop[COOP ? (TP_BLOCK / 32) * COOP_WARP_WORDS : 1];
-  trace_persistent<COUNT, PhotonRaySource, COOP>(nodes, tris, parent_leaf, src, next_ray, stack,
-                                                 counters, coop);
+  __shared__ int defer[DEFER ? 2 * DEFER_SLOTS * TP_BLOCK : 1];
+  trace_persistent<COUNT, PhotonRaySource, COOP, DEFER>(nodes, tris, parent_leaf, src, next_ray,
+                                                        stack, counters, coop, defer);
 }
 
 enum { PH_NEW = 0, PH_MEDIUM = 1, PH_SURFACE = 2, PH_INIT = 3 };  // where a photon resumes
@@ -1589,6 +1590,9 @@ static int photon_stage(gpt_ctx *ctx, SppmCtx *sx, const SppmScene &S, const Pho
     const bool coop = gpt_trace_coop(ctx, tree);
     auto kern = count_visits ? (coop ? k_ph_trace<true, true> : k_ph_trace<true, false>)
                              : (coop ? k_ph_trace<false, true> : k_ph_trace<false, false>);
+    if (gpt_trace_defer(ctx))
+      kern = count_visits ? (coop ? k_ph_trace<true, true, true> : k_ph_trace<true, false, true>)
+                          : (coop ? k_ph_trace<false, true, true> : k_ph_trace<false, false, true>);
     kern<<<grid, TP_BLOCK, 0, st>>>(src, tree.nodes, tree.tris, tree.parent_leaf, cursor,
                                     ctx->d_counters);
     GPT_LAUNCH_CHECK(ctx);

@@ -30,15 +30,17 @@ struct ArraySource {
   }
 };
 
-template <bool NORMALIZE, bool COUNT, bool COOP>
+template <bool NORMALIZE, bool COUNT, bool COOP, bool DEFER>
 __global__ void __launch_bounds__(TP_BLOCK, TP_MINBLOCKS)
 k_trace(const float4 *__restrict__ nodes, const float4 *__restrict__ tris,
         const int *__restrict__ parent_leaf, ArraySource<NORMALIZE> src, int *next_ray,
         unsigned long long *counters) {
   __shared__ int stack[TP_STACK_SMEM * TP_BLOCK];
   __shared__ int coop[COOP ? (TP_BLOCK / 32) * COOP_WARP_WORDS : 1];
-  trace_persistent<COUNT, ArraySource<NORMALIZE>, COOP>(nodes, tris, parent_leaf, src, next_ray,
-                                                        stack, counters, coop);
+  __shared__ int defer[DEFER ? 2 * DEFER_SLOTS * TP_BLOCK : 1];
+  trace_persistent<COUNT, ArraySource<NORMALIZE>, COOP, DEFER>(nodes, tris, parent_leaf, src,
+                                                               next_ray, stack, counters, coop,
+                                                               defer);
 }
 
 template <class K>
@@ -65,6 +67,17 @@ bool gpt_trace_coop(const gpt_ctx *ctx, const BvhDev &b) {
   return on && b.n < (1 << COOP_NODE_BITS);
 }
 
+// Whether the persistent trace kernels batch a warp's triangle tests (deferred leaf tests,
+// trace_persistent.cuh): on unless gpt_set_trace_leaf_batching / GPT_TRACE_DEFER=0 says otherwise.
+bool gpt_trace_defer(const gpt_ctx *ctx) {
+  static int env = -1;
+  if (env < 0) {
+    const char *e = getenv("GPT_TRACE_DEFER");
+    env = e ? (atoi(e) != 0) : 1;
+  }
+  return ctx->trace_defer >= 0 ? ctx->trace_defer != 0 : env != 0;
+}
+
 int gpt_trace_launch(gpt_ctx *ctx, int which, const float4 *d_rays, int64_t n, float4 *d_hits,
                      bool normalize, bool count) {
   if (which < 0 || which > 2) return gpt_fail(ctx, GPT_E_INVALID, "bad BVH id", __FILE__, __LINE__);
@@ -78,17 +91,19 @@ int gpt_trace_launch(gpt_ctx *ctx, int which, const float4 *d_rays, int64_t n, f
   GPT_CUDA(ctx, cudaMemsetAsync(next_ray, 0, sizeof(int), ctx->stream));
   cudaStream_t st = ctx->stream;
   const bool coop = gpt_trace_coop(ctx, b);
-#define GPT_TRACE_LAUNCH(NORM, CNT, COOP)                                                  \
+  const bool defer = gpt_trace_defer(ctx);
+#define GPT_TRACE_LAUNCH(NORM, CNT, COOP, DEFER)                                           \
   do {                                                                                     \
-    static int grid = persistent_grid(k_trace<NORM, CNT, COOP>);                           \
+    static int grid = persistent_grid(k_trace<NORM, CNT, COOP, DEFER>);                    \
     long long need = (n + TP_BLOCK - 1) / TP_BLOCK;                                        \
     ArraySource<NORM> src{d_rays, d_hits, (int)n};                                         \
-    k_trace<NORM, CNT, COOP><<<(unsigned)(need < grid ? need : grid), TP_BLOCK, 0, st>>>(  \
+    k_trace<NORM, CNT, COOP, DEFER><<<(unsigned)(need < grid ? need : grid), TP_BLOCK, 0, st>>>( \
         b.nodes, b.tris, b.parent_leaf, src, next_ray, c);                                 \
   } while (0)
 #define GPT_TRACE_LAUNCH2(NORM, CNT)                                                       \
   do {                                                                                     \
-    if (coop) GPT_TRACE_LAUNCH(NORM, CNT, true); else GPT_TRACE_LAUNCH(NORM, CNT, false);  \
+    if (coop) { if (defer) GPT_TRACE_LAUNCH(NORM, CNT, true, true); else GPT_TRACE_LAUNCH(NORM, CNT, true, false); } \
+    else { if (defer) GPT_TRACE_LAUNCH(NORM, CNT, false, true); else GPT_TRACE_LAUNCH(NORM, CNT, false, false); } \
   } while (0)
   if (normalize) { if (count) GPT_TRACE_LAUNCH2(true, true); else GPT_TRACE_LAUNCH2(true, false); }
   else { if (count) GPT_TRACE_LAUNCH2(false, true); else GPT_TRACE_LAUNCH2(false, false); }

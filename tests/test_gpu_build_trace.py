@@ -107,8 +107,9 @@ def _doubled(sc):
 @pytest.mark.parametrize("scene_kind", ["small", "doubled", "C1"])
 def test_trace_tail_modes_agree(scene_kind):
     """The cooperative tail of the persistent trace (gpt_set_trace_tail) visits nodes in another
-    order than the per-lane walk; hits must be bit-identical, ties included, and equal to the
-    reference replay where that is affordable."""
+    order than the per-lane walk, and the batched triangle tests (gpt_set_trace_leaf_batching) test
+    leaves later than they are found; hits must be bit-identical, ties included, and equal to
+    the reference replay where that is affordable."""
     from gpu_pathtracer_b200.api import PathTracer
     sc = S.make_scene("C1") if scene_kind == "C1" else S.make_scene("small", n=40, textured=True)
     if scene_kind == "doubled":
@@ -119,21 +120,26 @@ def test_trace_tail_modes_agree(scene_kind):
     sets = [rays.random_rays(50000), rays.edge_case_rays(sc, 8192), rays.camera_rays(sc)[::3].copy(),
             rays.random_rays(37)]
     out = {}
-    for mode in (0, 1):
-        pt.set_trace_tail(mode)
+    # ... and the same for the batched triangle tests (gpt_set_trace_leaf_batching): every
+    # (tail, batching) combination against (0, 0), the plain test-where-found walk
+    for mode in (0, 1, 2, 3):
+        pt.set_trace_tail(mode & 1)
+        pt.set_trace_leaf_batching(mode >> 1)
         trees = (cabi.GPT_BVH_MAIN,) if scene_kind == "C1" else (cabi.GPT_BVH_MAIN, cabi.GPT_BVH_TRANSPARENT)
         out[mode] = [pt.trace(r, w) for r in sets for w in trees]
     pt.set_trace_tail(-1)
-    for a, b in zip(out[0], out[1]):
-        for k in ("leaf_id", "tri_id", "t", "bary"):
-            _eq(a[k], b[k], f"{scene_kind} {k}")
+    pt.set_trace_leaf_batching(-1)
+    for mode in (1, 2, 3):
+        for a, b in zip(out[0], out[mode]):
+            for k in ("leaf_id", "tri_id", "t", "bary"):
+                _eq(a[k], b[k], f"{scene_kind} mode {mode} {k}")
     assert any((a["tri_id"] >= 0).any() for a in out[1])
     if scene_kind == "doubled":
         from tests.refreplay import RefReplay
         ref = RefReplay(sc)
         want = ref.trace(sets[0], cabi.GPT_BVH_MAIN)
-        _eq(out[1][0]["leaf_id"], want["leaf_id"], "doubled vs replay leaf_id")
-        _eq(out[1][0]["t"], want["t"], "doubled vs replay t")
+        _eq(out[3][0]["leaf_id"], want["leaf_id"], "doubled vs replay leaf_id")
+        _eq(out[3][0]["t"], want["t"], "doubled vs replay t")
 
 
 def test_against_committed_golden_vectors():
