@@ -27,7 +27,7 @@ constexpr int TP_BLOCK = TP_BLOCK_V;  // threads per persistent trace block (a b
 #endif
 constexpr int TP_STACK_SMEM = TP_STACK_SMEM_V;   // levels kept in shared memory; deeper levels spill to local
 #ifndef TP_REFILL_V
-#define TP_REFILL_V 20
+#define TP_REFILL_V 12
 #endif
 constexpr int TP_REFILL = TP_REFILL_V;  // idle lanes that trigger a refill
 
