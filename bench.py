@@ -500,8 +500,22 @@ def main():
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         torch.cuda.set_device(local_rank)
-        dist.init_process_group("nccl", rank=rank, world_size=world,
-                                device_id=torch.device(f"cuda:{local_rank}"))
+        # NCCL prints its version banner on STDOUT when the communicator comes up (NCCL_DEBUG =
+        # VERSION on the pool's boxes); the contract is ONE JSON line there, so stdout points at
+        # stderr until the first collective has run
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", rank=rank, world_size=world,
+                                    device_id=torch.device(f"cuda:{local_rank}"))
+            warm = torch.zeros(1, device=f"cuda:{local_rank}")
+            dist.all_reduce(warm)
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved_stdout, 1)
+            os.close(saved_stdout)
     try:
         if args.workload == "C4":
             run_sppm(args, rank, world, local_rank)
