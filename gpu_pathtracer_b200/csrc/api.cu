@@ -161,6 +161,8 @@ int gpt_set_materials(gpt_ctx *ctx, const GptMaterials *m) {
     d.ke[0] = m->ke_x[i]; d.ke[1] = m->ke_y[i]; d.ke[2] = m->ke_z[i];
     d.tf[0] = m->tf_x[i]; d.tf[1] = m->tf_y[i]; d.tf[2] = m->tf_z[i];
     d.path_length = m->path_length[i];
+    if (i == 0) ctx->max_path_length = 0.f;
+    if (d.path_length > ctx->max_path_length) ctx->max_path_length = d.path_length;
     d.t_r = m->t_r[i];
     d.n_i = m->n_i[i];
     d.bm = m->bm[i];

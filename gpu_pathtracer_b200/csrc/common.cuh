@@ -108,6 +108,7 @@ struct gpt_ctx {
   std::vector<int> obj_num, obj_off;         // object_num_primitives / object_primitive_offset_idx
   uint64_t launches = 0;                     // kernels launched since last reset
   bool prof_time_stages = false, prof_count_visits = false;
+  float max_path_length = 0.f;  // largest sub-surface lookup radius of the materials (sss.cu grid)
   int wavefront_groups = 0;  // 0 = automatic (render.cu)
   int pipeline = -1;         // path tracer: 0 = rounds of launches, 1 = streaming (two persistent kernels), -1 = default (env GPT_PIPELINE, else by frame size)
   int trace_defer = -1;      // path tracer: batch the triangle tests of a warp (deferred leaf tests): -1 = default (on, env GPT_TRACE_DEFER), 0 off, 1 on
@@ -202,6 +203,17 @@ struct SssTree {           // per scene OBJECT; n == 0 for objects without sub-s
   const float4 *snodes;
   const float4 *spos;
   const int *visit;
+  // candidate grid (ours): the same (location, visit position) records sorted by the cell of a
+  // uniform grid over the object's points, cell edge >= the largest lookup radius of the scene;
+  // gstart[c] .. gstart[c + 1] = the records of cell c = x + gnx * (y + gny * z).
+  // gpos == nullptr: no grid, the search tree finds the candidates.
+  const float4 *gpos;
+  const int *gstart;
+  float gox, goy, goz, ginv;
+  int gnx, gny, gnz;
+  // the leaf records once more, in VISIT order (vleaf[2 k] = leaf[2 visit[k]]; filled after the
+  // first pass wrote the colours): the ordered sum of a lookup reads them front to back
+  const float4 *vleaf;
 };
 struct SssView {
   const SssTree *trees;    // device, one per object; nullptr when the scene has no SSS points

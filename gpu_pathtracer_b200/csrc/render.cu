@@ -252,6 +252,44 @@ static __device__ __noinline__ V3 sss_lookup_ref_walk(const SssTree &t, V3 c, fl
 // that walk in a private bitmap, then add them up by scanning the bitmap in increasing order.  Same terms, same order, same result; ~100x fewer node visits.  The bitmap comes
 // from a pool (probe + atomicCAS); with the pool exhausted the reference walk above runs.
 __device__ int g_sss_debug_mode = 0;  // 0 fast, 1 reference walk, 2 skip (timing experiments)
+// SssTree grid: the cell of a coordinate -- the same expression as grid_cell() in sss.cu
+__device__ __forceinline__ int sss_grid_cell(float x, float o, float inv, int n) {
+  float f = floorf((x - o) * inv);
+  return f < 0.f ? 0 : (f >= (float)n ? n - 1 : (int)f);
+}
+// Candidates from the uniform grid (sss.cu build_candidate_grid): the cells the sphere's box
+// touches -- at most 3 per axis, the cell edge is >= every lookup radius -- are runs of
+// consecutive records along x, read with independent 16-byte loads instead of ~4000 DEPENDENT
+// node fetches of the search tree.  The cell of a coordinate is the same fp32 expression as on
+// the host and monotone in it, and the box is widened by more than the rounding of dist(), so
+// no accepted point is missed.  (Its own function: inlined, it changed the register allocation
+// of the whole shade kernel, 96 -> 72 with spills.)
+static __device__ __noinline__ void sss_mark_grid(const SssTree &t, V3 c, float r, uint32_t *bm,
+                                                  int &wlo_out, int &whi_out) {
+  int wlo = wlo_out, whi = whi_out;
+  const float g = 1e-5f * (fabsf(c.x) + fabsf(c.y) + fabsf(c.z) + r + 1.f);
+  const float lo = r + g;
+  int x0 = sss_grid_cell(c.x - lo, t.gox, t.ginv, t.gnx), x1 = sss_grid_cell(c.x + lo, t.gox, t.ginv, t.gnx);
+  int y0 = sss_grid_cell(c.y - lo, t.goy, t.ginv, t.gny), y1 = sss_grid_cell(c.y + lo, t.goy, t.ginv, t.gny);
+  int z0 = sss_grid_cell(c.z - lo, t.goz, t.ginv, t.gnz), z1 = sss_grid_cell(c.z + lo, t.goz, t.ginv, t.gnz);
+  for (int z = z0; z <= z1; z++)
+    for (int y = y0; y <= y1; y++) {
+      const int row = t.gnx * (y + t.gny * z);
+      const int jb = __ldg(t.gstart + row + x0), je = __ldg(t.gstart + row + x1 + 1);
+      for (int j = jb; j < je; j++) {
+        float4 a = __ldg(t.gpos + j);
+        float d = dist(c, V3{a.x, a.y, a.z});
+        if (d <= r) {
+          int i = __float_as_int(a.w);
+          bm[i >> 5] |= 1u << (i & 31);
+          wlo = min(wlo, i >> 5);
+          whi = max(whi, i >> 5);
+        }
+      }
+    }
+  wlo_out = wlo;
+  whi_out = whi;
+}
 struct BitmapPool {  // by value: a reference into the kernel parameters would be spilled
   uint32_t *bm_pool;
   int *bm_busy;
@@ -276,6 +314,9 @@ static __device__ __noinline__ V3 sss_lookup(BitmapPool sv, const SssTree &t, V3
   int wlo = sv.bm_words, whi = -1;
   int stack[64];
   int sp = 0, node = 0;
+  if (t.gpos) {
+    sss_mark_grid(t, c, r, bm, wlo, whi);
+  } else
   while (true) {
     const float4 *q = t.snodes + 4 * (size_t)node;
     float4 q0 = __ldg(q), q1 = __ldg(q + 1), q2 = __ldg(q + 2), q3 = __ldg(q + 3);
@@ -326,9 +367,9 @@ static __device__ __noinline__ V3 sss_lookup(BitmapPool sv, const SssTree &t, V3
     while (bits) {
       int b = __ffs(bits) - 1;
       bits &= bits - 1;
-      const float4 *lf = t.leaf + 2 * (size_t)__ldg(t.visit + 32 * w + b);
-      float4 a = __ldg(lf);
-      float4 col = lf[1];  // written by the first pass of this launch sequence: no __ldg
+      const float4 *lf = t.vleaf + 2 * (size_t)(32 * w + b);  // visit order: no index load, neighbours share lines
+      float4 a = lf[0];
+      float4 col = lf[1];  // written after the first pass of this launch sequence: no __ldg
       found = true;
       float wgt = 1.0f / dist(V3{a.x, a.y, a.z}, c);
       wgt = (float)fmin(9999.99, (double)wgt);
@@ -552,7 +593,7 @@ __device__ __forceinline__ bool shade_slot(const PathState &ps, const RenderPara
 }
 #undef PS_LD
 
-__global__ void __launch_bounds__(PT_BLOCK)
+__global__ void __launch_bounds__(PT_BLOCK, 5)  // 5 blocks per SM = the 96-register form (ptxas picks 72 + spills or 114 on its own, both slower)
 k_pt_shade(PathState ps, RenderParams p, const int *__restrict__ queue,
            const int *__restrict__ count, int *next_queue, int *next_count, SceneDev sc,
            TexAtlas atlas, const float4 *__restrict__ main_tris, LightTree lt, float *fb,

@@ -27,6 +27,8 @@ struct SssObj {
   int obj = 0, tri_off = 0, tri_num = 0, pt_off = 0;
   BvhDev bvh;      // the reference's tree (degenerate keys, see k_sss_morton)
   BvhDev search;   // same points, true Morton keys: finds the candidates of a lookup fast
+  float4 *gpos = nullptr;  // candidate grid (SssTree::gpos / gstart)
+  int *gstart = nullptr;
 };
 
 struct SssCtx {
@@ -43,6 +45,8 @@ struct SssCtx {
   int *rank = nullptr;         // pts scratch: creation index -> leaf-order index
   int *leafpos = nullptr;      // pts scratch: leaf-order index -> position in the reference walk
   int *visit = nullptr;        // npoints: position in the walk -> leaf-order index, per object
+  int *visit_global = nullptr; // the same with the object's point offset added (index into leaf)
+  float4 *vleaf = nullptr;     // 2 x npoints: leaf records in visit order (after the first pass)
   uint32_t *vkeys = nullptr, *vkeys_alt = nullptr, *vhist = nullptr;  // pts scratch (rank sort)
   int *vvals = nullptr, *vvals_alt = nullptr;
   uint32_t *bm_pool = nullptr;
@@ -199,14 +203,81 @@ SssCtx *sss_of(gpt_ctx *ctx) { return static_cast<SssCtx *>(ctx->sss_state); }
 
 }  // namespace
 
+// The cell a coordinate falls in; host and device (render.cu sss_lookup) must agree bit for bit,
+// so it is ONE expression of non-contracted fp32 operations: floorf((x - origin) * inv), clamped.
+static inline int grid_cell(float x, float o, float inv, int n) {
+  float f = floorf((x - o) * inv);
+  int c = f < 0.f ? 0 : (f >= (float)n ? n - 1 : (int)f);
+  return c;
+}
+
+// Candidate grid of one SSS object (SssTree::gpos / gstart): built on the host from the search
+// records -- 10^5 points, once per build -- by a counting sort over the cells.
+static int build_candidate_grid(gpt_ctx *ctx, SssObj &so, const float4 *d_spos, int pts, SssTree &tr) {
+  static int use_grid = -1;
+  if (use_grid < 0) {
+    const char *e = getenv("GPT_SSS_GRID");
+    use_grid = e ? atoi(e) : 1;
+  }
+  if (!use_grid || pts < 2 || !(ctx->max_path_length > 0.f)) return GPT_OK;
+  std::vector<float4> h((size_t)pts);
+  GPT_CUDA(ctx, cudaMemcpyAsync(h.data(), d_spos, sizeof(float4) * (size_t)pts, cudaMemcpyDeviceToHost, ctx->stream));
+  GPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  float lo[3] = {h[0].x, h[0].y, h[0].z}, hi[3] = {h[0].x, h[0].y, h[0].z};
+  for (const float4 &q : h) {
+    const float v[3] = {q.x, q.y, q.z};
+    for (int a = 0; a < 3; a++) {
+      if (!(v[a] == v[a]) || fabsf(v[a]) > 1e30f) return GPT_OK;  // not a finite cloud: keep the tree
+      lo[a] = fminf(lo[a], v[a]);
+      hi[a] = fmaxf(hi[a], v[a]);
+    }
+  }
+  float cell = ctx->max_path_length;
+  for (int a = 0; a < 3; a++) cell = fmaxf(cell, (hi[a] - lo[a]) / 200.f);  // <= ~200 cells per axis
+  if (!(cell > 0.f)) return GPT_OK;
+  const float inv = 1.0f / cell;
+  int n[3];
+  for (int a = 0; a < 3; a++) {
+    n[a] = (int)floorf((hi[a] - lo[a]) * inv) + 1;
+    if (n[a] < 1) n[a] = 1;
+    if (n[a] > 256) n[a] = 256;
+  }
+  const size_t ncell = (size_t)n[0] * n[1] * n[2];
+  std::vector<int> start(ncell + 1, 0), cid((size_t)pts);
+  for (int j = 0; j < pts; j++) {
+    int cx = grid_cell(h[j].x, lo[0], inv, n[0]), cy = grid_cell(h[j].y, lo[1], inv, n[1]),
+        cz = grid_cell(h[j].z, lo[2], inv, n[2]);
+    cid[j] = cx + n[0] * (cy + n[1] * cz);
+    start[(size_t)cid[j] + 1]++;
+  }
+  for (size_t c = 0; c < ncell; c++) start[c + 1] += start[c];
+  std::vector<int> fill(start.begin(), start.end() - 1);
+  std::vector<float4> sorted((size_t)pts);
+  for (int j = 0; j < pts; j++) sorted[(size_t)fill[cid[j]]++] = h[j];
+  GPT_TRY(gpt_upload(ctx, &so.gpos, sorted.data(), sorted.size()));
+  GPT_TRY(gpt_upload(ctx, &so.gstart, start.data(), start.size()));
+  GPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // the uploads read the vectors above
+  tr.gpos = so.gpos;
+  tr.gstart = so.gstart;
+  tr.gox = lo[0]; tr.goy = lo[1]; tr.goz = lo[2];
+  tr.ginv = inv;
+  tr.gnx = n[0]; tr.gny = n[1]; tr.gnz = n[2];
+  return GPT_OK;
+}
+
 extern "C" void gpt_sss_free(gpt_ctx *ctx) {
   if (!ctx || !ctx->sss_state) return;
   SssCtx *sx = sss_of(ctx);
   void *p[] = {sx->cdf, sx->rng, sx->pts_created, sx->pts, sx->leaf, sx->aabb, sx->keys,
                sx->obj_flag, sx->trees, sx->spos, sx->rank, sx->bm_pool, sx->bm_busy,
-               sx->leafpos, sx->visit, sx->vkeys, sx->vkeys_alt, sx->vhist, sx->vvals, sx->vvals_alt};
+               sx->leafpos, sx->visit, sx->visit_global, sx->vleaf, sx->vkeys, sx->vkeys_alt, sx->vhist, sx->vvals, sx->vvals_alt};
   for (void *q : p) gpt_free(ctx, q);
-  for (SssObj &o : sx->objs) { gpt_lbvh_free(ctx, o.bvh); gpt_lbvh_free(ctx, o.search); }
+  for (SssObj &o : sx->objs) {
+    gpt_lbvh_free(ctx, o.bvh);
+    gpt_lbvh_free(ctx, o.search);
+    gpt_free(ctx, o.gpos);
+    gpt_free(ctx, o.gstart);
+  }
   delete sx;
   ctx->sss_state = nullptr;
 }
@@ -227,8 +298,29 @@ bool gpt_sss_view(gpt_ctx *ctx, SssView *out, bool *first_pass_done) {
   return true;
 }
 
+__global__ void __launch_bounds__(256)
+k_sss_add_offset(const int *__restrict__ in, int n, int off, int *out) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < n) out[k] = in[k] + off;
+}
+
+// vleaf[2 k .. 2 k + 1] = leaf[2 visit[k] .. ]: the records in the order the lookups add them up
+__global__ void __launch_bounds__(256)
+k_sss_vleaf(const float4 *__restrict__ leaf, const int *__restrict__ visit, int n, float4 *vleaf) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  int j = visit[k];
+  vleaf[2 * (size_t)k] = leaf[2 * (size_t)j];
+  vleaf[2 * (size_t)k + 1] = leaf[2 * (size_t)j + 1];
+}
+
 void gpt_sss_mark_first_pass_done(gpt_ctx *ctx) {
-  if (sss_of(ctx)) sss_of(ctx)->first_pass_done = true;
+  SssCtx *sx = sss_of(ctx);
+  if (!sx) return;
+  sx->first_pass_done = true;
+  if (sx->vleaf && sx->npoints > 0)  // the colours exist now: the visit-order copy of the records
+    k_sss_vleaf<<<(sx->npoints + 255) / 256, 256, 0, ctx->stream>>>(sx->leaf, sx->visit_global,
+                                                                  sx->npoints, sx->vleaf);
 }
 
 // The reference walk (bvh_traversal_pts.h) tests a node's leaf children when it visits the node,
@@ -322,6 +414,8 @@ int gpt_sss_prepare(gpt_ctx *ctx) {
   GPT_TRY(gpt_alloc(ctx, &sx->rank, (size_t)pts));
   GPT_TRY(gpt_alloc(ctx, &sx->leafpos, (size_t)pts));
   GPT_TRY(gpt_alloc(ctx, &sx->visit, (size_t)np));
+  GPT_TRY(gpt_alloc(ctx, &sx->visit_global, (size_t)np));
+  GPT_TRY(gpt_alloc(ctx, &sx->vleaf, 2 * (size_t)np));
   GPT_TRY(gpt_alloc(ctx, &sx->vkeys, (size_t)pts));
   GPT_TRY(gpt_alloc(ctx, &sx->vkeys_alt, (size_t)pts));
   GPT_TRY(gpt_alloc(ctx, &sx->vvals, (size_t)pts));
@@ -364,12 +458,18 @@ int gpt_sss_prepare(gpt_ctx *ctx) {
                                   cudaMemcpyDeviceToDevice, st));
     k_sss_invert<<<(pts + 255) / 256, 256, 0, st>>>(sx->visit + so.pt_off, pts, sx->leafpos);
     GPT_LAUNCH_CHECK(ctx);
+    k_sss_add_offset<<<(pts + 255) / 256, 256, 0, st>>>(sx->visit + so.pt_off, pts, so.pt_off,
+                                                       sx->visit_global + so.pt_off);
+    GPT_LAUNCH_CHECK(ctx);
     k_sss_spos<<<(pts + 255) / 256, 256, 0, st>>>(sx->pts_created + 3 * (size_t)so.pt_off,
                                                  so.search.sorted_prim, sx->rank, sx->leafpos, pts,
                                                  sx->spos + so.pt_off);
     GPT_LAUNCH_CHECK(ctx);
-    trees[so.obj] = SssTree{so.bvh.nodes, sx->leaf + 2 * (size_t)so.pt_off, pts, 0,
-                            so.search.nodes, sx->spos + so.pt_off, sx->visit + so.pt_off};
+    SssTree tr{so.bvh.nodes, sx->leaf + 2 * (size_t)so.pt_off, pts, 0,
+               so.search.nodes, sx->spos + so.pt_off, sx->visit + so.pt_off,
+               nullptr, nullptr, 0.f, 0.f, 0.f, 0.f, 0, 0, 0, sx->vleaf + 2 * (size_t)so.pt_off};
+    GPT_TRY(build_candidate_grid(ctx, so, sx->spos + so.pt_off, pts, tr));
+    trees[so.obj] = tr;
   }
   // candidate bitmaps: one bit per point; enough of them for every resident shade thread to hold
   // one (148 SMs x 640 threads) at 1.4x for the probing, within 2 GB
