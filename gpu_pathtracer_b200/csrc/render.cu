@@ -269,6 +269,10 @@ static __device__ __noinline__ void sss_mark_grid(const SssTree &t, V3 c, float 
   int wlo = wlo_out, whi = whi_out;
   const float g = 1e-5f * (fabsf(c.x) + fabsf(c.y) + fabsf(c.z) + r + 1.f);
   const float lo = r + g;
+  // T = the largest float whose square root rounds to <= r
+  float T = r * r;
+  while (sqrtf(T) > r) T = __uint_as_float(__float_as_uint(T) - 1u);
+  while (sqrtf(__uint_as_float(__float_as_uint(T) + 1u)) <= r) T = __uint_as_float(__float_as_uint(T) + 1u);
   int x0 = sss_grid_cell(c.x - lo, t.gox, t.ginv, t.gnx), x1 = sss_grid_cell(c.x + lo, t.gox, t.ginv, t.gnx);
   int y0 = sss_grid_cell(c.y - lo, t.goy, t.ginv, t.gny), y1 = sss_grid_cell(c.y + lo, t.goy, t.ginv, t.gny);
   int z0 = sss_grid_cell(c.z - lo, t.goz, t.ginv, t.gnz), z1 = sss_grid_cell(c.z + lo, t.goz, t.ginv, t.gnz);
@@ -278,8 +282,11 @@ static __device__ __noinline__ void sss_mark_grid(const SssTree &t, V3 c, float 
       const int jb = __ldg(t.gstart + row + x0), je = __ldg(t.gstart + row + x1 + 1);
       for (int j = jb; j < je; j++) {
         float4 a = __ldg(t.gpos + j);
-        float d = dist(c, V3{a.x, a.y, a.z});
-        if (d <= r) {
+        // dist(c, a) <= r without the square root: same d2 as length(c - a) forms, and sqrtf
+        // (correctly rounded, monotone) is <= r exactly for d2 <= T
+        const float dx = c.x - a.x, dy = c.y - a.y, dz = c.z - a.z;
+        const float d2 = dx * dx + dy * dy + dz * dz;
+        if (d2 <= T) {
           int i = __float_as_int(a.w);
           bm[i >> 5] |= 1u << (i & 31);
           wlo = min(wlo, i >> 5);
@@ -372,7 +379,10 @@ static __device__ __noinline__ V3 sss_lookup(BitmapPool sv, const SssTree &t, V3
       float4 col = lf[1];  // written after the first pass of this launch sequence: no __ldg
       found = true;
       float wgt = 1.0f / dist(V3{a.x, a.y, a.z}, c);
-      wgt = (float)fmin(9999.99, (double)wgt);
+      // (float)fmin(9999.99, (double)wgt) without the fp64 round trip: (float)9999.99 is
+      // 9999.990234375f > 9999.99, so every float below it is < 9999.99 and is kept, everything
+      // else (NaN included, as fmin does) becomes it
+      wgt = wgt < 9999.990234375f ? wgt : 9999.990234375f;
       sum_w += wgt;
       color = color + wgt * V3{col.x, col.y, col.z};
     }
