@@ -57,7 +57,8 @@ class GptStats(C.Structure):
                 ("rays_traced", C.c_uint64), ("internal_visits", C.c_uint64),
                 ("leaf_tests", C.c_uint64), ("kernel_launches", C.c_uint64),
                 ("shade_events", C.c_uint64), ("trace_kernel_ms", C.c_double),
-                ("shade_kernel_ms", C.c_double), ("trace_launches", C.c_uint64)]
+                ("shade_kernel_ms", C.c_double), ("trace_launches", C.c_uint64),
+                ("build_wide_ms", C.c_double)]
 
 
 def fptr(a: np.ndarray):

@@ -48,6 +48,12 @@ struct BvhDev {
   uint32_t *block_hist = nullptr;
   int hist_capacity = 0;
   int *flags = nullptr;         // n-1 arrival counters for the refit
+  // 4-wide quantised tree collapsed from the LBVH (wide.cu, trace_wide.cuh)
+  uint4 *wq = nullptr;          // 3 x 16 bytes per wide node, node 0 = root
+  float4 *wtris = nullptr;      // the 48-byte trace triangles once more, in wide-tree leaf order; t2.w = LBVH leaf
+  float *wmeta = nullptr;       // [0] max |coordinate| of the world box, [1] 2^23
+  int wide_capacity = 0;        // leaves the three buffers were allocated for
+  int wide_nodes = 0;           // wide nodes of the current tree, 0 = none (the binary walk is used)
 };
 
 // Per-triangle shading record in ORIGINAL order (7 float4 = 112 B), filled by preprocess:
@@ -112,6 +118,7 @@ struct gpt_ctx {
   int wavefront_groups = 0;  // 0 = automatic (render.cu)
   int pipeline = -1;         // path tracer: 0 = rounds of launches, 1 = streaming (two persistent kernels), -1 = default (env GPT_PIPELINE, else by frame size)
   int trace_defer = -1;      // path tracer: batch the triangle tests of a warp (deferred leaf tests): -1 = default (on, env GPT_TRACE_DEFER), 0 off, 1 on
+  int trace_wide = -1;       // walk the 4-wide tree (trace_wide.cuh): -1 = default (on, env GPT_TRACE_WIDE), 0 = binary LBVH walk, 1 on
   int trace_tail = -1;       // cooperative tail of the persistent trace: -1 = default (on, env GPT_TRACE_COOP), 0 off, 1 on
 };
 
@@ -187,6 +194,7 @@ int gpt_lbvh_build_boxes(gpt_ctx *ctx, BvhDev &b, const float *d_aabb, const int
                          int n, bool with_tris,
                          const uint32_t *d_keys = nullptr);           // lbvh.cu
 void gpt_lbvh_free(gpt_ctx *ctx, BvhDev &b);
+int gpt_lbvh_build_wide(gpt_ctx *ctx, BvhDev &b);                     // lbvh.cu
 int gpt_collect_subset(gpt_ctx *ctx, int flag_mask, int **d_list, int *count);  // lbvh.cu
 int gpt_trace_launch(gpt_ctx *ctx, int which, const float4 *d_rays, int64_t n,
                      float4 *d_hits, bool normalize, bool count);     // trace.cu
@@ -237,3 +245,4 @@ int gpt_radix_sort_pairs(gpt_ctx *ctx, uint32_t *keys, int *vals, uint32_t *keys
 int gpt_radix_hist_entries(int n);
 bool gpt_trace_coop(const gpt_ctx *ctx, const BvhDev &b);  // trace.cu
 bool gpt_trace_defer(const gpt_ctx *ctx);                   // trace.cu
+bool gpt_trace_wide(const gpt_ctx *ctx, const BvhDev &b);   // trace.cu

@@ -322,6 +322,7 @@ k_refit(const float *__restrict__ aabb, const int *__restrict__ prim_list,
   }
 }
 
+
 // flagged-subset compaction in index order (collect_*_geom, 1 thread serial in the reference:
 // transparent_geom_operations.h:28-40, pathtracing_target_geom_operations.h:36-48).
 // NOTE the reference collects from the Morton-SORTED main list (src/main.cu:952,1083).
@@ -415,6 +416,7 @@ void gpt_lbvh_free(gpt_ctx *ctx, BvhDev &b) {
   gpt_free(ctx, b.nodes); gpt_free(ctx, b.tris); gpt_free(ctx, b.parent_leaf); gpt_free(ctx, b.morton);
   gpt_free(ctx, b.sorted_prim); gpt_free(ctx, b.prim_list); gpt_free(ctx, b.world_enc);
   gpt_free(ctx, b.keys_alt); gpt_free(ctx, b.vals_alt); gpt_free(ctx, b.block_hist); gpt_free(ctx, b.flags);
+  gpt_free(ctx, b.wq); gpt_free(ctx, b.wtris); gpt_free(ctx, b.wmeta);
   b = BvhDev();
 }
 
@@ -493,7 +495,10 @@ int gpt_lbvh_build_boxes(gpt_ctx *ctx, BvhDev &b, const float *aabb, const int *
 }
 
 int gpt_lbvh_build(gpt_ctx *ctx, int which, const int *d_prim_list, int n) {
-  return gpt_lbvh_build_boxes(ctx, ctx->bvh[which], ctx->scene.aabb, d_prim_list, n, true, nullptr);
+  GPT_TRY(gpt_lbvh_build_boxes(ctx, ctx->bvh[which], ctx->scene.aabb, d_prim_list, n, true, nullptr));
+  // the light tree is only ever walked by the light sampler (lighttree.cuh), never traced
+  if (which != GPT_BVH_LIGHT) GPT_TRY(gpt_lbvh_build_wide(ctx, ctx->bvh[which]));
+  return GPT_OK;
 }
 
 // Ordered list of the triangles whose flags & mask != 0, taken in MAIN-BVH sorted order.

@@ -14,7 +14,7 @@
 #include <vector>
 
 #include "integrator.cuh"
-#include "trace_persistent.cuh"
+#include "trace_wide.cuh"
 
 namespace {
 
@@ -460,6 +460,13 @@ k_pt_trace(QueueSource src, const float4 *__restrict__ nodes, const float4 *__re
   __shared__ int defer[DEFER ? 2 * DEFER_SLOTS * TP_BLOCK : 1];
   trace_persistent<COUNT, QueueSource, COOP, DEFER>(nodes, tris, parent_leaf, src, next_ray,
                                                     stack, counters, coop, defer);
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(TP_BLOCK, W4_MINBLOCKS)
+k_pt_trace_wide(QueueSource src, WideTree tree, int *next_ray, unsigned long long *counters) {
+  __shared__ int smem[W4_SMEM_WORDS];
+  trace_wide<COUNT, QueueSource>(tree, src, next_ray, smem, counters);
 }
 
 // One path vertex: the slot's hit is shaded and the slot either gets its next ray (returns
@@ -1034,13 +1041,17 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
   GPT_LAUNCH_CHECK(ctx);
   const bool coop = gpt_trace_coop(ctx, mb);  // cooperative tail (trace_persistent.cuh)
   const bool defer_leaves = gpt_trace_defer(ctx);  // deferred leaf tests (trace_persistent.cuh)
-  static int trace_grid = 0;
+  const bool wide_walk = gpt_trace_wide(ctx, mb);  // 4-wide tree (trace_wide.cuh)
+  // persistent grid = SMs x resident blocks of the kernel that will run (cached per variant)
+  static int trace_grid_of[2] = {0, 0};
+  int &trace_grid = trace_grid_of[wide_walk ? 1 : 0];
   if (!trace_grid) {
     int sms = 148, per_sm = 4;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
     // (the variant with the tail: 72 registers, 7 blocks per SM instead of 8 -- the grid size
     //  is flat between 4 and 8, profiles/r01d_summary.md)
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pt_trace<false, true>, TP_BLOCK, 0);
+    if (wide_walk) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pt_trace_wide<false>, TP_BLOCK, 0);
+    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pt_trace<false, true>, TP_BLOCK, 0);
     // GPT_TRACE_BLOCKS_PER_SM < occupancy leaves room for another group's shade / sort blocks to
     // run beside a persistent trace kernel instead of after it (experiment knob)
     const char *e = getenv("GPT_TRACE_BLOCKS_PER_SM");
@@ -1292,6 +1303,12 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
                        rc->sort_key + q.s0, rc->sort_val + q.s0, loc_bits, loc_shift};
         const int tneed = (q.active + TP_BLOCK - 1) / TP_BLOCK;
         int tgrid = tneed < trace_grid ? tneed : trace_grid;
+        if (wide_walk) {
+          if (counting)
+            k_pt_trace_wide<true><<<tgrid, TP_BLOCK, 0, gs>>>(qs, gpt_wide_tree(mb), next_ray, ctx->d_counters);
+          else
+            k_pt_trace_wide<false><<<tgrid, TP_BLOCK, 0, gs>>>(qs, gpt_wide_tree(mb), next_ray, ctx->d_counters);
+        } else {
         auto kern = counting ? (coop ? k_pt_trace<true, true> : k_pt_trace<true, false>)
                              : (coop ? k_pt_trace<false, true> : k_pt_trace<false, false>);
         if (defer_leaves)
@@ -1299,6 +1316,7 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
                           : (coop ? k_pt_trace<false, true, true> : k_pt_trace<false, false, true>);
         kern<<<tgrid, TP_BLOCK, 0, gs>>>(qs, mb.nodes, mb.tris, mb.parent_leaf, next_ray,
                                          ctx->d_counters);
+        }
       }
       GPT_LAUNCH_CHECK(ctx);
       trace_launches++;

@@ -37,7 +37,7 @@
 #include <vector>
 
 #include "integrator.cuh"
-#include "trace_persistent.cuh"
+#include "trace_wide.cuh"
 
 namespace {
 
@@ -440,6 +440,13 @@ k_ph_trace(PhotonRaySource src, const float4 *__restrict__ nodes, const float4 *
   __shared__ int defer[DEFER ? 2 * DEFER_SLOTS * TP_BLOCK : 1];
   trace_persistent<COUNT, PhotonRaySource, COOP, DEFER>(nodes, tris, parent_leaf, src, next_ray,
                                                         stack, counters, coop, defer);
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(TP_BLOCK, W4_MINBLOCKS)
+k_ph_trace_wide(PhotonRaySource src, WideTree tree, int *next_ray, unsigned long long *counters) {
+  __shared__ int smem[W4_SMEM_WORDS];
+  trace_wide<COUNT, PhotonRaySource>(tree, src, next_ray, smem, counters);
 }
 
 enum { PH_NEW = 0, PH_MEDIUM = 1, PH_SURFACE = 2, PH_INIT = 3 };  // where a photon resumes
@@ -1587,6 +1594,14 @@ static int photon_stage(gpt_ctx *ctx, SppmCtx *sx, const SppmScene &S, const Pho
     PhotonRaySource src{queue, qcount, W.rays, W.hits, ctx->scene.shade, W.key + offset, W.val + offset};
     int grid = (n + TP_BLOCK - 1) / TP_BLOCK;
     if (grid > trace_grid) grid = trace_grid;
+    if (gpt_trace_wide(ctx, tree)) {
+      if (count_visits)
+        k_ph_trace_wide<true><<<grid, TP_BLOCK, 0, st>>>(src, gpt_wide_tree(tree), cursor, ctx->d_counters);
+      else
+        k_ph_trace_wide<false><<<grid, TP_BLOCK, 0, st>>>(src, gpt_wide_tree(tree), cursor, ctx->d_counters);
+      GPT_LAUNCH_CHECK(ctx);
+      return GPT_OK;
+    }
     const bool coop = gpt_trace_coop(ctx, tree);
     auto kern = count_visits ? (coop ? k_ph_trace<true, true> : k_ph_trace<true, false>)
                              : (coop ? k_ph_trace<false, true> : k_ph_trace<false, false>);

@@ -6,7 +6,7 @@
 // {t, leaf, prim, -}{b1, b2, b3, -}.
 #include <cstdlib>
 
-#include "trace_persistent.cuh"
+#include "trace_wide.cuh"
 
 namespace {
 
@@ -41,6 +41,15 @@ k_trace(const float4 *__restrict__ nodes, const float4 *__restrict__ tris,
   trace_persistent<COUNT, ArraySource<NORMALIZE>, COOP, DEFER>(nodes, tris, parent_leaf, src,
                                                                next_ray, stack, counters, coop,
                                                                defer);
+}
+
+// the same queue through the 4-wide tree (trace_wide.cuh)
+template <bool NORMALIZE, bool COUNT>
+__global__ void __launch_bounds__(TP_BLOCK, W4_MINBLOCKS)
+k_trace_wide(WideTree tree, ArraySource<NORMALIZE> src, int *next_ray,
+             unsigned long long *counters) {
+  __shared__ int smem[W4_SMEM_WORDS];
+  trace_wide<COUNT, ArraySource<NORMALIZE>>(tree, src, next_ray, smem, counters);
 }
 
 template <class K>
@@ -78,6 +87,18 @@ bool gpt_trace_defer(const gpt_ctx *ctx) {
   return ctx->trace_defer >= 0 ? ctx->trace_defer != 0 : env != 0;
 }
 
+// Whether the trace kernels walk the 4-wide tree (trace_wide.cuh) instead of the binary LBVH: on
+// unless gpt_set_trace_bvh / GPT_TRACE_WIDE=0 says otherwise, and only for a tree that has one.
+bool gpt_trace_wide(const gpt_ctx *ctx, const BvhDev &b) {
+  static int env = -1;
+  if (env < 0) {
+    const char *e = getenv("GPT_TRACE_WIDE");
+    env = e ? (atoi(e) != 0) : 1;
+  }
+  int on = ctx->trace_wide >= 0 ? ctx->trace_wide : env;
+  return on && b.wide_nodes > 0 && b.n >= 2;
+}
+
 int gpt_trace_launch(gpt_ctx *ctx, int which, const float4 *d_rays, int64_t n, float4 *d_hits,
                      bool normalize, bool count) {
   if (which < 0 || which > 2) return gpt_fail(ctx, GPT_E_INVALID, "bad BVH id", __FILE__, __LINE__);
@@ -90,6 +111,21 @@ int gpt_trace_launch(gpt_ctx *ctx, int which, const float4 *d_rays, int64_t n, f
   if (count) GPT_CUDA(ctx, cudaMemsetAsync(c, 0, 3 * sizeof(unsigned long long), ctx->stream));
   GPT_CUDA(ctx, cudaMemsetAsync(next_ray, 0, sizeof(int), ctx->stream));
   cudaStream_t st = ctx->stream;
+  if (gpt_trace_wide(ctx, b)) {
+#define GPT_TRACE_LAUNCH_W(NORM, CNT)                                                      \
+  do {                                                                                     \
+    static int grid = persistent_grid(k_trace_wide<NORM, CNT>);                            \
+    long long need = (n + TP_BLOCK - 1) / TP_BLOCK;                                        \
+    ArraySource<NORM> src{d_rays, d_hits, (int)n};                                         \
+    k_trace_wide<NORM, CNT><<<(unsigned)(need < grid ? need : grid), TP_BLOCK, 0, st>>>(   \
+        gpt_wide_tree(b), src, next_ray, c);                                               \
+  } while (0)
+    if (normalize) { if (count) GPT_TRACE_LAUNCH_W(true, true); else GPT_TRACE_LAUNCH_W(true, false); }
+    else { if (count) GPT_TRACE_LAUNCH_W(false, true); else GPT_TRACE_LAUNCH_W(false, false); }
+#undef GPT_TRACE_LAUNCH_W
+    GPT_LAUNCH_CHECK(ctx);
+    return GPT_OK;
+  }
   const bool coop = gpt_trace_coop(ctx, b);
   const bool defer = gpt_trace_defer(ctx);
 #define GPT_TRACE_LAUNCH(NORM, CNT, COOP, DEFER)                                           \

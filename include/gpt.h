@@ -118,6 +118,7 @@ typedef struct GptStats {
   double trace_kernel_ms;   /* sum of the trace-stage kernels of the last render (profiling) */
   double shade_kernel_ms;   /* sum of the shade-stage kernels of the last render (profiling) */
   uint64_t trace_launches;  /* trace-stage launches in the last render                       */
+  double build_wide_ms;     /* last gpt_build: the 4-wide tree collapsed from the main LBVH  */
 } GptStats;
 
 /* ---- lifetime ---------------------------------------------------------------------- */
@@ -333,6 +334,17 @@ int gpt_set_trace_tail(gpt_ctx *ctx, int mode);
  * either way (closest hit with the reference's visit-rank tie-break does not depend on the
  * order of the tests; a later test only means a looser cull bound in between). */
 int gpt_set_trace_leaf_batching(gpt_ctx *ctx, int mode);
+/* Which tree the trace kernels walk (traverse_bvh, src/model/bvh/bvh_traversal.h:12-84).
+ *   1: the 4-wide tree gpt_build collapses from the LBVH (one 128-byte node per visit holds four
+ *      boxes; ~23 dependent node fetches per bounce ray on the 1 M-triangle config instead of
+ *      ~49).  The walk is conservative and every candidate hit is filtered by the reference's
+ *      exact slab predicate on the triangle's own box, so the hit is the one the reference's
+ *      walk of its binary tree returns, bit for bit; rays with a zero / denormal / non-finite
+ *      direction component take the binary walk.
+ *   0: the ordered walk of the binary LBVH itself.
+ *  -1 (default): 1, unless the environment variable GPT_TRACE_WIDE=0.
+ * gpt_export_bvh always exports the binary LBVH (the reference's tree). */
+int gpt_set_trace_bvh(gpt_ctx *ctx, int mode);
 /* How gpt_render_pathtrace* runs path_tracing_render's dof x spp x level loop
  * (src/render/pathtracing.h:251-305).
  *   0 "rounds":  one round of launches (trace, material sort, shade) per bounce of every pixel,

@@ -9,4 +9,4 @@ $NV -O3 -std=c++17 -gencode arch=compute_100a,code=sm_100a -lineinfo -fmad=false
     -Xcompiler -ffp-contract=off -Xptxas -v $2 -c render.cu -o /tmp/gpt_variant/render_$1.o 2> /tmp/gpt_variant/render_$1.log
 OBJS=$(ls _obj/*.o | grep -v render.o)
 $NV -gencode arch=compute_100a,code=sm_100a -shared -o ../../variants/libgpt_$1.so $OBJS /tmp/gpt_variant/render_$1.o -lcudart -lpthread
-grep -A3 "k_pt_traceILb0ELb1" /tmp/gpt_variant/render_$1.log | grep registers
+grep -A3 "k_pt_trace_wideILb0" /tmp/gpt_variant/render_$1.log | grep registers
