@@ -35,12 +35,19 @@ int gpt_create(int device, gpt_ctx **out) {
     return GPT_E_CUDA;
   }
   cudaMemset(ctx->d_counters, 0, 8 * sizeof(unsigned long long));
-  {  // gpt_alloc (common.cuh): keep freed blocks in the pool instead of returning them to the OS
-    cudaMemPool_t pool;
-    if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
-      uint64_t keep = UINT64_MAX;
-      cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+  {  // gpt_alloc (common.cuh): a private pool that keeps freed blocks instead of returning them
+    cudaMemPoolProps props = {};
+    props.allocType = cudaMemAllocationTypePinned;
+    props.handleTypes = cudaMemHandleTypeNone;
+    props.location.type = cudaMemLocationTypeDevice;
+    props.location.id = device;
+    if (cudaMemPoolCreate(&ctx->pool, &props) != cudaSuccess) {
+      cudaFree(ctx->d_counters);
+      delete ctx;
+      return GPT_E_CUDA;
     }
+    uint64_t keep = UINT64_MAX;
+    cudaMemPoolSetAttribute(ctx->pool, cudaMemPoolAttrReleaseThreshold, &keep);
   }
   ctx->stream = ctx->own_stream;
   ctx->params.render_mode = 1;
@@ -83,6 +90,9 @@ void gpt_destroy(gpt_ctx *ctx) {
   gpt_free(ctx, s.mats); gpt_free(ctx, s.tex_r); gpt_free(ctx, s.tex_g); gpt_free(ctx, s.tex_b);
   gpt_free(ctx, s.bg_r); gpt_free(ctx, s.bg_g); gpt_free(ctx, s.bg_b);
   cudaFree(ctx->d_counters);  // plain cudaMalloc in gpt_create
+  cudaStreamSynchronize(ctx->stream);
+  cudaStreamSynchronize(ctx->own_stream);
+  if (ctx->pool) cudaMemPoolDestroy(ctx->pool);  // everything gpt_alloc ever handed out goes back to the device
   cudaEventDestroy(ctx->ev0);
   cudaEventDestroy(ctx->ev1);
   cudaStreamDestroy(ctx->own_stream);
@@ -103,6 +113,14 @@ int gpt_set_stream(gpt_ctx *ctx, uint64_t cuda_stream) {
 int gpt_synchronize(gpt_ctx *ctx) {
   if (!ctx) return GPT_E_INVALID;
   GPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  // the asynchronous entry points (gpt_trace_device) cannot report a traversal-stack overflow
+  // themselves: it surfaces here
+  unsigned long long overflow = 0;
+  GPT_CUDA(ctx, cudaMemcpy(&overflow, ctx->d_counters + 3, sizeof(overflow), cudaMemcpyDeviceToHost));
+  if (overflow) {
+    cudaMemset(ctx->d_counters + 3, 0, sizeof(overflow));
+    return gpt_fail(ctx, GPT_E_UNSUPPORTED, "traversal stack overflow (> 64 levels) in an earlier asynchronous call", __FILE__, __LINE__);
+  }
   return GPT_OK;
 }
 
@@ -230,6 +248,8 @@ int gpt_set_camera(gpt_ctx *ctx, const GptCamera *cam) {
 
 int gpt_set_params(gpt_ctx *ctx, const GptParams *p) {
   if (!ctx || !p) return GPT_E_INVALID;
+  if (p->rng_mode != 0 && p->rng_mode != 1)
+    return gpt_fail(ctx, GPT_E_INVALID, "rng_mode must be 0 (reference streams) or 1 (per-sample streams)", __FILE__, __LINE__);
   ctx->params = *p;
   return GPT_OK;
 }
@@ -303,6 +323,7 @@ int gpt_build(gpt_ctx *ctx) {
   ctx->stats.build_all_ms = ms;
   ctx->stats.kernel_launches = ctx->launches;
   ctx->built = true;
+  ctx->build_epoch++;
   return GPT_OK;
 }
 
@@ -405,8 +426,11 @@ int gpt_trace(gpt_ctx *ctx, int which, const float *rays, int64_t n, int32_t *le
   GPT_CUDA(ctx, cudaSetDevice(ctx->device));
   float4 *d_rays = nullptr, *d_hits = nullptr;
   GPT_TRY(gpt_alloc(ctx, &d_rays, 2 * (size_t)n));
-  GPT_TRY(gpt_alloc(ctx, &d_hits, 2 * (size_t)n));
-  int rc = GPT_OK;
+  int rc = gpt_alloc(ctx, &d_hits, 2 * (size_t)n);
+  if (rc != GPT_OK) {
+    gpt_free(ctx, d_rays);
+    return rc;
+  }
   std::vector<float4> h(2 * (size_t)n);
   do {
     if (cudaMemcpyAsync(d_rays, rays, 32 * (size_t)n, cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess) { rc = GPT_E_CUDA; break; }

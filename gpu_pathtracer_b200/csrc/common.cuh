@@ -107,6 +107,10 @@ struct gpt_ctx {
   GptParams params{};
   GptStats stats{};
   bool have_mesh = false, have_mats = false, have_cam = false, built = false;
+  // bumped by gpt_build: anything derived from the built scene and cached elsewhere (the
+  // light-tree side arrays of render.cu / sppm.cu) is stale when its epoch differs
+  uint64_t build_epoch = 0;
+  cudaMemPool_t pool = nullptr;              // this context's own stream-ordered pool (gpt_alloc)
   unsigned long long *d_counters = nullptr;  // [0] V_int [1] V_leaf [2] rays [3] overflow
   void *render_state = nullptr;              // owned by render.cu
   void *sppm_state = nullptr;                // owned by sppm.cu
@@ -141,8 +145,9 @@ int gpt_fail(gpt_ctx *ctx, int code, const char *what, const char *file, int lin
     GPT_CUDA((ctx), cudaGetLastError()); \
   } while (0)
 
-// Device memory comes from the device's stream-ordered pool (release threshold = keep
-// everything, set in gpt_create): a scene upload + build is ~60 buffers, and with plain
+// Device memory comes from a stream-ordered pool OWNED by the context (release threshold = keep
+// everything; destroyed, and so returned to the device, by gpt_destroy -- the device's default
+// pool is process-global and is left alone): a scene upload + build is ~60 buffers, and with plain
 // cudaMalloc / cudaFree the driver calls alone cost more than the kernels (C2: build 10.6 ms
 // of which < 2 ms is GPU work).  Every allocation and free is ordered on ctx->stream; the
 // wavefront-group streams fork from and join back into it, so that order covers them too.
@@ -153,7 +158,7 @@ template <class T>
 static inline int gpt_alloc(gpt_ctx *ctx, T **p, size_t count) {
   if (*p) { gpt_free(ctx, *p); *p = nullptr; }
   if (count == 0) count = 1;
-  GPT_CUDA(ctx, cudaMallocAsync((void **)p, count * sizeof(T), ctx->stream));
+  GPT_CUDA(ctx, cudaMallocFromPoolAsync((void **)p, count * sizeof(T), ctx->pool, ctx->stream));
   return GPT_OK;
 }
 template <class T>

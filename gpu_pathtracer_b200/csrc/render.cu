@@ -30,6 +30,7 @@ struct RenderCtx {
   float *node_energy = nullptr;
   int *lt_flags = nullptr;
   int light_n = 0;
+  uint64_t light_epoch = 0;       // ctx->build_epoch the light-tree arrays were made for
   uint32_t *rng_init = nullptr;   // cached curand_init states for (width, height, rank set)
   int rng_w = 0, rng_h = 0, rng_rank = -1, rng_nranks = 0;
   // Independent wavefront groups (slot ranges), each on its own stream with its own queues,
@@ -891,6 +892,7 @@ static int build_light_tree(gpt_ctx *ctx, RenderCtx *rc) {
   GPT_TRY(gpt_build_light_tree_arrays(ctx, &rc->leaf_info, &rc->node_info, &rc->node_energy,
                                       &rc->lt_flags));
   rc->light_n = ctx->bvh[GPT_BVH_LIGHT].n;
+  rc->light_epoch = ctx->build_epoch;
   return GPT_OK;
 }
 
@@ -1003,7 +1005,9 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
   if (n == 0) return GPT_OK;
   PathState ps = rc->ps;
   ps.capacity = n;  // stride of the RNG planes for this render
-  if (rc->light_n != ctx->bvh[GPT_BVH_LIGHT].n || new_map) GPT_TRY(build_light_tree(ctx, rc));
+  // (a rebuilt scene with the same number of lights must not be sampled with the old records)
+  if (rc->light_n != ctx->bvh[GPT_BVH_LIGHT].n || rc->light_epoch != ctx->build_epoch || new_map)
+    GPT_TRY(build_light_tree(ctx, rc));
 
   RenderParams p;
   p.cam = derive_camera(ctx->cam);
@@ -1062,7 +1066,9 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
   uint64_t rays = 0, shades = 0, trace_launches = 0;
   const bool timing = ctx->prof_time_stages, counting = ctx->prof_count_visits;
   size_t nev = 0;
-  if (counting) GPT_CUDA(ctx, cudaMemsetAsync(ctx->d_counters, 0, 3 * sizeof(unsigned long long), st));
+  // [0..2] visit counters (profiling), [3] traversal-stack overflow flag: a stale flag of an
+  // earlier call must not fail this one, and an overflow in this one must not go unnoticed
+  GPT_CUDA(ctx, cudaMemsetAsync(ctx->d_counters, 0, 4 * sizeof(unsigned long long), st));
   auto stamp = [&]() -> cudaError_t {
     if (!timing) return cudaSuccess;
     if (nev == rc->events.size()) {
@@ -1363,9 +1369,12 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
     }
     int h_fin[RenderCtx::CNT * RenderCtx::MAX_GROUPS];
     GPT_CUDA(ctx, cudaMemcpyAsync(h_fin, ps.counts, sizeof(int) * CNT * G, cudaMemcpyDeviceToHost, st));
-    unsigned long long h_rays = 0;
+    unsigned long long h_rays = 0, h_overflow = 0;
     GPT_CUDA(ctx, cudaMemcpyAsync(&h_rays, ray_counter, sizeof(h_rays), cudaMemcpyDeviceToHost, st));
+    GPT_CUDA(ctx, cudaMemcpyAsync(&h_overflow, ctx->d_counters + 3, sizeof(h_overflow), cudaMemcpyDeviceToHost, st));
     GPT_CUDA(ctx, cudaStreamSynchronize(st));
+    if (h_overflow)
+      return gpt_fail(ctx, GPT_E_UNSUPPORTED, "traversal stack overflow (> 64 levels)", __FILE__, __LINE__);
     for (int g = 0; g < G; g++) {
       active += h_fin[CNT * g + grp[g].c];
       if (h_fin[CNT * g + 4]) list_overflow = true;

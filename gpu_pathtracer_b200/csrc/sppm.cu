@@ -1351,6 +1351,7 @@ struct SppmCtx {
   float *node_energy = nullptr;
   int *lt_flags = nullptr;
   int light_n = 0;
+  uint64_t light_epoch = 0;  // ctx->build_epoch the light-tree arrays were made for
   uint64_t rays_total = 0;
 };
 
@@ -1370,10 +1371,11 @@ static int make_scene_view(gpt_ctx *ctx, SppmCtx *sx, SppmScene &S) {
          &lb = ctx->bvh[GPT_BVH_LIGHT];
   if (lb.n < 2)
     return gpt_fail(ctx, GPT_E_INVALID, "SPPM needs >= 2 emissive triangles (src/main.cu:1124-1125)", __FILE__, __LINE__);
-  if (sx->light_n != lb.n) {
+  if (sx->light_n != lb.n || sx->light_epoch != ctx->build_epoch) {
     GPT_TRY(gpt_build_light_tree_arrays(ctx, &sx->leaf_info, &sx->node_info, &sx->node_energy,
                                         &sx->lt_flags));
     sx->light_n = lb.n;
+    sx->light_epoch = ctx->build_epoch;
   }
   S.main_t = TreeRef{mb.nodes, mb.tris, mb.parent_leaf, mb.n};
   S.transp_t = TreeRef{tb.nodes, tb.tris, tb.parent_leaf, tb.n};

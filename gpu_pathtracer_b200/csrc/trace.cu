@@ -108,7 +108,8 @@ int gpt_trace_launch(gpt_ctx *ctx, int which, const float4 *d_rays, int64_t n, f
   if (n > 0x7fffffff) return gpt_fail(ctx, GPT_E_INVALID, "more than 2^31 rays in one call", __FILE__, __LINE__);
   unsigned long long *c = ctx->d_counters;
   int *next_ray = reinterpret_cast<int *>(c + 4);
-  if (count) GPT_CUDA(ctx, cudaMemsetAsync(c, 0, 3 * sizeof(unsigned long long), ctx->stream));
+  // [0..2] visit counters, [3] the stack-overflow flag: cleared for every call (it was sticky)
+  GPT_CUDA(ctx, cudaMemsetAsync(c, 0, 4 * sizeof(unsigned long long), ctx->stream));
   GPT_CUDA(ctx, cudaMemsetAsync(next_ray, 0, sizeof(int), ctx->stream));
   cudaStream_t st = ctx->stream;
   if (gpt_trace_wide(ctx, b)) {

@@ -43,8 +43,11 @@
 #ifndef W4_DRAIN_ALL
 #define W4_DRAIN_ALL 0     // at the refill point: 1 = empty every queue, 0 = only until the lanes whose walk is over are done
 #endif
-constexpr int W4_QSLOTS = 6;         // queue entries per lane (one per visited node with leaf hits)
-constexpr int W4_QPASS = 4;          // a test pass runs when a lane has more than this many leaves queued
+#ifndef W4_QPASS_V
+#define W4_QPASS_V 4
+#endif
+constexpr int W4_QPASS = W4_QPASS_V;     // a test pass runs when a lane has more than this many leaves queued
+constexpr int W4_QSLOTS = W4_QPASS + 2;  // queue entries per lane (<= one per queued leaf before a step, one more after it)
 constexpr float W4_EPS = 1.1e-5f;    // relative margin of the dominant-axis cull (trace_core.cuh: 1e-5)
 constexpr float W4_MARGIN = 9.5367431640625e-07f;  // 2^-20 = 16 ulp: see w4_node_consts
 constexpr float W4_STEPS = 1.25f;    // margin in grid steps: see w4_node_consts

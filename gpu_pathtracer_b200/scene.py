@@ -438,26 +438,58 @@ def bottle_scene(width=1920, height=1080, spp=8, dof=8, level=8, name="C3") -> S
                                 pathtracing_level=level), name=name)
 
 
+def sky_texture(height: int = 32, width: int = 64, seed: int = 5) -> dict:
+    """A non-constant equirectangular background (horizon glow + value noise), quantised to
+    k/255 like an 8-bit image the reference's loader would have read."""
+    v, u = np.meshgrid((np.arange(height) + 0.5) / height, (np.arange(width) + 0.5) / width,
+                       indexing="ij")
+    n = value_noise(u * 6, v * 3, seed)
+    img = np.stack([0.35 + 0.6 * np.exp(-((v - 0.5) * 4) ** 2) * (0.6 + 0.4 * n),
+                    0.45 + 0.4 * n, 0.95 - 0.5 * v], -1)
+    img = (np.clip(np.rint(img * 255.0), 0, 255) / 255.0).astype(F32)
+    return dict(r=np.ascontiguousarray(img[..., 0].ravel()), g=np.ascontiguousarray(img[..., 1].ravel()),
+                b=np.ascontiguousarray(img[..., 2].ravel()), height=height, width=width)
+
+
 def small_scene(n: int = 24, width: int = 128, height: int = 128, spp: int = 2,
                 level: int = 4, glass: bool = True, metal: bool = True,
-                textured: bool = False, sss_pts: int = 0, name: str = "small") -> Scene:
-    """Small everything-in-one scene for parity tests that the host replay finishes fast."""
+                textured: bool = False, sss_pts: int = 0, all_maps: bool = False,
+                sky: bool = False, name: str = "small") -> Scene:
+    """Small everything-in-one scene for parity tests that the host replay finishes fast.
+    all_maps: the metal sphere gets a specular-colour map (map_Ks) and an exponent map (map_Ns),
+    the lights an emission map (map_Ke) -- Material::_get_texture for every slot
+    (material.h:653-727).  sky: a 64 x 32 non-constant equirectangular background
+    (_get_sky_color, pathtracing.h:69-82)."""
     mats = MaterialBuilder()
     kw = {}
     if textured:
         kw = dict(map_kd=mats.add_texture(checker_texture(64, 8)),
                   map_bump=mats.add_texture(bump_texture(64)), bm=0.3)
     m_terrain = mats.add("terrain", kd=(0.7, 0.7, 0.7), **kw)
-    m_metal = mats.add("metal", kd=(0.05, 0.05, 0.05), ks=(0.9, 0.9, 0.9), n_s=200.0)
+    mkw, lkw = {}, {}
+    if all_maps:
+        ks_img = 0.35 + 0.65 * checker_texture(32, 4)
+        ks_img[..., 2] *= 0.6
+        ns_img = np.repeat(value_noise(*np.meshgrid(np.linspace(0, 4, 32), np.linspace(0, 4, 32)), 3)[..., None], 3, -1)
+        mkw = dict(map_ks=mats.add_texture(ks_img), map_ns=mats.add_texture(0.2 + 0.8 * ns_img))
+        ke_img = 0.5 + 0.5 * checker_texture(16, 2)
+        ke_img[..., 0] *= 0.8
+        lkw = dict(map_ke=mats.add_texture(ke_img))
+    m_metal = mats.add("metal", kd=(0.05, 0.05, 0.05), ks=(0.9, 0.9, 0.9), n_s=200.0, **mkw)
     m_glass = mats.add("glass", t_r=1.0, n_i=1.5, n_s=1e6, priority=1)
     m_liquid = mats.add("liquid", tf=(0.8, 0.9, 1.0), t_r=1.0, n_i=1.33, n_s=1e6, priority=2)
-    m_light = mats.add("light", ke=(15.0, 15.0, 15.0))
+    m_light = mats.add("light", ke=(15.0, 15.0, 15.0), **lkw)
     mb = MeshBuilder()
     v, f, nrm, uv = terrain(n, 1984)
     mb.add(v, f, m_terrain, normals=nrm, uvs=uv)
     if metal:
         sv, sf, sn = icosphere((-3.0, 2.0, 0.0), 1.5, 2)
-        mb.add(sv, sf, m_metal, normals=sn)
+        suv = None
+        if all_maps:  # spherical uv so that the specular / exponent maps vary over the sphere
+            d = sn / np.linalg.norm(sn, axis=1, keepdims=True)
+            suv = np.stack([0.5 + np.arctan2(d[:, 2], d[:, 0]) / (2 * np.pi),
+                            0.5 + np.arcsin(np.clip(d[:, 1], -1, 1)) / np.pi], 1).astype(F32)
+        mb.add(sv, sf, m_metal, normals=sn, uvs=suv)
     if glass:
         sv, sf, sn = icosphere((3.0, 2.0, 1.0), 1.6, 2)
         mb.add(sv, sf, m_glass, normals=sn)
@@ -471,10 +503,34 @@ def small_scene(n: int = 24, width: int = 128, height: int = 128, spp: int = 2,
         sv, sf, sn = icosphere((-4.0, 3.5, 3.5), 0.8, 1)
         mb.add(sv, sf, m_wax, normals=sn)
     _add_lights(mb, m_light)
+    sc = Scene(mb.finish(), mats.finish(), default_camera(width, height),
+               default_params(pathtracing_sample_size=spp, pathtracing_level=level,
+                              sss_pts_per_object=sss_pts),
+               name=name)
+    if sky:
+        sc.bg = sky_texture()
+    return sc
+
+
+def nested_shells_scene(shells: int = 14, width: int = 128, height: int = 128) -> Scene:
+    """`shells` concentric glass spheres of distinct materials whose priority number grows
+    inwards: a ray entering them piles every one onto its nested-dielectric list
+    (add_new_material, material_list_operations.h:9-24)."""
+    mats = MaterialBuilder()
+    m_floor = mats.add("floor", kd=(0.6, 0.6, 0.6))
+    m_light = mats.add("light", ke=(15.0, 15.0, 15.0))
+    mb = MeshBuilder()
+    v, f, uv = quad((-12, -2.0, -12), (-12, -2.0, 12), (12, -2.0, 12), (12, -2.0, -12))
+    mb.add(v, f, m_floor, uvs=uv)
+    for k in range(shells):
+        m = mats.add(f"shell{k}", tf=(1, 1, 1), t_r=1.0, n_i=1.0 + 0.02 * (k + 1), n_s=1e6,
+                     priority=k + 1)
+        sv, sf, sn = icosphere((0.0, 2.0, 0.0), 3.0 - 0.15 * k, 2)
+        mb.add(sv, sf, m, normals=sn)
+    _add_lights(mb, m_light)
     return Scene(mb.finish(), mats.finish(), default_camera(width, height),
-                 default_params(pathtracing_sample_size=spp, pathtracing_level=level,
-                                sss_pts_per_object=sss_pts),
-                 name=name)
+                 default_params(pathtracing_sample_size=1, pathtracing_level=40),
+                 name="shells")
 
 
 def sppm_scene(cells: int = 91, width: int = 1920, height: int = 1080, photons: int = 10_000_000,
@@ -557,6 +613,8 @@ def make_scene(kind: str, **kw) -> Scene:
         return bottle_scene(**kw)
     if kind == "small":
         return small_scene(**kw)
+    if kind == "shells":
+        return nested_shells_scene(**kw)
     raise ValueError(kind)
 
 

@@ -512,3 +512,77 @@ int orc_trace(OrcCtx *c, int which, const float *rays, int64_t n, int32_t *leaf_
   }
   return GPT_OK;
 }
+
+/* ---- visit counts of the ORDERED, CULLING walk the CUDA path's binary-tree kernels do
+ *      (gpu_pathtracer_b200/csrc/trace_core.cuh trace_ray, trace_persistent.cuh tp_step): the
+ *      reference's predicate per child (above), the extra dominant-axis cull against t_best
+ *      with the 1e-5 relative margin, leaves tested where they are found (left, then right),
+ *      nearer internal child first.  SURVEY.md 8(d) takes the algorithmic bytes of the trace
+ *      stage from these counts (gpt_stats.internal_visits / leaf_tests); this restatement pins
+ *      them (tests/test_gpu_counters.py).  It is the checker of OUR culling rule -- the
+ *      reference itself never culls (traverse() above). -------------------------------------- */
+static void slab_nf(float lo, float hi, float o, float inv, float *tn, float *tf) {
+  float a1 = (lo - o) * inv, a2 = (hi - o) * inv;
+  if (a1 < a2) { *tn = a1; *tf = a2; } else { *tn = a2; *tf = a1; }
+}
+int orc_trace_count(OrcCtx *c, int which, const float *rays, int64_t n, uint64_t *v_int,
+                    uint64_t *v_leaf, int32_t *leaf_id) {
+  const OrcBvh *b = &c->bvh[which];
+  if (b->n < 2) return GPT_E_INVALID;
+  uint64_t vi = 0, vl = 0;
+  for (int64_t r = 0; r < n; r++) {
+    const float *q = rays + 8 * r;
+    v3 o = V(q[0], q[1], q[2]), d = vunit(V(q[4], q[5], q[6]));
+    float ix = 1.0f / d.x, iy = 1.0f / d.y, iz = 1.0f / d.z;
+    float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
+    int kz = (ax >= ay && ax >= az) ? 0 : ((ay >= ax && ay >= az) ? 1 : 2);
+    float best = q[3];
+    int hit_leaf = -1, stack[128], sp = 0, node = 0;
+    for (;;) {
+      int cr[2] = {b->left[node], b->right[node]}, go[2];
+      float tnear[2], tcull[2];
+      vi++;
+      for (int k = 0; k < 2; k++) {
+        const float *bb = child_box(c, b, cr[k]);
+        float txn, txx, tyn, tyx, tzn, tzx;
+        slab_nf(bb[0], bb[1], o.x, ix, &txn, &txx);
+        slab_nf(bb[2], bb[3], o.y, iy, &tyn, &tyx);
+        slab_nf(bb[4], bb[5], o.z, iz, &tzn, &tzx);
+        int ok = (txn <= tyx) && (tyn <= txx);
+        float txyn = fmaxf(txn, tyn), txyx = fminf(txx, tyx);
+        ok = ok && (txyn <= tzx) && (tzn <= txyx);
+        float tn = kz == 0 ? txn : (kz == 1 ? tyn : tzn), tf = kz == 0 ? txx : (kz == 1 ? tyx : tzx);
+        float margin = 1e-5f * fmaxf(fabsf(tn), fabsf(tf));
+        tnear[k] = tn;
+        tcull[k] = tn - margin;
+        go[k] = ok && !(tf + margin < 0.f);
+      }
+      for (int k = 0; k < 2; k++) {
+        if (go[k] && cr[k] < 0) {
+          go[k] = 0;
+          if (tcull[k] > best) continue;
+          float tt, bary[3];
+          vl++;
+          /* tri_hit rejects t > t_max; equal t replaces only for a later visit rank, which does
+           * not change the counts */
+          if (tri_hit(c, b->prim[~cr[k]], o, d, best, &tt, bary)) { best = tt; hit_leaf = ~cr[k]; }
+        }
+      }
+      int gl = go[0] && !(tcull[0] > best), gr = go[1] && !(tcull[1] > best);
+      if (gl && gr) {
+        int lfirst = tnear[0] <= tnear[1];
+        stack[sp++] = lfirst ? cr[1] : cr[0];
+        node = lfirst ? cr[0] : cr[1];
+      } else if (gl || gr) {
+        node = gl ? cr[0] : cr[1];
+      } else {
+        if (sp == 0) break;
+        node = stack[--sp];
+      }
+    }
+    if (leaf_id) leaf_id[r] = hit_leaf;
+  }
+  *v_int = vi;
+  *v_leaf = vl;
+  return GPT_OK;
+}

@@ -87,3 +87,14 @@ class Oracle:
                                   cabi.iptr(out["leaf_id"]), cabi.iptr(out["tri_id"]),
                                   cabi.fptr(out["t"]), cabi.fptr(out["bary"])))
         return out
+
+    def trace_count(self, rays: np.ndarray, which=0) -> dict:
+        """V_int / V_leaf of the ordered, culling walk of the CUDA binary-tree kernels
+        (oracle.c orc_trace_count)."""
+        rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 8)
+        n = rays.shape[0]
+        vi, vl = C.c_uint64(), C.c_uint64()
+        leaf = np.zeros(n, np.int32)
+        _check(self.lib.orc_trace_count(self.ctx, which, cabi.fptr(rays), C.c_int64(n),
+                                        C.byref(vi), C.byref(vl), cabi.iptr(leaf)))
+        return dict(internal_visits=vi.value, leaf_tests=vl.value, leaf_id=leaf)

@@ -3,9 +3,12 @@ path_tracing_render with identical per-pixel XORWOW streams (seed 1984, seq = pi
 
 Shading uses libm functions (powf, cos, sin, atan2 ...) whose CUDA and glibc versions differ
 in the last ulp, so the bar here is a TOLERANCE, stated per test: the two images must agree
-to 1e-3 relative on >= 99.5 % of the pixels, and the mean luminance to 0.5 %.  (A pixel only
-falls outside when a 1-ulp difference flips a discrete decision -- a Russian-roulette-like
-branch on a uniform, a texel index, a hit/miss at a silhouette.)"""
+to 1e-3 relative on >= 99.5 % of the pixels, the mean luminance to 0.5 %, and the RMSE must
+stay below RMSE_FRAC of the mean luminance.  (A pixel only falls outside when a 1-ulp
+difference flips a discrete decision -- a Russian-roulette-like branch on a uniform, a texel
+index, a hit/miss at a silhouette; such a pixel then differs by a whole sample's radiance,
+which is what the RMSE bound has to leave room for: at 2-4 samples per pixel one flipped
+sample in 0.5 % of the pixels is an RMSE of a few per cent of the mean.)"""
 import numpy as np
 import pytest
 
@@ -13,8 +16,10 @@ from gpu_pathtracer_b200 import scene as S
 
 pytestmark = pytest.mark.gpu
 
+RMSE_FRAC = 0.10  # RMSE <= 10 % of the mean luminance (measured: 0.5-4 %)
 
-def _compare(sc, window=None, min_frac=0.995):
+
+def _compare(sc, window=None, min_frac=0.995, rmse_frac=RMSE_FRAC):
     from gpu_pathtracer_b200.api import PathTracer
     from tests.refreplay import RefReplay
     pt = PathTracer(sc)
@@ -34,6 +39,7 @@ def _compare(sc, window=None, min_frac=0.995):
           f"rmse {rmse:.3e}, exact {np.mean(got == want):.4f}")
     assert frac >= min_frac, frac
     assert abs(lum_g - lum_w) <= 5e-3 * abs(lum_w)
+    assert rmse <= rmse_frac * abs(lum_w), (rmse, lum_w)
     if window is None:  # same paths => (almost) the same number of closest-hit traversals
         rays_g, rays_w = pt.stats()["rays_traced"], ref.render_rays
         assert abs(rays_g - rays_w) <= 5e-3 * rays_w, (rays_g, rays_w)
@@ -52,6 +58,61 @@ def test_metal_glass_nested():
 def test_textured_bump():
     _compare(S.make_scene("small", n=24, width=128, height=128, spp=2, level=4, textured=True,
                           name="textured"))
+
+
+def test_all_texture_slots_and_equirect_sky():
+    """SURVEY a-11: Material::_get_texture for the specular / emission / n_s slots
+    (material.h:653-727) and _get_sky_color on a non-constant 64 x 32 equirectangular
+    background (pathtracing.h:69-82), on top of the diffuse + bump maps of the test above."""
+    sc = S.make_scene("small", n=24, width=128, height=128, spp=2, level=4, textured=True,
+                      all_maps=True, sky=True, name="all_maps")
+    m = sc.materials
+    for slot in ("specular", "emission", "n_s", "diffuse", "bump"):
+        assert (m["height_" + slot] > 1).any(), slot
+    assert sc.bg["height"] * sc.bg["width"] >= 64 * 32 and np.ptp(sc.bg["r"]) > 0.1
+    _compare(sc)
+
+
+def test_nested_dielectric_depth_limit_is_an_error():
+    """Deviation: the nested-dielectric list holds 12 materials (the
+    reference reserves 400 pointers).  Deeper nesting must FAIL the render with
+    GPT_E_UNSUPPORTED, never render something else silently; 10 shells still render."""
+    from gpu_pathtracer_b200.api import GptError, PathTracer
+    ok = PathTracer(S.make_scene("shells", shells=10))
+    ok.build()
+    assert np.isfinite(ok.render_pathtrace()).all()
+    deep = PathTracer(S.make_scene("shells", shells=14))
+    deep.build()
+    with pytest.raises(GptError, match="nested-dielectric"):
+        deep.render_pathtrace()
+
+
+def test_rebuild_with_another_scene_on_one_context():
+    """the light-tree side arrays are cached per context; a second scene with the
+    SAME number of emissive triangles must not be lit with the first scene's records."""
+    from gpu_pathtracer_b200.api import PathTracer
+    a = S.make_scene("small", n=24, width=128, height=128, spp=2, level=4, name="A")
+    b = S.make_scene("small", n=24, width=128, height=128, spp=2, level=4, name="B")
+    m = b.mesh  # move and brighten the lights of B: same count, other geometry and energy
+    lights = np.isin(m["material_idx"], [i for i, n in enumerate(b.materials["material_names"]) if n == "light"])
+    vid = np.unique(np.concatenate([m[k][lights] for k in ("point_1_idx", "point_2_idx", "point_3_idx")]))
+    m["x"] = m["x"].copy(); m["z"] = m["z"].copy()
+    m["x"][vid] += 2.5; m["z"][vid] -= 3.0
+    li = b.materials["material_names"].index("light")
+    for k in ("ke_x", "ke_y", "ke_z"):
+        b.materials[k] = b.materials[k].copy()
+    b.materials["ke_x"][li], b.materials["ke_y"][li], b.materials["ke_z"][li] = 30.0, 10.0, 5.0
+    fresh = PathTracer(b)
+    fresh.build()
+    want = fresh.render_pathtrace()
+    pt = PathTracer(a)
+    pt.build()
+    first = pt.render_pathtrace()
+    pt.set_scene(b)
+    pt.build()
+    got = pt.render_pathtrace()
+    assert np.array_equal(got, want), "stale per-context state after a rebuild"
+    assert not np.array_equal(got, first)
 
 
 def test_depth_of_field_bottle():
