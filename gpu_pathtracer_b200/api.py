@@ -29,7 +29,7 @@ gpt_sppm_init gpt_sppm_pass gpt_sppm_flux_device gpt_sppm_update gpt_sppm_resolv
 gpt_sppm_stats gpt_sppm_export_hit_points gpt_sppm_export_photons gpt_sppm_import_photons
 gpt_sppm_pass_stages gpt_sppm_import_hit_points gpt_sss_export_points gpt_tonemap_u8 gpt_write_ppm_u8
 gpt_save_image gpt_sppm_debug_image gpt_sss_debug_image gpt_stats
-gpt_synchronize gpt_set_profiling gpt_set_wavefront_groups gpt_set_trace_tail gpt_set_trace_leaf_batching gpt_set_pipeline gpt_set_trace_bvh
+gpt_synchronize gpt_set_profiling gpt_set_wavefront_groups gpt_set_trace_tail gpt_set_trace_leaf_batching gpt_set_pipeline gpt_set_trace_bvh gpt_set_fast_rng_lanes
 gpt_scene_files_parse gpt_scene_files_view gpt_scene_files_material_name
 gpt_scene_files_texture_name gpt_scene_files_free gpt_load_scene_files""".split()
 
@@ -158,6 +158,16 @@ class PathTracer:
         """gpt_set_trace_leaf_batching: 1 batch a warp's triangle tests (deferred leaf tests),
         0 test every leaf where it is found, -1 default.  Bit-identical hits."""
         self._check(self.lib.gpt_set_trace_leaf_batching(self.ctx, C.c_int(int(mode))))
+
+    def set_fast_rng_lanes(self, lanes=0):
+        """rng_mode 1: independent sample streams per pixel (0 = default 8)."""
+        self._check(self.lib.gpt_set_fast_rng_lanes(self.ctx, C.c_int(int(lanes))))
+
+    def set_params(self, **kw):
+        """Update render scalars (GptParams) of the current scene and re-send them."""
+        self.scene.params.update(kw)
+        p = cabi.pack_params(self.scene.params)
+        self._check(self.lib.gpt_set_params(self.ctx, C.byref(p)))
 
     def set_trace_bvh(self, mode=-1):
         """gpt_set_trace_bvh: 1 walk the 4-wide tree, 0 the binary LBVH, -1 default ('wide' /

@@ -479,6 +479,12 @@ int gpt_set_trace_tail(gpt_ctx *ctx, int mode) {
   return GPT_OK;
 }
 
+int gpt_set_fast_rng_lanes(gpt_ctx *ctx, int lanes) {
+  if (!ctx || lanes < 0 || lanes > 64) return GPT_E_INVALID;
+  ctx->fast_lanes = lanes;
+  return GPT_OK;
+}
+
 int gpt_set_trace_bvh(gpt_ctx *ctx, int mode) {
   if (!ctx || mode < -1 || mode > 1) return GPT_E_INVALID;
   ctx->trace_wide = mode;

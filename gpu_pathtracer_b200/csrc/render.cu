@@ -33,6 +33,9 @@ struct RenderCtx {
   uint64_t light_epoch = 0;       // ctx->build_epoch the light-tree arrays were made for
   uint32_t *rng_init = nullptr;   // cached curand_init states for (width, height, rank set)
   int rng_w = 0, rng_h = 0, rng_rank = -1, rng_nranks = 0;
+  int rng_lanes = 0, rng_conc = 0;  // rng_mode 1: lanes per pixel the cache holds / lanes per wave the pixel map holds
+  size_t rng_init_cap = 0;        // words allocated for rng_init
+  float4 *partial = nullptr;      // rng_mode 1: a slot's colour sum (one per slot of a wave)
   // Independent wavefront groups (slot ranges), each on its own stream with its own queues,
   // counters and read-back ring, so the tail of one group's trace overlaps the others' work.
   static constexpr int MAX_GROUPS = 8, RING = 4;
@@ -46,6 +49,8 @@ struct RenderCtx {
   int hist_stride = 0;
   uint32_t *sort_key = nullptr, *sort_key_alt = nullptr, *sort_hist = nullptr;
   int *sort_val = nullptr, *sort_val_alt = nullptr;
+  int *classq = nullptr;          // PT_NCLASS material-class lists per group (k_pt_trace -> k_pt_shade)
+  int *ccount = nullptr;          // MAX_GROUPS x 3 (rotation) x PT_NCLASS list lengths
   int *sq_cells = nullptr, *sq_ctl = nullptr;  // streaming pipeline: 9 rings + control words
   int sq_capacity = 0;                         // cells per ring
   float *d_fb = nullptr;          // internal framebuffer for the host API
@@ -64,6 +69,11 @@ struct RenderParams {
   int mode;           // 0 = camera paths into the frame buffer, 1 = SSS first pass (paths start
                       //     at the SSS points, do_sss_first_pass pathtracing.h:202-249)
   int use_sss;        // mode 0: SSS point trees exist -> compute_color_sss at SSS hits
+  // rng_mode 1 (fast_lanes > 0): a pixel's dof x spp samples are dealt to fast_lanes independent
+  // streams (curand sequence pixel * fast_lanes + lane); a wave renders lanes lane0 .. of every
+  // pixel, slot s = (lane - lane0) * npix + pixel slot, and leaves each slot's sum in `partial`
+  int fast_lanes, lane0, npix, total_samples;
+  float4 *partial;
   SssView sss;
 };
 
@@ -73,6 +83,17 @@ __global__ void __launch_bounds__(128) k_rng_init(uint32_t *rng, const int *pixe
   if (s >= n) return;
   Rng r;
   curand_init(1984, pixel[s], 0, &r.s);
+  rng_store_packed(r, rng, s);
+}
+
+// rng_mode 1: stream of (pixel, lane) = curand sequence pixel * lanes + lane; state index lane * npix + p
+__global__ void __launch_bounds__(128)
+k_rng_init_lanes(uint32_t *rng, const int *pixel, int npix, int lanes) {
+  size_t s = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= (size_t)npix * lanes) return;
+  const int lane = (int)(s / npix), pl = (int)(s % npix);
+  Rng r;
+  curand_init(1984, (unsigned long long)pixel[pl] * lanes + lane, 0, &r.s);
   rng_store_packed(r, rng, s);
 }
 
@@ -415,40 +436,103 @@ k_pt_start(PathState ps, RenderParams p, int n, float *fb) {
   ps.cm[2 * (size_t)s] = make_float4(0.f, 0.f, 0.f, __int_as_float(0));
   start_sample(ps, s, o, d);
   ps.queue[0][s] = s;
-  fb[3 * (size_t)pix] = 0.f; fb[3 * (size_t)pix + 1] = 0.f; fb[3 * (size_t)pix + 2] = 0.f;
+  if (p.fast_lanes == 0) { fb[3 * (size_t)pix] = 0.f; fb[3 * (size_t)pix + 1] = 0.f; fb[3 * (size_t)pix + 2] = 0.f; }
+}
+
+// rng_mode 1, after a wave: fb[pixel] (+)= the sums of the wave's lanes in lane order; the last
+// wave scales by 1 / samples.  The frame is the same whatever the number of lanes per wave.
+__global__ void __launch_bounds__(PT_BLOCK)
+k_pt_combine(const int *__restrict__ pixel, const float4 *__restrict__ partial, int npix, int lanes,
+             int first, int last, float inv_samples, float *fb) {
+  int pl = blockIdx.x * blockDim.x + threadIdx.x;
+  if (pl >= npix) return;
+  const size_t o = 3 * (size_t)pixel[pl];
+  V3 acc = first ? V3{0.f, 0.f, 0.f} : V3{fb[o], fb[o + 1], fb[o + 2]};
+  for (int c = 0; c < lanes; c++) {
+    const float4 v = partial[(size_t)c * npix + pl];
+    acc = acc + V3{v.x, v.y, v.z};
+  }
+  if (last) acc = acc * inv_samples;
+  fb[o] = acc.x; fb[o + 1] = acc.y; fb[o + 2] = acc.z;
 }
 
 // trace stage: persistent warps pull active slots from the queue (trace_persistent.cuh)
+//
+// What the shade stage wants is its slots grouped by the code they will run (the material at the
+// hit): that keeps its warps converged and its instruction cache warm.  Round 1 got there with a
+// stable radix sort between the two stages -- three more launches in each of the spp x level
+// dependent rounds of a frame (9 % of the GPU time at 1080p, and ~15 us of pure latency per
+// round on a tile-sharded frame).  Now the trace kernel itself appends every
+// finished slot to the list of its material class (PT_NCLASS lists per group, one warp-aggregated
+// atomicAdd per class and warp) and the shade kernel reads the lists back to back: the same
+// grouping, no sort, two launches per round.  A pixel's result does not depend on the order
+// its slot is shaded in, so the frame is bit-identical (test).
+constexpr int PT_NCLASS = 16;  // 15 material classes (material id mod 15) + misses
 struct QueueSource {
   PathState ps;
   const int *queue;
   const int *qcount;
   const float4 *shade;   // per-triangle shading records (material id in s6.y)
-  uint32_t *sort_key;    // out: shade-coherence key of queue entry i (material, 127 = miss)
-  int *sort_val;         // out: its slot
+  uint32_t *sort_key;    // sort mode -- out: shade-coherence key of queue entry i (material, 127 = miss)
+  int *sort_val;         //              out: its slot
   int loc_bits, loc_shift;  // minor key: the hit leaf's top loc_bits bits (Morton order = place)
+  int *classq;           // class mode (sort_key == nullptr): PT_NCLASS lists of cstride slots
+  int cstride;
+  int *ccount;           // their lengths
   __device__ int count() const { return *qcount; }
   __device__ void load(int i, float4 &o, float4 &d) const {
     int s = queue[i];
     o = ps.rays[2 * (size_t)s];
     d = ps.rays[2 * (size_t)s + 1];
   }
-  __device__ void store(int i, const TraceLane &l) const {
+  __device__ int material_of(const TraceLane &l) const {
+    return l.leaf >= 0 ? (__float_as_int(__ldg(&shade[7 * (size_t)l.prim + 6].y)) & 127) : 127;
+  }
+  __device__ int write_hit(int i, const TraceLane &l) const {
     int s = queue[i];
     ps.hits[2 * (size_t)s] = make_float4(l.t, __int_as_float(l.leaf), __int_as_float(l.prim), 0.f);
     ps.hits[2 * (size_t)s + 1] = make_float4(l.b1, l.b2, l.b3, 0.f);
-    // Key for the material sort that precedes shade: paths that will run the same BSDF code
-    // become neighbours, which is what keeps warps converged (and the instruction cache warm)
-    // in k_pt_shade.
-    // ... and, within a material, paths that hit the same part of the scene: their textures /
-    // shading records share cache lines, and the rays they spawn start close together, which
-    // is what the NEXT trace wants (shade appends to the next queue in this order).
-    uint32_t key = 127u << loc_bits;
-    if (l.leaf >= 0)
-      key = (((uint32_t)__float_as_int(__ldg(&shade[7 * (size_t)l.prim + 6].y)) & 127u) << loc_bits) |
-            ((uint32_t)l.leaf >> loc_shift);
-    sort_key[i] = key;
-    sort_val[i] = s;
+    return s;
+  }
+  __device__ void store(int i, const TraceLane &l) const {  // one lane on its own
+    const int s = write_hit(i, l);
+    const int m = material_of(l);
+    if (sort_key) {
+      // Key for the material sort that precedes shade: paths that will run the same BSDF code
+      // become neighbours ... and, within a material, paths that hit the same part of the
+      // scene: their textures / shading records share cache lines, and the rays they spawn
+      // start close together, which is what the NEXT trace wants.
+      uint32_t key = (uint32_t)m << loc_bits;
+      if (l.leaf >= 0) key |= (uint32_t)l.leaf >> loc_shift;
+      sort_key[i] = key;
+      sort_val[i] = s;
+    } else {
+      const int c = m == 127 ? PT_NCLASS - 1 : m % (PT_NCLASS - 1);
+      classq[(size_t)c * cstride + atomicAdd(ccount + c, 1)] = s;
+    }
+  }
+  // called by all 32 lanes; the lanes with fin set hand their ray's record over
+  __device__ void store_warp(bool fin, int i, const TraceLane &l) const {
+    if (sort_key) {
+      if (fin) store(i, l);
+      return;
+    }
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    int c = -1, s = 0;
+    if (fin) {
+      s = write_hit(i, l);
+      const int m = material_of(l);
+      c = m == 127 ? PT_NCLASS - 1 : m % (PT_NCLASS - 1);
+    }
+    const unsigned peers = __match_any_sync(FULL, c);
+    if (fin) {
+      const int leader = __ffs(peers) - 1;
+      int base = 0;
+      if (lane == leader) base = atomicAdd(ccount + c, __popc(peers));
+      base = __shfl_sync(peers, base, leader);
+      classq[(size_t)c * cstride + base + __popc(peers & ((1u << lane) - 1u))] = s;
+    }
   }
 };
 
@@ -572,6 +656,23 @@ __device__ __forceinline__ bool shade_slot(const PathState &ps, const RenderPara
         o = V3{co.x, co.y, co.z};
         d = generate_dir(V3{0.f, 0.f, 0.f}, V3{cn.x, cn.y, cn.z}, 0, 1.f, rng);
       }
+    } else if (p.fast_lanes) {
+      // this slot's lane gets samples lane, lane + lanes, ... of the pixel's dof x spp (dof index =
+      // sample / spp); as in the reference a new camera ray is drawn when the dof index changes
+      // and reused otherwise, so one lane reproduces the reference's stream exactly
+      const int lane = p.lane0 + s / p.npix;
+      if (sidx >= (p.total_samples - lane + p.fast_lanes - 1) / p.fast_lanes) {
+        finished = true;
+      } else if ((lane + sidx * p.fast_lanes) / p.sample_size != (lane + (sidx - 1) * p.fast_lanes) / p.sample_size) {
+        int pix = ps.pixel[s];
+        camera_ray(p.cam, pix / p.cam.width + .5f, pix % p.cam.width + .5f, rng, o, d);
+        ps.cam[2 * (size_t)s] = make_float4(o.x, o.y, o.z, 0.f);
+        ps.cam[2 * (size_t)s + 1] = make_float4(d.x, d.y, d.z, 0.f);
+      } else {
+        float4 co = PS_LD(ps.cam + 2 * (size_t)s), cd = PS_LD(ps.cam + 2 * (size_t)s + 1);
+        o = V3{co.x, co.y, co.z};
+        d = V3{cd.x, cd.y, cd.z};
+      }
     } else if (sidx >= p.sample_size) {
       sidx = 0;
       k++;
@@ -594,6 +695,9 @@ __device__ __forceinline__ bool shade_slot(const PathState &ps, const RenderPara
       V3 out = (color * p.inv_samples) * V3{pa.w, pb.x, pb.y};
       p.sss.leaf[2 * (size_t)s + 1] = make_float4(out.x, out.y, out.z, 0.f);
       alive = false;
+    } else if (finished && p.fast_lanes) {
+      p.partial[s] = make_float4(color.x, color.y, color.z, 0.f);
+      alive = false;
     } else if (finished) {
       int pix = ps.pixel[s];
       V3 out = color * p.inv_samples;
@@ -615,7 +719,9 @@ __global__ void __launch_bounds__(PT_BLOCK, 5)  // 5 blocks per SM = the 96-regi
 k_pt_shade(PathState ps, RenderParams p, const int *__restrict__ queue,
            const int *__restrict__ count, int *next_queue, int *next_count, SceneDev sc,
            TexAtlas atlas, const float4 *__restrict__ main_tris, LightTree lt, float *fb,
-           int *error_flag, unsigned long long *ray_counter, int *zero_a, int *zero_b) {
+           int *error_flag, unsigned long long *ray_counter, int *zero_a, int *zero_b,
+           const int *__restrict__ classq, int cstride, const int *__restrict__ ccount,
+           int *czero) {
   int a = blockIdx.x * blockDim.x + threadIdx.x;
   if (a == 0) {
     atomicAdd(ray_counter, (unsigned long long)*count);  // rays traced this iteration
@@ -624,10 +730,22 @@ k_pt_shade(PathState ps, RenderParams p, const int *__restrict__ queue,
     *zero_a = 0;
     *zero_b = 0;
   }
+  // class lengths of the round after next (read last by the previous round's shade)
+  if (classq && a < PT_NCLASS) czero[a] = 0;
   bool alive = false;
   int s = -1;
   if (a < *count) {
-    s = queue[a];
+    if (classq) {  // entry a of the PT_NCLASS class lists laid end to end
+      int c = 0, before = 0;
+#pragma unroll
+      for (int k = 0; k < PT_NCLASS - 1; k++) {
+        const int len = __ldg(ccount + k);
+        if (c == k && a >= before + len) { c = k + 1; before += len; }
+      }
+      s = classq[(size_t)c * cstride + (a - before)];
+    } else {
+      s = queue[a];
+    }
     alive = shade_slot<false>(ps, p, s, sc, atlas, main_tris, lt, fb, error_flag);
   }
   // warp-aggregated compaction of the surviving slots into the next queue
@@ -903,6 +1021,8 @@ static int reserve_paths(gpt_ctx *ctx, RenderCtx *rc, int n) {
   GPT_TRY(gpt_alloc(ctx, &ps.pixel, N));
   GPT_TRY(gpt_alloc(ctx, &ps.rng, 8 * N));
   GPT_TRY(gpt_alloc(ctx, &rc->rng_init, 8 * N));
+  rc->rng_init_cap = 8 * N;
+  GPT_TRY(gpt_alloc(ctx, &rc->partial, N));
   GPT_TRY(gpt_alloc(ctx, &ps.rays, 2 * N));
   GPT_TRY(gpt_alloc(ctx, &ps.hits, 2 * N));
   GPT_TRY(gpt_alloc(ctx, &ps.ma, 2 * N));
@@ -915,6 +1035,8 @@ static int reserve_paths(gpt_ctx *ctx, RenderCtx *rc, int n) {
   GPT_TRY(gpt_alloc(ctx, &rc->sort_key_alt, N));
   GPT_TRY(gpt_alloc(ctx, &rc->sort_val, N));
   GPT_TRY(gpt_alloc(ctx, &rc->sort_val_alt, N));
+  GPT_TRY(gpt_alloc(ctx, &rc->classq, (size_t)PT_NCLASS * N));
+  GPT_TRY(gpt_alloc(ctx, &rc->ccount, (size_t)RenderCtx::MAX_GROUPS * 3 * PT_NCLASS));
   rc->hist_stride = gpt_radix_hist_entries(n);
   GPT_TRY(gpt_alloc(ctx, &rc->sort_hist, (size_t)rc->hist_stride * RenderCtx::MAX_GROUPS));
   if (!rc->h_counts) {
@@ -948,7 +1070,25 @@ static std::vector<int> tile_pixels(int W, int H, int rank, int nranks) {
   return px;
 }
 
-static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool sss_pass = false) {
+// rng_mode 1 ("fast", gpt.h GptParams.rng_mode).  The reference gives a pixel ONE XORWOW stream and
+// runs its dof x spp samples one after the other on it (pathtracing.h:277-293), so a frame is a
+// chain of dof x spp x level dependent rounds however few pixels a GPU renders: that chain, not
+// throughput, is what an 8-way tile-sharded frame is made of.  Here the samples of
+// a pixel are dealt to `lanes` independent streams (sequence pixel * lanes + lane) that run side
+// by side, `conc` of them at a time: the chain is lanes times shorter, and a rank with an eighth
+// of the pixels keeps as many paths in flight as a whole frame does.  The image is a function of
+// the scene and of `lanes` only -- not of conc, the rank count or the run -- because lane sums are
+// added in lane order; with lanes = 1 it IS the reference-mode image.  It is another Monte-Carlo
+// estimate of the same integral, not the reference's bit pattern: compared statistically
+// (tests/test_gpu_render.py::test_fast_rng_mode).
+struct FastWave {
+  int lanes, lane0, conc;
+  bool first, last;
+};
+constexpr long long GPT_FAST_TARGET_SLOTS = 2200000;  // paths in flight a wave aims for (~ a 1080p frame)
+
+static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool sss_pass = false,
+                         const FastWave *fw = nullptr) {
   if (!ctx->built) return gpt_fail(ctx, GPT_E_INVALID, "gpt_build first", __FILE__, __LINE__);
   if (!ctx->have_cam) return gpt_fail(ctx, GPT_E_INVALID, "gpt_set_camera first", __FILE__, __LINE__);
   if (nranks < 1 || rank < 0 || rank >= nranks) return GPT_E_INVALID;
@@ -956,6 +1096,37 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
   if (gp.pathtracing_sample_size < 1 || gp.pathtracing_level < 1 || gp.dof_sample_size < 1)
     return gpt_fail(ctx, GPT_E_INVALID, "sample_size, level and dof_sample_size must be >= 1", __FILE__, __LINE__);
   GPT_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (!sss_pass && !fw && gp.rng_mode == 1) {
+    const long long total = (long long)gp.pathtracing_sample_size * gp.dof_sample_size;
+    int lanes = ctx->fast_lanes > 0 ? ctx->fast_lanes : 8;
+    if (lanes > total) lanes = (int)total;
+    long long npix = 0;
+    {
+      const int W = ctx->cam.width, H = ctx->cam.height, tx = (W + 31) / 32, ty = (H + 31) / 32;
+      for (int t = rank; t < tx * ty; t += nranks)
+        npix += (long long)std::min(32, W - (t % tx) * 32) * std::min(32, H - (t / tx) * 32);
+    }
+    if (npix == 0) return GPT_OK;
+    long long target = GPT_FAST_TARGET_SLOTS;
+    if (const char *e = getenv("GPT_FAST_TARGET_SLOTS")) target = atoll(e);  // tests: force several waves
+    int conc = (int)std::max(1LL, std::min((long long)lanes, target / npix));
+    GptStats sum{};
+    for (int lane0 = 0; lane0 < lanes; lane0 += conc) {
+      FastWave w{lanes, lane0, conc, lane0 == 0, lane0 + conc >= lanes};
+      GPT_TRY(render_device(ctx, d_fb, rank, nranks, false, &w));
+      const GptStats &st = ctx->stats;
+      sum.render_ms += st.render_ms; sum.rays_traced += st.rays_traced; sum.shade_events += st.shade_events;
+      sum.kernel_launches += st.kernel_launches; sum.trace_launches += st.trace_launches;
+      sum.trace_kernel_ms += st.trace_kernel_ms; sum.shade_kernel_ms += st.shade_kernel_ms;
+      sum.internal_visits += st.internal_visits; sum.leaf_tests += st.leaf_tests;
+    }
+    ctx->stats.render_ms = sum.render_ms; ctx->stats.rays_traced = sum.rays_traced;
+    ctx->stats.shade_events = sum.shade_events; ctx->stats.kernel_launches = sum.kernel_launches;
+    ctx->stats.trace_launches = sum.trace_launches; ctx->stats.trace_kernel_ms = sum.trace_kernel_ms;
+    ctx->stats.shade_kernel_ms = sum.shade_kernel_ms; ctx->stats.internal_visits = sum.internal_visits;
+    ctx->stats.leaf_tests = sum.leaf_tests;
+    return GPT_OK;
+  }
   RenderCtx *rc = rc_of(ctx);
   SssView sv{};
   bool sss_done = true;
@@ -969,9 +1140,10 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
   ctx->launches = 0;
   int W = ctx->cam.width, H = ctx->cam.height;
   bool new_map = !(rc->rng_w == W && rc->rng_h == H && rc->rng_rank == rank &&
-                   rc->rng_nranks == nranks);
+                   rc->rng_nranks == nranks && rc->rng_lanes == (fw ? fw->lanes : 0) &&
+                   rc->rng_conc == (fw ? fw->conc : 0));
   std::vector<int> px;
-  int n;
+  int n, npix = 0;
   if (sss_pass) {
     n = sv.npoints;
     int cap_before = rc->ps.capacity;
@@ -981,18 +1153,33 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
     rc->rng_w = rc->rng_h = 0;  // the slot -> pixel map is overwritten by this pass
   } else if (new_map) {
     px = tile_pixels(W, H, rank, nranks);
-    n = (int)px.size();
+    npix = n = (int)px.size();
     if (n == 0) return GPT_OK;  // more ranks than tiles: nothing to render here
+    if (fw) {  // the pixel list once per concurrent lane: slot (c, p) = c * npix + p
+      if ((long long)npix * fw->conc > 0x7fffffffLL) return gpt_fail(ctx, GPT_E_INVALID, "too many slots", __FILE__, __LINE__);
+      px.resize((size_t)npix * fw->conc);
+      for (int c = 1; c < fw->conc; c++) std::copy(px.begin(), px.begin() + npix, px.begin() + (size_t)c * npix);
+      n = npix * fw->conc;
+    }
     GPT_TRY(reserve_paths(ctx, rc, n));
     GPT_CUDA(ctx, cudaMemcpyAsync(rc->ps.pixel, px.data(), sizeof(int) * (size_t)n,
                                   cudaMemcpyHostToDevice, ctx->stream));
     // init_curand_state (src/main.cu:1208): once per image layout, cached
-    int cap = rc->ps.capacity;
-    (void)cap;
-    k_rng_init<<<(n + 127) / 128, 128, 0, ctx->stream>>>(rc->rng_init, rc->ps.pixel, n);
+    if (fw) {
+      const size_t words = 8 * (size_t)npix * fw->lanes;
+      if (words > rc->rng_init_cap) {
+        GPT_TRY(gpt_alloc(ctx, &rc->rng_init, words));
+        rc->rng_init_cap = words;
+      }
+      const size_t states = (size_t)npix * fw->lanes;
+      k_rng_init_lanes<<<(unsigned)((states + 127) / 128), 128, 0, ctx->stream>>>(rc->rng_init, rc->ps.pixel, npix, fw->lanes);
+    } else {
+      k_rng_init<<<(n + 127) / 128, 128, 0, ctx->stream>>>(rc->rng_init, rc->ps.pixel, n);
+    }
     GPT_LAUNCH_CHECK(ctx);
     GPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     rc->rng_w = W; rc->rng_h = H; rc->rng_rank = rank; rc->rng_nranks = nranks;
+    rc->rng_lanes = fw ? fw->lanes : 0; rc->rng_conc = fw ? fw->conc : 0;
     rc->light_n = 0;
   } else {
     n = 0;
@@ -1001,7 +1188,9 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
       int x0 = (t % tx) * 32, y0 = (t / tx) * 32;
       n += (std::min(32, W - x0)) * (std::min(32, H - y0));
     }
+    npix = n;
   }
+  if (fw) n = npix * std::min(fw->conc, fw->lanes - fw->lane0);  // slots of this wave
   if (n == 0) return GPT_OK;
   PathState ps = rc->ps;
   ps.capacity = n;  // stride of the RNG planes for this render
@@ -1021,6 +1210,11 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
   p.inv_samples = sss_pass ? (float)(1.0 / gp.pathtracing_sample_size)
                            : (float)(1.0 / gp.pathtracing_sample_size / gp.dof_sample_size);
   p.mode = sss_pass ? 1 : 0;
+  p.fast_lanes = fw ? fw->lanes : 0;
+  p.lane0 = fw ? fw->lane0 : 0;
+  p.npix = npix;
+  p.total_samples = gp.pathtracing_sample_size * gp.dof_sample_size;
+  p.partial = rc->partial;
   p.use_sss = (!sss_pass && have_sss) ? 1 : 0;
   p.sss = sv;
 
@@ -1036,8 +1230,8 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
   }
   GPT_CUDA(ctx, cudaEventRecord(ctx->ev0, st));
   if (!sss_pass)
-    GPT_CUDA(ctx, cudaMemcpyAsync(ps.rng, rc->rng_init, sizeof(uint32_t) * 8 * (size_t)n,
-                                  cudaMemcpyDeviceToDevice, st));
+    GPT_CUDA(ctx, cudaMemcpyAsync(ps.rng, rc->rng_init + (fw ? 8 * (size_t)npix * fw->lane0 : 0),
+                                  sizeof(uint32_t) * 8 * (size_t)n, cudaMemcpyDeviceToDevice, st));
   if (sss_pass)
     k_sss_start<<<(n + PT_BLOCK - 1) / PT_BLOCK, PT_BLOCK, 0, st>>>(ps, p, n);
   else
@@ -1046,22 +1240,25 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
   const bool coop = gpt_trace_coop(ctx, mb);  // cooperative tail (trace_persistent.cuh)
   const bool defer_leaves = gpt_trace_defer(ctx);  // deferred leaf tests (trace_persistent.cuh)
   const bool wide_walk = gpt_trace_wide(ctx, mb);  // 4-wide tree (trace_wide.cuh)
-  // persistent grid = SMs x resident blocks of the kernel that will run (cached per variant)
+  static int wide_min_rays = -1;
+  if (wide_min_rays < 0) { const char *e = getenv("GPT_TRACE_WIDE_MIN_RAYS"); wide_min_rays = e ? atoi(e) : 190000; }
+  // persistent grid = SMs x resident blocks of the kernel that runs: [0] binary walk, [1] wide walk
   static int trace_grid_of[2] = {0, 0};
-  int &trace_grid = trace_grid_of[wide_walk ? 1 : 0];
-  if (!trace_grid) {
-    int sms = 148, per_sm = 4;
+  if (!trace_grid_of[0]) {
+    int sms = 148, per_sm[2] = {4, 4};
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
     // (the variant with the tail: 72 registers, 7 blocks per SM instead of 8 -- the grid size
     //  is flat between 4 and 8, profiles/r01d_summary.md)
-    if (wide_walk) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pt_trace_wide<false>, TP_BLOCK, 0);
-    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_pt_trace<false, true>, TP_BLOCK, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm[0], k_pt_trace<false, true>, TP_BLOCK, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm[1], k_pt_trace_wide<false>, TP_BLOCK, 0);
     // GPT_TRACE_BLOCKS_PER_SM < occupancy leaves room for another group's shade / sort blocks to
     // run beside a persistent trace kernel instead of after it (experiment knob)
     const char *e = getenv("GPT_TRACE_BLOCKS_PER_SM");
     int cap = e ? atoi(e) : 0;
-    if (cap > 0 && cap < per_sm) per_sm = cap;
-    trace_grid = sms * (per_sm > 0 ? per_sm : 1);
+    for (int k = 0; k < 2; k++) {
+      if (cap > 0 && cap < per_sm[k]) per_sm[k] = cap;
+      trace_grid_of[k] = sms * (per_sm[k] > 0 ? per_sm[k] : 1);
+    }
   }
   uint64_t rays = 0, shades = 0, trace_launches = 0;
   const bool timing = ctx->prof_time_stages, counting = ctx->prof_count_visits;
@@ -1089,7 +1286,7 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
     }
     pipeline = env_pipe >= 0 ? env_pipe : (n <= GPT_STREAM_AUTO_MAX_SLOTS ? 1 : 0);
   }
-  if (sss_pass || timing) pipeline = 0;  // the SSS first pass and stage timing use the rounds
+  if (sss_pass || timing || fw) pipeline = 0;  // the SSS first pass, stage timing and rng_mode 1 use the rounds
   if (pipeline == 1) {
     // ---- streaming pipeline: two persistent kernels side by side (see k_pt_shade_stream) ------
     int cells = 1024;
@@ -1262,6 +1459,17 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
     h_init[CNT * g] = grp[g].n;
   }
   GPT_CUDA(ctx, cudaMemcpyAsync(ps.counts, h_init, sizeof(int) * CNT * G, cudaMemcpyHostToDevice, st));
+  // how the shade stage gets its slots grouped by material: class lists written by the trace
+  // kernel (default) or the round-1 radix sort between the stages (GPT_SHADE_SORT=1, A/B)
+  // Measured on rank 0's share of C2 (tools/shard_time.py, r02): a full 1080p frame is faster with
+  // the sort (the appends make the trace warps wait for their atomics: 27.6 vs 25.2 ms of trace
+  // at 8 spp), a 1/8 share -- where a round is pure latency -- with the lists (17.4 vs 18.1 ms at
+  // 16 spp).  GPT_SHADE_SORT=1 / 0 forces one; default: lists for groups of <= 100 000 slots.
+  static int shade_sort = -2;
+  if (shade_sort == -2) { const char *e = getenv("GPT_SHADE_SORT"); shade_sort = e ? atoi(e) : -1; }
+  const bool class_lists = shade_sort >= 0 ? !shade_sort : (grp[0].n <= 100000);
+  if (class_lists)
+    GPT_CUDA(ctx, cudaMemsetAsync(rc->ccount, 0, sizeof(int) * RenderCtx::MAX_GROUPS * 3 * PT_NCLASS, st));
 
   unsigned long long *ray_counter = ctx->d_counters + 6;
   GPT_CUDA(ctx, cudaMemsetAsync(ray_counter, 0, sizeof(unsigned long long), st));
@@ -1306,10 +1514,17 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
       GPT_CUDA(ctx, stamp());
       {
         QueueSource qs{ps, ps.queue[q.cur] + q.s0, d_counts + c0, ctx->scene.shade,
-                       rc->sort_key + q.s0, rc->sort_val + q.s0, loc_bits, loc_shift};
+                       class_lists ? nullptr : rc->sort_key + q.s0, rc->sort_val + q.s0, loc_bits, loc_shift,
+                       rc->classq + (size_t)PT_NCLASS * q.s0, q.n, rc->ccount + (3 * g + c0) * PT_NCLASS};
         const int tneed = (q.active + TP_BLOCK - 1) / TP_BLOCK;
+        const bool wide_now = wide_walk && q.active >= wide_min_rays;
+        const int trace_grid = trace_grid_of[wide_now ? 1 : 0];
         int tgrid = tneed < trace_grid ? tneed : trace_grid;
-        if (wide_walk) {
+        // The wide walk wins on throughput (1080p frame at 16 spp: 76 vs 85 ms), the binary walk
+        // with its cooperative tail on latency, i.e. when every ray of the launch is in flight at
+        // once and the launch lasts as long as its slowest ray (a quarter of the frame: 26.5 vs
+        // 29.2 ms, an eighth: 18.1 vs 20.7 ms).  GPT_TRACE_WIDE_MIN_RAYS moves the switch.
+        if (wide_now) {
           if (counting)
             k_pt_trace_wide<true><<<tgrid, TP_BLOCK, 0, gs>>>(qs, gpt_wide_tree(mb), next_ray, ctx->d_counters);
           else
@@ -1333,7 +1548,8 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
       static int no_sort = -1;  // experiment knob: shade in queue order
       if (no_sort < 0) { const char *e = getenv("GPT_NO_SORT"); no_sort = e ? atoi(e) : 0; }
       ctx->stream = gs;  // the sort enqueues on ctx->stream
-      if (no_sort) sorted_slots = rc->sort_val + q.s0;
+      if (class_lists) sorted_slots = nullptr;
+      else if (no_sort) sorted_slots = rc->sort_val + q.s0;
       else rc_err = gpt_radix_sort_pairs(ctx, rc->sort_key + q.s0, rc->sort_val + q.s0,
                                     rc->sort_key_alt + q.s0, rc->sort_val_alt + q.s0,
                                     hist, q.active, 7 + loc_bits, &sk, &sorted_slots, d_counts + c0);
@@ -1342,7 +1558,10 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
       k_pt_shade<<<grid, PT_BLOCK, 0, gs>>>(ps, p, sorted_slots, d_counts + c0,
                                            ps.queue[q.cur ^ 1] + q.s0, d_counts + c1,
                                            ctx->scene, atlas, mb.tris, lt, d_fb, d_counts + 4,
-                                           ray_counter, d_counts + c2, d_counts + 3);
+                                           ray_counter, d_counts + c2, d_counts + 3,
+                                           class_lists ? rc->classq + (size_t)PT_NCLASS * q.s0 : nullptr, q.n,
+                                           rc->ccount + (3 * g + c0) * PT_NCLASS,
+                                           rc->ccount + (3 * g + c2) * PT_NCLASS);
       GPT_LAUNCH_CHECK(ctx);
       GPT_CUDA(ctx, stamp());
       q.cur ^= 1;
@@ -1383,6 +1602,11 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
   }
   if (list_overflow)
     return gpt_fail(ctx, GPT_E_UNSUPPORTED, "nested-dielectric list deeper than 12", __FILE__, __LINE__);
+  if (fw) {
+    k_pt_combine<<<(npix + PT_BLOCK - 1) / PT_BLOCK, PT_BLOCK, 0, st>>>(
+        ps.pixel, rc->partial, npix, n / npix, fw->first ? 1 : 0, fw->last ? 1 : 0, p.inv_samples, d_fb);
+    GPT_LAUNCH_CHECK(ctx);
+  }
   GPT_CUDA(ctx, cudaEventRecord(ctx->ev1, st));
   GPT_CUDA(ctx, cudaEventSynchronize(ctx->ev1));
   float ms = 0.f;
@@ -1423,7 +1647,8 @@ void gpt_render_free(gpt_ctx *ctx) {
   void *p[] = {ps.pixel, ps.rng, ps.rays, ps.hits, ps.ma, ps.cm, ps.cam,
                ps.queue[0], ps.queue[1], ps.counts, rc->leaf_info, rc->node_info,
                rc->node_energy, rc->lt_flags, rc->rng_init, rc->d_fb, rc->sort_key,
-               rc->sort_key_alt, rc->sort_hist, rc->sort_val, rc->sort_val_alt, rc->sq_cells, rc->sq_ctl};
+               rc->sort_key_alt, rc->sort_hist, rc->sort_val, rc->sort_val_alt, rc->sq_cells, rc->sq_ctl,
+               rc->classq, rc->ccount, rc->partial};
   for (void *q : p) gpt_free(ctx, q);
   if (rc->h_counts) cudaFreeHost(rc->h_counts);
   if (rc->fork_ev) cudaEventDestroy(rc->fork_ev);

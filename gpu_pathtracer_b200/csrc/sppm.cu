@@ -417,6 +417,9 @@ struct PhotonRaySource {
     o = rays[2 * (size_t)s];
     d = rays[2 * (size_t)s + 1];
   }
+  __device__ void store_warp(bool fin, int i, const TraceLane &l) const {
+    if (fin) store(i, l);
+  }
   __device__ void store(int i, const TraceLane &l) const {
     int s = queue[i];
     hits[2 * (size_t)s] = make_float4(l.t, __int_as_float(l.leaf), __int_as_float(l.prim), 0.f);

@@ -24,6 +24,9 @@ struct ArraySource {
       d.x = d.x / len; d.y = d.y / len; d.z = d.z / len;
     }
   }
+  __device__ void store_warp(bool fin, int i, const TraceLane &l) const {
+    if (fin) store(i, l);
+  }
   __device__ void store(int i, const TraceLane &l) const {
     hits[2 * (size_t)i] = make_float4(l.t, __int_as_float(l.leaf), __int_as_float(l.prim), 0.f);
     hits[2 * (size_t)i + 1] = make_float4(l.b1, l.b2, l.b3, 0.f);

@@ -353,7 +353,9 @@ struct WideTree {        // what the kernels need of a BvhDev
   const int *parent_leaf;
 };
 
-// Same Source concept and the same persistent-warp schedule as trace_persistent (ray refill at
+// Same Source concept as trace_persistent plus
+//   void store_warp(bool fin, int i, const TraceLane &l);  called by all 32 lanes, stores for those with fin
+// and the same persistent-warp schedule (ray refill at
 // TP_REFILL idle lanes, triangle tests batched per warp); the step is the wide one.
 template <bool COUNT, class Source>
 __device__ __forceinline__ void trace_wide(const WideTree tr, Source src, int *next_ray,
@@ -374,15 +376,19 @@ __device__ __forceinline__ void trace_wide(const WideTree tr, Source src, int *n
   W4Queue Q(smem + W4_STACK * TP_BLOCK);
   unsigned vi = 0, vl = 0;
   bool exhausted = false;
+  // called by all 32 lanes: the lanes whose walk is over and whose queue is empty hand their
+  // record to the source (store_warp lets a source aggregate what the lanes of a warp append)
   auto finish = [&]() {
+    const bool fin = L.ray >= 0 && L.node < 0 && Q.pend == 0;
+    if (__ballot_sync(FULL, fin) == 0) return;
     TraceLane R;
     R.t = INFINITY; R.leaf = -1; R.prim = -1; R.b1 = R.b2 = R.b3 = 0.f;
-    if (L.kzneg & W4_HAVE_HIT) {
+    if (fin && (L.kzneg & W4_HAVE_HIT)) {
       R.t = rec[0]; R.b1 = rec[TP_BLOCK]; R.b2 = rec[2 * TP_BLOCK]; R.b3 = rec[3 * TP_BLOCK];
       R.leaf = __float_as_int(rec[4 * TP_BLOCK]); R.prim = __float_as_int(rec[5 * TP_BLOCK]);
     }
-    src.store(L.ray, R);
-    L.ray = -1;
+    src.store_warp(fin, L.ray, R);
+    if (fin) L.ray = -1;
   };
   auto fallback = [&](int ray) {
     float4 ro, rd;
@@ -430,7 +436,7 @@ __device__ __forceinline__ void trace_wide(const WideTree tr, Source src, int *n
         if (Q.pend > 0) w4_leaf_test<COUNT>(tr.nodes, tr.wtris, tr.parent_leaf, L, Q, rec, vl);
         pass = __ballot_sync(FULL, Q.pend > W4_QPASS) != 0;
       }
-      if (L.ray >= 0 && L.node < 0 && Q.pend == 0) finish();
+      finish();
       const int nwalk = __popc(__ballot_sync(FULL, L.ray >= 0 && L.node >= 0));
       if (nwalk == 0 || (!exhausted && 32 - nwalk >= TP_REFILL)) break;
     }
@@ -439,7 +445,7 @@ __device__ __forceinline__ void trace_wide(const WideTree tr, Source src, int *n
     while (__ballot_sync(FULL, W4_DRAIN_ALL ? Q.pend > 0 : (Q.pend > 0 && L.ray >= 0 && L.node < 0))) {
       if (Q.pend > 0) w4_leaf_test<COUNT>(tr.nodes, tr.wtris, tr.parent_leaf, L, Q, rec, vl);
     }
-    if (L.ray >= 0 && L.node < 0 && Q.pend == 0) finish();
+    finish();
   }
   if (COUNT) {
     atomicAdd(counters, (unsigned long long)vi);

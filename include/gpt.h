@@ -102,7 +102,13 @@ typedef struct GptParams {
   int32_t ppm_max_bounce;
   float ppm_alpha;
   float ppm_radius_scaling_factor;
-  int32_t rng_mode;                 /* 0 = reference streams (seed 1984, seq = pixel) */
+  int32_t rng_mode;                 /* 0 = reference streams (seed 1984, seq = pixel): a pixel's
+                                       samples run one after the other on its one stream
+                                       (src/render/pathtracing.h:277-293, src/util/general.h:8-16);
+                                       1 = fast: the samples of a pixel are dealt to L independent
+                                       streams (seq = pixel * L + lane, gpt_set_fast_rng_lanes)
+                                       that run side by side -- same estimator, other random
+                                       numbers, a chain of dependent rounds L times shorter */
 } GptParams;
 
 typedef struct GptStats {
@@ -334,6 +340,10 @@ int gpt_set_trace_tail(gpt_ctx *ctx, int mode);
  * either way (closest hit with the reference's visit-rank tie-break does not depend on the
  * order of the tests; a later test only means a looser cull bound in between). */
 int gpt_set_trace_leaf_batching(gpt_ctx *ctx, int mode);
+/* rng_mode 1: independent sample streams per pixel, 1..64 (0 = default, 8); clamped to
+ * dof_sample_size * pathtracing_sample_size.  The image depends on this number (and the scene)
+ * only, not on the rank count; with 1 lane it is the rng_mode 0 image bit for bit. */
+int gpt_set_fast_rng_lanes(gpt_ctx *ctx, int lanes);
 /* Which tree the trace kernels walk (traverse_bvh, src/model/bvh/bvh_traversal.h:12-84).
  *   1: the 4-wide tree gpt_build collapses from the LBVH (one 128-byte node per visit holds four
  *      boxes; ~23 dependent node fetches per bounce ray on the 1 M-triangle config instead of

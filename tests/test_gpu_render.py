@@ -115,6 +115,45 @@ def test_rebuild_with_another_scene_on_one_context():
     assert not np.array_equal(got, first)
 
 
+def test_fast_rng_mode(monkeypatch):
+    """rng_mode 1 (gpt.h): a pixel's samples on L independent streams.  (a) L = 1 is the
+    reference-mode frame bit for bit; (b) the frame does not depend on how many lanes run at a
+    time nor on the tile split; (c) it is another estimate of the same image: against the
+    reference-stream frame the mean luminance agrees to 1 % and the RMSE is what two independent
+    estimates of this sample count differ by (measured between L = 4 and L = 8, which share no
+    stream), within 25 %."""
+    import torch
+    from gpu_pathtracer_b200.api import PathTracer
+    sc = S.make_scene("small", n=24, width=160, height=128, spp=16, level=4, name="fast")
+    pt = PathTracer(sc)
+    pt.build()
+    ref = pt.render_pathtrace().copy()
+    pt.set_params(rng_mode=1)
+    pt.set_fast_rng_lanes(1)
+    assert np.array_equal(pt.render_pathtrace(), ref), "1 lane must be the reference-mode frame"
+    pt.set_fast_rng_lanes(8)
+    f8 = pt.render_pathtrace().copy()
+    monkeypatch.setenv("GPT_FAST_TARGET_SLOTS", str(3 * 160 * 128))  # 3 lanes per wave: 3 waves
+    assert np.array_equal(pt.render_pathtrace(), f8), "frame depends on lanes per wave"
+    H, W = sc.camera["height"], sc.camera["width"]
+    fb = torch.zeros((H, W, 3), dtype=torch.float32, device="cuda")
+    for r in range(3):
+        pt.render_pathtrace_device(fb.data_ptr(), r, 3)
+    pt.synchronize()
+    assert np.array_equal(fb.cpu().numpy(), f8), "frame depends on the tile split"
+    monkeypatch.delenv("GPT_FAST_TARGET_SLOTS")
+    pt.set_fast_rng_lanes(4)
+    f4 = pt.render_pathtrace().copy()
+    assert not np.array_equal(f4, f8)
+    rm = lambda a, b: float(np.sqrt(np.mean((a - b) ** 2)))
+    noise = rm(f4, f8)
+    print(f"fast mode: rmse(ref, L8) {rm(ref, f8):.4e}, rmse(ref, L4) {rm(ref, f4):.4e}, "
+          f"rmse(L4, L8) {noise:.4e}, means {ref.mean():.5f} {f8.mean():.5f} {f4.mean():.5f}")
+    assert abs(f8.mean() - ref.mean()) <= 0.01 * ref.mean()
+    assert abs(f4.mean() - ref.mean()) <= 0.01 * ref.mean()
+    assert rm(ref, f8) <= 1.25 * noise and rm(ref, f4) <= 1.25 * noise
+
+
 def test_depth_of_field_bottle():
     sc = S.make_scene("C3", width=160, height=120, spp=2, dof=2, level=8)
     # 4 samples x 8 bounces through two nested dielectrics: more uniform-vs-Schlick decisions

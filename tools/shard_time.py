@@ -15,10 +15,14 @@ ap.add_argument("--nranks", type=int, default=4)
 ap.add_argument("--spp", type=int, default=16)
 ap.add_argument("--workload", default="C2")
 ap.add_argument("--only-rank0", action="store_true")
+ap.add_argument("--rng-mode", type=int, default=0)
+ap.add_argument("--lanes", type=int, default=0)
 a = ap.parse_args()
 sc = S.make_scene(a.workload, spp=a.spp)
+sc.params["rng_mode"] = a.rng_mode
 pt = PathTracer(sc)
 pt.build()
+pt.set_fast_rng_lanes(a.lanes)
 fb = torch.zeros((sc.camera["height"], sc.camera["width"], 3), dtype=torch.float32, device="cuda")
 out = []
 for nr in sorted({1, a.nranks}):
