@@ -193,7 +193,7 @@ def run_ours(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
     from gpu_pathtracer_b200.api import PathTracer
-    from gpu_pathtracer_b200.parallel import gather_frame
+    from gpu_pathtracer_b200.parallel import init_comm
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
@@ -207,6 +207,7 @@ def run_ours(args, rank, world, local_rank):
     stream = torch.cuda.Stream(device=dev)
     torch.cuda.set_stream(stream)
     pt.set_stream(stream.cuda_stream)
+    init_comm(pt, rank, world)  # libgpt.so's own NCCL communicator (gpt_comm_init)
     build_stats = pt.build()
     build_ms = min(pt.rebuild_main_bvh() for _ in range(5))
     fb = torch.zeros((H, W, 3), dtype=torch.float32, device=dev)
@@ -268,7 +269,7 @@ def run_ours(args, rank, world, local_rank):
         if world > 1:
             fb.zero_()
             pt.render_pathtrace_device(fb.data_ptr(), rank, world)
-            gather_frame(fb, dst=0)
+            pt.gather_frame(fb.data_ptr(), 0)  # gpt_gather_frame: ncclReduce on the context's stream
             if rank == 0:
                 frame_host.copy_(fb.view(H, W, 3))
                 torch.cuda.current_stream().synchronize()
@@ -353,7 +354,7 @@ def run_sppm(args, rank, world, local_rank):
     import torch.distributed as dist
     from gpu_pathtracer_b200 import scene as S
     from gpu_pathtracer_b200.api import PathTracer
-    from gpu_pathtracer_b200.parallel import allreduce_flux, device_tensor, photon_range
+    from gpu_pathtracer_b200.parallel import init_comm, photon_range
 
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
@@ -363,11 +364,10 @@ def run_sppm(args, rank, world, local_rank):
     stream = torch.cuda.Stream(device=dev)
     torch.cuda.set_stream(stream)
     pt.set_stream(stream.cuda_stream)
+    init_comm(pt, rank, world)  # libgpt.so's own NCCL communicator (gpt_comm_init)
     pt.build()
     pt.sppm_init()
     b, e = photon_range(photons, rank, world)
-    ptr, nfl = pt.sppm_flux_device()
-    flux = device_tensor(ptr, nfl, dev)
     flush = torch.empty(L2_FLUSH_BYTES // 4, dtype=torch.float32, device=dev)
 
     def barrier():
@@ -378,9 +378,7 @@ def run_sppm(args, rank, world, local_rank):
     def one_pass(p):
         pt.sppm_pass(p, b, e)
         r = pt.stats()["rays_traced"]
-        if world > 1:
-            allreduce_flux(flux)
-            stream.synchronize()
+        pt.sppm_allreduce()  # gpt_sppm_allreduce: stream-ordered, a no-op with one rank
         pt.sppm_update(p)
         return r
 

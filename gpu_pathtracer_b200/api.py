@@ -30,6 +30,7 @@ gpt_sppm_stats gpt_sppm_export_hit_points gpt_sppm_export_photons gpt_sppm_impor
 gpt_sppm_pass_stages gpt_sppm_import_hit_points gpt_sss_export_points gpt_tonemap_u8 gpt_write_ppm_u8
 gpt_save_image gpt_sppm_debug_image gpt_sss_debug_image gpt_stats
 gpt_synchronize gpt_set_profiling gpt_set_wavefront_groups gpt_set_trace_tail gpt_set_trace_leaf_batching gpt_set_pipeline gpt_set_trace_bvh gpt_set_fast_rng_lanes
+gpt_comm_unique_id gpt_comm_init gpt_comm_info gpt_comm_destroy gpt_sppm_allreduce gpt_gather_frame
 gpt_scene_files_parse gpt_scene_files_view gpt_scene_files_material_name
 gpt_scene_files_texture_name gpt_scene_files_free gpt_load_scene_files""".split()
 
@@ -158,6 +159,34 @@ class PathTracer:
         """gpt_set_trace_leaf_batching: 1 batch a warp's triangle tests (deferred leaf tests),
         0 test every leaf where it is found, -1 default.  Bit-identical hits."""
         self._check(self.lib.gpt_set_trace_leaf_batching(self.ctx, C.c_int(int(mode))))
+
+    # -- multi-GPU: the library's own NCCL communicator (include/gpt.h "multi-GPU") -----------
+    @staticmethod
+    def comm_unique_id() -> bytes:
+        buf = C.create_string_buffer(128)
+        rc = load_library().gpt_comm_unique_id(buf)
+        if rc != 0:
+            raise GptError(f"gpt_comm_unique_id failed with {rc} (libnccl.so.2 not loadable?)")
+        return buf.raw
+
+    def comm_init(self, unique_id: bytes, rank: int, nranks: int):
+        buf = C.create_string_buffer(bytes(unique_id), 128)
+        self._check(self.lib.gpt_comm_init(self.ctx, buf, C.c_int(rank), C.c_int(nranks)))
+
+    def comm_info(self) -> dict:
+        r, n, v = C.c_int(), C.c_int(), C.c_int()
+        self._check(self.lib.gpt_comm_info(self.ctx, C.byref(r), C.byref(n), C.byref(v)))
+        return dict(rank=r.value, nranks=n.value, nccl_version=v.value)
+
+    def comm_destroy(self):
+        self._check(self.lib.gpt_comm_destroy(self.ctx))
+
+    def sppm_allreduce(self):
+        """The per-pass all-reduce of the hit-point accumulators, on the context's stream."""
+        self._check(self.lib.gpt_sppm_allreduce(self.ctx))
+
+    def gather_frame(self, d_rgb: int, root: int = 0):
+        self._check(self.lib.gpt_gather_frame(self.ctx, C.c_void_p(d_rgb), C.c_int(root)))
 
     def set_fast_rng_lanes(self, lanes=0):
         """rng_mode 1: independent sample streams per pixel (0 = default 8)."""

@@ -77,10 +77,13 @@ static void free_scene(gpt_ctx *ctx, SceneDev &s) {
   s.bg_r = br; s.bg_g = bg; s.bg_b = bb; s.bg_h = bh; s.bg_w = bw;
 }
 
+int gpt_comm_destroy(gpt_ctx *ctx);  // comm.cu
+
 void gpt_destroy(gpt_ctx *ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   cudaDeviceSynchronize();
+  gpt_comm_destroy(ctx);
   gpt_render_free(ctx);
   gpt_sppm_free(ctx);
   gpt_sss_free(ctx);

@@ -10,6 +10,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <string.h>
+
 #include <string>
 #include <vector>
 
@@ -120,6 +122,8 @@ struct gpt_ctx {
   bool prof_time_stages = false, prof_count_visits = false;
   float max_path_length = 0.f;  // largest sub-surface lookup radius of the materials (sss.cu grid)
   int wavefront_groups = 0;  // 0 = automatic (render.cu)
+  void *nccl_comm = nullptr;  // ncclComm_t of gpt_comm_init (comm.cu)
+  int comm_rank = 0, comm_nranks = 1;
   int fast_lanes = 0;        // rng_mode 1: independent sample streams per pixel, 0 = default (8)
   int pipeline = -1;         // path tracer: 0 = rounds of launches, 1 = streaming (two persistent kernels), -1 = default (env GPT_PIPELINE, else by frame size)
   int trace_defer = -1;      // path tracer: batch the triangle tests of a warp (deferred leaf tests): -1 = default (on, env GPT_TRACE_DEFER), 0 off, 1 on

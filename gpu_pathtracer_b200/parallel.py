@@ -50,6 +50,24 @@ def gather_frame(frame, dst: int = 0, group=None):
     return frame
 
 
+def init_comm(pt, rank: int, nranks: int, group=None):
+    """Bring up the LIBRARY's own NCCL communicator (gpt_comm_init, include/gpt.h "multi-GPU") on
+    PathTracer `pt`.  torch.distributed is used for one thing only: to hand rank 0's 128-byte
+    ncclUniqueId to the other ranks (any backend, gloo included); the collectives of the path then
+    run inside libgpt.so on the context's stream."""
+    import torch.distributed as dist
+    if nranks <= 1:
+        return
+    box = [pt.comm_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(box, src=0, group=group)
+    pt.comm_init(box[0], rank, nranks)
+
+
+def _lib_comm_ranks(pt) -> int:
+    info = getattr(pt, "comm_info", None)
+    return info()["nranks"] if info is not None else 1
+
+
 class _DevicePtr:
     """A raw device pointer dressed up with __cuda_array_interface__ so torch can alias it."""
 
@@ -71,7 +89,9 @@ def sppm_frame(pt, rank: int = 0, nranks: int = 1, passes: int | None = None, fl
     index range over the ranks: each rank traces its photons, builds its photon trees, runs the
     (replicated) eye pass and gathers into ALL hit points; the per-hit-point accumulators are
     summed over ranks -- the only collective of the path -- and every rank applies the same
-    radius / flux update, so hit-point state stays replicated.  `pt` is a PathTracer (or
+    radius / flux update, so hit-point state stays replicated.  With the library's communicator up
+    (``init_comm``) the sum is gpt_sppm_allreduce inside libgpt.so; otherwise (CPU tests over gloo,
+    a caller that owns its own process group) it is torch.distributed on the aliased buffer.  `pt` is a PathTracer (or
     anything with its sppm_* methods); `flux_tensor()` returns the tensor aliasing the
     accumulator buffer (defaults to the device buffer of pt.sppm_flux_device())."""
     n_photons = int(pt.scene.params["ppm_num_photon_per_pass"])
@@ -79,9 +99,14 @@ def sppm_frame(pt, rank: int = 0, nranks: int = 1, passes: int | None = None, fl
     b, e = photon_range(n_photons, rank, nranks)
     pt.sppm_init()
     flux = None
+    lib_comm = nranks > 1 and _lib_comm_ranks(pt) == nranks
     for p in range(passes):
         pt.sppm_pass(p, b, e)
-        if nranks > 1:
+        if lib_comm:
+            # gpt_sppm_allreduce: ncclAllReduce on the context's stream, between the traversal and
+            # the update half of the pass -- stream-ordered, no host synchronisation
+            pt.sppm_allreduce()
+        elif nranks > 1:
             if flux is None:
                 if flux_tensor is not None:
                     flux = flux_tensor()

@@ -30,7 +30,7 @@ extern "C" {
 #define GPT_E_CUDA (-2)      /* a CUDA runtime call failed (text in gpt_last_error)        */
 #define GPT_E_NODEVICE (-3)  /* no CUDA device: there is NO CPU fallback                   */
 #define GPT_E_UNSUPPORTED (-4)
-#define GPT_E_NCCL (-5)
+#define GPT_E_NCCL (-5)      /* an NCCL call failed, or libnccl.so.2 could not be loaded         */
 
 /* which acceleration structure (the reference builds three: src/main.cu:826-1197) */
 #define GPT_BVH_MAIN 0         /* all triangles          src/main.cu:826-918   */
@@ -237,6 +237,34 @@ int gpt_render_pathtrace(gpt_ctx *ctx, float *out_rgb);
 /* Render only pixels whose 32x32 tile index t satisfies t % nranks == rank; other pixels
  * are left untouched in d_out_rgb (DEVICE pointer, P x 3).  Asynchronous. */
 int gpt_render_pathtrace_device(gpt_ctx *ctx, void *d_out_rgb, int rank, int nranks);
+
+/* ---- multi-GPU: one process (or thread) per GPU, each with its own context and
+ *      the whole scene; rank r renders the 32x32 tiles t with t % nranks == r and traces the
+ *      photons of its index range.  The reference has no counterpart (single GPU).
+ *      NCCL is loaded at run time (libnccl.so.2); all calls are enqueued on the context's stream.
+ *
+ *      path tracing:  gpt_render_pathtrace_device(ctx, d_rgb, rank, nranks)   -- d_rgb zeroed first
+ *                     gpt_gather_frame(ctx, d_rgb, 0)                          -- root has the frame
+ *      SPPM, per pass: gpt_sppm_pass(ctx, pass, begin_r, end_r);
+ *                     gpt_sppm_allreduce(ctx);   <- the ONE collective of the data path: between the
+ *                                                   traversal and the update half of
+ *                                                   update_hit_point_parameters
+ *                                                   (bvh_traversal_photon.h:207-225, main.cu:1780)
+ *                     gpt_sppm_update(ctx, pass);
+ * ----------------------------------------------------------------------------------------- */
+#define GPT_NCCL_UNIQUE_ID_BYTES 128
+/* ncclGetUniqueId: call on one rank, hand the 128 bytes to the others by any means. */
+int gpt_comm_unique_id(void *out_id);
+/* ncclCommInitRank on the context's device; collective over the nranks contexts. */
+int gpt_comm_init(gpt_ctx *ctx, const void *nccl_unique_id, int rank, int nranks);
+/* rank / nranks of the communicator (0 / 1 without one) and the NCCL version in use. */
+int gpt_comm_info(gpt_ctx *ctx, int *rank, int *nranks, int *nccl_version);
+int gpt_comm_destroy(gpt_ctx *ctx);
+/* ncclAllReduce(sum) of the 8 P floats of gpt_sppm_flux_device, in place.  No-op with one rank. */
+int gpt_sppm_allreduce(gpt_ctx *ctx);
+/* ncclReduce(sum) of a P x 3 fp32 DEVICE frame to `root`, in place: frames that are zero outside
+ * their own tiles add up to the image exactly.  No-op with one rank. */
+int gpt_gather_frame(gpt_ctx *ctx, void *d_rgb, int root);
 
 /* ---- sub-surface scattering: replaces src/main.cu:642-824 (point clouds per
  *      SSS object + per-object point LBVHs, built by gpt_build when sss_pts_per_object > 0),
