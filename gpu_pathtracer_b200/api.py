@@ -30,7 +30,7 @@ gpt_sppm_stats gpt_sppm_export_hit_points gpt_sppm_export_photons gpt_sppm_impor
 gpt_sppm_pass_stages gpt_sppm_import_hit_points gpt_sss_export_points gpt_tonemap_u8 gpt_write_ppm_u8
 gpt_save_image gpt_sppm_debug_image gpt_sss_debug_image gpt_stats
 gpt_synchronize gpt_set_profiling gpt_set_wavefront_groups gpt_set_trace_tail gpt_set_trace_leaf_batching gpt_set_pipeline gpt_set_trace_bvh gpt_set_fast_rng_lanes
-gpt_comm_unique_id gpt_comm_init gpt_comm_info gpt_comm_destroy gpt_sppm_allreduce gpt_gather_frame
+gpt_trace_static gpt_comm_unique_id gpt_comm_init gpt_comm_info gpt_comm_destroy gpt_sppm_allreduce gpt_gather_frame
 gpt_scene_files_parse gpt_scene_files_view gpt_scene_files_material_name
 gpt_scene_files_texture_name gpt_scene_files_free gpt_load_scene_files""".split()
 
@@ -263,6 +263,20 @@ class PathTracer:
         self._check(self.lib.gpt_trace(self.ctx, which, cabi.fptr(rays), C.c_int64(n),
                                        cabi.iptr(out["leaf_id"]), cabi.iptr(out["tri_id"]),
                                        cabi.fptr(out["t"]), cabi.fptr(out["bary"])))
+        return out
+
+    TRACE_STATIC_MAX_RAYS = 131072  # GPT_TRACE_STATIC_MAX_RAYS (include/gpt.h)
+
+    def trace_static(self, rays: np.ndarray, which=0) -> dict:
+        """gpt_trace_static: gpt_trace with its staging and scratch in a static device array --
+        no allocation of any kind, at most TRACE_STATIC_MAX_RAYS rays per call."""
+        rays = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 8)
+        n = rays.shape[0]
+        out = dict(leaf_id=np.zeros(n, np.int32), tri_id=np.zeros(n, np.int32),
+                   t=np.zeros(n, np.float32), bary=np.zeros((n, 3), np.float32))
+        self._check(self.lib.gpt_trace_static(self.ctx, which, cabi.fptr(rays), C.c_int64(n),
+                                              cabi.iptr(out["leaf_id"]), cabi.iptr(out["tri_id"]),
+                                              cabi.fptr(out["t"]), cabi.fptr(out["bary"])))
         return out
 
     def trace_device(self, d_rays: int, n: int, d_hits: int, which=0):

@@ -4,7 +4,9 @@
 // [level][thread] (bank-conflict free), nodes / triangles fetched as 16-byte words through
 // the read-only path.  Rays: 2 x float4 {ox,oy,oz,tmax}{dx,dy,dz,-}; hits: 2 x float4
 // {t, leaf, prim, -}{b1, b2, b3, -}.
+#include <cstdio>
 #include <cstdlib>
+#include <mutex>
 
 #include "trace_wide.cuh"
 
@@ -150,5 +152,97 @@ int gpt_trace_launch(gpt_ctx *ctx, int which, const float4 *d_rays, int64_t n, f
 #undef GPT_TRACE_LAUNCH2
 #undef GPT_TRACE_LAUNCH
   GPT_LAUNCH_CHECK(ctx);
+  return GPT_OK;
+}
+
+// ---- gpt_trace_static: closest hits for HOST ray / hit buffers without any allocation -----------
+// No counterpart in the reference; added for callers that
+// cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+// it).  gpt_trace stages its rays and hit records in buffers it takes from the context's pool on
+// every call; here the staging AND the kernel's own scratch (the persistent kernel's ray cursor,
+// the visit counters, the stack-overflow flag) live in one file-scope device array of a fixed,
+// modest size that every GPU that loads the library holds until exit:
+//   float4 [0, 16)                       256 bytes of control words, laid out like ctx->d_counters
+//                                        (u64 [0] V_int [1] V_leaf [2] rays [3] overflow, int cursor at u64 [4])
+//   float4 [16, 16 + 2 MAX)              rays, 2 float4 each
+//   float4 [16 + 2 MAX, 16 + 4 MAX)      hit records, 2 float4 each
+// = 256 + 64 * GPT_TRACE_STATIC_MAX_RAYS bytes = 8 MiB + 256 B.  The array keeps the last call's
+// contents: the control words are cleared at the start of every call (the cursor MUST start at
+// zero), rays and hits are fully overwritten for the n rays of the call.  All calls on a device
+// share the array, whatever their context: two calls that overlap on the GPU race.  (This
+// function returns only after its own work is complete, so calls from one host thread never do.)
+constexpr int TS_MAX = GPT_TRACE_STATIC_MAX_RAYS;
+constexpr int TS_CTL = 16;  // float4 words of control data
+static __device__ __align__(256) float4 g_trace_static[TS_CTL + 4 * (size_t)TS_MAX];
+
+// In host code `g_trace_static` is a host-side stand-in for the symbol, NOT a device address:
+// the address a kernel can use comes from cudaGetSymbolAddress, once per device, with that
+// device current.
+static int trace_static_base(gpt_ctx *ctx, float4 **base) {
+  static float4 *per_device[64] = {nullptr};
+  static std::mutex mu;
+  const int dev = ctx->device;
+  if (dev < 0 || dev >= 64) return gpt_fail(ctx, GPT_E_INVALID, "device index beyond 63", __FILE__, __LINE__);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!per_device[dev]) {
+    GPT_CUDA(ctx, cudaSetDevice(dev));
+    float4 *p = nullptr;
+    GPT_CUDA(ctx, cudaGetSymbolAddress((void **)&p, g_trace_static));
+    if (!p) return gpt_fail(ctx, GPT_E_CUDA, "cudaGetSymbolAddress returned a null address", __FILE__, __LINE__);
+    per_device[dev] = p;
+  }
+  *base = per_device[dev];
+  return GPT_OK;
+}
+
+extern "C" int gpt_trace_static(gpt_ctx *ctx, int which, const float *rays, int64_t n,
+                                int32_t *leaf_id, int32_t *tri_id, float *t, float *bary) {
+  if (!ctx || !ctx->built) return gpt_fail(ctx, GPT_E_INVALID, "gpt_build first", __FILE__, __LINE__);
+  if (n < 0 || (n > 0 && !rays)) return GPT_E_INVALID;
+  if (n > TS_MAX) {
+    char msg[200];
+    snprintf(msg, sizeof(msg), "gpt_trace_static: %lld rays exceed the static scratch (GPT_TRACE_STATIC_MAX_RAYS = %d); split the call or use gpt_trace",
+             (long long)n, TS_MAX);
+    return gpt_fail(ctx, GPT_E_INVALID, msg, __FILE__, __LINE__);
+  }
+  if (which < 0 || which > 2) return gpt_fail(ctx, GPT_E_INVALID, "bad BVH id", __FILE__, __LINE__);
+  BvhDev &b = ctx->bvh[which];
+  if (b.n < 2) return gpt_fail(ctx, GPT_E_INVALID, "BVH not built (needs >= 2 leaves)", __FILE__, __LINE__);
+  if (n == 0) return GPT_OK;
+  GPT_CUDA(ctx, cudaSetDevice(ctx->device));
+  float4 *base = nullptr;
+  GPT_TRY(trace_static_base(ctx, &base));
+  unsigned long long *ctl = reinterpret_cast<unsigned long long *>(base);
+  int *cursor = reinterpret_cast<int *>(ctl + 4);
+  float4 *d_rays = base + TS_CTL, *d_hits = base + TS_CTL + 2 * (size_t)TS_MAX;
+  cudaStream_t st = ctx->stream;
+  GPT_CUDA(ctx, cudaMemsetAsync(base, 0, TS_CTL * sizeof(float4), st));  // cursor, counters, overflow flag
+  GPT_CUDA(ctx, cudaMemcpyAsync(d_rays, rays, 32 * (size_t)n, cudaMemcpyHostToDevice, st));
+  ctx->launches = 0;
+  const long long need = (n + TP_BLOCK - 1) / TP_BLOCK;
+  ArraySource<true> src{d_rays, d_hits, (int)n};
+  if (gpt_trace_wide(ctx, b)) {
+    static int grid = persistent_grid(k_trace_wide<true, false>);
+    k_trace_wide<true, false><<<(unsigned)(need < grid ? need : grid), TP_BLOCK, 0, st>>>(
+        gpt_wide_tree(b), src, cursor, ctl);
+  } else {
+    static int grid = persistent_grid(k_trace<true, false, false, false>);
+    k_trace<true, false, false, false><<<(unsigned)(need < grid ? need : grid), TP_BLOCK, 0, st>>>(
+        b.nodes, b.tris, b.parent_leaf, src, cursor, ctl);
+  }
+  GPT_LAUNCH_CHECK(ctx);
+  // hit record of ray i = float4 pair {t, leaf, prim, -}{b1, b2, b3, -}: strided copies scatter the
+  // fields straight into the caller's arrays (no host staging buffer either)
+  const char *h = reinterpret_cast<const char *>(d_hits);
+  if (t) GPT_CUDA(ctx, cudaMemcpy2DAsync(t, 4, h, 32, 4, (size_t)n, cudaMemcpyDeviceToHost, st));
+  if (leaf_id) GPT_CUDA(ctx, cudaMemcpy2DAsync(leaf_id, 4, h + 4, 32, 4, (size_t)n, cudaMemcpyDeviceToHost, st));
+  if (tri_id) GPT_CUDA(ctx, cudaMemcpy2DAsync(tri_id, 4, h + 8, 32, 4, (size_t)n, cudaMemcpyDeviceToHost, st));
+  if (bary) GPT_CUDA(ctx, cudaMemcpy2DAsync(bary, 12, h + 16, 32, 12, (size_t)n, cudaMemcpyDeviceToHost, st));
+  unsigned long long overflow = 0;
+  GPT_CUDA(ctx, cudaMemcpyAsync(&overflow, ctl + 3, sizeof(overflow), cudaMemcpyDeviceToHost, st));
+  GPT_CUDA(ctx, cudaStreamSynchronize(st));
+  if (overflow) return gpt_fail(ctx, GPT_E_UNSUPPORTED, "traversal stack overflow (> 64 levels)", __FILE__, __LINE__);
+  ctx->stats.rays_traced = (uint64_t)n;
+  ctx->stats.kernel_launches = ctx->launches;
   return GPT_OK;
 }

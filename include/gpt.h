@@ -224,6 +224,21 @@ int gpt_export_bvh(gpt_ctx *ctx, int which, uint32_t *morton /*n, sorted*/,
  *      tri_id = original triangle index or -1, t, bary = {b1,b2,b3}. ------------------- */
 int gpt_trace(gpt_ctx *ctx, int which, const float *rays, int64_t n, int32_t *leaf_id,
               int32_t *tri_id, float *t, float *bary);
+/* gpt_trace without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid it).  Same arguments, same results bit for bit as
+ * gpt_trace, but the device staging of rays and hit records and the trace kernel's scratch (ray
+ * cursor, counters, overflow flag) live in one file-scope `static __device__` array of
+ * 256 + 64 * GPT_TRACE_STATIC_MAX_RAYS bytes (8 MiB) that every GPU loading the library holds
+ * until exit; the call makes no cudaMalloc / cudaFree / pool allocation and needs no host
+ * staging buffer.  n > GPT_TRACE_STATIC_MAX_RAYS returns GPT_E_INVALID with a message (split the
+ * call, or use gpt_trace).  The array is shared by every context on the device and keeps the last
+ * call's contents (what must start at zero is cleared per call): calls that overlap on the GPU
+ * race -- the function returns only once its own work is complete, so serialise callers per
+ * device. */
+#define GPT_TRACE_STATIC_MAX_RAYS 131072
+int gpt_trace_static(gpt_ctx *ctx, int which, const float *rays, int64_t n, int32_t *leaf_id,
+                     int32_t *tri_id, float *t, float *bary);
 /* Same, all pointers are DEVICE pointers; hits: n x 4 x 4 bytes {t, leaf_id, b1, b2}
  * with leaf_id stored as int32 bits.  Asynchronous on the context's stream. */
 int gpt_trace_device(gpt_ctx *ctx, int which, const void *d_rays, int64_t n, void *d_hits);
