@@ -36,6 +36,10 @@ def parse():
                     help="gpt_set_pipeline: rounds of launches / two persistent kernels")
     ap.add_argument("--cpu-budget-s", type=float, default=15.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-ref-cuda", action="store_true",
+                    help="skip the run of the reference's own CUDA binary after the timed region")
+    ap.add_argument("--fast-rng", type=int, default=0,
+                    help="rng_mode 1 with this many sample lanes per pixel (0 = reference streams)")
     return ap.parse_args()
 
 
@@ -126,6 +130,7 @@ def reference_window(sc, budget_s: float, nthreads: int):
     ref = RefReplay(sc)
     H, W = sc.camera["height"], sc.camera["width"]
     rays, ms, rows_done = 0, 0.0, 0
+    windows = []  # (r0, r1, c0, c1, reference pixels): kept for the parity block
     # horizontal strips around the image centre (terrain + spheres), alternating below / above;
     # a strip has one row per host thread, because the replay hands out work by rows
     strip = max(1, nthreads)
@@ -136,14 +141,50 @@ def reference_window(sc, budget_s: float, nthreads: int):
         r0 = H // 2 + off if k % 2 == 0 else H // 2 - off - strip
         if r0 < 0 or r0 + strip > H:
             break
-        ref.render_pathtrace(window=(r0, r0 + strip, cols[0], cols[1]), nthreads=nthreads)
+        px = ref.render_pathtrace(window=(r0, r0 + strip, cols[0], cols[1]), nthreads=nthreads)
+        windows.append((r0, r0 + strip, cols[0], cols[1], px[r0:r0 + strip, cols[0]:cols[1]].copy()))
         rays += ref.render_rays
         ms += ref.render_ms
         rows_done += strip
         k += 1
-    return dict(mrays=rays / ms / 1e3, rays=rays, ms=ms,
+    npx = rows_done * (cols[1] - cols[0])
+    return dict(mrays=rays / ms / 1e3, rays=rays, ms=ms, windows=windows,
+                frame_fraction=npx / float(H * W),
                 sample=f"{rows_done} image rows x columns [{cols[0]},{cols[1]}) around the centre "
-                       f"of the same frame at full spp ({rays} rays, {ms / 1e3:.1f} s)")
+                       f"of the same frame at full spp = {100.0 * npx / (H * W):.2f} % of its pixels "
+                       f"({rays} rays, {ms / 1e3:.1f} s)")
+
+
+# Stated tolerance of the bench's own parity check: the GPU frame of this run
+# against the reference replay's pixels of the same window, identical per-pixel RNG streams.
+PARITY_MIN_FRAC_1E3 = 0.97   # pixels within 1e-3 relative (libm ulps flip a discrete decision in
+                             # a few pixels; at 64 spp such a pixel keeps a shifted RNG stream)
+PARITY_MAX_RMSE_FRAC = 0.05  # RMSE <= 5 % of the window's mean value
+PARITY_MAX_REL_LUM = 5e-3    # mean luminance within 0.5 %
+
+
+def parity_block(frame, windows):
+    """frame: (H, W, 3) host array of the GPU arm; windows: reference_window()['windows']."""
+    got = np.concatenate([frame[r0:r1, c0:c1].reshape(-1, 3) for r0, r1, c0, c1, _ in windows])
+    want = np.concatenate([px.reshape(-1, 3) for *_, px in windows])
+    close = (np.abs(got - want) <= 1e-3 * (1.0 + np.abs(want))).all(axis=-1)
+    mean_w = float(want.mean())
+    rmse = float(np.sqrt(np.mean((got.astype(np.float64) - want) ** 2)))
+    rel_lum = abs(float(got.mean()) - mean_w) / max(abs(mean_w), 1e-30)
+    rows = sum(r1 - r0 for r0, r1, *_ in windows)
+    c0, c1 = windows[0][2], windows[0][3]
+    out = {
+        "against": "reference replay (oracle/_ref/libref_replay.so), same per-pixel RNG streams",
+        "window": f"{rows} rows x columns [{c0},{c1}) around the image centre, {got.shape[0]} pixels",
+        "frac_within_1e-3": float(close.mean()), "frac_bit_equal": float((got == want).all(axis=-1).mean()),
+        "rmse": rmse, "rmse_over_mean": rmse / max(abs(mean_w), 1e-30), "rel_mean_lum": rel_lum,
+        "finite": bool(np.isfinite(got).all()),
+        "tolerance": {"frac_within_1e-3_min": PARITY_MIN_FRAC_1E3,
+                      "rmse_over_mean_max": PARITY_MAX_RMSE_FRAC, "rel_mean_lum_max": PARITY_MAX_REL_LUM},
+    }
+    out["ok"] = bool(out["finite"] and out["frac_within_1e-3"] >= PARITY_MIN_FRAC_1E3
+                     and out["rmse_over_mean"] <= PARITY_MAX_RMSE_FRAC and rel_lum <= PARITY_MAX_REL_LUM)
+    return out
 
 
 def run_reference(args, rank, world):
@@ -158,11 +199,12 @@ def run_reference(args, rank, world):
     sc = make_workload(args.workload, args.spp)
     cores = os.cpu_count() or 1
     times, rays = [], []
-    sample = ""
+    sample, frac = "", 0.0
     for s in range(args.warmup + args.steps):
         r = reference_window(sc, 6.0 if s >= args.warmup else 1.0, cores)
         if s >= args.warmup:
             times.append(r["ms"]); rays.append(r["rays"]); sample = r["sample"]
+            frac = r["frame_fraction"]
     ms_per_step = float(np.mean(times))
     val = float(np.sum(rays) / np.sum(times) / 1e3)
     line = {
@@ -172,12 +214,68 @@ def run_reference(args, rank, world):
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_text(sc, args)},
         "cpu_baseline": {"value": val, "unit": "Mrays/s", "cores": cores, "kind": "reference",
-                         "sample": "per step: " + sample},
+                         "frame_fraction": frac, "sample": "per step: " + sample},
         "e2e": {"value": val, "unit": "Mrays/s", "h2d_bytes_per_step": 0,
                 "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
+
+
+def ref_cuda_block(sc, workload: str, rays: float, our_ms: float) -> dict:
+    """north_star's GPU baseline: the reference's OWN CUDA build (unmodified sources + the jpeg
+    stub, the reference Makefile's flags with SM=100; oracle/_ref/gpu_path_tracing_100, built by
+    `make -C oracle refcuda`) run on the same scene written to OBJ/MTL/master files, on the same
+    GPU, after the timed region.  Its "Rendering" stage (print_end_process around
+    path_tracing_render + sync, src/main.cu:1266) against our frame time; the ray count is
+    ours, which equals the reference's traverse_bvh(node_list[0]) call count sample for sample."""
+    import re
+    import shutil
+    import tempfile
+    from gpu_pathtracer_b200 import scene as S
+    binary = os.path.join(ROOT, "oracle", "_ref", "gpu_path_tracing_100")
+    if not os.path.exists(binary):
+        return {"unavailable": "oracle/_ref/gpu_path_tracing_100 not built (make -C oracle refcuda)"}
+    folder = tempfile.mkdtemp(prefix="gpt_refcuda_")
+    try:
+        master = S.write_scene_files(sc, folder, workload)
+        t0 = time.perf_counter()
+        try:
+            r = subprocess.run([binary, master, os.path.join(folder, "ref_out")],
+                               capture_output=True, text=True, timeout=900)
+        except subprocess.TimeoutExpired:
+            return {"unavailable": "reference CUDA binary did not finish in 900 s"}
+        wall = time.perf_counter() - t0
+        if r.returncode != 0:
+            return {"unavailable": f"reference CUDA binary exited with {r.returncode}: "
+                                   + (r.stdout[-200:] + r.stderr[-200:]).replace("\n", " | ")}
+        stages = dict((m.group(1).strip(), float(m.group(2))) for m in re.finditer(
+            r"Done with process : (.*)\nThe process took  :\s*([0-9.]+) seconds", r.stdout))
+        render_s = stages.get("Rendering")
+        if not render_s:
+            return {"unavailable": "no 'Rendering' stage line in the reference binary's output"}
+        return {"binary": "oracle/_ref/gpu_path_tracing_100 (reference sources unmodified + jpeg "
+                          "stub, -O3 -gencode arch=compute_100,code=sm_100, default FMA)",
+                "render_s": render_s, "wall_s": wall, "value": rays / render_s / 1e6,
+                "unit": "Mrays/s", "ours_over_ref_cuda": (render_s * 1e3) / our_ms,
+                "note": "same scene files, same GPU, run after the timed region; rays = our "
+                        "closest-hit count (identical paths); Rendering = the reference's own "
+                        "print_end_process seconds (10 ms resolution)"}
+    finally:
+        shutil.rmtree(folder, ignore_errors=True)
+
+
+def newest_traffic_capture(workload: str):
+    """profiles/*_trace_traffic_<workload>.json written by tools/trace_traffic.py from an ncu
+    metrics pass over every trace launch of whole frames; None when there is no capture."""
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", f"*_trace_traffic_{workload}.json")))
+    if not files:
+        return None, None
+    try:
+        return json.load(open(files[-1])), os.path.relpath(files[-1], ROOT)
+    except Exception:
+        return None, None
 
 
 def scene_bytes(sc) -> int:
@@ -203,6 +301,9 @@ def run_ours(args, rank, world, local_rank):
     H, W = sc.camera["height"], sc.camera["width"]
     pt = PathTracer(sc, device=local_rank)
     pt.set_pipeline(args.pipeline)
+    if args.fast_rng:
+        pt.set_params(rng_mode=1)
+        pt.set_fast_rng_lanes(args.fast_rng)
     # a real (non-legacy) stream: the library launches on it and the events below time it
     stream = torch.cuda.Stream(device=dev)
     torch.cuda.set_stream(stream)
@@ -250,7 +351,8 @@ def run_ours(args, rank, world, local_rank):
     st_c = pt.stats()
     pt.set_profiling()
     v_int, v_leaf = st_c["internal_visits"], st_c["leaf_tests"]
-    alg_bytes = 48.0 * rays + 64.0 * v_int + 48.0 * v_leaf
+    v_wide = st_c["wide_node_visits"]  # the share of v_int made on 48-byte nodes of the 4-wide tree
+    alg_bytes = 48.0 * rays + 64.0 * (v_int - v_wide) + 48.0 * v_wide + 48.0 * v_leaf
     trace_ms, shade_ms = st_t["trace_kernel_ms"], st_t["shade_kernel_ms"]
     n_trace = max(1, st_t["trace_launches"])
 
@@ -287,6 +389,8 @@ def run_ours(args, rank, world, local_rank):
     rays_all = tot.item()
     if rank != 0:
         return
+    # the full frame of the e2e leg on the host (N > 1: after gpt_gather_frame on rank 0)
+    frame = frame_host.numpy() if world > 1 else img
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -297,6 +401,33 @@ def run_ours(args, rank, world, local_rank):
     value = rays_all / (ms_per_step * 1e-3) / 1e6
     spp_total = sc.params["pathtracing_sample_size"] * sc.params["dof_sample_size"]
     achieved = alg_bytes / (trace_ms * 1e-3) / 1e9 if trace_ms > 0 else 0.0
+    cap, cap_file = newest_traffic_capture(args.workload)
+    rays_per_launch = rays / max(1, n_trace)
+    roofline = {
+        "bound": "hbm",
+        "kernel": "k_pt_trace_wide" if 2 * v_wide >= v_int else "k_pt_trace",
+        "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+        "what": "ALGORITHMIC bytes (SURVEY 8d: 48 B per ray + 48 B per visit of a 4-wide node + "
+                "64 B per visit of a binary LBVH node + 48 B per triangle test, from the kernels' "
+                "own visit counters -- the binary walk's are pinned against a host count in "
+                "tests/test_gpu_counters.py) / summed event time of the trace launches of a "
+                "stage-timed frame.  On C1-C4 the tree is L2 resident, so this is an L2-served "
+                "proxy, not HBM headroom: physical_* are the DRAM bytes ncu counted",
+        "wide_share_of_node_visits": v_wide / max(1, v_int),
+        "launches": int(n_trace), "algorithmic_bytes_per_launch": alg_bytes / n_trace,
+        "avg_launch_ms": trace_ms / n_trace,
+        "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback",
+        # physical bytes: ncu metrics pass over EVERY trace launch of whole frames of this
+        # workload (tools/trace_traffic.py), per ray, scaled to this run's rays per launch
+        "traffic": (cap["dram_bytes_per_ray"] * rays_per_launch) if cap else None,
+        "traffic_source": cap_file,
+    }
+    if cap:
+        roofline["physical_dram_gbs"] = cap["dram_bytes_per_ray"] * rays / (trace_ms * 1e-3) / 1e9
+        roofline["physical_frac"] = roofline["physical_dram_gbs"] / peak
+        roofline["l2_gbs"] = cap["l2_bytes_per_ray"] * rays / (trace_ms * 1e-3) / 1e9
+        roofline["l2_bytes_per_ray"] = cap["l2_bytes_per_ray"]
+        roofline["dram_bytes_per_ray"] = cap["dram_bytes_per_ray"]
     line = {
         "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
@@ -310,6 +441,9 @@ def run_ours(args, rank, world, local_rank):
             "cache": "L2 flushed (512 MiB write) between timed steps",
             "sharding": "scene replicated, 32x32 pixel tiles dealt round-robin to ranks",
             "pipeline": {"default": "rounds (library default)"}.get(args.pipeline, args.pipeline),
+            "rng": ("reference streams (seed 1984, seq = pixel; rng_mode 0)" if not args.fast_rng else
+                    f"rng_mode 1: {args.fast_rng} independent sample lanes per pixel (NOT the "
+                    "reference's sample order; statistical parity only)"),
             "spp_per_s": spp_total / (ms_per_step * 1e-3),
             "rays_per_frame": rays_all,
             "lbvh_build_ms": build_ms, "build_all_ms": build_stats["build_all_ms"],
@@ -323,27 +457,33 @@ def run_ours(args, rank, world, local_rank):
                 "h2d_bytes_per_step": scene_bytes(sc), "d2h_bytes_per_step": H * W * 12,
                 "what": "gpt_set_mesh/materials/textures + gpt_build + gpt_render_pathtrace "
                         "with page-locked host arrays in, page-locked host frame out"},
-        "roofline": {"bound": "hbm", "kernel": "k_pt_trace",
-                     "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak,
-                     # physical DRAM bytes per launch: ncu --set full on this kernel at C2
-                     # (profiles/r01g_k_pt_trace_raw.csv: 50.4-55.3 MB read + 2.7-3.3 MB write per
-                     # 518 400-ray launch = 107 B per ray), scaled to this run's rays per launch
-                     "traffic": (107.0 * rays / max(1, n_trace)) if args.workload == "C2" else None,
-                     "traffic_source": "ncu r01g capture, 102-113 B/ray (C2 only)",
-                     "launches": int(n_trace),
-                     "algorithmic_bytes_per_launch": alg_bytes / n_trace,
-                     "avg_launch_ms": trace_ms / n_trace,
-                     "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback"},
+        "roofline": roofline,
         "clocks": clocks,
     }
+    rc = 0
     if not args.no_cpu_baseline:
-        cb = reference_window(sc, args.cpu_budget_s, 1)
+        # the reference's own path_tracing_render on a window of the SAME frame: timed on one host
+        # thread at N = 1 (cpu_baseline), on all host threads otherwise; its pixels are kept and
+        # compared with the same window of the GPU frame of this run (parity)
+        nthreads = 1 if world == 1 else (os.cpu_count() or 1)
+        cb = reference_window(sc, args.cpu_budget_s, nthreads)
         if cb:
-            line["cpu_baseline"] = {
-                "value": cb["mrays"], "unit": "Mrays/s", "cores": 1, "kind": "reference",
-                "sample": cb["sample"] + f", 1 thread of {os.cpu_count()} host cores"}
+            if world == 1:
+                line["cpu_baseline"] = {
+                    "value": cb["mrays"], "unit": "Mrays/s", "cores": 1, "kind": "reference",
+                    "frame_fraction": cb["frame_fraction"],
+                    "sample": cb["sample"] + f", 1 thread of {os.cpu_count()} host cores"}
+            if not args.fast_rng:
+                line["parity"] = parity_block(frame, cb["windows"])
+                if not line["parity"]["ok"]:
+                    rc = 3
+    if world == 1 and not args.no_ref_cuda and args.workload in ("C1", "C2", "C3"):
+        line["ref_cuda"] = ref_cuda_block(sc, args.workload, rays_all, ms_per_step)
     print(json.dumps(line), flush=True)
+    if rc:
+        sys.stderr.write("bench.py: the GPU frame is outside the stated tolerance of the reference "
+                         "replay's pixels (see \"parity\" in the line)\n")
+        raise SystemExit(rc)
 
 
 def run_sppm(args, rank, world, local_rank):

@@ -58,7 +58,8 @@ class GptStats(C.Structure):
                 ("leaf_tests", C.c_uint64), ("kernel_launches", C.c_uint64),
                 ("shade_events", C.c_uint64), ("trace_kernel_ms", C.c_double),
                 ("shade_kernel_ms", C.c_double), ("trace_launches", C.c_uint64),
-                ("build_wide_ms", C.c_double)]
+                ("build_wide_ms", C.c_double), ("wide_node_visits", C.c_uint64),
+                ("wide_leaf_tests", C.c_uint64)]
 
 
 def fptr(a: np.ndarray):

@@ -408,7 +408,7 @@ int gpt_trace_count_device(gpt_ctx *ctx, int which, const void *d_rays, int64_t 
   float4 *hits = nullptr;
   GPT_TRY(gpt_alloc(ctx, &hits, 2 * (size_t)n));
   int rc = gpt_trace_launch(ctx, which, (const float4 *)d_rays, n, hits, true, true);
-  unsigned long long c[4] = {0, 0, 0, 0};
+  unsigned long long c[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   if (rc == GPT_OK) {
     cudaMemcpyAsync(c, ctx->d_counters, sizeof(c), cudaMemcpyDeviceToHost, ctx->stream);
     cudaStreamSynchronize(ctx->stream);
@@ -417,6 +417,8 @@ int gpt_trace_count_device(gpt_ctx *ctx, int which, const void *d_rays, int64_t 
   GPT_TRY(rc);
   ctx->stats.internal_visits = c[0];
   ctx->stats.leaf_tests = c[1];
+  ctx->stats.wide_node_visits = c[5];
+  ctx->stats.wide_leaf_tests = c[7];
   ctx->stats.rays_traced = (uint64_t)n;
   return GPT_OK;
 }

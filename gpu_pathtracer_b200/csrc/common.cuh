@@ -113,7 +113,7 @@ struct gpt_ctx {
   // light-tree side arrays of render.cu / sppm.cu) is stale when its epoch differs
   uint64_t build_epoch = 0;
   cudaMemPool_t pool = nullptr;              // this context's own stream-ordered pool (gpt_alloc)
-  unsigned long long *d_counters = nullptr;  // [0] V_int [1] V_leaf [2] rays [3] overflow
+  unsigned long long *d_counters = nullptr;  // [0] V_int [1] V_leaf [2] rays [3] overflow [4] trace.cu cursor [5] wide-node share of [0] [6] render ray count [7] wide-walk share of [1]
   void *render_state = nullptr;              // owned by render.cu
   void *sppm_state = nullptr;                // owned by sppm.cu
   void *sss_state = nullptr;                 // owned by sss.cu

@@ -1266,6 +1266,8 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
   // [0..2] visit counters (profiling), [3] traversal-stack overflow flag: a stale flag of an
   // earlier call must not fail this one, and an overflow in this one must not go unnoticed
   GPT_CUDA(ctx, cudaMemsetAsync(ctx->d_counters, 0, 4 * sizeof(unsigned long long), st));
+  GPT_CUDA(ctx, cudaMemsetAsync(ctx->d_counters + 5, 0, sizeof(unsigned long long), st));
+  GPT_CUDA(ctx, cudaMemsetAsync(ctx->d_counters + 7, 0, sizeof(unsigned long long), st));
   auto stamp = [&]() -> cudaError_t {
     if (!timing) return cudaSuccess;
     if (nev == rc->events.size()) {
@@ -1365,10 +1367,12 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
     ctx->stats.kernel_launches = ctx->launches;
     ctx->stats.trace_launches = 1;
     if (counting) {
-      unsigned long long c[4];
+      unsigned long long c[8];
       GPT_CUDA(ctx, cudaMemcpy(c, ctx->d_counters, sizeof(c), cudaMemcpyDeviceToHost));
       ctx->stats.internal_visits = c[0];
       ctx->stats.leaf_tests = c[1];
+      ctx->stats.wide_node_visits = c[5];
+      ctx->stats.wide_leaf_tests = c[7];
     }
     if (h_ctl[SQ_ERR])
       return gpt_fail(ctx, GPT_E_UNSUPPORTED, "nested-dielectric list deeper than 12", __FILE__, __LINE__);
@@ -1629,10 +1633,12 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
     ctx->stats.shade_kernel_ms = ts;
   }
   if (counting) {
-    unsigned long long c[4];
+    unsigned long long c[8];
     GPT_CUDA(ctx, cudaMemcpy(c, ctx->d_counters, sizeof(c), cudaMemcpyDeviceToHost));
     ctx->stats.internal_visits = c[0];
     ctx->stats.leaf_tests = c[1];
+    ctx->stats.wide_node_visits = c[5];
+    ctx->stats.wide_leaf_tests = c[7];
   }
   if (active > 0) return gpt_fail(ctx, GPT_E_INVALID, "path queue did not drain", __FILE__, __LINE__);
   return GPT_OK;

@@ -1462,12 +1462,14 @@ static int sppm_check_errors(gpt_ctx *ctx, SppmCtx *sx) {
 }
 
 static int sppm_collect_rays(gpt_ctx *ctx, SppmCtx *sx) {
-  unsigned long long c[4];
+  unsigned long long c[8];
   GPT_CUDA(ctx, cudaMemcpyAsync(c, ctx->d_counters, sizeof(c), cudaMemcpyDeviceToHost, ctx->stream));
   GPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   ctx->stats.rays_traced = c[2];
   ctx->stats.internal_visits = c[0];
   ctx->stats.leaf_tests = c[1];
+  ctx->stats.wide_node_visits = c[5];
+  ctx->stats.wide_leaf_tests = c[7];
   sx->rays_total += c[2];
   if (c[3]) return gpt_fail(ctx, GPT_E_INVALID, "traversal stack overflow", __FILE__, __LINE__);
   return GPT_OK;
@@ -1520,6 +1522,8 @@ int gpt_sppm_init(gpt_ctx *ctx) {
   cudaStream_t st = ctx->stream;
   GPT_CUDA(ctx, cudaMemsetAsync(sx->d_counts, 0, 4 * sizeof(int), st));
   GPT_CUDA(ctx, cudaMemsetAsync(ctx->d_counters, 0, 4 * sizeof(unsigned long long), st));
+  GPT_CUDA(ctx, cudaMemsetAsync(ctx->d_counters + 5, 0, sizeof(unsigned long long), st));
+  GPT_CUDA(ctx, cudaMemsetAsync(ctx->d_counters + 7, 0, sizeof(unsigned long long), st));
   GPT_CUDA(ctx, cudaMemsetAsync(sx->hp.flux, 0, sizeof(float4) * 2 * (size_t)sx->P, st));
   sx->rays_total = 0;
   sx->ph_first = -1;  // fresh photon streams
@@ -1705,6 +1709,8 @@ int gpt_sppm_pass_stages(gpt_ctx *ctx, int pass, int64_t photon_begin, int64_t p
   GPT_TRY(make_scene_view(ctx, sx, S));
   cudaStream_t st = ctx->stream;
   GPT_CUDA(ctx, cudaMemsetAsync(ctx->d_counters, 0, 4 * sizeof(unsigned long long), st));
+  GPT_CUDA(ctx, cudaMemsetAsync(ctx->d_counters + 5, 0, sizeof(unsigned long long), st));
+  GPT_CUDA(ctx, cudaMemsetAsync(ctx->d_counters + 7, 0, sizeof(unsigned long long), st));
   GPT_CUDA(ctx, cudaEventRecord(ctx->ev0, st));
   if (stage_mask & 1) {
     sx->n_surf = sx->n_vol = 0;

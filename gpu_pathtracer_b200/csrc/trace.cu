@@ -115,6 +115,8 @@ int gpt_trace_launch(gpt_ctx *ctx, int which, const float4 *d_rays, int64_t n, f
   int *next_ray = reinterpret_cast<int *>(c + 4);
   // [0..2] visit counters, [3] the stack-overflow flag: cleared for every call (it was sticky)
   GPT_CUDA(ctx, cudaMemsetAsync(c, 0, 4 * sizeof(unsigned long long), ctx->stream));
+  GPT_CUDA(ctx, cudaMemsetAsync(ctx->d_counters + 5, 0, sizeof(unsigned long long), ctx->stream));
+  GPT_CUDA(ctx, cudaMemsetAsync(ctx->d_counters + 7, 0, sizeof(unsigned long long), ctx->stream));
   GPT_CUDA(ctx, cudaMemsetAsync(next_ray, 0, sizeof(int), ctx->stream));
   cudaStream_t st = ctx->stream;
   if (gpt_trace_wide(ctx, b)) {

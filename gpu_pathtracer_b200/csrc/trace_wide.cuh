@@ -450,6 +450,10 @@ __device__ __forceinline__ void trace_wide(const WideTree tr, Source src, int *n
   if (COUNT) {
     atomicAdd(counters, (unsigned long long)vi);
     atomicAdd(counters + 1, (unsigned long long)vl);
+    // the wide walk's own share of the two totals (48-byte nodes: the roofline numerator
+    // prices a wide visit differently from a 64-byte binary node)
+    atomicAdd(counters + 5, (unsigned long long)vi);
+    atomicAdd(counters + 7, (unsigned long long)vl);
   }
 }
 

@@ -125,6 +125,8 @@ typedef struct GptStats {
   double shade_kernel_ms;   /* sum of the shade-stage kernels of the last render (profiling) */
   uint64_t trace_launches;  /* trace-stage launches in the last render                       */
   double build_wide_ms;     /* last gpt_build: the 4-wide tree collapsed from the main LBVH  */
+  uint64_t wide_node_visits; /* the share of internal_visits that were 48-byte nodes of the 4-wide tree */
+  uint64_t wide_leaf_tests;  /* the share of leaf_tests made by the wide walk                            */
 } GptStats;
 
 /* ---- lifetime ---------------------------------------------------------------------- */
