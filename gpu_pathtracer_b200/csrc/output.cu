@@ -24,16 +24,15 @@ k_tonemap(const float *__restrict__ rgb, size_t n, unsigned char *out) {
   out[i] = (unsigned char)(int)(255.f * c);
 }
 
-__global__ void __launch_bounds__(256) k_fill_int(int *v, size_t n, int x) {
-  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) v[i] = x;
-}
-
 // Camera::compute_i / compute_j (camera.h:54-66) of the direction eye -> point.  Several
 // points can land on one pixel; the reference lets the last writer win (a race), here the
-// point with the HIGHEST index wins (deterministic).
+// point with the HIGHEST index IN THE REFERENCE'S ARRAY ORDER wins -- what the reference's
+// kernel does when its threads run in index order, i.e. the host replay's answer.  `order`
+// maps a point of our array to its index in the reference's array (nullptr: the same order);
+// winner words are (order + 1) << 32 | our index, 0 = no point.
 __global__ void __launch_bounds__(256)
-k_splat_pick(CameraDev cam, const float *__restrict__ loc, int loc_stride, int n, int *winner) {
+k_splat_pick(CameraDev cam, const float *__restrict__ loc, int loc_stride, int n,
+             const int *__restrict__ order, unsigned long long *winner) {
   int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= n) return;
   V3 p = V3{loc[(size_t)idx * loc_stride], loc[(size_t)idx * loc_stride + 1],
@@ -44,33 +43,37 @@ k_splat_pick(CameraDev cam, const float *__restrict__ loc, int loc_stride, int n
   int j = (int)floorf((float)((double)w2 + (double)w2 / cam.tan_half_fovx * (double)dot(dir + cam.w, cam.u)));
   int i = (int)floorf((float)((double)h2 - (double)h2 / cam.tan_half_fovy * (double)dot(dir + cam.w, cam.v)));
   int pix = i * cam.width + j;
-  if (pix < cam.width * cam.height && i >= 0 && j >= 0) atomicMax(winner + pix, idx);
+  if (pix < cam.width * cam.height && i >= 0 && j >= 0) {
+    const unsigned long long key = (unsigned long long)((order ? order[idx] : idx) + 1);
+    atomicMax(winner + pix, (key << 32) | (unsigned)idx);
+  }
 }
 __global__ void __launch_bounds__(256)
-k_splat_write(const int *__restrict__ winner, const float *__restrict__ col, int col_stride,
-              int npix, float *out) {
+k_splat_write(const unsigned long long *__restrict__ winner, const float *__restrict__ col,
+              int col_stride, int npix, float *out) {
   int pix = blockIdx.x * blockDim.x + threadIdx.x;
   if (pix >= npix) return;
-  int w = winner[pix];
-  for (int k = 0; k < 3; k++) out[3 * (size_t)pix + k] = w < 0 ? 0.f : col[(size_t)w * col_stride + k];
+  const unsigned long long w = winner[pix];
+  const size_t idx = (size_t)(w & 0xffffffffull);
+  for (int k = 0; k < 3; k++) out[3 * (size_t)pix + k] = w == 0 ? 0.f : col[idx * col_stride + k];
 }
 
 }  // namespace
 
 // device-side splat used by the SPPM / SSS debug images
 extern "C" int gpt_splat_device(gpt_ctx *ctx, const float *d_loc, int loc_stride,
-                                const float *d_col, int col_stride, int n, float *out_rgb_host) {
+                                const float *d_col, int col_stride, int n, const int *d_order,
+                                float *out_rgb_host) {
   if (!ctx->have_cam) return gpt_fail(ctx, GPT_E_INVALID, "gpt_set_camera first", __FILE__, __LINE__);
   int W = ctx->cam.width, H = ctx->cam.height, P = W * H;
-  int *d_win = nullptr;
+  unsigned long long *d_win = nullptr;
   float *d_out = nullptr;
   GPT_TRY(gpt_alloc(ctx, &d_win, (size_t)P));
   GPT_TRY(gpt_alloc(ctx, &d_out, 3 * (size_t)P));
   cudaStream_t st = ctx->stream;
-  k_fill_int<<<(P + 255) / 256, 256, 0, st>>>(d_win, (size_t)P, -1);
-  GPT_LAUNCH_CHECK(ctx);
+  GPT_CUDA(ctx, cudaMemsetAsync(d_win, 0, sizeof(unsigned long long) * (size_t)P, st));
   if (n > 0) {
-    k_splat_pick<<<(n + 255) / 256, 256, 0, st>>>(derive_camera(ctx->cam), d_loc, loc_stride, n, d_win);
+    k_splat_pick<<<(n + 255) / 256, 256, 0, st>>>(derive_camera(ctx->cam), d_loc, loc_stride, n, d_order, d_win);
     GPT_LAUNCH_CHECK(ctx);
   }
   k_splat_write<<<(P + 255) / 256, 256, 0, st>>>(d_win, d_col, col_stride, P, d_out);

@@ -1880,7 +1880,7 @@ int gpt_sppm_import_hit_points(gpt_ctx *ctx, const float *loc_radius, const floa
 // src/main.cu:1362-1382), 1 = surface photons, 2 = volume photons of the last pass
 // (src/main.cu:1517-1551).  out_rgb: P x 3 host floats.
 int gpt_splat_device(gpt_ctx *ctx, const float *d_loc, int loc_stride, const float *d_col,
-                     int col_stride, int n, float *out_rgb_host);  // output.cu
+                     int col_stride, int n, const int *d_order, float *out_rgb_host);  // output.cu
 int gpt_sppm_debug_image(gpt_ctx *ctx, int which, float *out_rgb) {
   if (!ctx || !out_rgb || which < 0 || which > 2) return GPT_E_INVALID;
   SppmCtx *sx = static_cast<SppmCtx *>(ctx->sppm_state);
@@ -1888,12 +1888,15 @@ int gpt_sppm_debug_image(gpt_ctx *ctx, int which, float *out_rgb) {
   GPT_CUDA(ctx, cudaSetDevice(ctx->device));
   if (which == 0)
     return gpt_splat_device(ctx, reinterpret_cast<const float *>(sx->hp.loc), 4,
-                            reinterpret_cast<const float *>(sx->hp.filter), 4, sx->P, out_rgb);
+                            reinterpret_cast<const float *>(sx->hp.filter), 4, sx->P, nullptr, out_rgb);
   const float4 *leaf = which == 1 ? sx->leaf_surf : sx->leaf_vol;
   int n = which == 1 ? sx->n_surf : sx->n_vol;
   if (n < 2) n = 0;  // no tree was built: nothing recorded
+  // the reference splats its photon lists BEFORE it sorts them for the trees (src/main.cu:1534,
+  // 1545 against :1561-): array order = compaction order = sorted_prim of our leaf order
+  const int *order = which == 1 ? sx->surf_bvh.sorted_prim : sx->vol_bvh.sorted_prim;
   return gpt_splat_device(ctx, reinterpret_cast<const float *>(leaf), 12,
-                          reinterpret_cast<const float *>(leaf) + 9, 12, n, out_rgb);
+                          reinterpret_cast<const float *>(leaf) + 9, 12, n, order, out_rgb);
 }
 
 int gpt_sppm_stats(gpt_ctx *ctx, int64_t *n_surface, int64_t *n_volume, double *mean_radius,

@@ -519,10 +519,11 @@ extern "C" int gpt_sss_export_points(gpt_ctx *ctx, int run_first_pass, int32_t *
 
 // "Creating point image" of the SSS points (src/main.cu:1244-1262): colour = point colour
 extern "C" int gpt_splat_device(gpt_ctx *ctx, const float *d_loc, int loc_stride,
-                                const float *d_col, int col_stride, int n, float *out_rgb_host);  // output.cu
+                                const float *d_col, int col_stride, int n, const int *d_order,
+                                float *out_rgb_host);  // output.cu
 extern "C" int gpt_sss_debug_image(gpt_ctx *ctx, float *out_rgb) {
   if (!ctx || !out_rgb) return GPT_E_INVALID;
   SssCtx *sx = sss_of(ctx);
   const float *leaf = sx ? reinterpret_cast<const float *>(sx->leaf) : nullptr;
-  return gpt_splat_device(ctx, leaf, 8, leaf ? leaf + 4 : nullptr, 8, sx ? sx->npoints : 0, out_rgb);
+  return gpt_splat_device(ctx, leaf, 8, leaf ? leaf + 4 : nullptr, 8, sx ? sx->npoints : 0, nullptr, out_rgb);
 }

@@ -44,6 +44,7 @@ static inline bool counted_traverse_bvh(Node *root, Ray ray, hit_record &rec) {
 #include "model/object/object_operations.h"
 #include "model/point/point.h"
 #include "model/point/ppm_hit_point.h"
+#include "model/point/point_operations.h"
 #include "model/ray/ray.h"
 #include "model/vector_and_matrix/vec3.h"
 #include "render/pathtracing.h"
@@ -1077,6 +1078,42 @@ int ref_sppm_resolve(RefCtx *c, int image_mode, int passes, float *out_rgb) {
     get_ppm_image_output(passes, fb.data(), s->hit_point_list, c->my_camera, image_mode);
   });
   for (int i = 0; i < s->P; i++) {
+    out_rgb[3 * i] = fb[i].x(); out_rgb[3 * i + 1] = fb[i].y(); out_rgb[3 * i + 2] = fb[i].z();
+  }
+  return GPT_OK;
+}
+
+// create_point_image (point_operations.h:19-75) launched as src/main.cu:1248, 1370, 1534, 1545
+// do, threads in index order (so the last writer of a pixel is the highest index).  which:
+// 0 = hit points (colour = filter), 1 / 2 = surface / volume photons of the last photon pass in
+// the order gather_recorded_photons left them (the reference splats them BEFORE the tree build
+// sorts the lists), 3 = SSS points (sorted per object by then).  out_rgb: P x 3, zero = no point.
+int ref_point_image(RefCtx *c, int which, float *out_rgb) {
+  const int W = c->cam.width, H = c->cam.height, P = W * H;
+  std::vector<vec3> fb((size_t)P, vec3(0, 0, 0));
+  const unsigned tx = 8;
+  if (which == 0) {
+    if (!c->sppm) return GPT_E_INVALID;
+    PPMHitPoint **hp = c->sppm->hit_point_list;
+    launch_1d(P / tx + 1, tx, [&] { create_point_image(fb.data(), c->my_camera, hp, P); });
+  } else if (which == 1 || which == 2) {
+    Sppm *s = c->sppm;
+    if (!s) return GPT_E_INVALID;
+    std::vector<Point *> surf((size_t)std::max(1, s->nphot)), vol((size_t)std::max(1, s->nphot));
+    int ns = 0, nv = 0;
+    launch_1d(1, 1, [&] { gather_recorded_photons(s->photon_list, surf.data(), vol.data(), s->nphot, &ns, &nv); });
+    Point **list = which == 1 ? surf.data() : vol.data();
+    const int n = which == 1 ? ns : nv;
+    launch_1d(n / tx + 1, tx, [&] { create_point_image(fb.data(), c->my_camera, list, n); });
+  } else if (which == 3) {
+    Sss *s = c->sss;
+    if (!s) return GPT_E_INVALID;
+    launch_1d(s->num_sss_points / tx + 1, tx,
+              [&] { create_point_image(fb.data(), c->my_camera, s->sss_pts, s->num_sss_points); });
+  } else {
+    return GPT_E_INVALID;
+  }
+  for (int i = 0; i < P; i++) {
     out_rgb[3 * i] = fb[i].x(); out_rgb[3 * i + 1] = fb[i].y(); out_rgb[3 * i + 2] = fb[i].z();
   }
   return GPT_OK;

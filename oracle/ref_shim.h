@@ -24,6 +24,8 @@
 #include <cstdlib>
 #include <iostream>
 #include <string>
+#include <fstream>   // before "#define private public": util/image_util.h pulls these in later
+#include <sstream>
 
 static thread_local uint3 shim_threadIdx = {0, 0, 0}, shim_blockIdx = {0, 0, 0};
 static thread_local dim3 shim_blockDim(1, 1, 1), shim_gridDim(1, 1, 1);

@@ -172,6 +172,14 @@ class RefReplay:
                                              C.c_int(nthreads or os.cpu_count() or 1)))
         return out
 
+    def point_image(self, which: int) -> np.ndarray:
+        """The reference's create_point_image (point_operations.h:19-75), threads in index order:
+        0 hit points, 1 / 2 surface / volume photons of the last photon pass, 3 SSS points."""
+        cam = self.scene.camera
+        out = np.zeros((cam["height"], cam["width"], 3), np.float32)
+        _check(self.lib.ref_point_image(self.ctx, C.c_int(which), cabi.fptr(out)))
+        return out
+
     def sppm_resolve(self, mode=0, passes=1) -> np.ndarray:
         """mode 0 global, 1 direct, 2 indirect (the C-ABI's numbering)."""
         cam = self.scene.camera

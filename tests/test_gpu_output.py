@@ -76,3 +76,55 @@ def test_sss_debug_splat():
     img = pt.sss_debug_image()
     assert (img.sum(-1) > 0).sum() > 50
     assert img.max() <= pts["color"].max() + 1e-6
+
+
+def test_sppm_debug_splats_equal_create_point_image():
+    """f-4 value parity: on the reference's own hit points and photons the three SPPM splats
+    are bit-identical to the reference's create_point_image (point_operations.h:19-75) run
+    with its threads in index order -- the last writer of a pixel is the highest index of the
+    REFERENCE's array order (photons: the order gather_recorded_photons leaves, before the tree
+    build sorts them, src/main.cu:1534-1551)."""
+    from gpu_pathtracer_b200.api import PathTracer
+    from tests.refreplay import RefReplay, available
+    if not available():
+        pytest.skip("oracle/_ref/libref_replay.so not available")
+    sc = S.make_scene("C4", cells=6, width=128, height=104, photons=60000, passes=1, sphere_subdiv=2)
+    ref = RefReplay(sc)
+    ref.sppm_init()
+    ref.sppm_pass(0, photon_rng=0, stages=1)
+    hp, ph = ref.sppm_export_hit_points(), ref.sppm_export_photons()
+    pt = PathTracer(sc, device=0)
+    pt.build()
+    pt.sppm_init()
+    pt.sppm_import_hit_points(hp["loc_radius"], hp["normal_vradius"], hp["filter"])
+    pt.sppm_import_photons(ph["kind"], ph["rec"])
+    for which in (0, 1, 2):
+        got, want = pt.sppm_debug_image(which), ref.point_image(which)
+        painted = (want.sum(-1) > 0).sum()
+        assert painted > 200, (which, painted)
+        assert np.array_equal(got.view(np.uint32), want.view(np.uint32)), which
+    # several photons per pixel: the winner rule is exercised, not only the projection
+    n_surface = int((ph["kind"] == 0).sum())
+    assert n_surface > 2 * (ref.point_image(1).sum(-1) > 0).sum()
+
+
+def test_sss_debug_splat_equals_create_point_image():
+    """The SSS point splat (src/main.cu:1244-1262: after the per-object trees sorted the points
+    and do_sss_first_pass coloured them) against the reference's kernel on the replay's points.
+    Positions and tree order are bit-exact (test_gpu_sss.py), colours carry libm ulps, so: the
+    same pixels are painted and the colours agree to 1e-3."""
+    from gpu_pathtracer_b200.api import PathTracer
+    from tests.refreplay import RefReplay, available
+    if not available():
+        pytest.skip("oracle/_ref/libref_replay.so not available")
+    sc = S.make_scene("small", n=16, width=128, height=128, spp=2, level=3, sss_pts=400)
+    ref = RefReplay(sc)
+    ref.sss_export_points(first_pass=True)
+    want = ref.point_image(3)
+    pt = PathTracer(sc, device=0)
+    pt.build()
+    pt.sss_export_points(first_pass=True)
+    got = pt.sss_debug_image()
+    assert np.array_equal(got.sum(-1) > 0, want.sum(-1) > 0)
+    assert (want.sum(-1) > 0).sum() > 50
+    assert np.allclose(got, want, rtol=1e-3, atol=1e-4)

@@ -21,7 +21,7 @@ sys.path.insert(0, ROOT)
 from gpu_pathtracer_b200 import scene as S  # noqa: E402
 from gpu_pathtracer_b200.api import PathTracer  # noqa: E402
 
-BIN = os.path.join(ROOT, "oracle", "_ref", "gpu_path_tracing_100")
+BIN = os.path.join(ROOT, "oracle", "_ref", os.environ.get("GPT_REF_BIN", "gpu_path_tracing_100"))
 
 
 def read_p3(path):
@@ -68,7 +68,7 @@ def main():
     ours = to_u8(img)
     diff = np.abs(ours - ref_img)
     out = {
-        "scene": kind, "triangles": sc.num_triangles,
+        "scene": kind, "triangles": sc.num_triangles, "reference_binary": os.path.basename(BIN),
         "frame": f"{sc.camera['width']}x{sc.camera['height']} @ {sc.params['pathtracing_sample_size']} spp",
         "ref_render_s": stages.get("Rendering"), "ref_total_wall_s": wall,
         "ref_main_bvh_build_s": sum(stages.get(k, 0.0) for k in build_keys),
