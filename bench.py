@@ -38,6 +38,7 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ref-cuda", action="store_true",
                     help="skip the run of the reference's own CUDA binary after the timed region")
+    ap.add_argument("--no-fast-rng", action="store_true", help="skip the config.fast_rng leg")
     ap.add_argument("--fast-rng", type=int, default=0,
                     help="rng_mode 1 with this many sample lanes per pixel (0 = reference streams)")
     return ap.parse_args()
@@ -372,6 +373,30 @@ def run_ours(args, rank, world, local_rank):
     total_ms = float(sum(step_ms))
     clocks = sampler.stop() if sampler else None
 
+    # ---- the same frames with rng_mode 1 (8 independent sample lanes per pixel: NOT the
+    #      reference's sample order, see config.fast_rng) -- reported beside the headline, which
+    #      stays on the reference's streams
+    fast_ms, fast_rays, fast_lanes = 0.0, 0, 8
+    if not args.fast_rng and not args.no_fast_rng:
+        pt.set_params(rng_mode=1)
+        pt.set_fast_rng_lanes(fast_lanes)
+        for _ in range(2):
+            flush.zero_()
+            pt.render_pathtrace_device(fb.data_ptr(), rank, world)
+        barrier()
+        fevs = []
+        for _ in range(min(args.steps, 5)):
+            flush.zero_()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(stream)
+            pt.render_pathtrace_device(fb.data_ptr(), rank, world)
+            b.record(stream)
+            fevs.append((a, b))
+            fast_rays = pt.stats()["rays_traced"]
+        barrier()
+        fast_ms = float(np.mean([a.elapsed_time(b) for a, b in fevs]))
+        pt.set_params(rng_mode=0)
+
     # ---- profiling passes (not timed): per-stage kernel time, then visit counts
     pt.set_profiling(time_stages=True)
     pt.render_pathtrace_device(fb.data_ptr(), rank, world)
@@ -410,13 +435,13 @@ def run_ours(args, rank, world, local_rank):
     barrier()
     e2e_ms = (time.perf_counter() - t0) / e2e_steps * 1e3
 
-    t = torch.tensor([total_ms, e2e_ms], dtype=torch.float64, device=dev)
-    tot = torch.tensor([float(rays)], dtype=torch.float64, device=dev)
+    t = torch.tensor([total_ms, e2e_ms, fast_ms], dtype=torch.float64, device=dev)
+    tot = torch.tensor([float(rays), float(fast_rays)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(tot, op=dist.ReduceOp.SUM)
-    total_ms, e2e_ms = t.tolist()
-    rays_all = tot.item()
+    total_ms, e2e_ms, fast_ms = t.tolist()
+    rays_all, fast_rays_all = tot.tolist()
     if rank != 0:
         return
     # the full frame of the e2e leg on the host (N > 1: after gpt_gather_frame on rank 0)
@@ -474,6 +499,12 @@ def run_ours(args, rank, world, local_rank):
             "rng": ("reference streams (seed 1984, seq = pixel; rng_mode 0)" if not args.fast_rng else
                     f"rng_mode 1: {args.fast_rng} independent sample lanes per pixel (NOT the "
                     "reference's sample order; statistical parity only)"),
+            "fast_rng": ({"what": f"rng_mode 1, {fast_lanes} independent sample lanes per pixel "
+                                  "(seq = pixel * L + lane): same estimator, other random numbers "
+                                  "than the reference -- statistical parity only (tests/test_gpu_"
+                                  "render.py::test_fast_rng_mode); max over ranks, L2 flushed",
+                          "value": fast_rays_all / (fast_ms * 1e-3) / 1e6, "unit": "Mrays/s",
+                          "ms_per_step": fast_ms} if fast_ms > 0 else None),
             "spp_per_s": spp_total / (ms_per_step * 1e-3),
             "rays_per_frame": rays_all,
             "lbvh_build_ms": build_ms, "build_all_ms": build_stats["build_all_ms"],

@@ -1482,6 +1482,7 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
     if (G > 1) GPT_CUDA(ctx, cudaStreamWaitEvent(rc->gstream[g], rc->fork_ev, 0));
   const long long max_iters = (long long)p.sample_size * p.dof_size * p.level + 8 + LAG;
   bool list_overflow = false;
+  std::vector<int> round_active;  // stage timing only: queue length the host sized each round with
   int remaining = 0;
   for (int g = 0; g < G; g++) remaining += grp[g].done ? 0 : 1;
   cudaStream_t const caller_stream = ctx->stream;
@@ -1545,6 +1546,7 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
       }
       GPT_LAUNCH_CHECK(ctx);
       trace_launches++;
+      if (timing) round_active.push_back(q.active);
       GPT_CUDA(ctx, stamp());
       // stable 7-bit radix sort of the active slots by material (ties keep tile order)
       uint32_t *sk = nullptr;
@@ -1622,13 +1624,19 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
   ctx->stats.trace_launches = trace_launches;
   if (timing) {  // three stamps per iteration: before trace, between, after shade
     double tt = 0, ts = 0;
+    // GPT_ROUND_LOG=path: one line per round of the stage-timed frame (round, queue length as
+    // the host knew it, trace ms, sort + shade ms) -- the data behind DESIGN 4.5's chain analysis
+    const char *log_path = getenv("GPT_ROUND_LOG");
+    FILE *lf = log_path ? fopen(log_path, "w") : nullptr;
     for (size_t k = 0; k + 2 < nev; k += 3) {
       float a = 0.f, b = 0.f;
       cudaEventElapsedTime(&a, rc->events[k], rc->events[k + 1]);
       cudaEventElapsedTime(&b, rc->events[k + 1], rc->events[k + 2]);
       tt += a;
       ts += b;
+      if (lf) fprintf(lf, "%zu %d %.4f %.4f\n", k / 3, k / 3 < round_active.size() ? round_active[k / 3] : -1, a, b);
     }
+    if (lf) fclose(lf);
     ctx->stats.trace_kernel_ms = tt;
     ctx->stats.shade_kernel_ms = ts;
   }
