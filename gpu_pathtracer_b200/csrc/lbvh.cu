@@ -12,6 +12,8 @@
 // Morton arithmetic is the same fp32 sequence, the sort is stable, delta() carries the
 // same index tie-break, and min/max unions are order-independent.
 #include "common.cuh"
+#include <cuda/atomic>
+
 #include "vecmath.cuh"
 
 namespace {
@@ -108,7 +110,7 @@ k_morton(const float *__restrict__ aabb, const int *__restrict__ prim_list, int 
 }
 
 // ---- stable LSD radix sort -------------------------------------------------------------
-// Pass = k_sort_hist (per-block digit counts, digit-major) -> k_sort_scan (exclusive scan)
+// Pass = k_sort_hist (per-block digit counts, digit-major) -> k_sort_scan_rows (exclusive scan per digit)
 //        -> k_sort_scatter (stable ranks via __match_any_sync + per-warp running counters).
 template <int ITEMS>
 __global__ void __launch_bounds__(SORT_THREADS)
@@ -128,53 +130,48 @@ k_sort_hist(const uint32_t *__restrict__ keys, int n, int shift, uint32_t mask,
   block_hist[(size_t)threadIdx.x * nblocks + blockIdx.x] = h[threadIdx.x];
 }
 
-// single-block exclusive scan of the m = (digits of this pass) * nblocks counters, in tiles of
-// 4096: coalesced 16-byte loads, warp-shuffle scans, one running carry
-__global__ void __launch_bounds__(1024) k_sort_scan(uint32_t *data, int m) {
-  __shared__ uint32_t wsum[32];
-  const int t = threadIdx.x, lane = t & 31, w = t >> 5;
-  uint32_t carry = 0;
-  for (int base = 0; base < m; base += 4096) {
-    const int i = base + 4 * t;
-    uint32_t v0 = 0, v1 = 0, v2 = 0, v3 = 0;
-    if (i + 3 < m) {
-      uint4 q = *reinterpret_cast<const uint4 *>(data + i);
-      v0 = q.x; v1 = q.y; v2 = q.z; v3 = q.w;
-    } else {
-      if (i < m) v0 = data[i];
-      if (i + 1 < m) v1 = data[i + 1];
-      if (i + 2 < m) v2 = data[i + 2];
-    }
-    const uint32_t s = v0 + v1 + v2 + v3;
-    uint32_t x = s;
+// block-wide exclusive scan of one value per thread (SORT_THREADS threads); returns the
+// exclusive prefix, *total = the sum over the block
+__device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t *wsum, uint32_t *total) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  uint32_t x = v;
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
-      if (lane >= o) x += y;
-    }
-    if (lane == 31) wsum[w] = x;
-    __syncthreads();
-    if (w == 0) {
-      uint32_t y = wsum[lane];
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        uint32_t z = __shfl_up_sync(0xffffffffu, y, o);
-        if (lane >= o) y += z;
-      }
-      wsum[lane] = y;
-    }
-    __syncthreads();
-    uint32_t p = carry + (w > 0 ? wsum[w - 1] : 0u) + (x - s);
-    if (i + 3 < m) {
-      *reinterpret_cast<uint4 *>(data + i) = make_uint4(p, p + v0, p + v0 + v1, p + v0 + v1 + v2);
-    } else {
-      if (i < m) data[i] = p;
-      if (i + 1 < m) data[i + 1] = p + v0;
-      if (i + 2 < m) data[i + 2] = p + v0 + v1;
-    }
-    carry += wsum[31];
-    __syncthreads();
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+    if (lane >= o) x += y;
   }
+  if (lane == 31) wsum[w] = x;
+  __syncthreads();
+  uint32_t base = 0, tot = 0;
+#pragma unroll
+  for (int k = 0; k < SORT_WARPS; k++) {
+    const uint32_t c = wsum[k];
+    if (k < w) base += c;
+    tot += c;
+  }
+  __syncthreads();
+  *total = tot;
+  return base + x - v;
+}
+
+// One block per digit: exclusive scan of that digit's row of per-block counts (digit-major
+// layout) in place, the row's sum into totals[digit].  The bases of the digits themselves -- a
+// 256-entry scan -- are recomputed by every scatter block (r02: the single-block scan over all
+// digits x blocks counters was 18 % of the 1 M-triangle build, 3 x 21 us).
+__global__ void __launch_bounds__(SORT_THREADS)
+k_sort_scan_rows(uint32_t *block_hist, int nblocks, uint32_t *totals) {
+  __shared__ uint32_t wsum[SORT_WARPS];
+  uint32_t *row = block_hist + (size_t)blockIdx.x * nblocks;
+  uint32_t carry = 0;
+  for (int base = 0; base < nblocks; base += SORT_THREADS) {
+    const int i = base + threadIdx.x;
+    const uint32_t v = i < nblocks ? row[i] : 0u;
+    uint32_t tot;
+    const uint32_t ex = block_exclusive_scan(v, wsum, &tot);
+    if (i < nblocks) row[i] = carry + ex;
+    carry += tot;
+  }
+  if (threadIdx.x == 0) totals[blockIdx.x] = carry;
 }
 
 template <int ITEMS>
@@ -182,8 +179,9 @@ __global__ void __launch_bounds__(SORT_THREADS)
 k_sort_scatter(const uint32_t *__restrict__ keys, const int *__restrict__ vals, int n,
                int shift, uint32_t mask, const uint32_t *__restrict__ block_hist, int nblocks,
                uint32_t *__restrict__ keys_out, int *__restrict__ vals_out,
-               const int *__restrict__ d_n) {
+               const int *__restrict__ d_n, const uint32_t *__restrict__ totals) {
   __shared__ uint32_t cnt[SORT_WARPS][256];  // running / total count per warp and digit
+  __shared__ uint32_t wsum[SORT_WARPS];
   if (d_n) n = min(n, __ldg(d_n));
   int w = threadIdx.x >> 5, l = threadIdx.x & 31;
   for (int d = threadIdx.x; d < SORT_WARPS * 256; d += SORT_THREADS) (&cnt[0][0])[d] = 0;
@@ -208,9 +206,12 @@ k_sort_scatter(const uint32_t *__restrict__ keys, const int *__restrict__ vals, 
     __syncwarp();
   }
   __syncthreads();
-  {  // exclusive scan over warps for digit d = threadIdx.x, plus the global base
+  {  // exclusive scan over warps for digit d = threadIdx.x, plus the global base = keys with
+     // a smaller digit (scan of the digit totals) + keys of this digit in earlier blocks
     int d = threadIdx.x;
-    uint32_t run = __ldg(block_hist + (size_t)d * nblocks + blockIdx.x);
+    uint32_t tot_all;
+    const uint32_t digit_base = block_exclusive_scan((uint32_t)d <= mask ? __ldg(totals + d) : 0u, wsum, &tot_all);
+    uint32_t run = digit_base + ((uint32_t)d <= mask ? __ldg(block_hist + (size_t)d * nblocks + blockIdx.x) : 0u);
 #pragma unroll
     for (int k = 0; k < SORT_WARPS; k++) {
       uint32_t c = cnt[k][d];
@@ -310,9 +311,11 @@ k_refit(const float *__restrict__ aabb, const int *__restrict__ prim_list,
     reinterpret_cast<float2 *>(slot)[0] = bx;
     reinterpret_cast<float2 *>(slot)[1] = by;
     reinterpret_cast<float2 *>(slot)[2] = bz;
-    __threadfence();
-    if (atomicAdd(flags + par, 1) == 0) return;  // first arrival: the sibling will climb
-    __threadfence();
+    // one acq_rel RMW instead of fence.sc + atom + fence.sc (r02: the refit is a chain of
+    // ~40 such hand-overs for the top of the tree): release publishes this child's slot,
+    // acquire makes the sibling's slot visible to the second arrival
+    cuda::atomic_ref<int, cuda::thread_scope_device> arrived(flags[par]);
+    if (arrived.fetch_add(1, cuda::std::memory_order_acq_rel) == 0) return;  // first arrival: the sibling will climb
     const float2 *sib = reinterpret_cast<const float2 *>(nf + (right ? 0 : 6));
     float2 sx = __ldcg(sib), sy = __ldcg(sib + 1), sz = __ldcg(sib + 2);
     bx = make_float2(fminf(bx.x, sx.x), fmaxf(bx.y, sx.y));
@@ -380,7 +383,7 @@ int gpt_radix_hist_entries(int n) {
   int a = (small_n + SORT_THREADS * SORT_ITEMS_SMALL - 1) / (SORT_THREADS * SORT_ITEMS_SMALL);
   int b = (n + SORT_TILE - 1) / SORT_TILE;
   int nblocks = a > b ? a : b;
-  return 256 * (nblocks > 0 ? nblocks : 1);
+  return 256 * (nblocks > 0 ? nblocks : 1) + 256;  // + the 256 digit totals behind the rows
 }
 
 int gpt_radix_sort_pairs(gpt_ctx *ctx, uint32_t *keys, int *vals, uint32_t *keys_alt,
@@ -398,11 +401,13 @@ int gpt_radix_sort_pairs(gpt_ctx *ctx, uint32_t *keys, int *vals, uint32_t *keys
     if (small) k_sort_hist<SORT_ITEMS_SMALL><<<nblocks, SORT_THREADS, 0, ctx->stream>>>(ka, n, shift, mask, block_hist, nblocks, d_n);
     else k_sort_hist<SORT_ITEMS><<<nblocks, SORT_THREADS, 0, ctx->stream>>>(ka, n, shift, mask, block_hist, nblocks, d_n);
     GPT_LAUNCH_CHECK(ctx);
-    // digit-major layout: only the digits this pass can produce need scanning
-    k_sort_scan<<<1, 1024, 0, ctx->stream>>>(block_hist, (int)(mask + 1) * nblocks);
+    // digit-major layout: one block per digit this pass can produce scans its row; the digit
+    // totals live behind the 256 rows (gpt_radix_hist_entries reserves them)
+    uint32_t *totals = block_hist + (size_t)256 * nblocks;
+    k_sort_scan_rows<<<(int)(mask + 1), SORT_THREADS, 0, ctx->stream>>>(block_hist, nblocks, totals);
     GPT_LAUNCH_CHECK(ctx);
-    if (small) k_sort_scatter<SORT_ITEMS_SMALL><<<nblocks, SORT_THREADS, 0, ctx->stream>>>(ka, va, n, shift, mask, block_hist, nblocks, kb, vb, d_n);
-    else k_sort_scatter<SORT_ITEMS><<<nblocks, SORT_THREADS, 0, ctx->stream>>>(ka, va, n, shift, mask, block_hist, nblocks, kb, vb, d_n);
+    if (small) k_sort_scatter<SORT_ITEMS_SMALL><<<nblocks, SORT_THREADS, 0, ctx->stream>>>(ka, va, n, shift, mask, block_hist, nblocks, kb, vb, d_n, totals);
+    else k_sort_scatter<SORT_ITEMS><<<nblocks, SORT_THREADS, 0, ctx->stream>>>(ka, va, n, shift, mask, block_hist, nblocks, kb, vb, d_n, totals);
     GPT_LAUNCH_CHECK(ctx);
     uint32_t *tk = ka; ka = kb; kb = tk;
     int *tv = va; va = vb; vb = tv;

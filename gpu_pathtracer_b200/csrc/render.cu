@@ -51,6 +51,9 @@ struct RenderCtx {
   int *sort_val = nullptr, *sort_val_alt = nullptr;
   int *classq = nullptr;          // PT_NCLASS material-class lists per group (k_pt_trace -> k_pt_shade)
   int *ccount = nullptr;          // MAX_GROUPS x 3 (rotation) x PT_NCLASS list lengths
+  float4 *sss_req = nullptr;      // deferred SSS lookups: 3 float4 per slot (a slot asks at most once a round)
+  int *sss_req_cnt = nullptr;     // MAX_GROUPS x 2 request counters (alternating rounds)
+  size_t sss_req_cap = 0;         // slots sss_req was allocated for
   int *sq_cells = nullptr, *sq_ctl = nullptr;  // streaming pipeline: 9 rings + control words
   int sq_capacity = 0;                         // cells per ring
   float *d_fb = nullptr;          // internal framebuffer for the host API
@@ -75,6 +78,11 @@ struct RenderParams {
   int fast_lanes, lane0, npix, total_samples;
   float4 *partial;
   SssView sss;
+  // r02 deferred SSS lookups (k_sss_lookup): a shade thread that hits an SSS material appends a
+  // request of three float4 -- (point, path_length) (diffuse tint, slot) (object, -, -, -) --
+  // instead of doing the lookup itself; nullptr = lookups stay in the shade thread
+  float4 *sss_req;
+  int *sss_req_count;
 };
 
 // ---- RNG init: curand_init(1984, pixel_index, 0) (general.h:15) ---------------------------
@@ -418,6 +426,133 @@ static __device__ __noinline__ V3 sss_lookup(BitmapPool sv, const SssTree &t, V3
   return color;
 }
 
+// The same lookup by a WHOLE WARP (k_sss_lookup).  Why: ncu on the C5 frame (profiles/
+// r02_summary.md) -- the thread-per-lookup form above runs its ordered sum at 5 of 32 lanes and
+// its candidate scan at 13, every load a dependent round trip, and because the material sort
+// puts all SSS hits into a few hundred warps those warps run ~8 ms while 90 % of the GPU idles.
+// Here all 32 lanes call with the same (t, c, r):
+//   mark:  the <= 9 candidate rows are read 32 records at a time (coalesced, independent loads),
+//          accepted points set their bit with a fire-and-forget atomicOr;
+//   sum:   32 bitmap words per step, one per lane; popc + warp prefix give every accepted point
+//          its position in the reference's visit order; the 32 next terms (w, w r, w g, w b)
+//          are computed side by side -- sqrt, IEEE divide, record fetch -- and parked in
+//          shared memory, then lanes 0..3 add one component each IN ORDER.
+// fp32 addition order, candidate test and weight are those of sss_lookup, so the result is
+// bit-identical to it and to the reference walk (tests/test_gpu_sss.py).
+static __device__ __noinline__ V3 sss_lookup_warp(BitmapPool sv, const SssTree &t, V3 c, float r,
+                                                  bool &found, float4 *sterm) {
+  constexpr unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  found = false;
+  if (t.n < 2) return V3{0.f, 0.f, 0.f};
+  int slot = -1;
+  if (lane == 0) {
+    unsigned h = ((blockIdx.x * blockDim.x + threadIdx.x) >> 5) * 2654435761u;
+    for (int probe = 0; probe < 64 && slot < 0; probe++) {
+      int i = (int)((h + (unsigned)probe * 40503u) % (unsigned)sv.bm_n);
+      if (atomicCAS(sv.bm_busy + i, 0, 1) == 0) slot = i;
+    }
+  }
+  slot = __shfl_sync(FULL, slot, 0);
+  if (slot < 0 || !t.gpos) {  // no private bitmap / no candidate grid: one lane walks the reference's tree
+    if (slot >= 0 && lane == 0) atomicExch(sv.bm_busy + slot, 0);
+    V3 col = V3{0.f, 0.f, 0.f};
+    bool f = false;
+    if (lane == 0) col = sss_lookup_ref_walk(t, c, r, f);
+    found = __shfl_sync(FULL, (int)f, 0) != 0;
+    return V3{__shfl_sync(FULL, col.x, 0), __shfl_sync(FULL, col.y, 0), __shfl_sync(FULL, col.z, 0)};
+  }
+  uint32_t *bm = sv.bm_pool + (size_t)slot * sv.bm_words;
+  // ---- mark (sss_mark_grid, 32 candidates at a time)
+  int wlo = sv.bm_words, whi = -1;
+  {
+    const float g = 1e-5f * (fabsf(c.x) + fabsf(c.y) + fabsf(c.z) + r + 1.f);
+    const float lo = r + g;
+    float T = r * r;  // the largest float whose square root rounds to <= r
+    while (sqrtf(T) > r) T = __uint_as_float(__float_as_uint(T) - 1u);
+    while (sqrtf(__uint_as_float(__float_as_uint(T) + 1u)) <= r) T = __uint_as_float(__float_as_uint(T) + 1u);
+    const int x0 = sss_grid_cell(c.x - lo, t.gox, t.ginv, t.gnx), x1 = sss_grid_cell(c.x + lo, t.gox, t.ginv, t.gnx);
+    const int y0 = sss_grid_cell(c.y - lo, t.goy, t.ginv, t.gny), y1 = sss_grid_cell(c.y + lo, t.goy, t.ginv, t.gny);
+    const int z0 = sss_grid_cell(c.z - lo, t.goz, t.ginv, t.gnz), z1 = sss_grid_cell(c.z + lo, t.goz, t.ginv, t.gnz);
+    for (int z = z0; z <= z1; z++)
+      for (int y = y0; y <= y1; y++) {
+        const int row = t.gnx * (y + t.gny * z);
+        const int jb = __ldg(t.gstart + row + x0), je = __ldg(t.gstart + row + x1 + 1);
+#pragma unroll 4
+        for (int j = jb + lane; j < je; j += 32) {
+          const float4 a = __ldg(t.gpos + j);
+          const float dx = c.x - a.x, dy = c.y - a.y, dz = c.z - a.z;
+          const float d2 = dx * dx + dy * dy + dz * dz;
+          if (d2 <= T) {
+            const int i = __float_as_int(a.w);
+            atomicOr(bm + (i >> 5), 1u << (i & 31));
+            wlo = min(wlo, i >> 5);
+            whi = max(whi, i >> 5);
+          }
+        }
+      }
+    wlo = __reduce_min_sync(FULL, wlo);
+    whi = __reduce_max_sync(FULL, whi);
+  }
+  __threadfence();  // the marks, before any lane reads a word another lane marked
+  __syncwarp();
+  // ---- ordered sum: lane 0 owns sum_w, lanes 1..3 colour r, g, b
+  float accv = 0.f;
+  for (int w0 = wlo; w0 <= whi; w0 += 32) {
+    const int w = w0 + lane;
+    const uint32_t bits = w <= whi ? __ldcg(bm + w) : 0u;
+    if (bits) bm[w] = 0u;  // leave the bitmap clean for its next user
+    const int cnt = __popc(bits);
+    int incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y = __shfl_up_sync(FULL, incl, o);
+      if (lane >= o) incl += y;
+    }
+    const int total = __shfl_sync(FULL, incl, 31), excl = incl - cnt;
+    for (int base = 0; base < total; base += 32) {
+      const int k = base + lane;
+      int src = 0;  // the lane whose word holds the k-th accepted point of this step
+#pragma unroll
+      for (int step = 16; step >= 1; step >>= 1) {
+        const int e = __shfl_sync(FULL, excl, (src + step) & 31);
+        if (src + step < 32 && e <= k) src += step;
+      }
+      const uint32_t wb = __shfl_sync(FULL, bits, src);
+      const int e0 = __shfl_sync(FULL, excl, src);
+      float4 term = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (k < total) {
+        const int b = (int)__fns(wb, 0, k - e0 + 1);
+        const float4 *lf = t.vleaf + 2 * (size_t)(32 * (w0 + src) + b);
+        const float4 a = lf[0], col = lf[1];
+        float wgt = 1.0f / dist(V3{a.x, a.y, a.z}, c);
+        wgt = wgt < 9999.990234375f ? wgt : 9999.990234375f;  // (float)fmin(9999.99, wgt), see sss_lookup
+        term = make_float4(wgt, wgt * col.x, wgt * col.y, wgt * col.z);
+      }
+      sterm[lane] = term;
+      __syncwarp();
+      if (lane < 4) {
+        const float *f = reinterpret_cast<const float *>(sterm) + lane;
+        const int nb = min(32, total - base);
+#pragma unroll 8
+        for (int i = 0; i < nb; i++) accv = accv + f[4 * i];
+      }
+      __syncwarp();
+      found = true;
+    }
+  }
+  __threadfence();  // the cleared words, before the bitmap changes hands
+  __syncwarp();
+  if (lane == 0) atomicExch(sv.bm_busy + slot, 0);
+  const float sum_w = __shfl_sync(FULL, accv, 0);
+  V3 color = V3{__shfl_sync(FULL, accv, 1), __shfl_sync(FULL, accv, 2), __shfl_sync(FULL, accv, 3)};
+  if (found) {
+    const float k = 1.0f / sum_w;
+    color = V3{color.x * k, color.y * k, color.z * k};
+  }
+  return color;
+}
+
 __global__ void __launch_bounds__(PT_BLOCK)
 k_pt_start(PathState ps, RenderParams p, int n, float *fb) {
   int s = blockIdx.x * blockDim.x + threadIdx.x;
@@ -559,6 +694,86 @@ k_pt_trace_wide(QueueSource src, WideTree tree, int *next_ray, unsigned long lon
 // streaming pipeline: a slot's state is written by whichever SM had it last while THIS kernel
 // runs, so it is read around the (incoherent) L1.
 #define PS_LD(ptr) (ASYNC ? __ldcg(ptr) : *(ptr))
+// A path just ended with `result` (its radiance; pathtracing.h:251-305 adds it to the pixel and
+// goes on with the pixel's next sample): accumulate, then either start the next sample of the
+// slot (returns true: the slot goes back to the trace stage) or write the pixel / partial sum /
+// SSS point colour.  Its own function since r02: k_sss_lookup ends the paths whose radiance is
+// a deferred point-cloud lookup.
+template <bool ASYNC>
+__device__ __forceinline__ bool finish_sample(const PathState &ps, const RenderParams &p, int s,
+                                              V3 result, Rng &rng, float *fb, int sidx) {
+  bool alive = true;
+  float4 cl = PS_LD(ps.cm + 2 * (size_t)s);
+  V3 color = V3{cl.x, cl.y, cl.z} + de_nan(result);
+  int k = __float_as_int(cl.w);
+  sidx++;
+  V3 o, d;
+  bool finished = false;
+  if (p.mode == 1) {
+    // do_sss_first_pass: every sample draws a fresh cosine-hemisphere ray at the point
+    if (sidx >= p.sample_size) {
+      finished = true;
+    } else {
+      float4 co = PS_LD(ps.cam + 2 * (size_t)s), cn = PS_LD(ps.cam + 2 * (size_t)s + 1);
+      o = V3{co.x, co.y, co.z};
+      d = generate_dir(V3{0.f, 0.f, 0.f}, V3{cn.x, cn.y, cn.z}, 0, 1.f, rng);
+    }
+  } else if (p.fast_lanes) {
+    // this slot's lane gets samples lane, lane + lanes, ... of the pixel's dof x spp (dof index =
+    // sample / spp); as in the reference a new camera ray is drawn when the dof index changes
+    // and reused otherwise, so one lane reproduces the reference's stream exactly
+    const int lane = p.lane0 + s / p.npix;
+    if (sidx >= (p.total_samples - lane + p.fast_lanes - 1) / p.fast_lanes) {
+      finished = true;
+    } else if ((lane + sidx * p.fast_lanes) / p.sample_size != (lane + (sidx - 1) * p.fast_lanes) / p.sample_size) {
+      int pix = ps.pixel[s];
+      camera_ray(p.cam, pix / p.cam.width + .5f, pix % p.cam.width + .5f, rng, o, d);
+      ps.cam[2 * (size_t)s] = make_float4(o.x, o.y, o.z, 0.f);
+      ps.cam[2 * (size_t)s + 1] = make_float4(d.x, d.y, d.z, 0.f);
+    } else {
+      float4 co = PS_LD(ps.cam + 2 * (size_t)s), cd = PS_LD(ps.cam + 2 * (size_t)s + 1);
+      o = V3{co.x, co.y, co.z};
+      d = V3{cd.x, cd.y, cd.z};
+    }
+  } else if (sidx >= p.sample_size) {
+    sidx = 0;
+    k++;
+    if (k >= p.dof_size) {
+      finished = true;
+    } else {
+      int pix = ps.pixel[s];
+      camera_ray(p.cam, pix / p.cam.width + .5f, pix % p.cam.width + .5f, rng, o, d);
+      ps.cam[2 * (size_t)s] = make_float4(o.x, o.y, o.z, 0.f);
+      ps.cam[2 * (size_t)s + 1] = make_float4(d.x, d.y, d.z, 0.f);
+    }
+  } else {
+    float4 co = PS_LD(ps.cam + 2 * (size_t)s), cd = PS_LD(ps.cam + 2 * (size_t)s + 1);
+    o = V3{co.x, co.y, co.z};
+    d = V3{cd.x, cd.y, cd.z};
+  }
+  if (finished && p.mode == 1) {
+    // color *= (1.0 / sample_size); color *= filter; point -> assign_color(color)
+    float4 pa = __ldg(p.sss.pts + 3 * (size_t)s), pb = __ldg(p.sss.pts + 3 * (size_t)s + 1);
+    V3 out = (color * p.inv_samples) * V3{pa.w, pb.x, pb.y};
+    p.sss.leaf[2 * (size_t)s + 1] = make_float4(out.x, out.y, out.z, 0.f);
+    alive = false;
+  } else if (finished && p.fast_lanes) {
+    p.partial[s] = make_float4(color.x, color.y, color.z, 0.f);
+    alive = false;
+  } else if (finished) {
+    int pix = ps.pixel[s];
+    V3 out = color * p.inv_samples;
+    fb[3 * (size_t)pix] = out.x; fb[3 * (size_t)pix + 1] = out.y; fb[3 * (size_t)pix + 2] = out.z;
+    alive = false;
+  } else {
+    ps.cm[2 * (size_t)s] = make_float4(color.x, color.y, color.z, __int_as_float(k));
+    ps.ma[2 * (size_t)s] = make_float4(1.f, 1.f, 1.f, __int_as_float(0));
+    ps.ma[2 * (size_t)s + 1] = make_float4(0.f, 0.f, 0.f, __int_as_float(sidx));
+    start_sample(ps, s, o, d);
+  }
+  return alive;
+}
+
 template <bool ASYNC>
 __device__ __forceinline__ bool shade_slot(const PathState &ps, const RenderParams &p, int s,
                                            const SceneDev &sc, const TexAtlas &atlas,
@@ -574,7 +789,7 @@ __device__ __forceinline__ bool shade_slot(const PathState &ps, const RenderPara
   int leaf = __float_as_int(h0.y);
   Rng rng;
   rng_load_packed<ASYNC>(rng, ps.rng, s);
-  bool done = false;
+  bool done = false, deferred = false;
   V3 result = V3{0.f, 0.f, 0.f};
   if (leaf >= 0) {
     int prim = __float_as_int(h0.z);
@@ -601,10 +816,19 @@ __device__ __forceinline__ bool shade_slot(const PathState &ps, const RenderPara
       factor = change_ref_ray(lt, sc.shade, sc.mats, atlas, point, normal, dir, ref,
                               p.pdf_weight, rng);
     if (sss_hit) {  // return compute_color_sss(...): the sample IS the point-cloud estimate
-      bool found;
-      V3 col = sss_lookup(BitmapPool{p.sss.bm_pool, p.sss.bm_busy, p.sss.bm_n, p.sss.bm_words},
-                          p.sss.trees[ts.obj], point, m.path_length, found);
-      result = found ? col * mat_diffuse(atlas, m, u, v) : V3{0.f, 0.f, 0.f};
+      if (!ASYNC && p.sss_req) {  // deferred: a whole warp of k_sss_lookup does it
+        const V3 tint = mat_diffuse(atlas, m, u, v);
+        const int r = atomicAdd(p.sss_req_count, 1);
+        p.sss_req[3 * (size_t)r] = make_float4(point.x, point.y, point.z, m.path_length);
+        p.sss_req[3 * (size_t)r + 1] = make_float4(tint.x, tint.y, tint.z, __int_as_float(s));
+        p.sss_req[3 * (size_t)r + 2] = make_float4(__int_as_float(ts.obj), 0.f, 0.f, 0.f);
+        deferred = true;
+      } else {
+        bool found;
+        V3 col = sss_lookup(BitmapPool{p.sss.bm_pool, p.sss.bm_busy, p.sss.bm_n, p.sss.bm_words},
+                            p.sss.trees[ts.obj], point, m.path_length, found);
+        result = found ? col * mat_diffuse(atlas, m, u, v) : V3{0.f, 0.f, 0.f};
+      }
       done = true;
     }
     // material list bookkeeping (pathtracing.h:144-162)
@@ -640,76 +864,8 @@ __device__ __forceinline__ bool shade_slot(const PathState &ps, const RenderPara
     result = bounce < 1 ? sky : acc + mask * sky;
     done = true;
   }
-  if (done) {
-    float4 cl = PS_LD(ps.cm + 2 * (size_t)s);
-    V3 color = V3{cl.x, cl.y, cl.z} + de_nan(result);
-    int k = __float_as_int(cl.w);
-    sidx++;
-    V3 o, d;
-    bool finished = false;
-    if (p.mode == 1) {
-      // do_sss_first_pass: every sample draws a fresh cosine-hemisphere ray at the point
-      if (sidx >= p.sample_size) {
-        finished = true;
-      } else {
-        float4 co = PS_LD(ps.cam + 2 * (size_t)s), cn = PS_LD(ps.cam + 2 * (size_t)s + 1);
-        o = V3{co.x, co.y, co.z};
-        d = generate_dir(V3{0.f, 0.f, 0.f}, V3{cn.x, cn.y, cn.z}, 0, 1.f, rng);
-      }
-    } else if (p.fast_lanes) {
-      // this slot's lane gets samples lane, lane + lanes, ... of the pixel's dof x spp (dof index =
-      // sample / spp); as in the reference a new camera ray is drawn when the dof index changes
-      // and reused otherwise, so one lane reproduces the reference's stream exactly
-      const int lane = p.lane0 + s / p.npix;
-      if (sidx >= (p.total_samples - lane + p.fast_lanes - 1) / p.fast_lanes) {
-        finished = true;
-      } else if ((lane + sidx * p.fast_lanes) / p.sample_size != (lane + (sidx - 1) * p.fast_lanes) / p.sample_size) {
-        int pix = ps.pixel[s];
-        camera_ray(p.cam, pix / p.cam.width + .5f, pix % p.cam.width + .5f, rng, o, d);
-        ps.cam[2 * (size_t)s] = make_float4(o.x, o.y, o.z, 0.f);
-        ps.cam[2 * (size_t)s + 1] = make_float4(d.x, d.y, d.z, 0.f);
-      } else {
-        float4 co = PS_LD(ps.cam + 2 * (size_t)s), cd = PS_LD(ps.cam + 2 * (size_t)s + 1);
-        o = V3{co.x, co.y, co.z};
-        d = V3{cd.x, cd.y, cd.z};
-      }
-    } else if (sidx >= p.sample_size) {
-      sidx = 0;
-      k++;
-      if (k >= p.dof_size) {
-        finished = true;
-      } else {
-        int pix = ps.pixel[s];
-        camera_ray(p.cam, pix / p.cam.width + .5f, pix % p.cam.width + .5f, rng, o, d);
-        ps.cam[2 * (size_t)s] = make_float4(o.x, o.y, o.z, 0.f);
-        ps.cam[2 * (size_t)s + 1] = make_float4(d.x, d.y, d.z, 0.f);
-      }
-    } else {
-      float4 co = PS_LD(ps.cam + 2 * (size_t)s), cd = PS_LD(ps.cam + 2 * (size_t)s + 1);
-      o = V3{co.x, co.y, co.z};
-      d = V3{cd.x, cd.y, cd.z};
-    }
-    if (finished && p.mode == 1) {
-      // color *= (1.0 / sample_size); color *= filter; point -> assign_color(color)
-      float4 pa = __ldg(p.sss.pts + 3 * (size_t)s), pb = __ldg(p.sss.pts + 3 * (size_t)s + 1);
-      V3 out = (color * p.inv_samples) * V3{pa.w, pb.x, pb.y};
-      p.sss.leaf[2 * (size_t)s + 1] = make_float4(out.x, out.y, out.z, 0.f);
-      alive = false;
-    } else if (finished && p.fast_lanes) {
-      p.partial[s] = make_float4(color.x, color.y, color.z, 0.f);
-      alive = false;
-    } else if (finished) {
-      int pix = ps.pixel[s];
-      V3 out = color * p.inv_samples;
-      fb[3 * (size_t)pix] = out.x; fb[3 * (size_t)pix + 1] = out.y; fb[3 * (size_t)pix + 2] = out.z;
-      alive = false;
-    } else {
-      ps.cm[2 * (size_t)s] = make_float4(color.x, color.y, color.z, __int_as_float(k));
-      ps.ma[2 * (size_t)s] = make_float4(1.f, 1.f, 1.f, __int_as_float(0));
-      ps.ma[2 * (size_t)s + 1] = make_float4(0.f, 0.f, 0.f, __int_as_float(sidx));
-      start_sample(ps, s, o, d);
-    }
-  }
+  if (done && !deferred) alive = finish_sample<ASYNC>(ps, p, s, result, rng, fb, sidx);
+  if (deferred) alive = false;  // k_sss_lookup finishes the sample and re-queues the slot
   rng_store_packed(rng, ps.rng, s);
   return alive;
 }
@@ -760,6 +916,40 @@ k_pt_shade(PathState ps, RenderParams p, const int *__restrict__ queue,
   }
 }
 
+
+// ---- deferred SSS lookups (r02) -------------------------------------------------------------------
+// compute_color_sss (pathtracing_sss.h:17-42) as a stage of its own: one WARP per request of the
+// round's request list (sss_lookup_warp), then lane 0 ends the sample exactly as the shade thread
+// would have -- result = found ? colour * tint : 0, finish_sample -- and puts the slot back into
+// the next round's queue.  Runs after k_pt_shade of the round on the group's stream.  The two
+// request counters of a group alternate between rounds; this launch zeroes the other one.
+constexpr int LK_BLOCK = 128;
+__global__ void __launch_bounds__(LK_BLOCK)
+k_sss_lookup(PathState ps, RenderParams p, const int *__restrict__ req_count, int *req_zero,
+             int *next_queue, int *next_count, float *fb) {
+  __shared__ float4 sterm[LK_BLOCK / 32][32];
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  const int warp = (blockIdx.x * LK_BLOCK + threadIdx.x) >> 5, nwarps = (gridDim.x * LK_BLOCK) >> 5;
+  if (blockIdx.x == 0 && threadIdx.x == 0) *req_zero = 0;
+  const int n = *req_count;
+  const BitmapPool pool{p.sss.bm_pool, p.sss.bm_busy, p.sss.bm_n, p.sss.bm_words};
+  for (int r = warp; r < n; r += nwarps) {
+    const float4 q0 = p.sss_req[3 * (size_t)r], q1 = p.sss_req[3 * (size_t)r + 1], q2 = p.sss_req[3 * (size_t)r + 2];
+    const int s = __float_as_int(q1.w), obj = __float_as_int(q2.x);
+    bool found;
+    const V3 col = sss_lookup_warp(pool, p.sss.trees[obj], V3{q0.x, q0.y, q0.z}, q0.w, found, sterm[wib]);
+    if (lane == 0) {
+      const V3 result = found ? col * V3{q1.x, q1.y, q1.z} : V3{0.f, 0.f, 0.f};
+      Rng rng;
+      rng_load_packed<false>(rng, ps.rng, s);
+      const int sidx = __float_as_int(ps.ma[2 * (size_t)s + 1].w);
+      const bool alive = finish_sample<false>(ps, p, s, result, rng, fb, sidx);
+      rng_store_packed(rng, ps.rng, s);
+      if (alive) next_queue[atomicAdd(next_count, 1)] = s;
+    }
+    __syncwarp();
+  }
+}
 
 // ---- streaming pipeline (barrier-free wavefront) ------------------------------------------------
 // The iteration loop above makes a frame a chain of dof x spp x level DEPENDENT rounds of
@@ -1217,16 +1407,41 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
   p.partial = rc->partial;
   p.use_sss = (!sss_pass && have_sss) ? 1 : 0;
   p.sss = sv;
+  p.sss_req = nullptr;
+  p.sss_req_count = nullptr;
 
   BvhDev &mb = ctx->bvh[GPT_BVH_MAIN], &lb = ctx->bvh[GPT_BVH_LIGHT];
   LightTree lt{lb.nodes, lb.tris, lb.parent_leaf, rc->leaf_info, rc->node_info, lb.n};
   TexAtlas atlas{ctx->scene.tex_r, ctx->scene.tex_g, ctx->scene.tex_b};
   cudaStream_t st = ctx->stream;
 
+  static int lookup_grid = 0;  // persistent grid of k_sss_lookup: every resident warp takes requests in turn
+  if (!lookup_grid) {
+    int per_sm = 0, sms = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_sss_lookup, LK_BLOCK, 0);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device);
+    lookup_grid = (sms > 0 ? sms : 148) * (per_sm > 0 ? per_sm : 4);
+  }
+  bool defer_sss = false;  // SSS lookups as a stage of their own (k_sss_lookup), rounds pipeline only
   {
     const char *e = getenv("GPT_SSS_DEBUG_MODE");
     int mode = e ? atoi(e) : 0;
     GPT_CUDA(ctx, cudaMemcpyToSymbolAsync(g_sss_debug_mode, &mode, sizeof(int), 0, cudaMemcpyHostToDevice, st));
+    // GPT_SSS_DEFER=0: the round-1 form, every lookup inside its shade thread (A/B, and what the
+    // debug modes 1 = reference walk / 2 = skip apply to)
+    static int env_defer = -1;
+    if (env_defer < 0) { const char *d = getenv("GPT_SSS_DEFER"); env_defer = d ? atoi(d) : 1; }
+    defer_sss = p.use_sss && mode == 0 && env_defer != 0;
+    if (defer_sss) {
+      if (rc->sss_req_cap < (size_t)n) {
+        gpt_free(ctx, rc->sss_req);
+        rc->sss_req = nullptr;
+        GPT_TRY(gpt_alloc(ctx, &rc->sss_req, 3 * (size_t)n));
+        rc->sss_req_cap = (size_t)n;
+      }
+      if (!rc->sss_req_cnt) GPT_TRY(gpt_alloc(ctx, &rc->sss_req_cnt, (size_t)RenderCtx::MAX_GROUPS * 2));
+      GPT_CUDA(ctx, cudaMemsetAsync(rc->sss_req_cnt, 0, sizeof(int) * RenderCtx::MAX_GROUPS * 2, st));
+    }
   }
   GPT_CUDA(ctx, cudaEventRecord(ctx->ev0, st));
   if (!sss_pass)
@@ -1268,15 +1483,24 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
   GPT_CUDA(ctx, cudaMemsetAsync(ctx->d_counters, 0, 4 * sizeof(unsigned long long), st));
   GPT_CUDA(ctx, cudaMemsetAsync(ctx->d_counters + 5, 0, sizeof(unsigned long long), st));
   GPT_CUDA(ctx, cudaMemsetAsync(ctx->d_counters + 7, 0, sizeof(unsigned long long), st));
+  // GPT_TIMELINE=path (debug): the same three stamps per round, but on each group's own stream
+  // with the groups left as they are, written as "group round t0 t1 t2" in ms since the frame
+  // began -- where a round's 0.2 ms go on a 1/8-frame share
+  static const char *timeline_path = getenv("GPT_TIMELINE");
+  const bool timeline = timeline_path != nullptr && !timing;
+  std::vector<int> stamp_group;
+  cudaStream_t stamp_stream = st;
+  int stamp_g = 0;
   auto stamp = [&]() -> cudaError_t {
-    if (!timing) return cudaSuccess;
+    if (!timing && !timeline) return cudaSuccess;
     if (nev == rc->events.size()) {
       cudaEvent_t e;
       cudaError_t r = cudaEventCreate(&e);
       if (r != cudaSuccess) return r;
       rc->events.push_back(e);
     }
-    return cudaEventRecord(rc->events[nev++], st);
+    if (timeline) stamp_group.push_back(stamp_g);
+    return cudaEventRecord(rc->events[nev++], timeline ? stamp_stream : st);
   };
   // ---- which pipeline ------------------------------------------------------------------------
   int pipeline = ctx->pipeline;
@@ -1516,6 +1740,8 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
       int *next_ray = d_counts + 3;
       const int c0 = q.c, c1 = (q.c + 1) % 3, c2 = (q.c + 2) % 3;
       uint32_t *hist = rc->sort_hist + (size_t)rc->hist_stride * g;
+      stamp_stream = gs;
+      stamp_g = g;
       GPT_CUDA(ctx, stamp());
       {
         QueueSource qs{ps, ps.queue[q.cur] + q.s0, d_counts + c0, ctx->scene.shade,
@@ -1561,6 +1787,10 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
                                     hist, q.active, 7 + loc_bits, &sk, &sorted_slots, d_counts + c0);
       ctx->stream = caller_stream;
       if (rc_err != GPT_OK) break;
+      if (defer_sss) {
+        p.sss_req = rc->sss_req + 3 * (size_t)q.s0;
+        p.sss_req_count = rc->sss_req_cnt + 2 * g + (int)(q.it & 1);
+      }
       k_pt_shade<<<grid, PT_BLOCK, 0, gs>>>(ps, p, sorted_slots, d_counts + c0,
                                            ps.queue[q.cur ^ 1] + q.s0, d_counts + c1,
                                            ctx->scene, atlas, mb.tris, lt, d_fb, d_counts + 4,
@@ -1569,6 +1799,13 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
                                            rc->ccount + (3 * g + c0) * PT_NCLASS,
                                            rc->ccount + (3 * g + c2) * PT_NCLASS);
       GPT_LAUNCH_CHECK(ctx);
+      if (defer_sss) {  // the round's SSS requests: one warp per lookup, then the slots rejoin the queue
+        int *cnt = rc->sss_req_cnt + 2 * g;
+        const int par = (int)(q.it & 1);
+        k_sss_lookup<<<lookup_grid, LK_BLOCK, 0, gs>>>(ps, p, cnt + par, cnt + (par ^ 1),
+                                                     ps.queue[q.cur ^ 1] + q.s0, d_counts + c1, d_fb);
+        GPT_LAUNCH_CHECK(ctx);
+      }
       GPT_CUDA(ctx, stamp());
       q.cur ^= 1;
       q.c = c1;
@@ -1622,6 +1859,16 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
   ctx->stats.shade_events = shades;
   ctx->stats.kernel_launches = ctx->launches;
   ctx->stats.trace_launches = trace_launches;
+  if (timeline) {
+    if (FILE *lf = fopen(timeline_path, "w")) {
+      for (size_t k = 0; k + 2 < nev; k += 3) {
+        float t[3] = {0.f, 0.f, 0.f};
+        for (int j = 0; j < 3; j++) cudaEventElapsedTime(&t[j], ctx->ev0, rc->events[k + j]);
+        fprintf(lf, "%d %zu %.4f %.4f %.4f\n", stamp_group[k], k / 3, t[0], t[1], t[2]);
+      }
+      fclose(lf);
+    }
+  }
   if (timing) {  // three stamps per iteration: before trace, between, after shade
     double tt = 0, ts = 0;
     // GPT_ROUND_LOG=path: one line per round of the stage-timed frame (round, queue length as
@@ -1662,7 +1909,7 @@ void gpt_render_free(gpt_ctx *ctx) {
                ps.queue[0], ps.queue[1], ps.counts, rc->leaf_info, rc->node_info,
                rc->node_energy, rc->lt_flags, rc->rng_init, rc->d_fb, rc->sort_key,
                rc->sort_key_alt, rc->sort_hist, rc->sort_val, rc->sort_val_alt, rc->sq_cells, rc->sq_ctl,
-               rc->classq, rc->ccount, rc->partial};
+               rc->classq, rc->ccount, rc->partial, rc->sss_req, rc->sss_req_cnt};
   for (void *q : p) gpt_free(ctx, q);
   if (rc->h_counts) cudaFreeHost(rc->h_counts);
   if (rc->fork_ev) cudaEventDestroy(rc->fork_ev);
