@@ -637,9 +637,14 @@ def run_sppm(args, rank, world, local_rank):
         dist.all_reduce(tot, op=dist.ReduceOp.SUM)
     total_ms, e2e_ms = t.tolist()
     rays_all, e2e_rays_all = tot.tolist()
-    # the eye pass is replicated on every rank: its rays are counted ONCE, not once per rank
-    rays_all -= (world - 1) * eye_rays * args.steps
-    e2e_rays_all -= (world - 1) * (init_rays + eye_rays * args.steps)
+    # the eye pass is sharded by tiles when N > 1 (each rank counts its own pixels' rays); only
+    # where it is replicated (GPT_SPPM_SHARD_EYE=0, and the init pass always) are its rays
+    # counted ONCE, not once per rank
+    eye_sharded = world > 1 and os.environ.get("GPT_SPPM_SHARD_EYE", "1") != "0"
+    if not eye_sharded:
+        rays_all -= (world - 1) * eye_rays * args.steps
+        e2e_rays_all -= (world - 1) * eye_rays * args.steps
+    e2e_rays_all -= (world - 1) * init_rays
     if rank != 0:
         return
     peaks = {}
@@ -665,7 +670,9 @@ def run_sppm(args, rank, world, local_rank):
             "rays": "closest-hit traversals of the main BVH: photon, eye, direct-light and "
                     "visibility rays (the replicated eye pass counted once)",
             "cache": "L2 flushed (512 MiB write) between timed steps",
-            "sharding": "scene + eye pass replicated, photons split by index range",
+            "sharding": ("scene replicated, photons split by index range; volume photons all-gathered, "
+                         "eye pass sharded by 32x32 tiles, hit points all-reduced (12 floats per pixel)"
+                         if eye_sharded else "scene + eye pass replicated, photons split by index range"),
             "rank0_stage_ms": stage, "photons_stored": [stats["n_surface"], stats["n_volume"]],
             "mean_radius": stats["mean_radius"],
         },

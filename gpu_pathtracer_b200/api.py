@@ -29,7 +29,7 @@ gpt_sppm_init gpt_sppm_pass gpt_sppm_flux_device gpt_sppm_update gpt_sppm_resolv
 gpt_sppm_stats gpt_sppm_export_hit_points gpt_sppm_export_photons gpt_sppm_import_photons
 gpt_sppm_pass_stages gpt_sppm_import_hit_points gpt_sss_export_points gpt_tonemap_u8 gpt_write_ppm_u8
 gpt_save_image gpt_sppm_debug_image gpt_sss_debug_image gpt_stats
-gpt_synchronize gpt_set_profiling gpt_set_wavefront_groups gpt_set_trace_tail gpt_set_trace_leaf_batching gpt_set_pipeline gpt_set_trace_bvh gpt_set_fast_rng_lanes
+gpt_synchronize gpt_set_profiling gpt_set_wavefront_groups gpt_set_trace_tail gpt_set_trace_leaf_batching gpt_set_pipeline gpt_set_trace_bvh gpt_set_fast_rng_lanes gpt_sppm_debug_eye_shard
 gpt_trace_static gpt_comm_unique_id gpt_comm_init gpt_comm_info gpt_comm_destroy gpt_sppm_allreduce gpt_gather_frame
 gpt_scene_files_parse gpt_scene_files_view gpt_scene_files_material_name
 gpt_scene_files_texture_name gpt_scene_files_free gpt_load_scene_files""".split()
@@ -416,6 +416,10 @@ class PathTracer:
         self._check(self.lib.gpt_sppm_pass_stages(self.ctx, C.c_int(pass_idx),
                                                   C.c_int64(photon_begin), C.c_int64(photon_end),
                                                   C.c_int(stages)))
+
+    def sppm_debug_eye_shard(self, rank: int = 0, nranks: int = 1):
+        """Test hook: tile ownership of the sharded eye pass without a communicator."""
+        self._check(self.lib.gpt_sppm_debug_eye_shard(self.ctx, C.c_int(rank), C.c_int(nranks)))
 
     def sppm_import_hit_points(self, loc_radius=None, normal_vradius=None, filter=None):
         arrs = [None if a is None else np.ascontiguousarray(a, dtype=np.float32)

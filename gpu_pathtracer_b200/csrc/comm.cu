@@ -30,6 +30,10 @@ struct NcclApi {
   decltype(&ncclCommDestroy) CommDestroy = nullptr;
   decltype(&ncclAllReduce) AllReduce = nullptr;
   decltype(&ncclReduce) Reduce = nullptr;
+  decltype(&ncclAllGather) AllGather = nullptr;
+  decltype(&ncclBroadcast) Broadcast = nullptr;
+  decltype(&ncclGroupStart) GroupStart = nullptr;
+  decltype(&ncclGroupEnd) GroupEnd = nullptr;
   decltype(&ncclGetErrorString) GetErrorString = nullptr;
   decltype(&ncclGetVersion) GetVersion = nullptr;
   bool ok = false;
@@ -48,8 +52,10 @@ NcclApi &nccl() {
 #define GPT_SYM(f) api.f = reinterpret_cast<decltype(api.f)>(dlsym(api.lib, "nccl" #f))
     GPT_SYM(GetUniqueId); GPT_SYM(CommInitRank); GPT_SYM(CommDestroy); GPT_SYM(AllReduce);
     GPT_SYM(Reduce); GPT_SYM(GetErrorString); GPT_SYM(GetVersion);
+    GPT_SYM(AllGather); GPT_SYM(Broadcast); GPT_SYM(GroupStart); GPT_SYM(GroupEnd);
 #undef GPT_SYM
-    api.ok = api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.AllReduce && api.Reduce;
+    api.ok = api.GetUniqueId && api.CommInitRank && api.CommDestroy && api.AllReduce && api.Reduce &&
+             api.AllGather && api.Broadcast && api.GroupStart && api.GroupEnd;
   });
   return api;
 }
@@ -65,6 +71,51 @@ int nccl_fail(gpt_ctx *ctx, ncclResult_t r, const char *file, int line) {
   } while (0)
 
 }  // namespace
+
+// ---- internal collectives of the sharded SPPM eye pass (sppm.cu; declared in common.cuh) -------
+// In-place SUM all-reduce of n floats on the context's stream.
+int gpt_comm_allreduce_f32(gpt_ctx *ctx, void *d_buf, size_t n) {
+  if (!ctx->nccl_comm || ctx->comm_nranks == 1) return GPT_OK;
+  GPT_NCCL(ctx, nccl().AllReduce(d_buf, d_buf, n, ncclFloat, ncclSum,
+                                 static_cast<ncclComm_t>(ctx->nccl_comm), ctx->stream));
+  return GPT_OK;
+}
+
+// Every rank's `mine` into counts[0 .. nranks) on the HOST (synchronises the stream).
+int gpt_comm_allgather_count(gpt_ctx *ctx, int mine, int *d_scratch /* nranks ints */, int *counts) {
+  const int R = ctx->comm_nranks, r = ctx->comm_rank;
+  GPT_CUDA(ctx, cudaMemcpyAsync(d_scratch + r, &mine, sizeof(int), cudaMemcpyHostToDevice, ctx->stream));
+  GPT_NCCL(ctx, nccl().AllGather(d_scratch + r, d_scratch, 1, ncclInt,
+                                 static_cast<ncclComm_t>(ctx->nccl_comm), ctx->stream));
+  GPT_CUDA(ctx, cudaMemcpyAsync(counts, d_scratch, sizeof(int) * R, cudaMemcpyDeviceToHost, ctx->stream));
+  GPT_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return GPT_OK;
+}
+
+// Variable-length all-gather in rank order: rank r's counts[r] elements of elem_bytes bytes land
+// behind those of the ranks before it in d_recv on every rank (one broadcast per rank, grouped).
+int gpt_comm_allgatherv(gpt_ctx *ctx, const void *d_send, void *d_recv, const int *counts,
+                        size_t elem_bytes) {
+  const int R = ctx->comm_nranks, me = ctx->comm_rank;
+  size_t off = 0, my_off = 0;
+  for (int r = 0; r < me; r++) my_off += (size_t)counts[r] * elem_bytes;
+  if (counts[me] > 0)
+    GPT_CUDA(ctx, cudaMemcpyAsync(static_cast<char *>(d_recv) + my_off, d_send,
+                                  (size_t)counts[me] * elem_bytes, cudaMemcpyDeviceToDevice, ctx->stream));
+  GPT_NCCL(ctx, nccl().GroupStart());
+  for (int r = 0; r < R; r++) {
+    const size_t bytes = (size_t)counts[r] * elem_bytes;
+    if (bytes) {
+      char *at = static_cast<char *>(d_recv) + off;
+      ncclResult_t rc = nccl().Broadcast(at, at, bytes, ncclChar, r,
+                                         static_cast<ncclComm_t>(ctx->nccl_comm), ctx->stream);
+      if (rc != ncclSuccess) { nccl().GroupEnd(); return nccl_fail(ctx, rc, __FILE__, __LINE__); }
+    }
+    off += bytes;
+  }
+  GPT_NCCL(ctx, nccl().GroupEnd());
+  return GPT_OK;
+}
 
 extern "C" {
 

@@ -244,6 +244,11 @@ struct SssView {
   int *bm_busy;
   int bm_n, bm_words;
 };
+// collectives used inside gpt_sppm_pass when a communicator is bound               // comm.cu
+int gpt_comm_allreduce_f32(gpt_ctx *ctx, void *d_buf, size_t n);
+int gpt_comm_allgather_count(gpt_ctx *ctx, int mine, int *d_scratch, int *counts);
+int gpt_comm_allgatherv(gpt_ctx *ctx, const void *d_send, void *d_recv, const int *counts,
+                        size_t elem_bytes);
 int gpt_sss_prepare(gpt_ctx *ctx);                                   // sss.cu
 bool gpt_sss_view(gpt_ctx *ctx, SssView *out, bool *first_pass_done);  // sss.cu
 void gpt_sss_mark_first_pass_done(gpt_ctx *ctx);                     // sss.cu

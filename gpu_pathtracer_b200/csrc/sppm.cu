@@ -800,7 +800,7 @@ __global__ void __launch_bounds__(256)
 k_photon_boxes(const float4 *__restrict__ raw, const int *__restrict__ list, int n, float *aabb) {
   int j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= n) return;
-  float4 p0 = __ldg(raw + 3 * (size_t)__ldg(list + j));
+  float4 p0 = __ldg(raw + 3 * (size_t)(list ? __ldg(list + j) : j));  // list == nullptr: raw is the list
   float *o = aabb + 6 * (size_t)j;
   o[0] = p0.x - GPT_SMALL; o[1] = p0.x + GPT_SMALL;
   o[2] = p0.y - GPT_SMALL; o[3] = p0.y + GPT_SMALL;
@@ -813,7 +813,8 @@ k_pack_photons(const float4 *__restrict__ raw, const int *__restrict__ list,
                const int *__restrict__ sorted_prim, int n, float4 *leaf) {
   int j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= n) return;
-  int src = __ldg(list + (sorted_prim ? __ldg(sorted_prim + j) : j));
+  int at = sorted_prim ? __ldg(sorted_prim + j) : j;
+  int src = list ? __ldg(list + at) : at;
   for (int k = 0; k < 3; k++) leaf[3 * (size_t)j + k] = __ldg(raw + 3 * (size_t)src + k);
 }
 
@@ -866,6 +867,13 @@ struct EyeParams {
   int init;
   float radius_multiplier;
   PhotonTree vol;
+  // r02 sharded eye pass (multi-GPU, SURVEY 8(e) second variant): this rank traces the eye paths
+  // of its own 32x32 tiles only (the path tracer's round-robin deal) and writes what the pass
+  // produces -- location, normal, filter, this pass's direct light -- as 12 floats per pixel into
+  // `xc`, zeros for the other ranks' pixels, so ONE sum all-reduce gives every rank every hit
+  // point (x + 0 + ... + 0 = x exactly, INFINITY included); k_eye_unpack then applies it.
+  int rank, nranks;
+  float4 *xc;  // 3 float4 per pixel: (loc, nrm.x) (nrm.yz, filter.xy) (filter.z, direct.xyz); nullptr = unsharded
 };
 
 struct HitPoints {
@@ -1073,7 +1081,17 @@ k_eye_pass(SppmScene S, EyeParams ep, HitPoints hp, const uint32_t *__restrict__
   __shared__ int stack_mem[SP_STACK * SP_BLOCK];
   int pix = blockIdx.x * blockDim.x + threadIdx.x;
   Tracer T{stack_mem + threadIdx.x, 0u};
-  if (pix < hp.P) {
+  bool mine = pix < hp.P;
+  if (mine && ep.xc) {
+    const int row = pix / ep.cam.width, col = pix % ep.cam.width;
+    const int tiles_x = (ep.cam.width + 31) / 32;
+    mine = ((row / 32) * tiles_x + col / 32) % ep.nranks == ep.rank;
+    if (!mine) {  // another rank's pixel: zeros into the exchange buffer and the volume term
+      for (int k = 0; k < 3; k++) ep.xc[3 * (size_t)pix + k] = make_float4(0.f, 0.f, 0.f, 0.f);
+      hp.flux[(size_t)hp.P + pix] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  }
+  if (mine) {
     int row = pix / ep.cam.width, col = pix % ep.cam.width;
     Rng rng;
     rng_load(rng, rng_init, pix, hp.P);
@@ -1117,6 +1135,13 @@ k_eye_pass(SppmScene S, EyeParams ep, HitPoints hp, const uint32_t *__restrict__
       }
       radius *= ep.radius_multiplier;
     }
+    if (ep.xc) {  // sharded: everything the pass produces goes through the exchange buffer
+      V3 loc = V3{INFINITY, INFINITY, INFINITY}, nrm = V3{0.f, 0.f, 1.f}, dn = V3{0.f, 0.f, 0.f};
+      if (er.hit && er.diffuse) { loc = er.point; nrm = er.normal; dn = de_nan(direct); }
+      ep.xc[3 * (size_t)pix] = make_float4(loc.x, loc.y, loc.z, nrm.x);
+      ep.xc[3 * (size_t)pix + 1] = make_float4(nrm.y, nrm.z, filter.x, filter.y);
+      ep.xc[3 * (size_t)pix + 2] = make_float4(filter.z, dn.x, dn.y, dn.z);
+    } else {
     if (er.hit && er.diffuse) {
       hp.loc[pix] = make_float4(er.point.x, er.point.y, er.point.z, radius);
       hp.nrm[pix] = make_float4(er.normal.x, er.normal.y, er.normal.z, vol_radius);
@@ -1128,11 +1153,28 @@ k_eye_pass(SppmScene S, EyeParams ep, HitPoints hp, const uint32_t *__restrict__
       hp.nrm[pix] = make_float4(0.f, 0.f, 1.f, vol_radius);
     }
     hp.filter[pix] = make_float4(filter.x, filter.y, filter.z, 0.f);
+    }
     if (!ep.init) hp.flux[(size_t)hp.P + pix] = make_float4(lm.x, lm.y, lm.z, 0.f);
   }
   unsigned tot = T.nrays;
   for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
   if ((threadIdx.x & 31) == 0 && tot) atomicAdd(S.counters + 2, (unsigned long long)tot);
+}
+
+// The sharded eye pass's results, after the all-reduce, into the hit points: exactly the stores of
+// the unsharded kernel (radii stay, direct light accumulates; `0 + d` for a miss is what the
+// unsharded pass's skipped add leaves, d being finite).
+__global__ void __launch_bounds__(256) k_eye_unpack(HitPoints hp, const float4 *__restrict__ xc) {
+  int pix = blockIdx.x * blockDim.x + threadIdx.x;
+  if (pix >= hp.P) return;
+  const float4 a = xc[3 * (size_t)pix], b = xc[3 * (size_t)pix + 1], c = xc[3 * (size_t)pix + 2];
+  hp.loc[pix] = make_float4(a.x, a.y, a.z, hp.loc[pix].w);
+  hp.nrm[pix] = make_float4(a.w, b.x, b.y, hp.nrm[pix].w);
+  hp.filter[pix] = make_float4(b.z, b.w, c.x, 0.f);
+  if (!(a.x == INFINITY)) {  // er.hit && er.diffuse on the owner
+    const float4 dr = hp.direct[pix];
+    hp.direct[pix] = make_float4(dr.x + c.y, dr.y + c.z, dr.z + c.w, 0.f);
+  }
 }
 
 // compute_average_radius (ray_tracing_pass.h:416-436): serial fp32 sum in pixel order, then
@@ -1356,7 +1398,31 @@ struct SppmCtx {
   int light_n = 0;
   uint64_t light_epoch = 0;  // ctx->build_epoch the light-tree arrays were made for
   uint64_t rays_total = 0;
+  // r02 sharded eye pass: exchange buffer, the volume photons of ALL ranks (compaction order of
+  // the whole pass = rank order, ranks own consecutive photon ranges), their tree's buffers
+  float4 *xc = nullptr;
+  float4 *vol_send = nullptr, *vol_all = nullptr, *leaf_vol_all = nullptr, *spheres_all = nullptr;
+  float *aabb_vol = nullptr;
+  int *d_rank_counts = nullptr;
+  int vol_send_cap = 0, vol_all_cap = 0;
+  bool vol_is_global = false;   // this pass's volume tree holds every rank's photons
+  int dbg_rank = 0, dbg_nranks = 1;  // gpt_sppm_debug_eye_shard: ownership without a communicator (tests)
 };
+
+// The eye pass is sharded when a communicator with > 1 ranks is bound (GPT_SPPM_SHARD_EYE=0 keeps
+// the round-1 replicated form), or when a test asked for it on one device.
+static bool eye_sharded(const gpt_ctx *ctx, const SppmCtx *sx, int *rank, int *nranks, bool *comm) {
+  static int env = -1;
+  if (env < 0) { const char *e = getenv("GPT_SPPM_SHARD_EYE"); env = e ? atoi(e) : 1; }
+  *comm = false;
+  if (ctx->nccl_comm && ctx->comm_nranks > 1 && env != 0) {
+    *rank = ctx->comm_rank; *nranks = ctx->comm_nranks; *comm = true;
+    return true;
+  }
+  if (sx->dbg_nranks > 1) { *rank = sx->dbg_rank; *nranks = sx->dbg_nranks; return true; }
+  *rank = 0; *nranks = 1;
+  return false;
+}
 
 SppmCtx *sx_of(gpt_ctx *ctx) {
   if (!ctx->sppm_state) ctx->sppm_state = new SppmCtx();
@@ -1481,9 +1547,24 @@ static int eye_pass(gpt_ctx *ctx, SppmCtx *sx, const SppmScene &S, int pass, boo
   ep.pass = pass;
   ep.init = init ? 1 : 0;
   ep.radius_multiplier = ctx->params.ppm_radius_scaling_factor;
-  ep.vol = PhotonTree{sx->vol_bvh.nodes, sx->spheres, sx->leaf_vol, init ? 0 : sx->n_vol};
+  ep.vol = sx->vol_is_global
+               ? PhotonTree{sx->vol_bvh.nodes, sx->spheres_all, sx->leaf_vol_all, init ? 0 : sx->n_vol}
+               : PhotonTree{sx->vol_bvh.nodes, sx->spheres, sx->leaf_vol, init ? 0 : sx->n_vol};
+  bool comm = false;
+  const bool sharded = !init && eye_sharded(ctx, sx, &ep.rank, &ep.nranks, &comm);
+  if (!sharded) { ep.rank = 0; ep.nranks = 1; }
+  ep.xc = nullptr;
+  if (sharded) {
+    if (!sx->xc) GPT_TRY(gpt_alloc(ctx, &sx->xc, 3 * (size_t)sx->P));
+    ep.xc = sx->xc;
+  }
   k_eye_pass<<<(sx->P + SP_BLOCK - 1) / SP_BLOCK, SP_BLOCK, 0, ctx->stream>>>(S, ep, sx->hp, sx->rng_pix);
   GPT_LAUNCH_CHECK(ctx);
+  if (sharded) {
+    if (comm) GPT_TRY(gpt_comm_allreduce_f32(ctx, sx->xc, 12 * (size_t)sx->P));
+    k_eye_unpack<<<(sx->P + 255) / 256, 256, 0, ctx->stream>>>(sx->hp, sx->xc);
+    GPT_LAUNCH_CHECK(ctx);
+  }
   return GPT_OK;
 }
 
@@ -1499,7 +1580,8 @@ void gpt_sppm_free(gpt_ctx *ctx) {
                sx->node_energy, sx->lt_flags, sx->wave.state, sx->wave.rays, sx->wave.hits,
                sx->wave.queue[0], sx->wave.queue[1], sx->wave.iqueue[0], sx->wave.iqueue[1],
                sx->wave.counts, sx->wave.key,
-               sx->wave.key_alt, sx->wave.val, sx->wave.val_alt};
+               sx->wave.key_alt, sx->wave.val, sx->wave.val_alt, sx->xc, sx->vol_send, sx->vol_all,
+               sx->leaf_vol_all, sx->spheres_all, sx->aabb_vol, sx->d_rank_counts};
   for (void *q : p) gpt_free(ctx, q);
   gpt_lbvh_free(ctx, sx->surf_bvh);
   gpt_lbvh_free(ctx, sx->vol_bvh);
@@ -1675,6 +1757,57 @@ static int sppm_build_trees(gpt_ctx *ctx, SppmCtx *sx, int count) {
                                                    sx->leaf_surf);
     GPT_LAUNCH_CHECK(ctx);
   }
+  sx->vol_is_global = false;
+  {
+    int rank = 0, nranks = 1;
+    bool comm = false;
+    if (eye_sharded(ctx, sx, &rank, &nranks, &comm) && comm) {
+      // every rank needs every volume photon: its eye paths gather against the WHOLE pass's
+      // sphere tree, which also makes the (prefix weighted, order dependent) volume term the
+      // single-GPU one.  Counts first (host), then a variable-length all-gather in rank order.
+      const int mine = sx->n_vol;
+      if (mine > sx->vol_send_cap) {
+        GPT_TRY(gpt_alloc(ctx, &sx->vol_send, 3 * (size_t)mine));
+        sx->vol_send_cap = mine;
+      }
+      if (mine > 0) {
+        k_pack_photons<<<(mine + 255) / 256, 256, 0, st>>>(sx->raw, vol_list, nullptr, mine, sx->vol_send);
+        GPT_LAUNCH_CHECK(ctx);
+      }
+      if (!sx->d_rank_counts) GPT_TRY(gpt_alloc(ctx, &sx->d_rank_counts, (size_t)nranks));
+      std::vector<int> counts((size_t)nranks, 0);
+      GPT_TRY(gpt_comm_allgather_count(ctx, mine, sx->d_rank_counts, counts.data()));
+      long long total = 0;
+      for (int c : counts) total += c;
+      if (total > 0x7fffffff) return gpt_fail(ctx, GPT_E_INVALID, "more than 2^31 volume photons in a pass", __FILE__, __LINE__);
+      if ((int)total > sx->vol_all_cap) {
+        const size_t N = (size_t)total;
+        GPT_TRY(gpt_alloc(ctx, &sx->vol_all, 3 * N));
+        GPT_TRY(gpt_alloc(ctx, &sx->leaf_vol_all, 3 * N));
+        GPT_TRY(gpt_alloc(ctx, &sx->spheres_all, 2 * N));
+        GPT_TRY(gpt_alloc(ctx, &sx->aabb_vol, 6 * N));
+        sx->vol_all_cap = (int)total;
+      }
+      GPT_TRY(gpt_comm_allgatherv(ctx, sx->vol_send, sx->vol_all, counts.data(), 3 * sizeof(float4)));
+      sx->n_vol = (int)total;
+      sx->vol_is_global = true;
+      if (sx->n_vol >= 2) {
+        const int n = sx->n_vol;
+        k_photon_boxes<<<(n + 255) / 256, 256, 0, st>>>(sx->vol_all, nullptr, n, sx->aabb_vol);
+        GPT_LAUNCH_CHECK(ctx);
+        GPT_TRY(gpt_lbvh_build_boxes(ctx, sx->vol_bvh, sx->aabb_vol, nullptr, n, false));
+        k_pack_photons<<<(n + 255) / 256, 256, 0, st>>>(sx->vol_all, nullptr, sx->vol_bvh.sorted_prim, n,
+                                                       sx->leaf_vol_all);
+        GPT_LAUNCH_CHECK(ctx);
+        GPT_CUDA(ctx, cudaMemsetAsync(sx->vol_bvh.flags, 0, sizeof(int) * (size_t)n, st));
+        k_sphere_refit<<<(n + 255) / 256, 256, 0, st>>>(sx->leaf_vol_all, n, sx->vol_bvh.nodes,
+                                                       sx->vol_bvh.parent_leaf, sx->vol_bvh.flags,
+                                                       sx->spheres_all);
+        GPT_LAUNCH_CHECK(ctx);
+      }
+      return GPT_OK;
+    }
+  }
   if (sx->n_vol >= 2) {
     int n = sx->n_vol;
     k_photon_boxes<<<(n + 255) / 256, 256, 0, st>>>(sx->raw, vol_list, n, sx->aabb);
@@ -1740,6 +1873,17 @@ int gpt_sppm_pass_stages(gpt_ctx *ctx, int pass, int64_t photon_begin, int64_t p
   GPT_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
   ctx->stats.render_ms = ms;
   ctx->stats.kernel_launches = ctx->launches;
+  return GPT_OK;
+}
+
+// Test hook: shard the eye pass as rank `rank` of `nranks` WITHOUT a communicator (no exchange:
+// the other ranks' pixels come out zero), so one device can check that the shards tile the
+// unsharded pass.  nranks <= 1 switches it off.
+int gpt_sppm_debug_eye_shard(gpt_ctx *ctx, int rank, int nranks) {
+  if (!ctx || rank < 0 || (nranks > 1 && rank >= nranks)) return GPT_E_INVALID;
+  SppmCtx *sx = sx_of(ctx);
+  sx->dbg_rank = nranks > 1 ? rank : 0;
+  sx->dbg_nranks = nranks > 1 ? nranks : 1;
   return GPT_OK;
 }
 
@@ -1889,7 +2033,7 @@ int gpt_sppm_debug_image(gpt_ctx *ctx, int which, float *out_rgb) {
   if (which == 0)
     return gpt_splat_device(ctx, reinterpret_cast<const float *>(sx->hp.loc), 4,
                             reinterpret_cast<const float *>(sx->hp.filter), 4, sx->P, nullptr, out_rgb);
-  const float4 *leaf = which == 1 ? sx->leaf_surf : sx->leaf_vol;
+  const float4 *leaf = which == 1 ? sx->leaf_surf : (sx->vol_is_global ? sx->leaf_vol_all : sx->leaf_vol);
   int n = which == 1 ? sx->n_surf : sx->n_vol;
   if (n < 2) n = 0;  // no tree was built: nothing recorded
   // the reference splats its photon lists BEFORE it sorts them for the trees (src/main.cu:1534,

@@ -341,6 +341,16 @@ int gpt_sppm_pass_stages(gpt_ctx *ctx, int pass, int64_t photon_begin, int64_t p
 /* parity import: replace the photons of the current pass by n caller-supplied ones (kind +
  * 12 floats each, as exported) and build both photon trees from them. */
 int gpt_sppm_import_photons(gpt_ctx *ctx, const int32_t *kind, const float *rec12, int64_t n);
+/* Multi-GPU SPPM, r02 (second variant).  With a communicator of > 1 ranks bound
+ * (gpt_comm_init), gpt_sppm_pass shards the eye pass too: the volume photons of all ranks are
+ * all-gathered in photon order (so every rank builds the WHOLE pass's sphere tree and the
+ * reference's prefix-weighted volume term, bvh_traversal_photon.h:62-78, is the single-GPU one),
+ * each rank traces the eye paths of its own 32x32 tiles only (ray_tracing_pass.h:490-594) and
+ * one sum all-reduce of 12 floats per pixel hands every rank every hit point; the surface
+ * gather and gpt_sppm_allreduce / gpt_sppm_update are unchanged.  Environment
+ * GPT_SPPM_SHARD_EYE=0 keeps the replicated eye pass.  This test hook applies the tile
+ * ownership WITHOUT a communicator (other ranks' pixels come out zero); nranks <= 1 = off. */
+int gpt_sppm_debug_eye_shard(gpt_ctx *ctx, int rank, int nranks);
 /* parity import: overwrite hit-point (location, surface radius) / (normal, volume radius) /
  * filter with caller-supplied P x 4 host floats (NULL = keep). */
 int gpt_sppm_import_hit_points(gpt_ctx *ctx, const float *loc_radius,

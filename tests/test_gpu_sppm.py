@@ -178,6 +178,44 @@ def test_multi_rank_photon_split_sums_to_single_rank():
     assert np.allclose(got[:, :3], want[:, :3], rtol=1e-4, atol=1e-4)
 
 
+def test_sharded_eye_pass_tiles_the_unsharded_pass():
+    """r02, SURVEY 8(e) second variant: the eye pass of rank r of 2 (tile ownership only, no
+    communicator: gpt_sppm_debug_eye_shard) leaves exactly the unsharded pass's hit points on its
+    own 32x32 tiles and zeros elsewhere, so the sum of the shards -- what the all-reduce of the
+    real thing computes -- IS the unsharded pass, bit for bit, volume term included."""
+    from gpu_pathtracer_b200.api import PathTracer
+    sc = _scene(width=128, height=96)
+    W, H = sc.camera["width"], sc.camera["height"]
+
+    def run(rank, nranks):
+        pt = PathTracer(sc, device=0)
+        pt.build()
+        pt.sppm_init()
+        pt.sppm_pass_stages(0, 1)      # photon trace + trees: identical on every context
+        pt.sppm_debug_eye_shard(rank, nranks)
+        pt.sppm_pass_stages(0, 2)      # the eye pass
+        return pt.sppm_export_hit_points()
+
+    base = run(0, 1)
+    shards = [run(r, 2) for r in range(2)]
+    rows, cols = np.divmod(np.arange(W * H), W)
+    owner = ((rows // 32) * ((W + 31) // 32) + cols // 32) % 2
+    keys = (("loc_radius", 3), ("normal_vradius", 3), ("filter", 3), ("lm", 3))
+    for r, sh in enumerate(shards):
+        mine = owner == r
+        assert mine.sum() > 1000
+        for k, c in keys:
+            assert np.array_equal(sh[k][mine, :c].view(np.uint32), base[k][mine, :c].view(np.uint32)), (r, k)
+            assert not sh[k][~mine, :c].any(), (r, k)
+        # radii are replicated state, not part of the exchange
+        assert np.array_equal(sh["loc_radius"][:, 3], base["loc_radius"][:, 3])
+        assert np.array_equal(sh["direct"][mine].view(np.uint32), base["direct"][mine].view(np.uint32))
+    for k, c in keys:
+        total = shards[0][k][:, :c] + shards[1][k][:, :c]
+        assert np.array_equal(total.view(np.uint32), base[k][:, :c].view(np.uint32)), k
+    assert np.isinf(base["loc_radius"][:, 0]).any() and (base["lm"][:, :3] > 0).any()
+
+
 def test_wavefront_photon_pass_equals_the_megakernel(monkeypatch):
     """The photon pass runs as a wavefront (k_photon_step / k_ph_trace / coherence sort); the
     one-thread-per-photon megakernel it replaced is kept as a cross-check.  Same photons, bit for
