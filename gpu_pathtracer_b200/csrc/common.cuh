@@ -49,7 +49,8 @@ struct BvhDev {
   int *vals_alt = nullptr;
   uint32_t *block_hist = nullptr;
   int hist_capacity = 0;
-  int *flags = nullptr;         // n-1 arrival counters for the refit
+  int *flags = nullptr;         // per internal node: last leaf of its range (k_emit -> k_node_boxes); arrival counters of the chain refit
+  float *levels = nullptr;      // 4-ary hierarchy of partial box unions over the sorted leaves (lbvh.cu k_leaf_levels)
   // 4-wide quantised tree collapsed from the LBVH (wide.cu, trace_wide.cuh)
   uint4 *wq = nullptr;          // 3 x 16 bytes per wide node, node 0 = root
   float4 *wtris = nullptr;      // the 48-byte trace triangles once more, in wide-tree leaf order; t2.w = LBVH leaf

@@ -247,7 +247,7 @@ __device__ __forceinline__ int delta(const uint32_t *__restrict__ keys, int n, i
 // doubling + binary searches of Karras 2012; same direction rule (d1 < d2 -> -1), same
 // delta_min, same unique split, same child / parent assignment.
 __global__ void __launch_bounds__(256)
-k_emit(const uint32_t *__restrict__ keys, int n, float4 *nodes, int *parent_leaf) {
+k_emit(const uint32_t *__restrict__ keys, int n, float4 *nodes, int *parent_leaf, int *range_last) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n - 1) return;
   uint32_t ki = __ldg(keys + i);
@@ -273,6 +273,7 @@ k_emit(const uint32_t *__restrict__ keys, int n, float4 *nodes, int *parent_leaf
   q3[0] = left;
   q3[1] = right;
   q3[3] = first;
+  range_last[i] = last;  // for k_node_boxes
   if (i == 0) q3[2] = -1;
   if (left >= 0) reinterpret_cast<int *>(nodes + 4 * (size_t)left + 3)[2] = 2 * i;
   else parent_leaf[~left] = 2 * i;
@@ -325,6 +326,145 @@ k_refit(const float *__restrict__ aabb, const int *__restrict__ prim_list,
   }
 }
 
+
+// ---- node boxes without the bottom-up chain (r02) ---------------------------------------------
+// k_refit above is a chain: the box of a node needs both children, so the top ~40 levels of a
+// 1 M-leaf tree are ~40 dependent (fence, atomic, load) hand-overs, 155 us of a 0.37 ms build.
+// An LBVH node covers a contiguous range [first, last] of the SORTED leaves, and a box is a
+// min / max -- associative, commutative, exact -- so the box of a range can be taken from ANY
+// set of partial unions that tile it.  k_leaf_levels builds a 4-ary hierarchy of partial unions
+// over the sorted leaves (level k = unions of 4^k consecutive leaves; levels 0..5 inside one
+// 1024-leaf block with shuffles, k_top_levels adds the few entries above), and k_node_boxes
+// gives every internal node its two child boxes with the usual bottom-up range query (at most
+// 3 + 3 entries per level): every node independent, no atomics, no fences.  Same boxes bit for
+// bit (tests/test_gpu_build_trace.py::test_bvh_bit_exact compares them with the reference's).
+constexpr int LV_BLOCK = 1024;  // leaves per block of k_leaf_levels = 4^5
+constexpr int LV_MAX = 17;      // 4^16 > 2^31 leaves
+struct Levels {
+  float *base;           // all levels back to back, 6 floats per entry: xmin xmax ymin ymax zmin zmax
+  long long off[LV_MAX]; // first float of level k
+  int count[LV_MAX];     // entries of level k = ceil(n / 4^k)
+  int nlevels;           // levels 0 .. nlevels - 1; the last one has a single entry
+};
+struct Box6 { float v[6]; };
+__device__ __forceinline__ Box6 box_empty() {
+  Box6 b;
+#pragma unroll
+  for (int k = 0; k < 3; k++) { b.v[2 * k] = INFINITY; b.v[2 * k + 1] = -INFINITY; }
+  return b;
+}
+__device__ __forceinline__ void box_add(Box6 &a, const float *p) {
+  const float2 x = *reinterpret_cast<const float2 *>(p), y = *reinterpret_cast<const float2 *>(p + 2),
+               z = *reinterpret_cast<const float2 *>(p + 4);
+  a.v[0] = fminf(a.v[0], x.x); a.v[1] = fmaxf(a.v[1], x.y);
+  a.v[2] = fminf(a.v[2], y.x); a.v[3] = fmaxf(a.v[3], y.y);
+  a.v[4] = fminf(a.v[4], z.x); a.v[5] = fmaxf(a.v[5], z.y);
+}
+__device__ __forceinline__ void box_store(float *p, const Box6 &a) {
+  reinterpret_cast<float2 *>(p)[0] = make_float2(a.v[0], a.v[1]);
+  reinterpret_cast<float2 *>(p)[1] = make_float2(a.v[2], a.v[3]);
+  reinterpret_cast<float2 *>(p)[2] = make_float2(a.v[4], a.v[5]);
+}
+__device__ __forceinline__ void box_shfl_xor(Box6 &a, int m) {
+#pragma unroll
+  for (int k = 0; k < 3; k++) {
+    a.v[2 * k] = fminf(a.v[2 * k], __shfl_xor_sync(0xffffffffu, a.v[2 * k], m));
+    a.v[2 * k + 1] = fmaxf(a.v[2 * k + 1], __shfl_xor_sync(0xffffffffu, a.v[2 * k + 1], m));
+  }
+}
+
+// One thread per sorted leaf: its box into level 0, the unions of 4 / 16 / 64 / 256 / 1024
+// leaves into levels 1..5; fused with the pack of the 48-byte trace triangle (TRIS).
+template <bool TRIS>
+__global__ void __launch_bounds__(LV_BLOCK)
+k_leaf_levels(const float *__restrict__ aabb, const int *__restrict__ prim_list,
+              const int *__restrict__ sorted_prim, int n, Levels lv, SceneDev s, float4 *tris) {
+  __shared__ float wbox[LV_BLOCK / 32][6];
+  const int j = blockIdx.x * LV_BLOCK + threadIdx.x, lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  Box6 b = box_empty();
+  if (j < n) {
+    const int sp = __ldg(sorted_prim + j);
+    const int p = prim_list ? __ldg(prim_list + sp) : sp;
+    box_add(b, aabb + 6 * (size_t)p);
+    box_store(lv.base + lv.off[0] + 6 * (size_t)j, b);
+    if (TRIS) {
+      const int a = __ldg(s.p1 + p), bb = __ldg(s.p2 + p), c = __ldg(s.p3 + p);
+      float4 *t = tris + 3 * (size_t)j;
+      t[0] = make_float4(__ldg(s.x + a), __ldg(s.y + a), __ldg(s.z + a), __ldg(s.x + bb));
+      t[1] = make_float4(__ldg(s.y + bb), __ldg(s.z + bb), __ldg(s.x + c), __ldg(s.y + c));
+      t[2] = make_float4(__ldg(s.z + c), __ldg(s.tolerance + p), __int_as_float(p), 0.f);
+    }
+  }
+  box_shfl_xor(b, 1); box_shfl_xor(b, 2);
+  if ((lane & 3) == 0 && j < n && lv.nlevels > 1) box_store(lv.base + lv.off[1] + 6 * (size_t)(j >> 2), b);
+  box_shfl_xor(b, 4); box_shfl_xor(b, 8);
+  if ((lane & 15) == 0 && j < n && lv.nlevels > 2) box_store(lv.base + lv.off[2] + 6 * (size_t)(j >> 4), b);
+  box_shfl_xor(b, 16);
+  if (lane == 0) {
+#pragma unroll
+    for (int k = 0; k < 6; k++) wbox[w][k] = b.v[k];
+  }
+  __syncthreads();
+  // levels 3 (2 warps), 4 (8 warps), 5 (the block): a handful of entries, thread t takes one
+  const int t = threadIdx.x;
+  const int base_leaf = blockIdx.x * LV_BLOCK;
+  if (t < 16 + 4 + 1) {
+    const int level = t < 16 ? 3 : (t < 20 ? 4 : 5);
+    const int e = t < 16 ? t : (t < 20 ? t - 16 : 0);           // entry inside the block
+    const int span = level == 3 ? 2 : (level == 4 ? 8 : 32);    // warps per entry
+    const int first_leaf = base_leaf + e * span * 32;
+    if (first_leaf < n && level < lv.nlevels) {
+      Box6 u = box_empty();
+      for (int k = 0; k < span; k++) box_add(u, wbox[e * span + k]);
+      box_store(lv.base + lv.off[level] + 6 * (size_t)(first_leaf >> (2 * level)), u);
+    }
+  }
+}
+
+// levels 6 and up: a few hundred entries at most, one block, level by level
+__global__ void __launch_bounds__(1024) k_top_levels(Levels lv) {
+  for (int level = 6; level < lv.nlevels; level++) {
+    const float *below = lv.base + lv.off[level - 1];
+    float *mine = lv.base + lv.off[level];
+    const int nb = lv.count[level - 1];
+    for (int e = threadIdx.x; e < lv.count[level]; e += blockDim.x) {
+      Box6 u = box_empty();
+      for (int k = 0; k < 4; k++)
+        if (4 * e + k < nb) box_add(u, below + 6 * (size_t)(4 * e + k));
+      box_store(mine + 6 * (size_t)e, u);
+    }
+    __syncthreads();
+  }
+}
+
+// union of the sorted leaves [a, b]: bottom-up walk of the 4-ary hierarchy
+__device__ __forceinline__ Box6 range_box(const Levels &lv, int a, int b) {
+  Box6 u = box_empty();
+  int lo = a, hi = b + 1, level = 0;
+  while (lo < hi) {
+    const float *L = lv.base + lv.off[level];
+    while (lo < hi && (lo & 3)) { box_add(u, L + 6 * (size_t)lo); lo++; }
+    while (lo < hi && (hi & 3)) { hi--; box_add(u, L + 6 * (size_t)hi); }
+    lo >>= 2; hi >>= 2; level++;
+  }
+  return u;
+}
+
+// compute_node_bounding_boxes (bvh_building.h:221-262) for every internal node at once: its
+// children cover [first, gamma] and [gamma + 1, last]
+__global__ void __launch_bounds__(256)
+k_node_boxes(float4 *nodes, const int *__restrict__ range_last, int n, Levels lv) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n - 1) return;
+  const int4 q3 = *reinterpret_cast<const int4 *>(nodes + 4 * (size_t)i + 3);
+  const int first = q3.w, last = __ldg(range_last + i);
+  const int gamma = q3.x >= 0 ? q3.x : ~q3.x;
+  const Box6 l = range_box(lv, first, gamma), r = range_box(lv, gamma + 1, last);
+  float4 *q = nodes + 4 * (size_t)i;
+  q[0] = make_float4(l.v[0], l.v[1], l.v[2], l.v[3]);
+  q[1] = make_float4(l.v[4], l.v[5], r.v[0], r.v[1]);
+  q[2] = make_float4(r.v[2], r.v[3], r.v[4], r.v[5]);
+}
 
 // flagged-subset compaction in index order (collect_*_geom, 1 thread serial in the reference:
 // transparent_geom_operations.h:28-40, pathtracing_target_geom_operations.h:36-48).
@@ -420,7 +560,7 @@ int gpt_radix_sort_pairs(gpt_ctx *ctx, uint32_t *keys, int *vals, uint32_t *keys
 void gpt_lbvh_free(gpt_ctx *ctx, BvhDev &b) {
   gpt_free(ctx, b.nodes); gpt_free(ctx, b.tris); gpt_free(ctx, b.parent_leaf); gpt_free(ctx, b.morton);
   gpt_free(ctx, b.sorted_prim); gpt_free(ctx, b.prim_list); gpt_free(ctx, b.world_enc);
-  gpt_free(ctx, b.keys_alt); gpt_free(ctx, b.vals_alt); gpt_free(ctx, b.block_hist); gpt_free(ctx, b.flags);
+  gpt_free(ctx, b.keys_alt); gpt_free(ctx, b.vals_alt); gpt_free(ctx, b.block_hist); gpt_free(ctx, b.flags); gpt_free(ctx, b.levels);
   gpt_free(ctx, b.wq); gpt_free(ctx, b.wtris); gpt_free(ctx, b.wmeta);
   b = BvhDev();
 }
@@ -442,6 +582,7 @@ static int lbvh_reserve(gpt_ctx *ctx, BvhDev &b, int n, bool with_tris) {
   GPT_TRY(gpt_alloc(ctx, &b.vals_alt, N));
   GPT_TRY(gpt_alloc(ctx, &b.block_hist, (size_t)gpt_radix_hist_entries(n)));
   GPT_TRY(gpt_alloc(ctx, &b.flags, N));
+  GPT_TRY(gpt_alloc(ctx, &b.levels, 8 * N + 6 * (size_t)LV_MAX));  // 6 N (1 + 1/4 + 1/16 + ...) floats, rounded up per level
   GPT_TRY(gpt_alloc(ctx, &b.world_enc, (size_t)8));
   b.capacity = n;
   return GPT_OK;
@@ -486,15 +627,44 @@ int gpt_lbvh_build_boxes(gpt_ctx *ctx, BvhDev &b, const float *aabb, const int *
   GPT_TRY(gpt_radix_sort_pairs(ctx, b.morton, b.sorted_prim, b.keys_alt, b.vals_alt,
                                b.block_hist, n, 30, &ko, &vo));
   if (ko != b.morton) return gpt_fail(ctx, GPT_E_INVALID, "sort parity", __FILE__, __LINE__);
-  k_emit<<<grid, 256, 0, st>>>(b.morton, n, b.nodes, b.parent_leaf);
+  k_emit<<<grid, 256, 0, st>>>(b.morton, n, b.nodes, b.parent_leaf, b.flags);
   GPT_LAUNCH_CHECK(ctx);
-  GPT_CUDA(ctx, cudaMemsetAsync(b.flags, 0, sizeof(int) * (size_t)n, st));
-  if (with_tris)
-    k_refit<true><<<grid, 256, 0, st>>>(aabb, d_prim_list, b.sorted_prim, n, b.nodes,
-                                        b.parent_leaf, b.flags, s, b.tris);
-  else
-    k_refit<false><<<grid, 256, 0, st>>>(aabb, d_prim_list, b.sorted_prim, n, b.nodes,
-                                         b.parent_leaf, b.flags, s, nullptr);
+  static int chain_refit = -1;  // GPT_LBVH_CHAIN_REFIT=1: the round-1 bottom-up refit (A/B)
+  if (chain_refit < 0) { const char *e = getenv("GPT_LBVH_CHAIN_REFIT"); chain_refit = e ? atoi(e) : 0; }
+  if (chain_refit) {
+    GPT_CUDA(ctx, cudaMemsetAsync(b.flags, 0, sizeof(int) * (size_t)n, st));
+    if (with_tris)
+      k_refit<true><<<grid, 256, 0, st>>>(aabb, d_prim_list, b.sorted_prim, n, b.nodes,
+                                          b.parent_leaf, b.flags, s, b.tris);
+    else
+      k_refit<false><<<grid, 256, 0, st>>>(aabb, d_prim_list, b.sorted_prim, n, b.nodes,
+                                           b.parent_leaf, b.flags, s, nullptr);
+    GPT_LAUNCH_CHECK(ctx);
+    return GPT_OK;
+  }
+  Levels lv;
+  lv.base = b.levels;
+  long long off = 0;
+  int cnt = n, nl = 0;
+  for (;;) {
+    lv.off[nl] = off;
+    lv.count[nl] = cnt;
+    off += 6LL * cnt;
+    nl++;
+    if (cnt == 1 || nl == LV_MAX) break;
+    cnt = (cnt + 3) / 4;
+  }
+  lv.nlevels = nl;
+  for (int k = nl; k < LV_MAX; k++) { lv.off[k] = 0; lv.count[k] = 0; }
+  const int lgrid = (n + LV_BLOCK - 1) / LV_BLOCK;
+  if (with_tris) k_leaf_levels<true><<<lgrid, LV_BLOCK, 0, st>>>(aabb, d_prim_list, b.sorted_prim, n, lv, s, b.tris);
+  else k_leaf_levels<false><<<lgrid, LV_BLOCK, 0, st>>>(aabb, d_prim_list, b.sorted_prim, n, lv, s, nullptr);
+  GPT_LAUNCH_CHECK(ctx);
+  if (nl > 6) {
+    k_top_levels<<<1, 1024, 0, st>>>(lv);
+    GPT_LAUNCH_CHECK(ctx);
+  }
+  k_node_boxes<<<grid, 256, 0, st>>>(b.nodes, b.flags, n, lv);
   GPT_LAUNCH_CHECK(ctx);
   return GPT_OK;
 }

@@ -870,8 +870,8 @@ struct EyeParams {
   // r02 sharded eye pass (multi-GPU, SURVEY 8(e) second variant): this rank traces the eye paths
   // of its own 32x32 tiles only (the path tracer's round-robin deal) and writes what the pass
   // produces -- location, normal, filter, this pass's direct light -- as 12 floats per pixel into
-  // `xc`, zeros for the other ranks' pixels, so ONE sum all-reduce gives every rank every hit
-  // point (x + 0 + ... + 0 = x exactly, INFINITY included); k_eye_unpack then applies it.
+  // `xc`, MINUS zeros for the other ranks' pixels, so ONE sum all-reduce gives every rank every
+  // hit point (x + (-0) + ... = x exactly; -0 and INFINITY included); k_eye_unpack applies it.
   int rank, nranks;
   float4 *xc;  // 3 float4 per pixel: (loc, nrm.x) (nrm.yz, filter.xy) (filter.z, direct.xyz); nullptr = unsharded
 };
@@ -1086,9 +1086,11 @@ k_eye_pass(SppmScene S, EyeParams ep, HitPoints hp, const uint32_t *__restrict__
     const int row = pix / ep.cam.width, col = pix % ep.cam.width;
     const int tiles_x = (ep.cam.width + 31) / 32;
     mine = ((row / 32) * tiles_x + col / 32) % ep.nranks == ep.rank;
-    if (!mine) {  // another rank's pixel: zeros into the exchange buffer and the volume term
-      for (int k = 0; k < 3; k++) ep.xc[3 * (size_t)pix + k] = make_float4(0.f, 0.f, 0.f, 0.f);
-      hp.flux[(size_t)hp.P + pix] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (!mine) {  // another rank's pixel: the identity of the sum into the exchange buffer and
+                  // the volume term.  That identity is MINUS zero: x + (-0) == x for every x,
+                  // -0 and INFINITY included, whereas (-0) + (+0) would turn into +0
+      for (int k = 0; k < 3; k++) ep.xc[3 * (size_t)pix + k] = make_float4(-0.f, -0.f, -0.f, -0.f);
+      hp.flux[(size_t)hp.P + pix] = make_float4(-0.f, -0.f, -0.f, -0.f);
     }
   }
   if (mine) {
