@@ -10,7 +10,7 @@ import sys
 import numpy as np
 import pytest
 
-pytestmark = pytest.mark.gpu
+pytestmark = pytest.mark.multigpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 WORKER = r'''
@@ -66,9 +66,6 @@ def _run(nranks, tmp_path):
 
 
 def test_two_rank_sppm_pass_equals_the_one_rank_pass(tmp_path):
-    import torch
-    if torch.cuda.device_count() < 2:
-        pytest.skip("needs two GPUs")
     one = _run(1, tmp_path)[0]
     two = _run(2, tmp_path)
     for k in ("loc_radius", "normal_vradius", "filter", "direct"):
