@@ -310,6 +310,28 @@ def newest_traffic_capture(workload: str):
         return None, None
 
 
+def newest_trace_capture_counters():
+    """Issue-slot utilisation, lanes per instruction and occupancy of the trace kernel from the
+    newest `ncu --set full` capture under profiles/ (*_k_pt_trace_raw.csv, first launch): the
+    kernel is issue-bound, so this -- not a byte count -- says how close it is to its ceiling."""
+    import csv
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_k_pt_trace_raw.csv")))
+    if not files:
+        return None
+    try:
+        rows = list(csv.reader(open(files[-1])))
+        hdr, row = rows[0], rows[2]
+        get = lambda k: float(row[hdr.index(k)].replace(",", ""))
+        return {"issue_slots_busy_frac": get("smsp__issue_active.avg.pct_of_peak_sustained_active") / 100.0,
+                "lanes_per_instruction": get("smsp__thread_inst_executed_per_inst_executed.ratio"),
+                "warps_active_frac": get("sm__warps_active.avg.pct_of_peak_sustained_active") / 100.0,
+                "kernel": row[hdr.index("Kernel Name")].split("(")[0].split("::")[-1][:40],
+                "source": os.path.relpath(files[-1], ROOT)}
+    except Exception:
+        return None
+
+
 def scene_bytes(sc) -> int:
     n = 0
     for d in (sc.mesh, sc.materials, sc.bg):
@@ -485,6 +507,9 @@ def run_ours(args, rank, world, local_rank):
         "traffic": (cap["dram_bytes_per_ray"] * rays_per_launch) if cap else None,
         "traffic_source": cap_file,
     }
+    ncu_counters = newest_trace_capture_counters()
+    if ncu_counters:
+        roofline["ncu"] = ncu_counters
     if cap:
         roofline["physical_dram_gbs"] = cap["dram_bytes_per_ray"] * rays / (trace_ms * 1e-3) / 1e9
         roofline["physical_frac"] = roofline["physical_dram_gbs"] / peak
