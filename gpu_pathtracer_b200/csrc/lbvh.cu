@@ -25,7 +25,7 @@ constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;   // 4096 keys per block
 // are latency: with 4096-key tiles 65 536 keys are 16 blocks whose threads walk 16 keys each,
 // 10 + 12 us for histogram + scatter.  Up to SORT_SMALL_N keys the tile is 1024 keys.
 constexpr int SORT_ITEMS_SMALL = 4;
-constexpr int SORT_SMALL_N = 1 << 18;
+constexpr int SORT_SMALL_N = 1 << 21;
 constexpr int SORT_WARPS = SORT_THREADS / 32;
 
 // ---- world box ---------------------------------------------------------------------
@@ -454,16 +454,19 @@ __device__ __forceinline__ Box6 range_box(const Levels &lv, int a, int b) {
 // children cover [first, gamma] and [gamma + 1, last]
 __global__ void __launch_bounds__(256)
 k_node_boxes(float4 *nodes, const int *__restrict__ range_last, int n, Levels lv) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  // one thread per CHILD (2 i = left of node i, 2 i + 1 = right): half the work per thread and
+  // twice the threads of a thread per node; a child's box is 6 floats = 3 float2 of the node
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = c >> 1, right = c & 1;
   if (i >= n - 1) return;
   const int4 q3 = *reinterpret_cast<const int4 *>(nodes + 4 * (size_t)i + 3);
-  const int first = q3.w, last = __ldg(range_last + i);
   const int gamma = q3.x >= 0 ? q3.x : ~q3.x;
-  const Box6 l = range_box(lv, first, gamma), r = range_box(lv, gamma + 1, last);
-  float4 *q = nodes + 4 * (size_t)i;
-  q[0] = make_float4(l.v[0], l.v[1], l.v[2], l.v[3]);
-  q[1] = make_float4(l.v[4], l.v[5], r.v[0], r.v[1]);
-  q[2] = make_float4(r.v[2], r.v[3], r.v[4], r.v[5]);
+  const int a = right ? gamma + 1 : q3.w, b = right ? __ldg(range_last + i) : gamma;
+  const Box6 u = range_box(lv, a, b);
+  float2 *slot = reinterpret_cast<float2 *>(nodes + 4 * (size_t)i) + (right ? 3 : 0);
+  slot[0] = make_float2(u.v[0], u.v[1]);
+  slot[1] = make_float2(u.v[2], u.v[3]);
+  slot[2] = make_float2(u.v[4], u.v[5]);
 }
 
 // flagged-subset compaction in index order (collect_*_geom, 1 thread serial in the reference:
@@ -664,7 +667,7 @@ int gpt_lbvh_build_boxes(gpt_ctx *ctx, BvhDev &b, const float *aabb, const int *
     k_top_levels<<<1, 1024, 0, st>>>(lv);
     GPT_LAUNCH_CHECK(ctx);
   }
-  k_node_boxes<<<grid, 256, 0, st>>>(b.nodes, b.flags, n, lv);
+  k_node_boxes<<<(int)((2LL * n + 255) / 256), 256, 0, st>>>(b.nodes, b.flags, n, lv);
   GPT_LAUNCH_CHECK(ctx);
   return GPT_OK;
 }
