@@ -1429,8 +1429,8 @@ static int render_device(gpt_ctx *ctx, float *d_fb, int rank, int nranks, bool s
     GPT_CUDA(ctx, cudaMemcpyToSymbolAsync(g_sss_debug_mode, &mode, sizeof(int), 0, cudaMemcpyHostToDevice, st));
     // GPT_SSS_DEFER=0: the round-1 form, every lookup inside its shade thread (A/B, and what the
     // debug modes 1 = reference walk / 2 = skip apply to)
-    static int env_defer = -1;
-    if (env_defer < 0) { const char *d = getenv("GPT_SSS_DEFER"); env_defer = d ? atoi(d) : 1; }
+    const char *d = getenv("GPT_SSS_DEFER");  // read per render, like the debug mode: tests flip it
+    const int env_defer = d ? atoi(d) : 1;
     defer_sss = p.use_sss && mode == 0 && env_defer != 0;
     if (defer_sss) {
       if (rc->sss_req_cap < (size_t)n) {

@@ -72,3 +72,41 @@ def test_fast_lookup_equals_the_reference_walk(monkeypatch):
         imgs[mode] = pt.render_pathtrace()
     assert np.array_equal(imgs["0"].view(np.uint32), imgs["1"].view(np.uint32))
     assert np.isfinite(imgs["0"]).all() and imgs["0"].max() > 0
+
+
+def test_warp_lookup_stage_equals_the_in_thread_lookup(monkeypatch):
+    """r02: SSS lookups as a stage of their own (k_sss_lookup, one warp per lookup, the ordered
+    fp32 sum on four lanes) against the round-1 form (each shade thread walks its own lookup,
+    GPT_SSS_DEFER=0): bit-identical frames and ray counts -- on the reference's RNG streams, with
+    rng_mode 1 (waves of sample lanes), on a tile-sharded render and with one wavefront group."""
+    import torch
+    from gpu_pathtracer_b200.api import PathTracer
+    sc = S.make_scene("small", n=16, width=160, height=128, spp=3, level=4, sss_pts=3000)
+    h, w = sc.camera["height"], sc.camera["width"]
+
+    def frames(defer):
+        monkeypatch.setenv("GPT_SSS_DEFER", defer)
+        pt = PathTracer(sc)
+        pt.set_params(rng_mode=0)  # set_params edits the shared scene dict: undo the last run's mode
+        pt.build()
+        out = {"ref_rng": pt.render_pathtrace(), "rays": pt.stats()["rays_traced"]}
+        pt.set_wavefront_groups(1)
+        out["one_group"] = pt.render_pathtrace()
+        pt.set_wavefront_groups(0)
+        fb = torch.zeros((h, w, 3), dtype=torch.float32, device="cuda")
+        for r in range(3):
+            pt.render_pathtrace_device(fb.data_ptr(), r, 3)
+        pt.synchronize()
+        out["three_ranks"] = fb.cpu().numpy()
+        pt.set_params(rng_mode=1)
+        pt.set_fast_rng_lanes(4)
+        out["fast_rng"] = pt.render_pathtrace()
+        return out
+
+    a, b = frames("1"), frames("0")
+    assert a["rays"] == b["rays"]
+    for k in ("ref_rng", "one_group", "three_ranks", "fast_rng"):
+        assert np.array_equal(a[k].view(np.uint32), b[k].view(np.uint32)), k
+    assert np.array_equal(a["ref_rng"].view(np.uint32), a["one_group"].view(np.uint32))
+    assert np.array_equal(a["ref_rng"].view(np.uint32), a["three_ranks"].view(np.uint32))
+    assert np.isfinite(a["fast_rng"]).all() and a["ref_rng"].max() > 0
