@@ -410,22 +410,24 @@ def run_ours(args, rank, world, local_rank):
     if not args.fast_rng and not args.no_fast_rng:
         pt.set_params(rng_mode=1)
         pt.set_fast_rng_lanes(fast_lanes)
-        for _ in range(2):
-            flush.zero_()
-            pt.render_pathtrace_device(fb.data_ptr(), rank, world)
-        barrier()
-        fevs = []
-        for _ in range(min(args.steps, 5)):
-            flush.zero_()
-            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a.record(stream)
-            pt.render_pathtrace_device(fb.data_ptr(), rank, world)
-            b.record(stream)
-            fevs.append((a, b))
-            fast_rays = pt.stats()["rays_traced"]
-        barrier()
-        fast_ms = float(np.mean([a.elapsed_time(b) for a, b in fevs]))
-        pt.set_params(rng_mode=0)
+        try:
+            for _ in range(2):
+                flush.zero_()
+                pt.render_pathtrace_device(fb.data_ptr(), rank, world)
+            barrier()
+            fevs = []
+            for _ in range(min(args.steps, 5)):
+                flush.zero_()
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record(stream)
+                pt.render_pathtrace_device(fb.data_ptr(), rank, world)
+                b.record(stream)
+                fevs.append((a, b))
+                fast_rays = pt.stats()["rays_traced"]
+            barrier()
+            fast_ms = float(np.mean([a.elapsed_time(b) for a, b in fevs]))
+        finally:
+            pt.set_params(rng_mode=0)  # everything below is on the reference's streams again
 
     # ---- profiling passes (not timed): per-stage kernel time, then visit counts
     pt.set_profiling(time_stages=True)
@@ -572,7 +574,10 @@ def run_ours(args, rank, world, local_rank):
                 if not line["parity"]["ok"]:
                     rc = 3
     if world == 1 and not args.no_ref_cuda and args.workload in ("C1", "C2", "C3"):
-        line["ref_cuda"] = ref_cuda_block(sc, args.workload, rays_all, ms_per_step)
+        try:
+            line["ref_cuda"] = ref_cuda_block(sc, args.workload, rays_all, ms_per_step)
+        except Exception as exc:  # noqa: BLE001 -- a reported baseline, never worth the line
+            line["ref_cuda"] = {"unavailable": f"{type(exc).__name__}: {exc}"[:300]}
     line["_rc"] = rc
     return line
 
@@ -776,7 +781,10 @@ def main():
         else:
             line = run_ours(args, rank, world, local_rank)
             if args.workload == "C2" and not args.no_also:
-                also = also_block(args, rank, world, local_rank)  # every rank takes part
+                try:  # an extra: it must never cost the headline line
+                    also = also_block(args, rank, world, local_rank)  # every rank takes part
+                except Exception as exc:  # noqa: BLE001
+                    also = {"error": f"{type(exc).__name__}: {exc}"[:300]}
                 if line is not None:
                     line["also"] = also
         if line is not None:
