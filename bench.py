@@ -165,9 +165,10 @@ def reference_window(sc, budget_s: float, nthreads: int):
 # independent Monte-Carlo estimate of the same integral.  At 2-4 spp that is < 0.1 % of the pixels
 # (tests/test_gpu_render.py), at C2's 64 spp x ~2.6 vertices it is ~10 % (measured r02b: 90.6 %
 # within 1e-3, 80.8 % bit-equal, RMSE 11 % of the mean = the per-pixel MC noise of those pixels,
-# mean luminance equal to 4.5e-4).  The bounds below are that measurement with a margin; the
-# unbiasedness bound (mean luminance) is the tight one.
-PARITY_MIN_FRAC_1E3 = 0.85
+# mean luminance equal to 4.5e-4; C3's 8 x 8 samples through nested glass: 85.6 % within 1e-3,
+# mean equal to 8e-4; C1: 99.0 %, 2e-5).  The bounds below are those measurements with a margin;
+# the unbiasedness bound (mean luminance) is the tight one.
+PARITY_MIN_FRAC_1E3 = 0.80
 PARITY_MAX_RMSE_FRAC = 0.20
 PARITY_MAX_REL_LUM = 5e-3
 
