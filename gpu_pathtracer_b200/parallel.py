@@ -87,10 +87,12 @@ def sppm_frame(pt, rank: int = 0, nranks: int = 1, passes: int | None = None, fl
                group=None, on_pass=None):
     """One render_mode-2 frame (src/main.cu:1282-1870) with the photons of every pass split by
     index range over the ranks: each rank traces its photons, builds its photon trees, runs the
-    (replicated) eye pass and gathers into ALL hit points; the per-hit-point accumulators are
-    summed over ranks -- the only collective of the path -- and every rank applies the same
-    radius / flux update, so hit-point state stays replicated.  With the library's communicator up
-    (``init_comm``) the sum is gpt_sppm_allreduce inside libgpt.so; otherwise (CPU tests over gloo,
+    eye pass and gathers into ALL hit points; the per-hit-point accumulators are summed over
+    ranks and every rank applies the same radius / flux update, so hit-point state stays
+    replicated.  With the library's communicator up (``init_comm``) gpt_sppm_pass also
+    all-gathers the volume photons and shards the eye pass by tiles (one more all-reduce hands
+    every rank every hit point), and the sum is gpt_sppm_allreduce inside
+    libgpt.so; otherwise the eye pass is replicated and (CPU tests over gloo,
     a caller that owns its own process group) it is torch.distributed on the aliased buffer.  `pt` is a PathTracer (or
     anything with its sppm_* methods); `flux_tensor()` returns the tensor aliasing the
     accumulator buffer (defaults to the device buffer of pt.sppm_flux_device())."""
