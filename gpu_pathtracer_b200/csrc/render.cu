@@ -497,10 +497,25 @@ static __device__ __noinline__ V3 sss_lookup_warp(BitmapPool sv, const SssTree &
   __threadfence();  // the marks, before any lane reads a word another lane marked
   __syncwarp();
   // ---- ordered sum: lane 0 owns sum_w, lanes 1..3 colour r, g, b
+  // Software pipeline over "units" of <= 32 consecutive terms (ncu, first version: the stage
+  // is latency bound -- long scoreboard 8 per issue -- by two dependent round trips per step,
+  // bitmap word then point records): the next step's bitmap word is fetched one step ahead,
+  // and a unit's record loads are issued BEFORE the four adding lanes run through the previous
+  // unit's terms, so the adds cover the fetch.  Units are summed in order: same association.
   float accv = 0.f;
+  int prev_nb = 0, buf = 0;   // terms parked in sterm[32 * (buf ^ 1) ..] that are not added yet
+  auto add_parked = [&](int which, int nb) {
+    if (lane < 4) {
+      const float *f = reinterpret_cast<const float *>(sterm + 32 * which) + lane;
+#pragma unroll 8
+      for (int i = 0; i < nb; i++) accv = accv + f[4 * i];
+    }
+  };
+  uint32_t bits_next = (wlo + lane <= whi) ? __ldcg(bm + wlo + lane) : 0u;
   for (int w0 = wlo; w0 <= whi; w0 += 32) {
     const int w = w0 + lane;
-    const uint32_t bits = w <= whi ? __ldcg(bm + w) : 0u;
+    const uint32_t bits = bits_next;
+    bits_next = (w + 32 <= whi) ? __ldcg(bm + w + 32) : 0u;
     if (bits) bm[w] = 0u;  // leave the bitmap clean for its next user
     const int cnt = __popc(bits);
     int incl = cnt;
@@ -520,27 +535,29 @@ static __device__ __noinline__ V3 sss_lookup_warp(BitmapPool sv, const SssTree &
       }
       const uint32_t wb = __shfl_sync(FULL, bits, src);
       const int e0 = __shfl_sync(FULL, excl, src);
+      float4 a = make_float4(0.f, 0.f, 0.f, 0.f), col = a;
+      if (k < total) {  // issue this unit's record loads ...
+        const int bbit = (int)__fns(wb, 0, k - e0 + 1);
+        const float4 *lf = t.vleaf + 2 * (size_t)(32 * (w0 + src) + bbit);
+        a = lf[0];
+        col = lf[1];
+      }
+      add_parked(buf ^ 1, prev_nb);  // ... and add the previous unit's terms while they fly
       float4 term = make_float4(0.f, 0.f, 0.f, 0.f);
       if (k < total) {
-        const int b = (int)__fns(wb, 0, k - e0 + 1);
-        const float4 *lf = t.vleaf + 2 * (size_t)(32 * (w0 + src) + b);
-        const float4 a = lf[0], col = lf[1];
         float wgt = 1.0f / dist(V3{a.x, a.y, a.z}, c);
         wgt = wgt < 9999.990234375f ? wgt : 9999.990234375f;  // (float)fmin(9999.99, wgt), see sss_lookup
         term = make_float4(wgt, wgt * col.x, wgt * col.y, wgt * col.z);
       }
-      sterm[lane] = term;
+      sterm[32 * buf + lane] = term;
       __syncwarp();
-      if (lane < 4) {
-        const float *f = reinterpret_cast<const float *>(sterm) + lane;
-        const int nb = min(32, total - base);
-#pragma unroll 8
-        for (int i = 0; i < nb; i++) accv = accv + f[4 * i];
-      }
-      __syncwarp();
+      prev_nb = min(32, total - base);
+      buf ^= 1;
       found = true;
     }
   }
+  add_parked(buf ^ 1, prev_nb);
+  __syncwarp();
   __threadfence();  // the cleared words, before the bitmap changes hands
   __syncwarp();
   if (lane == 0) atomicExch(sv.bm_busy + slot, 0);
@@ -927,7 +944,7 @@ constexpr int LK_BLOCK = 128;
 __global__ void __launch_bounds__(LK_BLOCK)
 k_sss_lookup(PathState ps, RenderParams p, const int *__restrict__ req_count, int *req_zero,
              int *next_queue, int *next_count, float *fb) {
-  __shared__ float4 sterm[LK_BLOCK / 32][32];
+  __shared__ float4 sterm[LK_BLOCK / 32][64];  // two units of 32 terms per warp (double buffer)
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const int warp = (blockIdx.x * LK_BLOCK + threadIdx.x) >> 5, nwarps = (gridDim.x * LK_BLOCK) >> 5;
   if (blockIdx.x == 0 && threadIdx.x == 0) *req_zero = 0;
