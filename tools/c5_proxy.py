@@ -15,8 +15,10 @@ ap.add_argument("--spp", type=int, default=4)
 ap.add_argument("--frames", type=int, default=2)
 ap.add_argument("--no-stage", action="store_true")
 ap.add_argument("--n", type=int, default=700)
+ap.add_argument("--width", type=int, default=1920)
+ap.add_argument("--height", type=int, default=1080)
 a = ap.parse_args()
-sc = S.make_scene("C5", n=a.n, width=1920, height=1080, spp=a.spp)
+sc = S.make_scene("C5", n=a.n, width=a.width, height=a.height, spp=a.spp)
 pt = PathTracer(sc)
 st0 = pt.build()
 img = pt.render_pathtrace()
