@@ -673,14 +673,13 @@ def run_sppm(args, rank, world, local_rank):
         dist.all_reduce(tot, op=dist.ReduceOp.SUM)
     total_ms, e2e_ms = t.tolist()
     rays_all, e2e_rays_all = tot.tolist()
-    # the eye pass is sharded by tiles when N > 1 (each rank counts its own pixels' rays); only
-    # where it is replicated (GPT_SPPM_SHARD_EYE=0, and the init pass always) are its rays
-    # counted ONCE, not once per rank
+    # the eye passes (init included) are sharded by tiles when N > 1 (each rank counts its own
+    # pixels' rays); only where they are replicated (GPT_SPPM_SHARD_EYE=0) are their rays counted
+    # ONCE, not once per rank
     eye_sharded = world > 1 and os.environ.get("GPT_SPPM_SHARD_EYE", "1") != "0"
     if not eye_sharded:
         rays_all -= (world - 1) * eye_rays * args.steps
-        e2e_rays_all -= (world - 1) * eye_rays * args.steps
-    e2e_rays_all -= (world - 1) * init_rays
+        e2e_rays_all -= (world - 1) * (init_rays + eye_rays * args.steps)
     if rank != 0:
         return
     peaks = {}

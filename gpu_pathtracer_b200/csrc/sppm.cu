@@ -873,7 +873,9 @@ struct EyeParams {
   // `xc`, MINUS zeros for the other ranks' pixels, so ONE sum all-reduce gives every rank every
   // hit point (x + (-0) + ... = x exactly; -0 and INFINITY included); k_eye_unpack applies it.
   int rank, nranks;
-  float4 *xc;  // 3 float4 per pixel: (loc, nrm.x) (nrm.yz, filter.xy) (filter.z, direct.xyz); nullptr = unsharded
+  float4 *xc;  // xstride float4 per pixel: (loc, nrm.x) (nrm.yz, filter.xy) (filter.z, direct.xyz) and,
+               // in the init pass (xstride 4), (radius, -, -, -); nullptr = unsharded
+  int xstride;
 };
 
 struct HitPoints {
@@ -1089,8 +1091,14 @@ k_eye_pass(SppmScene S, EyeParams ep, HitPoints hp, const uint32_t *__restrict__
     if (!mine) {  // another rank's pixel: the identity of the sum into the exchange buffer and
                   // the volume term.  That identity is MINUS zero: x + (-0) == x for every x,
                   // -0 and INFINITY included, whereas (-0) + (+0) would turn into +0
-      for (int k = 0; k < 3; k++) ep.xc[3 * (size_t)pix + k] = make_float4(-0.f, -0.f, -0.f, -0.f);
-      hp.flux[(size_t)hp.P + pix] = make_float4(-0.f, -0.f, -0.f, -0.f);
+      for (int k = 0; k < ep.xstride; k++)
+        ep.xc[ep.xstride * (size_t)pix + k] = make_float4(-0.f, -0.f, -0.f, -0.f);
+      if (ep.init) {
+        hp.direct[pix] = make_float4(0.f, 0.f, 0.f, 0.f);
+        hp.indirect[pix] = make_float4(0.f, 0.f, 0.f, 0.f);
+      } else {
+        hp.flux[(size_t)hp.P + pix] = make_float4(-0.f, -0.f, -0.f, -0.f);
+      }
     }
   }
   if (mine) {
@@ -1140,9 +1148,11 @@ k_eye_pass(SppmScene S, EyeParams ep, HitPoints hp, const uint32_t *__restrict__
     if (ep.xc) {  // sharded: everything the pass produces goes through the exchange buffer
       V3 loc = V3{INFINITY, INFINITY, INFINITY}, nrm = V3{0.f, 0.f, 1.f}, dn = V3{0.f, 0.f, 0.f};
       if (er.hit && er.diffuse) { loc = er.point; nrm = er.normal; dn = de_nan(direct); }
-      ep.xc[3 * (size_t)pix] = make_float4(loc.x, loc.y, loc.z, nrm.x);
-      ep.xc[3 * (size_t)pix + 1] = make_float4(nrm.y, nrm.z, filter.x, filter.y);
-      ep.xc[3 * (size_t)pix + 2] = make_float4(filter.z, dn.x, dn.y, dn.z);
+      float4 *x = ep.xc + ep.xstride * (size_t)pix;
+      x[0] = make_float4(loc.x, loc.y, loc.z, nrm.x);
+      x[1] = make_float4(nrm.y, nrm.z, filter.x, filter.y);
+      x[2] = make_float4(filter.z, dn.x, dn.y, dn.z);
+      if (ep.init) x[3] = make_float4(radius, -0.f, -0.f, -0.f);
     } else {
     if (er.hit && er.diffuse) {
       hp.loc[pix] = make_float4(er.point.x, er.point.y, er.point.z, radius);
@@ -1166,12 +1176,17 @@ k_eye_pass(SppmScene S, EyeParams ep, HitPoints hp, const uint32_t *__restrict__
 // The sharded eye pass's results, after the all-reduce, into the hit points: exactly the stores of
 // the unsharded kernel (radii stay, direct light accumulates; `0 + d` for a miss is what the
 // unsharded pass's skipped add leaves, d being finite).
-__global__ void __launch_bounds__(256) k_eye_unpack(HitPoints hp, const float4 *__restrict__ xc) {
+__global__ void __launch_bounds__(256)
+k_eye_unpack(HitPoints hp, const float4 *__restrict__ xc, int xstride, int init) {
   int pix = blockIdx.x * blockDim.x + threadIdx.x;
   if (pix >= hp.P) return;
-  const float4 a = xc[3 * (size_t)pix], b = xc[3 * (size_t)pix + 1], c = xc[3 * (size_t)pix + 2];
-  hp.loc[pix] = make_float4(a.x, a.y, a.z, hp.loc[pix].w);
-  hp.nrm[pix] = make_float4(a.w, b.x, b.y, hp.nrm[pix].w);
+  const float4 *x = xc + xstride * (size_t)pix;
+  const float4 a = x[0], b = x[1], c = x[2];
+  // the init pass also sets the radii: surface = its own estimate, volume = INFINITY
+  // (PPMHitPoint::PPMHitPoint, ppm_hit_point.h:173-188); later passes keep them
+  const float radius = init ? x[3].x : hp.loc[pix].w, vradius = init ? INFINITY : hp.nrm[pix].w;
+  hp.loc[pix] = make_float4(a.x, a.y, a.z, radius);
+  hp.nrm[pix] = make_float4(a.w, b.x, b.y, vradius);
   hp.filter[pix] = make_float4(b.z, b.w, c.x, 0.f);
   if (!(a.x == INFINITY)) {  // er.hit && er.diffuse on the owner
     const float4 dr = hp.direct[pix];
@@ -1553,18 +1568,19 @@ static int eye_pass(gpt_ctx *ctx, SppmCtx *sx, const SppmScene &S, int pass, boo
                ? PhotonTree{sx->vol_bvh.nodes, sx->spheres_all, sx->leaf_vol_all, init ? 0 : sx->n_vol}
                : PhotonTree{sx->vol_bvh.nodes, sx->spheres, sx->leaf_vol, init ? 0 : sx->n_vol};
   bool comm = false;
-  const bool sharded = !init && eye_sharded(ctx, sx, &ep.rank, &ep.nranks, &comm);
+  const bool sharded = eye_sharded(ctx, sx, &ep.rank, &ep.nranks, &comm);  // the init pass too
   if (!sharded) { ep.rank = 0; ep.nranks = 1; }
   ep.xc = nullptr;
+  ep.xstride = init ? 4 : 3;
   if (sharded) {
-    if (!sx->xc) GPT_TRY(gpt_alloc(ctx, &sx->xc, 3 * (size_t)sx->P));
+    if (!sx->xc) GPT_TRY(gpt_alloc(ctx, &sx->xc, 4 * (size_t)sx->P));
     ep.xc = sx->xc;
   }
   k_eye_pass<<<(sx->P + SP_BLOCK - 1) / SP_BLOCK, SP_BLOCK, 0, ctx->stream>>>(S, ep, sx->hp, sx->rng_pix);
   GPT_LAUNCH_CHECK(ctx);
   if (sharded) {
-    if (comm) GPT_TRY(gpt_comm_allreduce_f32(ctx, sx->xc, 12 * (size_t)sx->P));
-    k_eye_unpack<<<(sx->P + 255) / 256, 256, 0, ctx->stream>>>(sx->hp, sx->xc);
+    if (comm) GPT_TRY(gpt_comm_allreduce_f32(ctx, sx->xc, 4 * (size_t)ep.xstride * sx->P));
+    k_eye_unpack<<<(sx->P + 255) / 256, 256, 0, ctx->stream>>>(sx->hp, sx->xc, ep.xstride, ep.init);
     GPT_LAUNCH_CHECK(ctx);
   }
   return GPT_OK;

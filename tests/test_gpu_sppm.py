@@ -197,6 +197,25 @@ def test_sharded_eye_pass_tiles_the_unsharded_pass():
         pt.sppm_pass_stages(0, 2)      # the eye pass
         return pt.sppm_export_hit_points()
 
+    def run_init(rank, nranks):
+        # the init pass is sharded the same way (5 eye paths per pixel and the radius estimate);
+        # without a communicator the global mean radius that follows is meaningless, so only
+        # what the eye paths themselves produce is compared
+        pt = PathTracer(sc, device=0)
+        pt.build()
+        pt.sppm_debug_eye_shard(rank, nranks)
+        pt.sppm_init()
+        return pt.sppm_export_hit_points()
+
+    rows0, cols0 = np.divmod(np.arange(W * H), W)
+    owner0 = ((rows0 // 32) * ((W + 31) // 32) + cols0 // 32) % 2
+    init_base, init_shards = run_init(0, 1), [run_init(r, 2) for r in range(2)]
+    for r, sh in enumerate(init_shards):
+        mine = owner0 == r
+        for k in ("loc_radius", "normal_vradius", "filter", "direct"):
+            assert np.array_equal(sh[k][mine, :3].view(np.uint32), init_base[k][mine, :3].view(np.uint32)), (r, k)
+        assert (sh["loc_radius"][~mine, :3].view(np.uint32) == 0x80000000).all()
+
     base = run(0, 1)
     shards = [run(r, 2) for r in range(2)]
     rows, cols = np.divmod(np.arange(W * H), W)
