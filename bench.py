@@ -544,6 +544,8 @@ def run_ours(args, rank, world, local_rank):
             "spp_per_s": spp_total / (ms_per_step * 1e-3),
             "rays_per_frame": rays_all,
             "lbvh_build_ms": build_ms, "build_all_ms": build_stats["build_all_ms"],
+            # 288 algorithmic bytes per triangle against the measured HBM peak
+            "lbvh_build_roofline_frac": 288.0 * sc.num_triangles / (build_ms * 1e-3) / 1e9 / peak,
             "rank0_stage_ms": {"trace": trace_ms, "shade": shade_ms,
                                "frame": float(np.mean(step_ms))},
             "avg_internal_visits_per_ray": v_int / max(1, rays),
